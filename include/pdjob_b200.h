@@ -1,0 +1,94 @@
+/* C ABI of libpdjob_b200.so - the sm_100a data plane of the B200 PaddleJob
+ * runtime.  Every entry point returns 0 on success and a non-zero code on
+ * failure; pdj_last_error() then returns a thread-local description.
+ *
+ * All kernels are launched on the cudaStream_t passed in and never
+ * synchronise the device, so they can be captured in CUDA graphs.
+ *
+ * Reference parity notes cite files of lfeng-nl/paddle-operator, which has no
+ * device code: it only publishes the rank/endpoint environment
+ * (controllers/paddlejob_helper.go:215-377) that Paddle's own collectives and
+ * parameter servers bootstrap from.  The entry points here are the hot paths
+ * of the workloads that environment launches.
+ */
+#ifndef PDJOB_B200_H_
+#define PDJOB_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#ifndef __CUDA_RUNTIME_H__
+typedef struct CUstream_st* cudaStream_t;
+#endif
+
+struct PdjComm;      /* see csrc/common.cuh; built by the Python side */
+struct PdjArena;
+struct PdjMulticast;
+
+#define PDJ_AR_TWOSHOT 0
+#define PDJ_AR_ONESHOT 1
+#define PDJ_AR_NVLS 2
+
+#define PDJ_BN_MAX_ROW_BLOCKS 512
+
+const char* pdj_last_error(void);
+
+/* ---- symmetric-memory runtime (csrc/comm_runtime.cu) ----------------------
+ * Stands in for the ConfigMap rendezvous of the reference
+ * (controllers/paddlejob_controller.go:289-306): besides PADDLE_* strings the
+ * ranks exchange one file descriptor each, naming their arena. */
+int pdj_device_count(void);
+int pdj_can_access_peer(int dev, int peer);
+int pdj_multicast_supported(int device);
+int pdj_arena_round_size(int device, size_t bytes, int nranks, size_t* out);
+int pdj_arena_create(int device, size_t bytes, struct PdjArena** out);
+int pdj_arena_export_fd(struct PdjArena* a, int* fd);
+int pdj_arena_import_fd(int device, int fd, size_t bytes, struct PdjArena** out);
+void* pdj_arena_ptr(struct PdjArena* a);
+size_t pdj_arena_bytes(struct PdjArena* a);
+int pdj_arena_destroy(struct PdjArena* a);
+int pdj_multicast_create(int device, int nranks, size_t bytes, struct PdjMulticast** out, int* fd);
+int pdj_multicast_import(int device, int fd, size_t bytes, struct PdjMulticast** out);
+int pdj_multicast_add_device(struct PdjMulticast* m);
+int pdj_multicast_bind(struct PdjMulticast* m, struct PdjArena* local, void** mc_ptr);
+int pdj_multicast_destroy(struct PdjMulticast* m);
+
+/* ---- collectives fused with scale / cast (csrc/collectives.cu) -------------
+ * Collective-mode wiring in the reference: controllers/paddlejob_helper.go:
+ * 261-265,319-322 (PADDLE_TRAINER_ENDPOINTS, PADDLE_TRAINERS_NUM,
+ * PADDLE_TRAINER_ID).  Offsets are bytes from the arena base and identical on
+ * every rank.  emulate != 0 runs all ranks as one cooperative launch over
+ * arenas that live on a single device (tests). */
+int pdj_barrier(const struct PdjComm* c, int emulate, cudaStream_t st);
+int pdj_allreduce_bf16(const struct PdjComm* c, size_t in_off, size_t out_off, size_t n_elems, float scale,
+                       int algo, int out_f32, int nblocks, int emulate, cudaStream_t st);
+int pdj_alltoall(const struct PdjComm* c, size_t in_off, size_t out_off, size_t chunk_bytes, int nblocks,
+                 int emulate, cudaStream_t st);
+int pdj_broadcast(const struct PdjComm* c, int root, size_t off, size_t bytes, int nblocks, int emulate,
+                  cudaStream_t st);
+
+/* ---- ResNet-50 step kernels (csrc/bn_act.cu, csrc/optim_misc.cu) -----------
+ * The workload of deploy/examples/resnet.yaml:13-19. NHWC bf16 activations
+ * viewed as [M, C]; fp32 statistics. */
+size_t pdj_bn_workspace_bytes(void);
+int pdj_bn_fwd(const void* x, const void* res, void* y, int M, int C, const float* gamma, const float* beta,
+               float eps, float momentum, float* running_mean, float* running_var, float* mean_rstd,
+               float* scale_shift, int relu, void* workspace, cudaStream_t st);
+int pdj_bn_bwd(const void* dy, const void* y, const void* x, void* dx, void* dres, int M, int C,
+               const float* gamma, const float* mean_rstd, float* dgamma_dbeta, void* dgb_bf16, float* coef,
+               int relu, void* workspace, cudaStream_t st);
+int pdj_sgd_momentum(float* w, float* mom, const void* grad, void* param, size_t n, size_t wd_split,
+                     const float* hyper, cudaStream_t st);
+int pdj_preprocess_u8(const void* in, void* out, size_t n_px, const float* mean3, const float* std3,
+                      cudaStream_t st);
+int pdj_softmax_xent(const void* logits, const int64_t* labels, void* dlogits, float* loss_sum, int rows,
+                     int ncls, float grad_scale, cudaStream_t st);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PDJOB_B200_H_ */

@@ -1,0 +1,404 @@
+// Fused training-mode BatchNorm (+residual add)(+ReLU) for NHWC bf16 tensors,
+// forward and backward.  ResNet-50 at bf16 on B200 is HBM-bound on exactly
+// these passes (the convolutions are tensor-core work in cuDNN); fusing the
+// normalise / add / activation passes and their backward removes about a third
+// of the activation traffic of a step.
+//
+// Reference parity: none - the reference launches a user image that runs
+// Paddle's ResNet (deploy/examples/resnet.yaml:13-19); this is the compute
+// layer BASELINE.json asks the runtime to own.
+//
+// x is viewed as [M, C] (M = N*H*W rows, C channels contiguous), C % 8 == 0,
+// C <= 2048 so that 256 % min(C/8,32) == 0.
+#include "common.cuh"
+#include "../../include/pdjob_b200.h"
+
+namespace {
+
+constexpr int kThreads = 256;
+
+struct Tile {
+  int cvt;        // channel-vectors (of 8) per block: min(C/8, 32)
+  int rows_par;   // rows processed in parallel by a block: 256 / cvt
+  int cv;         // this thread's channel-vector index within the tensor
+  int row0;       // this thread's first row
+  int row_step;   // row stride between iterations
+};
+
+__device__ __forceinline__ Tile make_tile(int C) {
+  Tile t;
+  const int c8 = C >> 3;
+  t.cvt = c8 < 32 ? c8 : 32;
+  t.rows_par = kThreads / t.cvt;
+  t.cv = blockIdx.y * t.cvt + (threadIdx.x % t.cvt);
+  t.row0 = blockIdx.x * t.rows_par + threadIdx.x / t.cvt;
+  t.row_step = gridDim.x * t.rows_par;
+  return t;
+}
+
+__device__ __forceinline__ void unpack8(const uint4& u, float* f) {
+  float2 a = pdj_bf2_to_f2(u.x), b = pdj_bf2_to_f2(u.y), c = pdj_bf2_to_f2(u.z), d = pdj_bf2_to_f2(u.w);
+  f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y; f[4] = c.x; f[5] = c.y; f[6] = d.x; f[7] = d.y;
+}
+__device__ __forceinline__ uint4 pack8(const float* f) {
+  uint4 o;
+  o.x = pdj_f2_to_bf2(f[0], f[1]); o.y = pdj_f2_to_bf2(f[2], f[3]);
+  o.z = pdj_f2_to_bf2(f[4], f[5]); o.w = pdj_f2_to_bf2(f[6], f[7]);
+  return o;
+}
+__device__ __forceinline__ uint4 ldg16(const void* p) { return __ldg(reinterpret_cast<const uint4*>(p)); }
+
+// Block-level reduction of 16 per-thread accumulators over the threads that
+// share a channel-vector, then one partial row per block:
+//   partial[blockIdx.x][k][C] for k in {0,1}, channel = cv*8 + j.
+// Returns true in the last block (per blockIdx.y) to arrive, after which all
+// partials of this channel tile are visible to it.
+__device__ __forceinline__ bool reduce_and_publish(const Tile& t, int C, const float* acc /*16*/,
+                                                   float* __restrict__ partial, unsigned int* __restrict__ counter) {
+  __shared__ float sm[16][kThreads + 1];
+  __shared__ bool is_last;
+#pragma unroll
+  for (int k = 0; k < 16; ++k) sm[k][threadIdx.x] = acc[k];
+  __syncthreads();
+  const int nout = t.cvt * 16;
+  for (int o = threadIdx.x; o < nout; o += kThreads) {
+    const int k = o / t.cvt, lcv = o % t.cvt;
+    float s = 0.f;
+    for (int j = 0; j < t.rows_par; ++j) s += sm[k][lcv + j * t.cvt];
+    const int ch = (blockIdx.y * t.cvt + lcv) * 8 + (k & 7);
+    partial[((size_t)blockIdx.x * 2 + (k >> 3)) * C + ch] = s;
+  }
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned int ticket = atomicAdd(&counter[blockIdx.y], 1u);
+    is_last = (ticket == gridDim.x - 1);
+    if (is_last) counter[blockIdx.y] = 0;  // self-reset for the next launch
+  }
+  __syncthreads();
+  if (is_last) __threadfence();
+  return is_last;
+}
+
+// ---- forward --------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads)
+bn_stats_kernel(const __nv_bfloat16* __restrict__ x, int M, int C, const float* __restrict__ gamma,
+                const float* __restrict__ beta, float eps, float momentum, float* __restrict__ running_mean,
+                float* __restrict__ running_var, float* __restrict__ mean_rstd /*[2][C]*/,
+                float* __restrict__ scale_shift /*[2][C]*/, float* __restrict__ partial,
+                unsigned int* __restrict__ counter) {
+  const Tile t = make_tile(C);
+  float acc[16];
+#pragma unroll
+  for (int k = 0; k < 16; ++k) acc[k] = 0.f;
+  const char* xp = reinterpret_cast<const char*>(x) + (size_t)t.cv * 16;
+  const size_t row_bytes = (size_t)C * 2;
+  int r = t.row0;
+  // Two independent rows per iteration for memory-level parallelism.
+  for (; r + t.row_step < M; r += 2 * t.row_step) {
+    const uint4 u0 = ldg16(xp + (size_t)r * row_bytes);
+    const uint4 u1 = ldg16(xp + (size_t)(r + t.row_step) * row_bytes);
+    float f[8], g[8];
+    unpack8(u0, f);
+    unpack8(u1, g);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      acc[j] += f[j] + g[j];
+      acc[8 + j] += f[j] * f[j] + g[j] * g[j];
+    }
+  }
+  if (r < M) {
+    float f[8];
+    unpack8(ldg16(xp + (size_t)r * row_bytes), f);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      acc[j] += f[j];
+      acc[8 + j] += f[j] * f[j];
+    }
+  }
+  if (!reduce_and_publish(t, C, acc, partial, counter)) return;
+  // Last block of this channel tile: finalise its channels.
+  const int nch = t.cvt * 8;
+  const float inv_m = 1.f / (float)M;
+  for (int o = threadIdx.x; o < nch; o += kThreads) {
+    const int ch = blockIdx.y * nch + o;
+    float s = 0.f, q = 0.f;
+    for (unsigned int b = 0; b < gridDim.x; ++b) {
+      s += partial[((size_t)b * 2 + 0) * C + ch];
+      q += partial[((size_t)b * 2 + 1) * C + ch];
+    }
+    const float mean = s * inv_m;
+    float var = q * inv_m - mean * mean;
+    var = var < 0.f ? 0.f : var;
+    const float rstd = rsqrtf(var + eps);
+    mean_rstd[ch] = mean;
+    mean_rstd[C + ch] = rstd;
+    const float sc = gamma[ch] * rstd;
+    scale_shift[ch] = sc;
+    scale_shift[C + ch] = beta[ch] - mean * sc;
+    if (running_mean != nullptr) {
+      const float unbiased = M > 1 ? var * ((float)M / (float)(M - 1)) : var;
+      running_mean[ch] = (1.f - momentum) * running_mean[ch] + momentum * mean;
+      running_var[ch] = (1.f - momentum) * running_var[ch] + momentum * unbiased;
+    }
+  }
+}
+
+template <bool RELU, bool RES>
+__global__ void __launch_bounds__(kThreads)
+bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ res,
+                __nv_bfloat16* __restrict__ y, size_t n_vec, int C, const float* __restrict__ scale_shift) {
+  const int c8 = C >> 3;
+  const int cv = threadIdx.x % c8;  // 256 % c8 == 0 and the grid stride is a multiple of 256
+  float sc[8], sh[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    sc[j] = scale_shift[cv * 8 + j];
+    sh[j] = scale_shift[C + cv * 8 + j];
+  }
+  const size_t stride = (size_t)gridDim.x * kThreads;
+  const uint4* xv = reinterpret_cast<const uint4*>(x);
+  const uint4* rv = reinterpret_cast<const uint4*>(res);
+  uint4* yv = reinterpret_cast<uint4*>(y);
+  size_t i = (size_t)blockIdx.x * kThreads + threadIdx.x;
+  for (; i + stride < n_vec; i += 2 * stride) {
+    const uint4 a0 = ldg16(xv + i), a1 = ldg16(xv + i + stride);
+    uint4 b0, b1;
+    if (RES) { b0 = ldg16(rv + i); b1 = ldg16(rv + i + stride); }
+    float f[8], g[8], p[8], q[8];
+    unpack8(a0, f); unpack8(a1, g);
+    if (RES) { unpack8(b0, p); unpack8(b1, q); }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      f[j] = fmaf(f[j], sc[j], sh[j]);
+      g[j] = fmaf(g[j], sc[j], sh[j]);
+      if (RES) { f[j] += p[j]; g[j] += q[j]; }
+      if (RELU) { f[j] = fmaxf(f[j], 0.f); g[j] = fmaxf(g[j], 0.f); }
+    }
+    yv[i] = pack8(f);
+    yv[i + stride] = pack8(g);
+  }
+  if (i < n_vec) {
+    float f[8], p[8];
+    unpack8(ldg16(xv + i), f);
+    if (RES) unpack8(ldg16(rv + i), p);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      f[j] = fmaf(f[j], sc[j], sh[j]);
+      if (RES) f[j] += p[j];
+      if (RELU) f[j] = fmaxf(f[j], 0.f);
+    }
+    yv[i] = pack8(f);
+  }
+}
+
+// ---- backward -------------------------------------------------------------
+// dz = dy * (y > 0) when RELU.  Pass 1: sum(dz), sum(dz * xhat) per channel;
+// the last block turns them into dgamma/dbeta and the three coefficients of
+//   dx = A*dz + B*x + Cc.
+template <bool RELU>
+__global__ void __launch_bounds__(kThreads)
+bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ y,
+                     const __nv_bfloat16* __restrict__ x, int M, int C, const float* __restrict__ gamma,
+                     const float* __restrict__ mean_rstd, float* __restrict__ dgamma_dbeta /*[2][C] fp32*/,
+                     __nv_bfloat16* __restrict__ dgb_bf16 /*[2][C] or null*/,
+                     float* __restrict__ coef /*[3][C]*/, float* __restrict__ partial,
+                     unsigned int* __restrict__ counter) {
+  const Tile t = make_tile(C);
+  float mu[8], rs[8], acc[16];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    mu[j] = mean_rstd[t.cv * 8 + j];
+    rs[j] = mean_rstd[C + t.cv * 8 + j];
+    acc[j] = 0.f;
+    acc[8 + j] = 0.f;
+  }
+  const size_t row_bytes = (size_t)C * 2;
+  const size_t coff = (size_t)t.cv * 16;
+  const char* dyp = reinterpret_cast<const char*>(dy) + coff;
+  const char* yp = reinterpret_cast<const char*>(y) + coff;
+  const char* xp = reinterpret_cast<const char*>(x) + coff;
+  for (int r = t.row0; r < M; r += t.row_step) {
+    const size_t o = (size_t)r * row_bytes;
+    const uint4 ud = ldg16(dyp + o), ux = ldg16(xp + o);
+    uint4 uy;
+    if (RELU) uy = ldg16(yp + o);
+    float d[8], xx[8], yy[8];
+    unpack8(ud, d);
+    unpack8(ux, xx);
+    if (RELU) unpack8(uy, yy);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float dz = RELU ? (yy[j] > 0.f ? d[j] : 0.f) : d[j];
+      acc[j] += dz;
+      acc[8 + j] += dz * (xx[j] - mu[j]) * rs[j];
+    }
+  }
+  if (!reduce_and_publish(t, C, acc, partial, counter)) return;
+  const int nch = t.cvt * 8;
+  const float inv_m = 1.f / (float)M;
+  for (int o = threadIdx.x; o < nch; o += kThreads) {
+    const int ch = blockIdx.y * nch + o;
+    float sdz = 0.f, sdzx = 0.f;
+    for (unsigned int b = 0; b < gridDim.x; ++b) {
+      sdz += partial[((size_t)b * 2 + 0) * C + ch];
+      sdzx += partial[((size_t)b * 2 + 1) * C + ch];
+    }
+    dgamma_dbeta[ch] = sdzx;
+    dgamma_dbeta[C + ch] = sdz;
+    if (dgb_bf16 != nullptr) {
+      dgb_bf16[ch] = __float2bfloat16(sdzx);
+      dgb_bf16[C + ch] = __float2bfloat16(sdz);
+    }
+    const float r = mean_rstd[C + ch], m = mean_rstd[ch];
+    const float A = gamma[ch] * r;
+    const float B = -A * r * sdzx * inv_m;
+    coef[ch] = A;
+    coef[C + ch] = B;
+    coef[2 * C + ch] = -B * m - A * sdz * inv_m;
+  }
+}
+
+template <bool RELU, bool WRITE_DZ>
+__global__ void __launch_bounds__(kThreads)
+bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ y,
+                    const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ dx,
+                    __nv_bfloat16* __restrict__ dres, size_t n_vec, int C, const float* __restrict__ coef) {
+  const int c8 = C >> 3;
+  const int cv = threadIdx.x % c8;
+  float A[8], B[8], Cc[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    A[j] = coef[cv * 8 + j];
+    B[j] = coef[C + cv * 8 + j];
+    Cc[j] = coef[2 * C + cv * 8 + j];
+  }
+  const size_t stride = (size_t)gridDim.x * kThreads;
+  const uint4* dyv = reinterpret_cast<const uint4*>(dy);
+  const uint4* yv = reinterpret_cast<const uint4*>(y);
+  const uint4* xv = reinterpret_cast<const uint4*>(x);
+  uint4* dxv = reinterpret_cast<uint4*>(dx);
+  uint4* drv = reinterpret_cast<uint4*>(dres);
+  for (size_t i = (size_t)blockIdx.x * kThreads + threadIdx.x; i < n_vec; i += stride) {
+    const uint4 ud = ldg16(dyv + i), ux = ldg16(xv + i);
+    uint4 uy;
+    if (RELU) uy = ldg16(yv + i);
+    float d[8], xx[8], yy[8], o[8];
+    unpack8(ud, d);
+    unpack8(ux, xx);
+    if (RELU) unpack8(uy, yy);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      if (RELU) d[j] = yy[j] > 0.f ? d[j] : 0.f;
+      o[j] = fmaf(A[j], d[j], fmaf(B[j], xx[j], Cc[j]));
+    }
+    dxv[i] = pack8(o);
+    if (WRITE_DZ) drv[i] = pack8(d);
+  }
+}
+
+int grid_rows(int M, int C, int sm_count) {
+  const int c8 = C / 8;
+  const int cvt = c8 < 32 ? c8 : 32;
+  const int gy = c8 / cvt;
+  const int rows_par = kThreads / cvt;
+  int gx = (2 * sm_count + gy - 1) / gy;         // about two blocks per SM in total
+  const int max_gx = (M + rows_par * 4 - 1) / (rows_par * 4);  // at least 4 rows per thread
+  if (gx > max_gx) gx = max_gx;
+  if (gx < 1) gx = 1;
+  if (gx > PDJ_BN_MAX_ROW_BLOCKS) gx = PDJ_BN_MAX_ROW_BLOCKS;
+  return gx;
+}
+
+int check_shape(int M, int C) {
+  const int c8 = C / 8;
+  if (C % 8 != 0 || c8 < 1 || c8 > 256 || (c8 & (c8 - 1)) != 0 || M < 1) {
+    pdj_set_error("bn: unsupported shape M=%d C=%d (C must be 8..2048, C/8 a power of two)", M, C);
+    return -1;
+  }
+  return 0;
+}
+
+int g_sm_count = 0;
+int sm_count() {
+  if (g_sm_count == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&g_sm_count, cudaDevAttrMultiProcessorCount, dev);
+    if (g_sm_count <= 0) g_sm_count = 148;
+  }
+  return g_sm_count;
+}
+
+int flat_grid(size_t n_vec) {
+  size_t want = (n_vec + (size_t)kThreads * 4 - 1) / ((size_t)kThreads * 4);
+  const size_t cap = (size_t)sm_count() * 8;
+  if (want > cap) want = cap;
+  if (want < 1) want = 1;
+  return (int)want;
+}
+
+}  // namespace
+
+extern "C" {
+
+size_t pdj_bn_workspace_bytes() {
+  // partials [PDJ_BN_MAX_ROW_BLOCKS][2][2048] fp32 + 64 counters
+  return (size_t)PDJ_BN_MAX_ROW_BLOCKS * 2 * 2048 * sizeof(float) + 256;
+}
+
+int pdj_bn_fwd(const void* x, const void* res, void* y, int M, int C, const float* gamma, const float* beta,
+               float eps, float momentum, float* running_mean, float* running_var, float* mean_rstd,
+               float* scale_shift, int relu, void* workspace, cudaStream_t st) {
+  if (check_shape(M, C)) return -1;
+  float* partial = reinterpret_cast<float*>(reinterpret_cast<char*>(workspace) + 256);
+  unsigned int* counter = reinterpret_cast<unsigned int*>(workspace);
+  const int c8 = C / 8, cvt = c8 < 32 ? c8 : 32;
+  dim3 g(grid_rows(M, C, sm_count()), c8 / cvt);
+  bn_stats_kernel<<<g, kThreads, 0, st>>>((const __nv_bfloat16*)x, M, C, gamma, beta, eps, momentum, running_mean,
+                                          running_var, mean_rstd, scale_shift, partial, counter);
+  PDJ_CUDA_CHECK(cudaGetLastError());
+  const size_t n_vec = (size_t)M * c8;
+  const int fg = flat_grid(n_vec);
+  const __nv_bfloat16* xb = (const __nv_bfloat16*)x;
+  const __nv_bfloat16* rb = (const __nv_bfloat16*)res;
+  __nv_bfloat16* yb = (__nv_bfloat16*)y;
+  if (relu && res) bn_apply_kernel<true, true><<<fg, kThreads, 0, st>>>(xb, rb, yb, n_vec, C, scale_shift);
+  else if (relu) bn_apply_kernel<true, false><<<fg, kThreads, 0, st>>>(xb, rb, yb, n_vec, C, scale_shift);
+  else if (res) bn_apply_kernel<false, true><<<fg, kThreads, 0, st>>>(xb, rb, yb, n_vec, C, scale_shift);
+  else bn_apply_kernel<false, false><<<fg, kThreads, 0, st>>>(xb, rb, yb, n_vec, C, scale_shift);
+  PDJ_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+int pdj_bn_bwd(const void* dy, const void* y, const void* x, void* dx, void* dres, int M, int C, const float* gamma,
+               const float* mean_rstd, float* dgamma_dbeta, void* dgb_bf16, float* coef, int relu,
+               void* workspace, cudaStream_t st) {
+  if (check_shape(M, C)) return -1;
+  float* partial = reinterpret_cast<float*>(reinterpret_cast<char*>(workspace) + 256);
+  unsigned int* counter = reinterpret_cast<unsigned int*>(workspace);
+  const int c8 = C / 8, cvt = c8 < 32 ? c8 : 32;
+  dim3 g(grid_rows(M, C, sm_count()), c8 / cvt);
+  const __nv_bfloat16* dyb = (const __nv_bfloat16*)dy;
+  const __nv_bfloat16* yb = (const __nv_bfloat16*)y;
+  const __nv_bfloat16* xb = (const __nv_bfloat16*)x;
+  if (relu)
+    bn_bwd_reduce_kernel<true><<<g, kThreads, 0, st>>>(dyb, yb, xb, M, C, gamma, mean_rstd, dgamma_dbeta,
+                                                       (__nv_bfloat16*)dgb_bf16, coef, partial, counter);
+  else
+    bn_bwd_reduce_kernel<false><<<g, kThreads, 0, st>>>(dyb, yb, xb, M, C, gamma, mean_rstd, dgamma_dbeta,
+                                                        (__nv_bfloat16*)dgb_bf16, coef, partial, counter);
+  PDJ_CUDA_CHECK(cudaGetLastError());
+  const size_t n_vec = (size_t)M * c8;
+  const int fg = flat_grid(n_vec);
+  __nv_bfloat16* dxb = (__nv_bfloat16*)dx;
+  __nv_bfloat16* drb = (__nv_bfloat16*)dres;
+  if (relu && dres) bn_bwd_apply_kernel<true, true><<<fg, kThreads, 0, st>>>(dyb, yb, xb, dxb, drb, n_vec, C, coef);
+  else if (relu) bn_bwd_apply_kernel<true, false><<<fg, kThreads, 0, st>>>(dyb, yb, xb, dxb, drb, n_vec, C, coef);
+  else if (dres) bn_bwd_apply_kernel<false, true><<<fg, kThreads, 0, st>>>(dyb, yb, xb, dxb, drb, n_vec, C, coef);
+  else bn_bwd_apply_kernel<false, false><<<fg, kThreads, 0, st>>>(dyb, yb, xb, dxb, drb, n_vec, C, coef);
+  PDJ_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+}  // extern "C"

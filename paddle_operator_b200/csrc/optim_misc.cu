@@ -1,0 +1,161 @@
+// Flat-buffer optimiser, input pre-processing and the classification loss.
+//
+// Reference parity: none in the reference (it has no training code); these are
+// the per-step kernels of the Collective-mode ResNet-50 workload that
+// deploy/examples/resnet.yaml launches, owned here by the runtime.
+#include "common.cuh"
+#include "../../include/pdjob_b200.h"
+
+namespace {
+
+// hyper = {lr, momentum, weight_decay, grad_scale}; read from device memory so
+// the launch can sit inside a CUDA graph while the schedule changes.
+__global__ void __launch_bounds__(256)
+sgd_momentum_kernel(float* __restrict__ w, float* __restrict__ mom, const __nv_bfloat16* __restrict__ grad,
+                    __nv_bfloat16* __restrict__ param, size_t n_vec, size_t wd_split_vec,
+                    const float* __restrict__ hyper) {
+  const float lr = hyper[0], mu = hyper[1], wd = hyper[2], gs = hyper[3];
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_vec; i += stride) {
+    const uint4 g4 = __ldg(reinterpret_cast<const uint4*>(grad) + i);
+    float4 w0 = reinterpret_cast<float4*>(w)[2 * i], w1 = reinterpret_cast<float4*>(w)[2 * i + 1];
+    float4 m0 = reinterpret_cast<float4*>(mom)[2 * i], m1 = reinterpret_cast<float4*>(mom)[2 * i + 1];
+    float g[8];
+    {
+      float2 a = pdj_bf2_to_f2(g4.x), b = pdj_bf2_to_f2(g4.y), c = pdj_bf2_to_f2(g4.z), d = pdj_bf2_to_f2(g4.w);
+      g[0] = a.x; g[1] = a.y; g[2] = b.x; g[3] = b.y; g[4] = c.x; g[5] = c.y; g[6] = d.x; g[7] = d.y;
+    }
+    float ww[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+    float mm[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
+    const float dec = i < wd_split_vec ? wd : 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float gj = fmaf(dec, ww[j], g[j] * gs);
+      mm[j] = fmaf(mu, mm[j], gj);
+      ww[j] = fmaf(-lr, mm[j], ww[j]);
+    }
+    reinterpret_cast<float4*>(w)[2 * i] = make_float4(ww[0], ww[1], ww[2], ww[3]);
+    reinterpret_cast<float4*>(w)[2 * i + 1] = make_float4(ww[4], ww[5], ww[6], ww[7]);
+    reinterpret_cast<float4*>(mom)[2 * i] = make_float4(mm[0], mm[1], mm[2], mm[3]);
+    reinterpret_cast<float4*>(mom)[2 * i + 1] = make_float4(mm[4], mm[5], mm[6], mm[7]);
+    uint4 o;
+    o.x = pdj_f2_to_bf2(ww[0], ww[1]); o.y = pdj_f2_to_bf2(ww[2], ww[3]);
+    o.z = pdj_f2_to_bf2(ww[4], ww[5]); o.w = pdj_f2_to_bf2(ww[6], ww[7]);
+    reinterpret_cast<uint4*>(param)[i] = o;
+  }
+}
+
+// uint8 NHWC (C = 3) -> bf16 NHWC, (x/255 - mean) / std per channel.
+__global__ void __launch_bounds__(256)
+preprocess_kernel(const uint8_t* __restrict__ in, __nv_bfloat16* __restrict__ out, size_t n_px, float m0, float m1,
+                  float m2, float s0, float s1, float s2) {
+  // One thread per 4 pixels = 12 input bytes (3 x u32) -> 12 bf16 (24 bytes).
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  const size_t n4 = n_px / 4;
+  const float mean[3] = {m0, m1, m2}, inv[3] = {1.f / (255.f * s0), 1.f / (255.f * s1), 1.f / (255.f * s2)};
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
+    const uint32_t* p = reinterpret_cast<const uint32_t*>(in) + i * 3;
+    const uint32_t u[3] = {__ldg(p), __ldg(p + 1), __ldg(p + 2)};
+    float f[12];
+#pragma unroll
+    for (int k = 0; k < 12; ++k) {
+      const float v = (float)((u[k >> 2] >> ((k & 3) * 8)) & 0xffu);
+      const int ch = k % 3;
+      f[k] = v * inv[ch] - mean[ch] / (ch == 0 ? s0 : (ch == 1 ? s1 : s2));
+    }
+    uint32_t* o = reinterpret_cast<uint32_t*>(out) + i * 6;
+#pragma unroll
+    for (int k = 0; k < 6; ++k) o[k] = pdj_f2_to_bf2(f[2 * k], f[2 * k + 1]);
+  }
+  // tail pixels (n_px % 4), handled by the first threads
+  const size_t tail0 = n4 * 4;
+  for (size_t px = tail0 + (size_t)blockIdx.x * blockDim.x + threadIdx.x; px < n_px; px += stride) {
+#pragma unroll
+    for (int ch = 0; ch < 3; ++ch) {
+      const float v = (float)in[px * 3 + ch];
+      const float s = ch == 0 ? s0 : (ch == 1 ? s1 : s2);
+      out[px * 3 + ch] = __float2bfloat16(v / (255.f * s) - mean[ch] / s);
+    }
+  }
+}
+
+// Softmax cross-entropy, forward and backward in one pass over the logits.
+// One block per row; writes dlogits = (softmax - onehot) * grad_scale (bf16),
+// and atomically accumulates loss_sum += -log p[label] (caller zeroes it).
+__global__ void __launch_bounds__(256)
+softmax_xent_kernel(const __nv_bfloat16* __restrict__ logits, const int64_t* __restrict__ labels,
+                    __nv_bfloat16* __restrict__ dlogits, float* __restrict__ loss_sum, int ncls, float grad_scale) {
+  __shared__ float red[32];
+  const int row = blockIdx.x;
+  const __nv_bfloat16* lr = logits + (size_t)row * ncls;
+  float mx = -INFINITY;
+  for (int j = threadIdx.x; j < ncls; j += blockDim.x) mx = fmaxf(mx, __bfloat162float(lr[j]));
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = mx;
+  __syncthreads();
+  mx = red[0];
+  for (int w = 1; w < (int)(blockDim.x >> 5); ++w) mx = fmaxf(mx, red[w]);
+  __syncthreads();
+  float sum = 0.f;
+  for (int j = threadIdx.x; j < ncls; j += blockDim.x) sum += __expf(__bfloat162float(lr[j]) - mx);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = sum;
+  __syncthreads();
+  sum = 0.f;
+  for (int w = 0; w < (int)(blockDim.x >> 5); ++w) sum += red[w];
+  const float inv = 1.f / sum;
+  const int lab = (int)labels[row];
+  __nv_bfloat16* dr = dlogits + (size_t)row * ncls;
+  for (int j = threadIdx.x; j < ncls; j += blockDim.x) {
+    const float p = __expf(__bfloat162float(lr[j]) - mx) * inv;
+    dr[j] = __float2bfloat16((p - (j == lab ? 1.f : 0.f)) * grad_scale);
+  }
+  if (threadIdx.x == 0) {
+    const float lp = __bfloat162float(lr[lab]) - mx - __logf(sum);
+    atomicAdd(loss_sum, -lp);
+  }
+}
+
+int grid_for(size_t n, int per_block) {
+  size_t g = (n + per_block - 1) / per_block;
+  if (g > 148 * 8) g = 148 * 8;
+  if (g < 1) g = 1;
+  return (int)g;
+}
+
+}  // namespace
+
+extern "C" {
+
+int pdj_sgd_momentum(float* w, float* mom, const void* grad, void* param, size_t n, size_t wd_split,
+                     const float* hyper, cudaStream_t st) {
+  if (n % 8 != 0 || wd_split % 8 != 0) {
+    pdj_set_error("pdj_sgd_momentum: n and wd_split must be multiples of 8");
+    return -1;
+  }
+  sgd_momentum_kernel<<<grid_for(n / 8, 256 * 2), 256, 0, st>>>(w, mom, (const __nv_bfloat16*)grad,
+                                                                (__nv_bfloat16*)param, n / 8, wd_split / 8, hyper);
+  PDJ_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+int pdj_preprocess_u8(const void* in, void* out, size_t n_px, const float* mean3, const float* std3,
+                      cudaStream_t st) {
+  preprocess_kernel<<<grid_for(n_px / 4 + 1, 256 * 4), 256, 0, st>>>((const uint8_t*)in, (__nv_bfloat16*)out, n_px,
+                                                                     mean3[0], mean3[1], mean3[2], std3[0], std3[1],
+                                                                     std3[2]);
+  PDJ_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+int pdj_softmax_xent(const void* logits, const int64_t* labels, void* dlogits, float* loss_sum, int rows, int ncls,
+                     float grad_scale, cudaStream_t st) {
+  softmax_xent_kernel<<<rows, 256, 0, st>>>((const __nv_bfloat16*)logits, labels, (__nv_bfloat16*)dlogits, loss_sum,
+                                            ncls, grad_scale);
+  PDJ_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+}  // extern "C"

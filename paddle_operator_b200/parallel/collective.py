@@ -1,0 +1,270 @@
+"""Collective-mode (data-parallel) training engine.
+
+One process per GPU.  Parameters, fp32 masters, momentum and gradients live in
+flat buffers; the gradient buffer sits in the symmetric arena so that the fused
+all-reduce kernels (csrc/collectives.cu) can reduce it in place across ranks,
+bucket by bucket, on a side stream while backward is still running.  The whole
+step (forward, loss, backward, bucket all-reduces, fused SGD) is captured once
+in a CUDA graph and replayed.
+
+Reference parity: "Collective" mode of the reference is worker.replicas > 1
+with no ps (controllers/paddlejob_helper.go:191-199); it hands each worker
+PADDLE_TRAINER_ID / PADDLE_TRAINERS_NUM / PADDLE_TRAINER_ENDPOINTS
+(controllers/paddlejob_helper.go:261-265,319-322) and Paddle's fleet does the
+rest with NCCL.  This module is "the rest", B200-first.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass, field
+from typing import Callable, Optional
+
+import torch
+
+from ..ops import optim as pdj_optim
+from .symm import AR_NVLS, AR_ONESHOT, AR_TWOSHOT, Communicator
+
+
+def _round_up(n: int, m: int) -> int:
+    return (n + m - 1) // m * m
+
+
+@dataclass
+class _Bucket:
+    start: int  # element offset in the flat buffers
+    end: int
+    params: list = field(default_factory=list)
+    gviews: list = field(default_factory=list)
+    pending: int = 0
+    grads: list = field(default_factory=list)
+    event: Optional[torch.cuda.Event] = None
+
+
+class FlatParams:
+    """Flat bf16 parameter / gradient buffers with fp32 master + momentum.
+
+    Layout follows reversed(model.parameters()) so that buckets complete in
+    address order during backward.  Every parameter starts on a 16-byte
+    boundary.  Convolution weights keep channels-last strides inside the flat
+    buffer.
+    """
+
+    def __init__(self, model: torch.nn.Module, device, comm: Optional[Communicator], bucket_bytes: int):
+        params = [p for p in model.parameters() if p.requires_grad]
+        order = list(reversed(params))
+        offs, cur = [], 0
+        for p in order:
+            offs.append(cur)
+            cur += _round_up(p.numel(), 8)
+        self.numel = _round_up(cur, 8 * 8)  # whole 16-byte vectors per rank for up to 8 ranks
+        self.comm = comm
+        self.device = device
+        self.param = torch.zeros(self.numel, dtype=torch.bfloat16, device=device)
+        self.master = torch.zeros(self.numel, dtype=torch.float32, device=device)
+        self.momentum = torch.zeros(self.numel, dtype=torch.float32, device=device)
+        if comm is not None:
+            self.grad_off = comm.alloc(self.numel * 2)
+            self.grad = comm.tensor(self.grad_off, (self.numel,), torch.bfloat16)
+        else:
+            self.grad_off = 0
+            self.grad = torch.zeros(self.numel, dtype=torch.bfloat16, device=device)
+        self.grad.zero_()
+        self.buckets: list[_Bucket] = []
+        self.views: dict[int, tuple[torch.Tensor, torch.Tensor, torch.Tensor]] = {}
+        cap = max(bucket_bytes // 2, 8)
+        b = _Bucket(0, 0)
+        for p, off in zip(order, offs):
+            n = p.numel()
+            pv = self._view(self.param, off, p)
+            gv = self._view(self.grad, off, p)
+            mv = self.master[off:off + n]
+            with torch.no_grad():
+                pv.copy_(p.data)
+                mv.copy_(p.data.reshape(-1) if p.dim() != 4 else p.data.permute(0, 2, 3, 1).reshape(-1))
+            p.data = pv
+            self.views[id(p)] = (pv, gv, mv)
+            b.params.append(p)
+            b.gviews.append(gv)
+            b.end = off + _round_up(n, 8)
+            if b.end - b.start >= cap:
+                self.buckets.append(b)
+                b = _Bucket(b.end, b.end)
+        if b.params:
+            self.buckets.append(b)
+        self.buckets[-1].end = self.numel
+        # masters were filled from the (bf16 or fp32) init values; make param == bf16(master)
+        self.param.copy_(self.master.to(torch.bfloat16))
+        self.bucket_of = {id(p): b for b in self.buckets for p in b.params}
+
+    @staticmethod
+    def _view(flat: torch.Tensor, off: int, p: torch.Tensor) -> torch.Tensor:
+        n = p.numel()
+        s = flat[off:off + n]
+        if p.dim() == 4:
+            o, i, kh, kw = p.shape
+            return s.view(o, kh, kw, i).permute(0, 3, 1, 2)  # channels-last strides
+        return s.view(p.shape)
+
+    def master_view(self, p: torch.Tensor) -> torch.Tensor:
+        return self.views[id(p)][2]
+
+
+class CollectiveTrainer:
+    """Data-parallel SGD trainer with fused all-reduce and CUDA-graph replay.
+
+    loss_fn(model, *inputs) -> scalar loss tensor.  `example_inputs` are static
+    device tensors; `step()` replays the captured graph on whatever they hold.
+    """
+
+    def __init__(self, model: torch.nn.Module, loss_fn: Callable, example_inputs: tuple,
+                 comm: Optional[Communicator] = None, lr: float = 0.1, momentum: float = 0.9,
+                 weight_decay: float = 1e-4, bucket_bytes: int = 16 << 20, use_graph: bool = True,
+                 comm_blocks: int = 24, algo: Optional[int] = None):
+        self.model = model
+        self.loss_fn = loss_fn
+        self.inputs = example_inputs
+        self.comm = comm if (comm is not None and comm.nranks > 1) else None
+        self.world = comm.nranks if comm is not None else 1
+        self.device = example_inputs[0].device
+        self.flat = FlatParams(model, self.device, self.comm, bucket_bytes)
+        self.hyper = torch.tensor([lr, momentum, weight_decay, 1.0], dtype=torch.float32, device=self.device)
+        self._hyper_host = torch.empty(4, dtype=torch.float32).pin_memory() if self.device.type == "cuda" else None
+        self.loss = torch.zeros((), dtype=torch.float32, device=self.device)
+        self.use_graph = use_graph and self.device.type == "cuda"
+        self.comm_blocks = comm_blocks
+        self.algo = algo
+        self.graph: Optional[torch.cuda.CUDAGraph] = None
+        self.kernels_per_step = 0  # launches of OUR kernels per step (counted at capture/eager time)
+        self._count = 0
+        self.comm_stream = torch.cuda.Stream(self.device) if self.comm is not None else None
+        self._attach_masters()
+        self._install_hooks()
+
+    # -- setup ---------------------------------------------------------------
+    def _attach_masters(self) -> None:
+        from ..ops.bn import FusedBnAct
+
+        for m in self.model.modules():
+            if isinstance(m, FusedBnAct):
+                m.weight_f32 = self.flat.master_view(m.weight)
+                m.bias_f32 = self.flat.master_view(m.bias)
+
+    def _install_hooks(self) -> None:
+        for b in self.flat.buckets:
+            for p in b.params:
+                p.register_post_accumulate_grad_hook(self._make_hook(b))
+
+    def _make_hook(self, bucket: _Bucket):
+        def hook(p: torch.Tensor):
+            bucket.grads.append((self.flat.views[id(p)][1], p.grad))
+            p.grad = None
+            bucket.pending -= 1
+            if bucket.pending == 0:
+                self._bucket_ready(bucket)
+
+        return hook
+
+    def _bucket_ready(self, b: _Bucket) -> None:
+        dst = [d for d, _ in b.grads]
+        src = [s for _, s in b.grads]
+        torch._foreach_copy_(dst, src)
+        b.grads.clear()
+        if self.comm is None:
+            return
+        main = torch.cuda.current_stream()
+        ev = torch.cuda.Event()
+        ev.record(main)
+        self.comm_stream.wait_event(ev)
+        n = b.end - b.start
+        off = self.flat.grad_off + b.start * 2
+        algo = self.algo if self.algo is not None else self.comm.pick_algo(n * 2)
+        if algo == AR_ONESHOT:
+            algo = AR_TWOSHOT  # in-place
+        self.comm.all_reduce_bf16(off, off, n, scale=1.0 / self.world, algo=algo, nblocks=self.comm_blocks,
+                                  stream=self.comm_stream)
+        self._count += 1
+        done = torch.cuda.Event()
+        done.record(self.comm_stream)
+        b.event = done
+
+    # -- one step ---------------------------------------------------------------
+    def _step_body(self) -> None:
+        from ..ops import bn as _bn  # noqa: F401  (kernels counted through module counters)
+
+        for b in self.flat.buckets:
+            b.pending = len(b.params)
+            b.event = None
+        loss = self.loss_fn(self.model, *self.inputs)
+        loss.backward()
+        main = torch.cuda.current_stream() if self.device.type == "cuda" else None
+        for b in self.flat.buckets:
+            if b.pending != 0:
+                raise RuntimeError("a parameter received no gradient; every parameter must take part in the step")
+            if b.event is not None:
+                main.wait_event(b.event)
+        pdj_optim.sgd_momentum_(self.flat.master, self.flat.momentum, self.flat.grad, self.flat.param, self.hyper,
+                                self.flat.numel)
+        self._count += 1
+        self.loss.copy_(loss.detach().float())
+
+    def capture(self, warmup: int = 2) -> None:
+        """Runs `warmup` eager steps on a side stream, then captures the step."""
+        if not self.use_graph:
+            return
+        s = torch.cuda.Stream(self.device)
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
+            for _ in range(warmup):
+                self._step_body()
+        torch.cuda.current_stream().wait_stream(s)
+        torch.cuda.synchronize(self.device)
+        if self.comm is not None:
+            self.comm.barrier()
+            torch.cuda.synchronize(self.device)
+        self.graph = torch.cuda.CUDAGraph()
+        self._count = 0
+        with torch.cuda.graph(self.graph):
+            self._step_body()
+        self.kernels_per_step = self._count + self._model_kernel_count()
+        torch.cuda.synchronize(self.device)
+
+    def _model_kernel_count(self) -> int:
+        """Hand-written kernel launches per step inside the model (fused BN:
+        2 forward + 2 backward per layer) and the loss (1)."""
+        from ..ops.bn import FusedBnAct
+
+        n = sum(4 for m in self.model.modules() if isinstance(m, FusedBnAct))
+        return n + 1
+
+    def step(self) -> torch.Tensor:
+        """Runs one optimisation step on the current contents of the static
+        inputs; returns the (device) loss tensor of that step."""
+        if self.graph is not None:
+            self.graph.replay()
+        else:
+            self._count = 0
+            self._step_body()
+            self.kernels_per_step = self._count + self._model_kernel_count()
+        return self.loss
+
+    def set_lr(self, lr: float) -> None:
+        if self._hyper_host is not None:
+            self._hyper_host.copy_(torch.tensor([lr, 0, 0, 0]))
+            self.hyper[0:1].copy_(self._hyper_host[0:1], non_blocking=True)
+        else:
+            self.hyper[0] = lr
+
+    # -- state (checkpoint / elastic re-shard) -------------------------------------
+    def state_dict(self) -> dict:
+        return {"master": self.flat.master, "momentum": self.flat.momentum, "hyper": self.hyper,
+                "buffers": {k: v for k, v in self.model.named_buffers()}}
+
+    def load_state_dict(self, sd: dict) -> None:
+        with torch.no_grad():
+            self.flat.master.copy_(sd["master"])
+            self.flat.momentum.copy_(sd["momentum"])
+            self.hyper.copy_(sd["hyper"])
+            self.flat.param.copy_(self.flat.master.to(torch.bfloat16))
+            bufs = dict(self.model.named_buffers())
+            for k, v in sd.get("buffers", {}).items():
+                if k in bufs:
+                    bufs[k].copy_(v)
