@@ -81,6 +81,22 @@ int pdj_bn_fwd(const void* x, const void* res, void* y, int M, int C, const floa
 int pdj_bn_bwd(const void* dy, const void* y, const void* x, void* dx, void* dres, int M, int C,
                const float* gamma, const float* mean_rstd, float* dgamma_dbeta, void* dgb_bf16, float* coef,
                int relu, void* workspace, cudaStream_t st);
+/* No counterpart in the reference (it has no device code and no allocator
+ * story).  Same result as pdj_bn_fwd, but takes no workspace and allocates
+ * nothing: its block partials and tickets live in a file-scope device array of
+ * PDJ_BN_NOALLOC_SCRATCH_BYTES that every GPU loading the library holds until
+ * exit.  For FFI callers without an allocator and for rank loops whose HBM
+ * budget is frozen (a late cudaMalloc/cudaFree would fail or synchronise the
+ * device under spinning peers).  Rejects C > PDJ_BN_NOALLOC_MAX_C or
+ * M > PDJ_BN_NOALLOC_MAX_ROWS.  The first call on a device resolves the array's
+ * address: make it before any stream capture.  All calls share the array, so
+ * calls that may overlap on the GPU race; serialise them. */
+#define PDJ_BN_NOALLOC_SCRATCH_BYTES ((2u << 20) + 256u)
+#define PDJ_BN_NOALLOC_MAX_C 2048
+#define PDJ_BN_NOALLOC_MAX_ROWS (1 << 24)
+int pdj_bn_fwd_noalloc(const void* x, const void* res, void* y, int M, int C, const float* gamma,
+                       const float* beta, float eps, float momentum, float* running_mean, float* running_var,
+                       float* mean_rstd, float* scale_shift, int relu, cudaStream_t st);
 int pdj_sgd_momentum(float* w, float* mom, const void* grad, void* param, size_t n, size_t wd_split,
                      const float* hyper, cudaStream_t st);
 int pdj_preprocess_u8(const void* in, void* out, size_t n_px, const float* mean3, const float* std3,

@@ -402,3 +402,130 @@ int pdj_bn_bwd(const void* dy, const void* y, const void* x, void* dx, void* dre
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------
+// pdj_bn_fwd_noalloc: the forward BatchNorm(+add)(+ReLU) for callers that must
+// not allocate device memory.
+//
+// Who that is: (1) plain C / FFI callers that drive this library without
+// PyTorch and therefore have no allocator to get a workspace from; (2) rank
+// loops that run after the job's HBM budget has been frozen (arena + framework
+// pool sized at start-up), where a late cudaMalloc can fail outright and, worse,
+// cudaMalloc/cudaFree synchronise the whole device - which stalls this rank while
+// its peers spin inside the fused collectives waiting for it.
+//
+// The block partial sums and the "last block" tickets that pdj_bn_fwd keeps in a
+// caller-provided workspace live here in one file-scope device array instead.
+// Every GPU that loads this library carries those PDJ_BN_NOALLOC_SCRATCH_BYTES
+// (2 MiB + 256 B) until the process exits.
+//
+// Limits: C a power-of-two multiple of 8 up to PDJ_BN_NOALLOC_MAX_C (2048) and
+// 1 <= M <= PDJ_BN_NOALLOC_MAX_ROWS (2^24 rows); anything else is rejected with
+// an error message and nothing is launched.
+//
+// Set-up: the first call on each device resolves the array's device address
+// (cudaGetSymbolAddress, which may also load the module) and caches it. Make
+// that first call during start-up, before any stream capture begins.
+//
+// Sharing: there is ONE array per device. All calls use it, and it keeps
+// whatever the previous call left behind; the ticket counters are therefore
+// cleared (cudaMemsetAsync on the caller's stream) at the start of every call,
+// the partial sums are fully rewritten before they are read. Two calls that can
+// overlap on the GPU (different streams, or graphs replayed concurrently) race
+// on the array and produce garbage - serialise them.
+//
+// Calls no cudaMalloc / cudaFree / allocating library routine.
+#include <mutex>
+
+namespace {
+
+constexpr size_t kNoAllocCounterBytes = 256;
+constexpr size_t kNoAllocPartialBytes = PDJ_BN_NOALLOC_SCRATCH_BYTES - kNoAllocCounterBytes;
+
+// In host code this name is only a handle for cudaGetSymbolAddress - never pass
+// it to a kernel directly.
+static __device__ __align__(256) unsigned char g_bn_noalloc_scratch[PDJ_BN_NOALLOC_SCRATCH_BYTES];
+
+constexpr int kMaxDevices = 64;
+void* g_noalloc_ptr[kMaxDevices] = {nullptr};
+int g_noalloc_sms[kMaxDevices] = {0};
+std::mutex g_noalloc_mu;
+
+// Once per device, with that device current.
+int noalloc_setup(int dev, void** ptr, int* sms) {
+  std::lock_guard<std::mutex> lk(g_noalloc_mu);
+  if (g_noalloc_ptr[dev] == nullptr) {
+    void* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&p, g_bn_noalloc_scratch);
+    if (e != cudaSuccess || p == nullptr) {
+      pdj_set_error("pdj_bn_fwd_noalloc: cudaGetSymbolAddress failed on device %d: %s", dev, cudaGetErrorString(e));
+      return e != cudaSuccess ? (int)e : -1;
+    }
+    int n = 0;
+    e = cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    if (e != cudaSuccess || n <= 0) {
+      pdj_set_error("pdj_bn_fwd_noalloc: cannot read the SM count of device %d: %s", dev, cudaGetErrorString(e));
+      return e != cudaSuccess ? (int)e : -1;
+    }
+    g_noalloc_sms[dev] = n;
+    g_noalloc_ptr[dev] = p;
+  }
+  *ptr = g_noalloc_ptr[dev];
+  *sms = g_noalloc_sms[dev];
+  return 0;
+}
+
+}  // namespace
+
+extern "C" int pdj_bn_fwd_noalloc(const void* x, const void* res, void* y, int M, int C, const float* gamma,
+                                  const float* beta, float eps, float momentum, float* running_mean,
+                                  float* running_var, float* mean_rstd, float* scale_shift, int relu,
+                                  cudaStream_t st) {
+  const int c8 = C / 8;
+  if (C % 8 != 0 || c8 < 1 || (c8 & (c8 - 1)) != 0 || C > PDJ_BN_NOALLOC_MAX_C) {
+    pdj_set_error("pdj_bn_fwd_noalloc: C=%d is not supported (power-of-two multiple of 8, at most %d)", C,
+                  PDJ_BN_NOALLOC_MAX_C);
+    return -1;
+  }
+  if (M < 1 || M > PDJ_BN_NOALLOC_MAX_ROWS) {
+    pdj_set_error("pdj_bn_fwd_noalloc: M=%d rows is outside 1..%d, the range the built-in scratch is sized for", M,
+                  PDJ_BN_NOALLOC_MAX_ROWS);
+    return -1;
+  }
+  int dev = 0;
+  PDJ_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices) {
+    pdj_set_error("pdj_bn_fwd_noalloc: device index %d is out of range", dev);
+    return -1;
+  }
+  void* scratch = nullptr;
+  int sms = 0;
+  if (int rc = noalloc_setup(dev, &scratch, &sms)) return rc;
+
+  unsigned int* counter = reinterpret_cast<unsigned int*>(scratch);
+  float* partial = reinterpret_cast<float*>(reinterpret_cast<char*>(scratch) + kNoAllocCounterBytes);
+  // Tickets must start at zero whatever the previous user of the array did.
+  PDJ_CUDA_CHECK(cudaMemsetAsync(counter, 0, kNoAllocCounterBytes, st));
+
+  const int cvt = c8 < 32 ? c8 : 32;
+  int gx = grid_rows(M, C, sms);
+  const int cap = (int)(kNoAllocPartialBytes / ((size_t)2 * C * sizeof(float)));  // row blocks that fit
+  if (gx > cap) gx = cap;
+  dim3 g(gx, c8 / cvt);
+  bn_stats_kernel<<<g, kThreads, 0, st>>>((const __nv_bfloat16*)x, M, C, gamma, beta, eps, momentum, running_mean,
+                                          running_var, mean_rstd, scale_shift, partial, counter);
+  PDJ_CUDA_CHECK(cudaGetLastError());
+  const size_t n_vec = (size_t)M * c8;
+  size_t fg = (n_vec + (size_t)kThreads * 4 - 1) / ((size_t)kThreads * 4);
+  if (fg > (size_t)sms * 8) fg = (size_t)sms * 8;
+  if (fg < 1) fg = 1;
+  const __nv_bfloat16* xb = (const __nv_bfloat16*)x;
+  const __nv_bfloat16* rb = (const __nv_bfloat16*)res;
+  __nv_bfloat16* yb = (__nv_bfloat16*)y;
+  if (relu && res) bn_apply_kernel<true, true><<<(int)fg, kThreads, 0, st>>>(xb, rb, yb, n_vec, C, scale_shift);
+  else if (relu) bn_apply_kernel<true, false><<<(int)fg, kThreads, 0, st>>>(xb, rb, yb, n_vec, C, scale_shift);
+  else if (res) bn_apply_kernel<false, true><<<(int)fg, kThreads, 0, st>>>(xb, rb, yb, n_vec, C, scale_shift);
+  else bn_apply_kernel<false, false><<<(int)fg, kThreads, 0, st>>>(xb, rb, yb, n_vec, C, scale_shift);
+  PDJ_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
