@@ -1,0 +1,274 @@
+"""In-memory object store: the stand-in for kube-apiserver + etcd.
+
+Holds Kubernetes-shaped dict objects keyed by (kind, namespace, name) with the
+semantics the reference controller relies on (controller-runtime client,
+controllers/paddlejob_controller.go:105-131,383-405,460-489,520-571):
+
+* resourceVersion bumped on every write; Update with a stale version -> Conflict
+* a status "subresource": update_status() touches only .status, update() never does
+* metadata.generation bumped when .spec changes
+* finalizers: delete() of an object with finalizers only sets deletionTimestamp;
+  the object goes away when the last finalizer is removed
+* owner references: deleting an owner garbage-collects its dependents
+  (background propagation)
+* watches: every change is delivered to subscribers, which is what drives the
+  reconcile work-queue
+* an index of objects by controlling owner (the `.metadata.controller` field
+  index of the reference, :520-532)
+"""
+from __future__ import annotations
+
+import copy
+import datetime as _dt
+import threading
+import uuid
+from typing import Callable, Iterable, Optional
+
+
+class StoreError(Exception):
+    pass
+
+
+class NotFound(StoreError):
+    pass
+
+
+class AlreadyExists(StoreError):
+    pass
+
+
+class Conflict(StoreError):
+    pass
+
+
+def _now() -> str:
+    return _dt.datetime.now(_dt.timezone.utc).strftime("%Y-%m-%dT%H:%M:%SZ")
+
+
+Key = tuple  # (kind, namespace, name)
+WatchFn = Callable[[str, dict], None]  # (event_type, object)
+
+
+class ObjectStore:
+    def __init__(self):
+        self._lock = threading.RLock()
+        self._objs: dict[Key, dict] = {}
+        self._rv = 0
+        self._watchers: list[WatchFn] = []
+
+    # -- helpers ----------------------------------------------------------------
+    @staticmethod
+    def key_of(obj: dict) -> Key:
+        m = obj.get("metadata") or {}
+        return (obj.get("kind", ""), m.get("namespace") or "default", m.get("name", ""))
+
+    def _next_rv(self) -> str:
+        self._rv += 1
+        return str(self._rv)
+
+    def _notify(self, typ: str, obj: dict) -> None:
+        for w in list(self._watchers):
+            w(typ, copy.deepcopy(obj))
+
+    def watch(self, fn: WatchFn) -> Callable[[], None]:
+        with self._lock:
+            self._watchers.append(fn)
+
+        def cancel():
+            with self._lock:
+                if fn in self._watchers:
+                    self._watchers.remove(fn)
+
+        return cancel
+
+    # -- CRUD ---------------------------------------------------------------------
+    def create(self, obj: dict) -> dict:
+        obj = copy.deepcopy(obj)
+        meta = obj.setdefault("metadata", {})
+        meta.setdefault("namespace", "default")
+        if not meta.get("name"):
+            raise StoreError("metadata.name is required")
+        key = self.key_of(obj)
+        with self._lock:
+            if key in self._objs:
+                raise AlreadyExists(f"{key[0]} {key[1]}/{key[2]} already exists")
+            for ref in meta.get("ownerReferences") or []:
+                if not ref.get("uid"):
+                    okey = (ref.get("kind", ""), meta["namespace"], ref.get("name", ""))
+                    owner = self._objs.get(okey)
+                    if owner is not None:
+                        ref["uid"] = owner["metadata"]["uid"]
+            meta["uid"] = meta.get("uid") or str(uuid.uuid4())
+            meta["resourceVersion"] = self._next_rv()
+            meta["generation"] = 1
+            meta["creationTimestamp"] = meta.get("creationTimestamp") or _now()
+            meta.pop("deletionTimestamp", None)
+            self._objs[key] = obj
+            self._notify("ADDED", obj)
+            return copy.deepcopy(obj)
+
+    def get(self, kind: str, namespace: str, name: str) -> dict:
+        with self._lock:
+            obj = self._objs.get((kind, namespace or "default", name))
+            if obj is None:
+                raise NotFound(f"{kind} {namespace}/{name} not found")
+            return copy.deepcopy(obj)
+
+    def try_get(self, kind: str, namespace: str, name: str) -> Optional[dict]:
+        try:
+            return self.get(kind, namespace, name)
+        except NotFound:
+            return None
+
+    def list(self, kind: str, namespace: Optional[str] = None, owner: Optional[str] = None,
+             owner_kind: str = "PaddleJob", labels: Optional[dict] = None) -> list[dict]:
+        """Objects of `kind`, optionally restricted to a namespace, to those
+        controlled by the named owner (the field index of the reference) and to
+        a label selector.  Sorted by name for determinism."""
+        out = []
+        with self._lock:
+            for (k, ns, _), obj in self._objs.items():
+                if k != kind or (namespace is not None and ns != namespace):
+                    continue
+                if owner is not None:
+                    ctrl = next((r for r in obj["metadata"].get("ownerReferences") or [] if r.get("controller")), None)
+                    if ctrl is None or ctrl.get("name") != owner or ctrl.get("kind") != owner_kind:
+                        continue
+                if labels:
+                    have = obj["metadata"].get("labels") or {}
+                    if any(have.get(a) != b for a, b in labels.items()):
+                        continue
+                out.append(copy.deepcopy(obj))
+        out.sort(key=lambda o: (o["metadata"].get("namespace", ""), o["metadata"]["name"]))
+        return out
+
+    def _check_rv(self, cur: dict, new: dict) -> None:
+        rv = str((new.get("metadata") or {}).get("resourceVersion", "") or "")
+        if rv and rv != cur["metadata"]["resourceVersion"]:
+            raise Conflict(f"{cur.get('kind')} {cur['metadata']['name']}: the object has been modified "
+                           f"(have {cur['metadata']['resourceVersion']}, update carries {rv})")
+
+    def update(self, obj: dict) -> dict:
+        """Replaces everything except .status.  Removes the object when it is
+        being deleted and the update drops the last finalizer."""
+        key = self.key_of(obj)
+        with self._lock:
+            cur = self._objs.get(key)
+            if cur is None:
+                raise NotFound(f"{key[0]} {key[1]}/{key[2]} not found")
+            self._check_rv(cur, obj)
+            new = copy.deepcopy(obj)
+            new["status"] = copy.deepcopy(cur.get("status", {}))
+            meta, cmeta = new.setdefault("metadata", {}), cur["metadata"]
+            for k in ("uid", "creationTimestamp", "deletionTimestamp"):
+                if k in cmeta:
+                    meta[k] = cmeta[k]
+                else:
+                    meta.pop(k, None)
+            meta["generation"] = cmeta.get("generation", 1) + (1 if new.get("spec") != cur.get("spec") else 0)
+            meta["resourceVersion"] = self._next_rv()
+            if meta.get("deletionTimestamp") and not meta.get("finalizers"):
+                self._remove(key)
+                return copy.deepcopy(new)
+            self._objs[key] = new
+            self._notify("MODIFIED", new)
+            return copy.deepcopy(new)
+
+    def update_status(self, obj: dict) -> dict:
+        key = self.key_of(obj)
+        with self._lock:
+            cur = self._objs.get(key)
+            if cur is None:
+                raise NotFound(f"{key[0]} {key[1]}/{key[2]} not found")
+            self._check_rv(cur, obj)
+            cur["status"] = copy.deepcopy(obj.get("status", {}))
+            cur["metadata"]["resourceVersion"] = self._next_rv()
+            self._notify("MODIFIED", cur)
+            return copy.deepcopy(cur)
+
+    def patch_status(self, kind: str, namespace: str, name: str, fn: Callable[[dict], None]) -> dict:
+        """Read-modify-write of .status without a resourceVersion check (what a
+        kubelet does to its pods)."""
+        with self._lock:
+            cur = self._objs.get((kind, namespace or "default", name))
+            if cur is None:
+                raise NotFound(f"{kind} {namespace}/{name} not found")
+            st = cur.setdefault("status", {})
+            fn(st)
+            cur["metadata"]["resourceVersion"] = self._next_rv()
+            self._notify("MODIFIED", cur)
+            return copy.deepcopy(cur)
+
+    def delete(self, kind: str, namespace: str, name: str) -> None:
+        key = (kind, namespace or "default", name)
+        with self._lock:
+            cur = self._objs.get(key)
+            if cur is None:
+                raise NotFound(f"{kind} {namespace}/{name} not found")
+            if cur["metadata"].get("finalizers"):
+                if not cur["metadata"].get("deletionTimestamp"):
+                    cur["metadata"]["deletionTimestamp"] = _now()
+                    cur["metadata"]["resourceVersion"] = self._next_rv()
+                    self._notify("MODIFIED", cur)
+                return
+            self._remove(key)
+
+    def _remove(self, key: Key) -> None:
+        obj = self._objs.pop(key, None)
+        if obj is None:
+            return
+        self._notify("DELETED", obj)
+        # garbage-collect dependents (background propagation)
+        uid = obj["metadata"].get("uid")
+        deps = [k for k, o in self._objs.items()
+                if k[1] == key[1] and any(r.get("uid") == uid or (not r.get("uid") and r.get("name") == key[2]
+                                                                     and r.get("kind") == key[0])
+                                          for r in o["metadata"].get("ownerReferences") or [])]
+        for k in deps:
+            d = self._objs.get(k)
+            if d is None:
+                continue
+            if d["metadata"].get("finalizers"):
+                d["metadata"]["deletionTimestamp"] = d["metadata"].get("deletionTimestamp") or _now()
+                self._notify("MODIFIED", d)
+            else:
+                self._remove(k)
+
+    def kinds(self) -> set[str]:
+        with self._lock:
+            return {k[0] for k in self._objs}
+
+    def dump(self) -> list[dict]:
+        with self._lock:
+            return [copy.deepcopy(o) for o in self._objs.values()]
+
+
+class EventRecorder:
+    """k8s Events on the job (controllers/paddlejob_controller.go:383-405,215):
+    Normal/Warning, reason, message.  Stored as Event objects so `pdj events`
+    and the tests can read the audit trail."""
+
+    def __init__(self, store: ObjectStore, component: str = "paddlejob-controller"):
+        self.store, self.component = store, component
+        self._n = 0
+        self._lock = threading.Lock()
+
+    def event(self, involved: dict, etype: str, reason: str, message: str) -> None:
+        with self._lock:
+            self._n += 1
+            n = self._n
+        m = involved.get("metadata") or {}
+        self.store.create({
+            "apiVersion": "v1", "kind": "Event",
+            "metadata": {"name": f"{m.get('name', 'obj')}.{n:08x}", "namespace": m.get("namespace", "default")},
+            "involvedObject": {"kind": involved.get("kind", ""), "name": m.get("name", ""),
+                               "namespace": m.get("namespace", "default"), "uid": m.get("uid", "")},
+            "type": etype, "reason": reason, "message": message,
+            "source": {"component": self.component}, "firstTimestamp": _now(), "count": 1,
+        })
+
+    def events_for(self, kind: str, namespace: str, name: str) -> list[dict]:
+        evs = [e for e in self.store.list("Event", namespace)
+               if e["involvedObject"]["kind"] == kind and e["involvedObject"]["name"] == name]
+        evs.sort(key=lambda e: e["metadata"]["name"])
+        return evs
