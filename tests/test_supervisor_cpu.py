@@ -1,0 +1,123 @@
+"""Real rank processes on CPU (tier T-proc of SURVEY.md section 4): the
+supervisor runs each Pod as a subprocess; ranks dump the environment they see."""
+import json
+import os
+import signal
+import time
+
+import pytest
+import yaml
+
+from paddle_operator_b200.runtime.cluster import LocalCluster
+from paddle_operator_b200.runtime.supervisor import resolve_command
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture
+def cluster(tmp_path):
+    c = LocalCluster(gpus=[0, 1, 2, 3], work_root=str(tmp_path / "work"),
+                     extra_env={"PDJ_ENV_DUMP_DIR": str(tmp_path / "dump")})
+    c.dump = tmp_path / "dump"
+    with c:
+        yield c
+
+
+def _dumps(c):
+    return {f[:-5]: json.load(open(c.dump / f)) for f in sorted(os.listdir(c.dump))}
+
+
+def test_env_dump_job_runs_to_completion_in_order(cluster):
+    cluster.apply(os.path.join(ROOT, "examples", "env_dump.yaml"))
+    assert cluster.wait("env-dump", timeout=60) == "Completed"
+    job = cluster.get("env-dump")
+    assert job.status.mode == "PS" and job.status.start_time and job.status.completion_time
+    assert job.status.ps.succeeded == 2 and job.status.worker.succeeded == 2 and job.status.heter.succeeded == 1
+    d = _dumps(cluster)
+    assert sorted(d) == ["env-dump-heter-0", "env-dump-ps-0", "env-dump-ps-1", "env-dump-worker-0", "env-dump-worker-1"]
+    w1, p0 = d["env-dump-worker-1"], d["env-dump-ps-0"]
+    assert w1["PADDLE_TRAINER_ID"] == "1" and w1["TRAINING_ROLE"] == "TRAINER" == w1["PADDLE_TRAINING_ROLE"]
+    assert p0["TRAINING_ROLE"] == "PSERVER" and d["env-dump-heter-0"]["TRAINING_ROLE"] == "HETER"
+    assert w1["PADDLE_TRAINERS_NUM"] == "2" and w1["TRAINER_PORTS_NUM"] == "20" and w1["PADDLE_PORT"] == "2379"
+    eps = w1["PADDLE_TRAINER_ENDPOINTS"].split(",")
+    assert len(eps) == 2 and all(e.startswith("127.") and e.endswith(":2379") for e in eps) and len(set(eps)) == 2
+    assert w1["POD_IP"] + ":2379" == eps[1] and w1["PADDLE_TRAINERS"] == ",".join(e.split(":")[0] for e in eps)
+    assert p0["PADDLE_PSERVERS_IP_PORT_LIST"].split(",")[0] == p0["POD_IP"] + ":2379"
+    assert w1["PADDLE_WITH_GLOO"] == "1" and w1["PADDLE_GLOO_HTTP_ENDPOINT"] == p0["POD_IP"] + ":2397"
+    assert len(w1["PADDLE_HETER_ENDPOINTS"].split(",")) == 1
+    # every rank of the job agrees on the global environment
+    for k in ("PADDLE_TRAINER_ENDPOINTS", "PADDLE_PSERVERS_IP_PORT_LIST", "PADDLE_HETER_ENDPOINTS"):
+        assert len({v[k] for v in d.values()}) == 1
+    # start order: ps before worker before heter (the coord gate)
+    started = {p["metadata"]["name"]: p["status"]["containerStatuses"][0] for p in cluster.pods("env-dump")}
+    assert all(cs["state"]["terminated"]["exitCode"] == 0 for cs in started.values())
+    logs = cluster.logs("env-dump-worker-0")
+    assert "PADDLE_TRAINER_ID" in logs
+
+
+def test_gpu_assignment_failure_and_restart_policy(cluster):
+    tmpl = {"spec": {"containers": [{"name": "m", "image": "x", "command": ["python", "-m",
+                                                                             "paddle_operator_b200.workloads.env_dump"],
+                                      "resources": {"limits": {"nvidia.com/gpu": 1}}}]}}
+    job = {"apiVersion": "batch.paddlepaddle.org/v1", "kind": "PaddleJob", "metadata": {"name": "col"},
+           "spec": {"worker": {"replicas": 3, "template": tmpl}}}
+    cluster.apply(job)
+    assert cluster.wait("col", timeout=60) == "Completed"
+    d = _dumps(cluster)
+    assert sorted(v["CUDA_VISIBLE_DEVICES"] for v in d.values()) == ["0", "1", "2"]
+    assert all(v["PDJ_LOCAL_DEVICE"] == "0" for v in d.values())
+    assert cluster.get("col").status.mode == "Collective"
+    assert cluster.pods("col") == []  # default cleanPodPolicy cleans a completed job
+    # a failing rank with restartPolicy Never fails the job, stickily
+    bad = yaml.safe_load(yaml.safe_dump(job))
+    bad["metadata"]["name"] = "bad"
+    bad["spec"]["worker"]["replicas"] = 1
+    bad["spec"]["worker"]["template"]["spec"]["containers"][0]["env"] = [{"name": "PDJ_ENV_DUMP_EXIT", "value": "3"}]
+    cluster.apply(bad)
+    assert cluster.wait("bad", timeout=60) == "Failed"
+    pod = cluster.pods("bad")[0]
+    assert pod["status"]["containerStatuses"][0]["state"]["terminated"]["exitCode"] == 3
+    # elastic jobs restart in place (OnFailure)
+    el = yaml.safe_load(yaml.safe_dump(bad))
+    el["metadata"]["name"] = "el"
+    el["spec"]["elastic"] = 1
+    cluster.apply(el)
+    deadline = time.time() + 30
+    while time.time() < deadline:
+        pods = cluster.pods("el")
+        if pods and (pods[0]["status"].get("containerStatuses") or [{}])[0].get("restartCount", 0) >= 2:
+            break
+        time.sleep(0.05)
+    else:
+        raise AssertionError("the elastic rank was not restarted in place")
+    assert cluster.get("el").status.phase != "Failed"
+    cluster.delete("el")
+    cluster.wait_deleted("el")
+
+
+def test_kill_rank_and_delete_job_terminates_processes(cluster):
+    tmpl = {"spec": {"containers": [{"name": "m", "image": "x", "command": ["python", "-c", "import time; time.sleep(60)"]}]}}
+    cluster.apply({"apiVersion": "batch.paddlepaddle.org/v1", "kind": "PaddleJob", "metadata": {"name": "sleepy"},
+                   "spec": {"worker": {"replicas": 2, "template": tmpl}}})
+    assert cluster.wait("sleepy", phases=("Running",), timeout=30) == "Running"
+    pids = [p["status"]["containerStatuses"][0]["pid"] for p in cluster.pods("sleepy")]
+    assert cluster.supervisor.kill_rank("default", "sleepy-worker-1", signal.SIGKILL)
+    assert cluster.wait("sleepy", timeout=30) == "Failed"
+    cluster.delete("sleepy")
+    cluster.wait_deleted("sleepy")
+    time.sleep(0.3)
+    for pid in pids:
+        try:
+            os.kill(pid, 0)
+            alive = open(f"/proc/{pid}/stat").read().split()[2] != "Z"
+        except (ProcessLookupError, FileNotFoundError):
+            alive = False
+        assert not alive
+
+
+def test_command_resolution():
+    assert resolve_command({"image": "registry.baidubce.com/paddle-operator/demo-wide-and-deep:v1"})[2] == \
+        "paddle_operator_b200.workloads.train_wide_deep"
+    c = resolve_command({"image": "x", "command": ["python"], "args": ["-m", "paddle.distributed.launch", "train_fleet.py"]})
+    assert c[1:] == ["-m", "paddle_operator_b200.workloads.train_resnet"]
+    assert resolve_command({"image": "unknown"}) is None
