@@ -97,6 +97,11 @@ int pdj_bn_bwd(const void* dy, const void* y, const void* x, void* dx, void* dre
 int pdj_bn_fwd_noalloc(const void* x, const void* res, void* y, int M, int C, const float* gamma,
                        const float* beta, float eps, float momentum, float* running_mean, float* running_var,
                        float* mean_rstd, float* scale_shift, int relu, cudaStream_t st);
+/* NHWC bf16 max pooling with a saved arg-max (csrc/pool.cu).  idx holds one byte per output element. */
+int pdj_maxpool_fwd(const void* x, void* y, void* idx, int N, int H, int W, int C, int k, int s, int p,
+                    cudaStream_t st);
+int pdj_maxpool_bwd(const void* dy, const void* idx, void* dx, int N, int H, int W, int C, int k, int s, int p,
+                    cudaStream_t st);
 int pdj_sgd_momentum(float* w, float* mom, const void* grad, void* param, size_t n, size_t wd_split,
                      const float* hyper, cudaStream_t st);
 int pdj_preprocess_u8(const void* in, void* out, size_t n_px, const float* mean3, const float* std3,

@@ -10,6 +10,8 @@
 //
 // x is viewed as [M, C] (M = N*H*W rows, C channels contiguous), C % 8 == 0,
 // C <= 2048 so that 256 % min(C/8,32) == 0.
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "../../include/pdjob_b200.h"
 
@@ -18,17 +20,17 @@ namespace {
 constexpr int kThreads = 256;
 
 struct Tile {
-  int cvt;        // channel-vectors (of 8) per block: min(C/8, 32)
+  int cvt;        // channel-vectors (of 8) per block: min(C/8, cvt_max)
   int rows_par;   // rows processed in parallel by a block: 256 / cvt
   int cv;         // this thread's channel-vector index within the tensor
   int row0;       // this thread's first row
   int row_step;   // row stride between iterations
 };
 
-__device__ __forceinline__ Tile make_tile(int C) {
+__device__ __forceinline__ Tile make_tile(int C, int cvt_max) {
   Tile t;
   const int c8 = C >> 3;
-  t.cvt = c8 < 32 ? c8 : 32;
+  t.cvt = c8 < cvt_max ? c8 : cvt_max;
   t.rows_par = kThreads / t.cvt;
   t.cv = blockIdx.y * t.cvt + (threadIdx.x % t.cvt);
   t.row0 = blockIdx.x * t.rows_par + threadIdx.x / t.cvt;
@@ -80,53 +82,83 @@ __device__ __forceinline__ bool reduce_and_publish(const Tile& t, int C, const f
   return is_last;
 }
 
+// Last-block finalisation: sums partial[b][k][ch0 + c] over the nb row blocks
+// with all 256 threads (256 / nch threads per channel, then a shared-memory
+// fold).  Returns true in the threads that own a channel (threadIdx.x < nch),
+// with the two sums in s and q.
+__device__ __forceinline__ bool sum_partials(const float* partial, int C, int ch0, int nch, unsigned int nb, float& s,
+                                             float& q) {
+  __shared__ float red[2][kThreads];
+  const int lanes = kThreads / nch;
+  const int c = threadIdx.x % nch;
+  const unsigned int sub = threadIdx.x / nch;
+  float a = 0.f, b2 = 0.f;
+#pragma unroll 4
+  for (unsigned int b = sub; b < nb; b += lanes) {
+    a += partial[((size_t)b * 2 + 0) * C + ch0 + c];
+    b2 += partial[((size_t)b * 2 + 1) * C + ch0 + c];
+  }
+  red[0][threadIdx.x] = a;
+  red[1][threadIdx.x] = b2;
+  __syncthreads();
+  if ((int)threadIdx.x >= nch) return false;
+  for (int j = 1; j < lanes; ++j) {
+    a += red[0][threadIdx.x + j * nch];
+    b2 += red[1][threadIdx.x + j * nch];
+  }
+  s = a;
+  q = b2;
+  return true;
+}
+
 // ---- forward --------------------------------------------------------------
+template <int U>
 __global__ void __launch_bounds__(kThreads)
 bn_stats_kernel(const __nv_bfloat16* __restrict__ x, int M, int C, const float* __restrict__ gamma,
                 const float* __restrict__ beta, float eps, float momentum, float* __restrict__ running_mean,
                 float* __restrict__ running_var, float* __restrict__ mean_rstd /*[2][C]*/,
                 float* __restrict__ scale_shift /*[2][C]*/, float* __restrict__ partial,
-                unsigned int* __restrict__ counter) {
-  const Tile t = make_tile(C);
+                unsigned int* __restrict__ counter, int cvt_max) {
+  const Tile t = make_tile(C, cvt_max);
   float acc[16];
 #pragma unroll
   for (int k = 0; k < 16; ++k) acc[k] = 0.f;
   const char* xp = reinterpret_cast<const char*>(x) + (size_t)t.cv * 16;
   const size_t row_bytes = (size_t)C * 2;
   int r = t.row0;
-  // Two independent rows per iteration for memory-level parallelism.
-  for (; r + t.row_step < M; r += 2 * t.row_step) {
-    const uint4 u0 = ldg16(xp + (size_t)r * row_bytes);
-    const uint4 u1 = ldg16(xp + (size_t)(r + t.row_step) * row_bytes);
-    float f[8], g[8];
-    unpack8(u0, f);
-    unpack8(u1, g);
+  const int rs = t.row_step;
+  // U independent rows per iteration: U x 16 B in flight per thread.
+  for (; r + (U - 1) * rs < M; r += U * rs) {
+    uint4 u[U];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      acc[j] += f[j] + g[j];
-      acc[8 + j] += f[j] * f[j] + g[j] * g[j];
+    for (int k = 0; k < U; ++k) u[k] = ldg16(xp + (size_t)(r + k * rs) * row_bytes);
+#pragma unroll
+    for (int k = 0; k < U; ++k) {
+      float f[8];
+      unpack8(u[k], f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        acc[j] += f[j];
+        acc[8 + j] = fmaf(f[j], f[j], acc[8 + j]);
+      }
     }
   }
-  if (r < M) {
+  for (; r < M; r += rs) {
     float f[8];
     unpack8(ldg16(xp + (size_t)r * row_bytes), f);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       acc[j] += f[j];
-      acc[8 + j] += f[j] * f[j];
+      acc[8 + j] = fmaf(f[j], f[j], acc[8 + j]);
     }
   }
   if (!reduce_and_publish(t, C, acc, partial, counter)) return;
   // Last block of this channel tile: finalise its channels.
   const int nch = t.cvt * 8;
   const float inv_m = 1.f / (float)M;
-  for (int o = threadIdx.x; o < nch; o += kThreads) {
-    const int ch = blockIdx.y * nch + o;
-    float s = 0.f, q = 0.f;
-    for (unsigned int b = 0; b < gridDim.x; ++b) {
-      s += partial[((size_t)b * 2 + 0) * C + ch];
-      q += partial[((size_t)b * 2 + 1) * C + ch];
-    }
+  float s, q;
+  if (sum_partials(partial, C, blockIdx.y * nch, nch, gridDim.x, s, q)) {
+    const int ch = blockIdx.y * nch + threadIdx.x;
     const float mean = s * inv_m;
     float var = q * inv_m - mean * mean;
     var = var < 0.f ? 0.f : var;
@@ -196,15 +228,15 @@ bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __rest
 // dz = dy * (y > 0) when RELU.  Pass 1: sum(dz), sum(dz * xhat) per channel;
 // the last block turns them into dgamma/dbeta and the three coefficients of
 //   dx = A*dz + B*x + Cc.
-template <bool RELU>
+template <bool RELU, int U>
 __global__ void __launch_bounds__(kThreads)
 bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ y,
                      const __nv_bfloat16* __restrict__ x, int M, int C, const float* __restrict__ gamma,
                      const float* __restrict__ mean_rstd, float* __restrict__ dgamma_dbeta /*[2][C] fp32*/,
                      __nv_bfloat16* __restrict__ dgb_bf16 /*[2][C] or null*/,
                      float* __restrict__ coef /*[3][C]*/, float* __restrict__ partial,
-                     unsigned int* __restrict__ counter) {
-  const Tile t = make_tile(C);
+                     unsigned int* __restrict__ counter, int cvt_max) {
+  const Tile t = make_tile(C, cvt_max);
   float mu[8], rs[8], acc[16];
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
@@ -218,7 +250,34 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
   const char* dyp = reinterpret_cast<const char*>(dy) + coff;
   const char* yp = reinterpret_cast<const char*>(y) + coff;
   const char* xp = reinterpret_cast<const char*>(x) + coff;
-  for (int r = t.row0; r < M; r += t.row_step) {
+  // sum(dz * xhat) = rstd * (sum(dz * x) - mean * sum(dz)): accumulate the raw
+  // sums here and fold mean / rstd in once per channel at the end.
+  int r = t.row0;
+  const int rstep = t.row_step;
+  for (; U == 2 && r + rstep < M; r += 2 * rstep) {
+    const size_t o0 = (size_t)r * row_bytes, o1 = (size_t)(r + rstep) * row_bytes;
+    const uint4 ud0 = ldg16(dyp + o0), ux0 = ldg16(xp + o0), ud1 = ldg16(dyp + o1), ux1 = ldg16(xp + o1);
+    uint4 uy0, uy1;
+    if (RELU) { uy0 = ldg16(yp + o0); uy1 = ldg16(yp + o1); }
+    float d[8], xx[8], yy[8];
+    unpack8(ud0, d); unpack8(ux0, xx);
+    if (RELU) unpack8(uy0, yy);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float dz = RELU ? (yy[j] > 0.f ? d[j] : 0.f) : d[j];
+      acc[j] += dz;
+      acc[8 + j] = fmaf(dz, xx[j] - mu[j], acc[8 + j]);
+    }
+    unpack8(ud1, d); unpack8(ux1, xx);
+    if (RELU) unpack8(uy1, yy);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float dz = RELU ? (yy[j] > 0.f ? d[j] : 0.f) : d[j];
+      acc[j] += dz;
+      acc[8 + j] = fmaf(dz, xx[j] - mu[j], acc[8 + j]);
+    }
+  }
+  for (; r < M; r += rstep) {
     const size_t o = (size_t)r * row_bytes;
     const uint4 ud = ldg16(dyp + o), ux = ldg16(xp + o);
     uint4 uy;
@@ -231,19 +290,17 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
     for (int j = 0; j < 8; ++j) {
       const float dz = RELU ? (yy[j] > 0.f ? d[j] : 0.f) : d[j];
       acc[j] += dz;
-      acc[8 + j] += dz * (xx[j] - mu[j]) * rs[j];
+      acc[8 + j] = fmaf(dz, xx[j] - mu[j], acc[8 + j]);
     }
   }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) acc[8 + j] *= rs[j];
   if (!reduce_and_publish(t, C, acc, partial, counter)) return;
   const int nch = t.cvt * 8;
   const float inv_m = 1.f / (float)M;
-  for (int o = threadIdx.x; o < nch; o += kThreads) {
-    const int ch = blockIdx.y * nch + o;
-    float sdz = 0.f, sdzx = 0.f;
-    for (unsigned int b = 0; b < gridDim.x; ++b) {
-      sdz += partial[((size_t)b * 2 + 0) * C + ch];
-      sdzx += partial[((size_t)b * 2 + 1) * C + ch];
-    }
+  float sdz, sdzx;
+  if (sum_partials(partial, C, blockIdx.y * nch, nch, gridDim.x, sdz, sdzx)) {
+    const int ch = blockIdx.y * nch + threadIdx.x;
     dgamma_dbeta[ch] = sdzx;
     dgamma_dbeta[C + ch] = sdz;
     if (dgb_bf16 != nullptr) {
@@ -297,13 +354,38 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* _
   }
 }
 
+int env_int(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return (v && *v) ? atoi(v) : dflt;
+}
+// Tuning knobs (read once): row blocks per SM for the two reduction kernels,
+// minimum rows per thread, rows in flight per thread in the statistics pass.
+int knob_blocks_per_sm() { static int v = env_int("PDJ_BN_BLOCKS_PER_SM", 4); return v; }
+int knob_min_rows() { static int v = env_int("PDJ_BN_MIN_ROWS", 4); return v; }
+int knob_stats_unroll() { static int v = env_int("PDJ_BN_STATS_UNROLL", 1); return v; }
+int knob_bwd_unroll() { static int v = env_int("PDJ_BN_BWD_UNROLL", 1); return v; }
+int knob_cvt() {
+  static int v = env_int("PDJ_BN_CVT", 4);
+  return (v == 1 || v == 2 || v == 4 || v == 8 || v == 16 || v == 32) ? v : 4;
+}
+
+template <typename... A>
+void launch_stats(dim3 g, cudaStream_t st, A... a) {
+  switch (knob_stats_unroll()) {
+    case 1: bn_stats_kernel<1><<<g, kThreads, 0, st>>>(a...); break;
+    case 4: bn_stats_kernel<4><<<g, kThreads, 0, st>>>(a...); break;
+    default: bn_stats_kernel<2><<<g, kThreads, 0, st>>>(a...); break;
+  }
+}
+
 int grid_rows(int M, int C, int sm_count) {
   const int c8 = C / 8;
-  const int cvt = c8 < 32 ? c8 : 32;
+  const int cvt = c8 < knob_cvt() ? c8 : knob_cvt();
   const int gy = c8 / cvt;
   const int rows_par = kThreads / cvt;
-  int gx = (2 * sm_count + gy - 1) / gy;         // about two blocks per SM in total
-  const int max_gx = (M + rows_par * 4 - 1) / (rows_par * 4);  // at least 4 rows per thread
+  int gx = (knob_blocks_per_sm() * sm_count + gy - 1) / gy;
+  const int mr = knob_min_rows();
+  const int max_gx = (M + rows_par * mr - 1) / (rows_par * mr);  // at least `mr` rows per thread
   if (gx > max_gx) gx = max_gx;
   if (gx < 1) gx = 1;
   if (gx > PDJ_BN_MAX_ROW_BLOCKS) gx = PDJ_BN_MAX_ROW_BLOCKS;
@@ -353,10 +435,10 @@ int pdj_bn_fwd(const void* x, const void* res, void* y, int M, int C, const floa
   if (check_shape(M, C)) return -1;
   float* partial = reinterpret_cast<float*>(reinterpret_cast<char*>(workspace) + 256);
   unsigned int* counter = reinterpret_cast<unsigned int*>(workspace);
-  const int c8 = C / 8, cvt = c8 < 32 ? c8 : 32;
+  const int c8 = C / 8, cvt = c8 < knob_cvt() ? c8 : knob_cvt();
   dim3 g(grid_rows(M, C, sm_count()), c8 / cvt);
-  bn_stats_kernel<<<g, kThreads, 0, st>>>((const __nv_bfloat16*)x, M, C, gamma, beta, eps, momentum, running_mean,
-                                          running_var, mean_rstd, scale_shift, partial, counter);
+  launch_stats(g, st, (const __nv_bfloat16*)x, M, C, gamma, beta, eps, momentum, running_mean, running_var, mean_rstd,
+               scale_shift, partial, counter, knob_cvt());
   PDJ_CUDA_CHECK(cudaGetLastError());
   const size_t n_vec = (size_t)M * c8;
   const int fg = flat_grid(n_vec);
@@ -377,17 +459,28 @@ int pdj_bn_bwd(const void* dy, const void* y, const void* x, void* dx, void* dre
   if (check_shape(M, C)) return -1;
   float* partial = reinterpret_cast<float*>(reinterpret_cast<char*>(workspace) + 256);
   unsigned int* counter = reinterpret_cast<unsigned int*>(workspace);
-  const int c8 = C / 8, cvt = c8 < 32 ? c8 : 32;
+  const int c8 = C / 8, cvt = c8 < knob_cvt() ? c8 : knob_cvt();
   dim3 g(grid_rows(M, C, sm_count()), c8 / cvt);
   const __nv_bfloat16* dyb = (const __nv_bfloat16*)dy;
   const __nv_bfloat16* yb = (const __nv_bfloat16*)y;
   const __nv_bfloat16* xb = (const __nv_bfloat16*)x;
-  if (relu)
-    bn_bwd_reduce_kernel<true><<<g, kThreads, 0, st>>>(dyb, yb, xb, M, C, gamma, mean_rstd, dgamma_dbeta,
-                                                       (__nv_bfloat16*)dgb_bf16, coef, partial, counter);
-  else
-    bn_bwd_reduce_kernel<false><<<g, kThreads, 0, st>>>(dyb, yb, xb, M, C, gamma, mean_rstd, dgamma_dbeta,
-                                                        (__nv_bfloat16*)dgb_bf16, coef, partial, counter);
+  __nv_bfloat16* dgb = (__nv_bfloat16*)dgb_bf16;
+  const int cm = knob_cvt();
+  if (knob_bwd_unroll() == 2) {
+    if (relu)
+      bn_bwd_reduce_kernel<true, 2><<<g, kThreads, 0, st>>>(dyb, yb, xb, M, C, gamma, mean_rstd, dgamma_dbeta, dgb, coef,
+                                                            partial, counter, cm);
+    else
+      bn_bwd_reduce_kernel<false, 2><<<g, kThreads, 0, st>>>(dyb, yb, xb, M, C, gamma, mean_rstd, dgamma_dbeta, dgb,
+                                                             coef, partial, counter, cm);
+  } else {
+    if (relu)
+      bn_bwd_reduce_kernel<true, 1><<<g, kThreads, 0, st>>>(dyb, yb, xb, M, C, gamma, mean_rstd, dgamma_dbeta, dgb, coef,
+                                                            partial, counter, cm);
+    else
+      bn_bwd_reduce_kernel<false, 1><<<g, kThreads, 0, st>>>(dyb, yb, xb, M, C, gamma, mean_rstd, dgamma_dbeta, dgb,
+                                                             coef, partial, counter, cm);
+  }
   PDJ_CUDA_CHECK(cudaGetLastError());
   const size_t n_vec = (size_t)M * c8;
   const int fg = flat_grid(n_vec);
@@ -507,13 +600,13 @@ extern "C" int pdj_bn_fwd_noalloc(const void* x, const void* res, void* y, int M
   // Tickets must start at zero whatever the previous user of the array did.
   PDJ_CUDA_CHECK(cudaMemsetAsync(counter, 0, kNoAllocCounterBytes, st));
 
-  const int cvt = c8 < 32 ? c8 : 32;
+  const int cvt = c8 < knob_cvt() ? c8 : knob_cvt();
   int gx = grid_rows(M, C, sms);
   const int cap = (int)(kNoAllocPartialBytes / ((size_t)2 * C * sizeof(float)));  // row blocks that fit
   if (gx > cap) gx = cap;
   dim3 g(gx, c8 / cvt);
-  bn_stats_kernel<<<g, kThreads, 0, st>>>((const __nv_bfloat16*)x, M, C, gamma, beta, eps, momentum, running_mean,
-                                          running_var, mean_rstd, scale_shift, partial, counter);
+  launch_stats(g, st, (const __nv_bfloat16*)x, M, C, gamma, beta, eps, momentum, running_mean, running_var, mean_rstd,
+               scale_shift, partial, counter, knob_cvt());
   PDJ_CUDA_CHECK(cudaGetLastError());
   const size_t n_vec = (size_t)M * c8;
   size_t fg = (n_vec + (size_t)kThreads * 4 - 1) / ((size_t)kThreads * 4);

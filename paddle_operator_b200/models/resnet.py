@@ -16,6 +16,7 @@ import torch
 import torch.nn as nn
 
 from ..ops.bn import FusedBnAct
+from ..ops.pool import FusedMaxPool2d
 
 
 class _TorchBnAct(nn.Module):
@@ -86,7 +87,7 @@ class ResNet(nn.Module):
         self.fused = fused
         self.conv1 = nn.Conv2d(3, width, 7, stride=2, padding=3, bias=False)
         self.bn1 = _bn(width, True, fused)
-        self.maxpool = nn.MaxPool2d(3, stride=2, padding=1)
+        self.maxpool = FusedMaxPool2d(3, 2, 1) if fused else nn.MaxPool2d(3, stride=2, padding=1)
         blocks = []
         inplanes = width
         for i, n in enumerate(layers):

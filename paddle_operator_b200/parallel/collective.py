@@ -232,7 +232,10 @@ class CollectiveTrainer:
         2 forward + 2 backward per layer) and the loss (1)."""
         from ..ops.bn import FusedBnAct
 
+        from ..ops.pool import FusedMaxPool2d
+
         n = sum(4 for m in self.model.modules() if isinstance(m, FusedBnAct))
+        n += sum(2 for m in self.model.modules() if isinstance(m, FusedMaxPool2d))
         return n + 1
 
     def step(self) -> torch.Tensor:
