@@ -71,6 +71,38 @@ int pdj_alltoall(const struct PdjComm* c, size_t in_off, size_t out_off, size_t 
 int pdj_broadcast(const struct PdjComm* c, int root, size_t off, size_t bytes, int nblocks, int emulate,
                   cudaStream_t st);
 
+/* ---- PS mode: GPU-sharded embedding tables (csrc/embedding.cu) -------------
+ * The PSERVER / TRAINER roles of the reference (api/v1/paddlejob_types.go:44-48,
+ * PADDLE_PSERVERS_IP_PORT_LIST at controllers/paddlejob_helper.go:258-260;
+ * pull / push semantics in docs/design-arch.md:49-74).  Row `id` lives on rank
+ * id % nranks at local row id / nranks.  All offsets are arena offsets.
+ *   lookup: out_deep[b, s, :] = bf16(table[id[b,s]]), out_wide[b] = sum_s wide[id[b,s]]
+ *   push  : sync  - staging[id] += grad (peer red.add), row registered with its owner
+ *           async - table[id]  -= lr * grad immediately (asynchronous SGD)
+ *   apply : owner applies SGD (0) or Adagrad (1) to its touched rows, clears staging */
+struct PdjEmbTable {
+  size_t deep_off;      /* fp32 [rows_per_shard, dim] */
+  size_t wide_off;      /* fp32 [rows_per_shard] (has_wide) */
+  size_t gdeep_off;     /* staging, same shapes */
+  size_t gwide_off;
+  size_t acc_deep_off;  /* Adagrad accumulators, same shapes */
+  size_t acc_wide_off;
+  size_t flag_off;      /* u32 [rows_per_shard]: row already in the touched list */
+  size_t list_off;      /* u32 [list_cap] */
+  size_t count_off;     /* u32 [2]: touched rows this step, last step */
+  long long rows_per_shard;
+  unsigned int list_cap;
+  int dim;              /* power of two, 4..128 */
+  int has_wide;
+};
+int pdj_emb_lookup(const struct PdjComm* c, const struct PdjEmbTable* t, size_t ids_off, size_t out_deep_off,
+                   size_t out_wide_off, int B, int S, int barrier, int nblocks, int emulate, cudaStream_t st);
+int pdj_emb_push(const struct PdjComm* c, const struct PdjEmbTable* t, size_t ids_off, size_t gdeep_off,
+                 size_t gwide_off, int B, int S, int async_sgd, float lr, float grad_scale, int nblocks, int emulate,
+                 cudaStream_t st);
+int pdj_emb_apply(const struct PdjComm* c, const struct PdjEmbTable* t, int optimizer, float lr, float eps,
+                  int nblocks, int emulate, cudaStream_t st);
+
 /* ---- ResNet-50 step kernels (csrc/bn_act.cu, csrc/optim_misc.cu) -----------
  * The workload of deploy/examples/resnet.yaml:13-19. NHWC bf16 activations
  * viewed as [M, C]; fp32 statistics. */

@@ -1,0 +1,268 @@
+// K2 / K3: GPU-sharded embedding tables - the parameter-server role of PS mode
+// with the all-to-all fused into the lookup (pull) and into the sparse
+// optimizer (push).
+//
+// Reference parity: PS mode in the reference is `spec.ps` + `spec.worker`
+// (controllers/paddlejob_helper.go:191-193): it creates PSERVER pods and TRAINER
+// pods and publishes PADDLE_PSERVERS_IP_PORT_LIST (helper.go:258-260); what the
+// roles do is described in docs/design-arch.md:7-9,49-58 - trainers pull
+// parameters and push gradients, pservers "run optimize functions to update
+// their parameters" - and executed by Paddle's brpc parameter server.  Here a
+// pserver shard is a slice of the table resident in one GPU's arena:
+//   row `id` lives on shard  id % nranks  at local row  id / nranks.
+//   pull  = every trainer reads the owner's HBM directly (peer ld over NVSwitch);
+//   push  = every trainer adds its row gradients into the owner's staging rows
+//           with peer `red.add` and registers the row in the owner's touched
+//           list; after a device barrier the owner applies SGD / Adagrad to the
+//           touched rows (gradients of repeated ids, from any trainer, are summed
+//           first: synchronous-SGD semantics, docs/design-arch.md:62-66);
+//   async = trainers apply `w -= lr * g` on the owner immediately with peer
+//           red.add and no barrier (asynchronous SGD, docs/design-arch.md:68-74).
+//
+// Everything is addressed by arena offsets so the same arguments are valid on
+// every rank; the single-GPU emulation runs all ranks in one cooperative launch.
+#include "common.cuh"
+#include "../../include/pdjob_b200.h"
+
+namespace {
+
+__device__ __forceinline__ float4 ld_f4(const void* p) {
+  float4 v;
+  asm volatile("ld.global.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(p)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ float ld_f1(const void* p) {
+  float v;
+  asm volatile("ld.global.L1::no_allocate.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void red_add_f4(void* p, float a, float b, float c, float d) {
+  asm volatile("red.relaxed.sys.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d)
+               : "memory");
+}
+__device__ __forceinline__ void red_add_f1(void* p, float a) {
+  asm volatile("red.relaxed.sys.global.add.f32 [%0], %1;" ::"l"(p), "f"(a) : "memory");
+}
+__device__ __forceinline__ uint32_t atom_exch_sys(uint32_t* p, uint32_t v) {
+  uint32_t old;
+  asm volatile("atom.relaxed.sys.global.exch.b32 %0, [%1], %2;" : "=r"(old) : "l"(p), "r"(v) : "memory");
+  return old;
+}
+__device__ __forceinline__ uint32_t atom_add_sys(uint32_t* p, uint32_t v) {
+  uint32_t old;
+  asm volatile("atom.relaxed.sys.global.add.u32 %0, [%1], %2;" : "=r"(old) : "l"(p), "r"(v) : "memory");
+  return old;
+}
+
+// One warp per sample: S slots, D floats per row, D/4 lanes per row.
+__global__ void __launch_bounds__(256)
+emb_lookup_kernel(PdjComm c, PdjEmbTable t, size_t ids_off, size_t out_deep_off, size_t out_wide_off, int B, int S,
+                  int do_barrier) {
+  const int rank = c.rank + blockIdx.y;
+  const int NR = c.nranks;
+  PdjSignalPad* me = pdj_pad(c, rank);
+  const uint32_t e = me->epoch[blockIdx.x];
+  if (do_barrier) pdj_block_barrier(c, rank, e + 1);  // owners finished applying the previous step
+  const int D = t.dim;
+  const int lpr = D >> 2;          // lanes per row
+  const int rpw = 32 / lpr;        // rows per warp iteration
+  const int lane = threadIdx.x & 31;
+  const int sub = lane / lpr, part = lane % lpr;
+  const long long* ids = reinterpret_cast<const long long*>(c.base[rank] + ids_off);
+  __nv_bfloat16* out_deep = reinterpret_cast<__nv_bfloat16*>(c.base[rank] + out_deep_off);
+  float* out_wide = reinterpret_cast<float*>(c.base[rank] + out_wide_off);
+  const int warps = (gridDim.x * blockDim.x) >> 5;
+  for (int b = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; b < B; b += warps) {
+    float wide = 0.f;
+    for (int s0 = 0; s0 < S; s0 += rpw) {
+      const int s = s0 + sub;
+      if (s < S) {
+        const long long id = ids[(size_t)b * S + s];
+        const int owner = (int)(id % NR);
+        const long long row = id / NR;
+        const float4 v = ld_f4(c.base[owner] + t.deep_off + ((size_t)row * D + part * 4) * 4);
+        uint2 o;
+        o.x = pdj_f2_to_bf2(v.x, v.y);
+        o.y = pdj_f2_to_bf2(v.z, v.w);
+        *reinterpret_cast<uint2*>(out_deep + ((size_t)b * S + s) * D + part * 4) = o;
+        if (part == 0 && t.has_wide) wide += ld_f1(c.base[owner] + t.wide_off + (size_t)row * 4);
+      }
+    }
+    if (t.has_wide) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) wide += __shfl_xor_sync(0xffffffffu, wide, o);
+      if (lane == 0) out_wide[b] = wide;
+    }
+  }
+  if (do_barrier && threadIdx.x == 0) me->epoch[blockIdx.x] = e + 1;
+}
+
+// Push.  mode 0 (sync): accumulate into the owner's staging rows and register
+// the row; mode 1 (async SGD): apply w -= lr * g on the owner directly.
+__global__ void __launch_bounds__(256)
+emb_push_kernel(PdjComm c, PdjEmbTable t, size_t ids_off, size_t gdeep_off, size_t gwide_off, int B, int S, int mode,
+                float lr, float grad_scale) {
+  const int rank = c.rank + blockIdx.y;
+  const int NR = c.nranks;
+  PdjSignalPad* me = pdj_pad(c, rank);
+  const uint32_t e = me->epoch[blockIdx.x];
+  const int D = t.dim;
+  const int lpr = D >> 2, rpw = 32 / lpr;
+  const int lane = threadIdx.x & 31;
+  const int sub = lane / lpr, part = lane % lpr;
+  const long long* ids = reinterpret_cast<const long long*>(c.base[rank] + ids_off);
+  const __nv_bfloat16* gdeep = reinterpret_cast<const __nv_bfloat16*>(c.base[rank] + gdeep_off);
+  const float* gwide = reinterpret_cast<const float*>(c.base[rank] + gwide_off);
+  const int warps = (gridDim.x * blockDim.x) >> 5;
+  const float k = mode == 1 ? -lr * grad_scale : grad_scale;
+  for (int b = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; b < B; b += warps) {
+    const float gw = t.has_wide ? gwide[b] * k : 0.f;
+    for (int s0 = 0; s0 < S; s0 += rpw) {
+      const int s = s0 + sub;
+      if (s >= S) continue;
+      const long long id = ids[(size_t)b * S + s];
+      const int owner = (int)(id % NR);
+      const long long row = id / NR;
+      const uint2 g = *reinterpret_cast<const uint2*>(gdeep + ((size_t)b * S + s) * D + part * 4);
+      const float2 g0 = pdj_bf2_to_f2(g.x), g1 = pdj_bf2_to_f2(g.y);
+      char* ob = c.base[owner];
+      const size_t deep_dst = (mode == 1 ? t.deep_off : t.gdeep_off) + ((size_t)row * D + part * 4) * 4;
+      red_add_f4(ob + deep_dst, g0.x * k, g0.y * k, g1.x * k, g1.y * k);
+      if (part == 0) {
+        if (t.has_wide) red_add_f1(ob + (mode == 1 ? t.wide_off : t.gwide_off) + (size_t)row * 4, gw);
+        if (mode == 0) {
+          uint32_t* flag = reinterpret_cast<uint32_t*>(ob + t.flag_off) + row;
+          if (atom_exch_sys(flag, 1u) == 0u) {
+            const uint32_t pos = atom_add_sys(reinterpret_cast<uint32_t*>(ob + t.count_off), 1u);
+            if (pos < t.list_cap) reinterpret_cast<uint32_t*>(ob + t.list_off)[pos] = (uint32_t)row;
+          }
+        }
+      }
+    }
+  }
+  // All pushes of all ranks have landed once every block of every rank has
+  // passed this barrier and the kernels have drained.
+  pdj_block_barrier(c, rank, e + 1);
+  if (threadIdx.x == 0) me->epoch[blockIdx.x] = e + 1;
+}
+
+// Owner-side optimizer over the touched rows.  opt 0 = SGD, 1 = Adagrad.
+__global__ void __launch_bounds__(256)
+emb_apply_kernel(PdjComm c, PdjEmbTable t, int opt, float lr, float eps) {
+  const int rank = c.rank + blockIdx.y;
+  char* base = c.base[rank];
+  const uint32_t n_raw = *reinterpret_cast<const uint32_t*>(base + t.count_off);
+  const uint32_t n = n_raw < t.list_cap ? n_raw : t.list_cap;
+  const uint32_t* list = reinterpret_cast<const uint32_t*>(base + t.list_off);
+  const int D = t.dim;
+  const int lpr = D >> 2;
+  const size_t total = (size_t)n * lpr;
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const uint32_t row = list[i / lpr];
+    const int part = (int)(i % lpr);
+    const size_t o = ((size_t)row * D + part * 4) * 4;
+    float4* gp = reinterpret_cast<float4*>(base + t.gdeep_off + o);
+    float4* wp = reinterpret_cast<float4*>(base + t.deep_off + o);
+    const float4 g = *gp;
+    float4 w = *wp;
+    if (opt == 1) {
+      float4* ap = reinterpret_cast<float4*>(base + t.acc_deep_off + o);
+      float4 a = *ap;
+      a.x += g.x * g.x; a.y += g.y * g.y; a.z += g.z * g.z; a.w += g.w * g.w;
+      *ap = a;
+      w.x -= lr * g.x * rsqrtf(a.x + eps); w.y -= lr * g.y * rsqrtf(a.y + eps);
+      w.z -= lr * g.z * rsqrtf(a.z + eps); w.w -= lr * g.w * rsqrtf(a.w + eps);
+    } else {
+      w.x -= lr * g.x; w.y -= lr * g.y; w.z -= lr * g.z; w.w -= lr * g.w;
+    }
+    *wp = w;
+    *gp = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (part == 0) {
+      if (t.has_wide) {
+        float* gwp = reinterpret_cast<float*>(base + t.gwide_off) + row;
+        float* wwp = reinterpret_cast<float*>(base + t.wide_off) + row;
+        const float gw = *gwp;
+        if (opt == 1) {
+          float* awp = reinterpret_cast<float*>(base + t.acc_wide_off) + row;
+          const float a = *awp + gw * gw;
+          *awp = a;
+          *wwp -= lr * gw * rsqrtf(a + eps);
+        } else {
+          *wwp -= lr * gw;
+        }
+        *gwp = 0.f;
+      }
+      reinterpret_cast<uint32_t*>(base + t.flag_off)[row] = 0u;
+    }
+  }
+}
+
+__global__ void emb_reset_count_kernel(PdjComm c, PdjEmbTable t) {
+  const int rank = c.rank + blockIdx.y;
+  if (threadIdx.x == 0) {
+    uint32_t* cnt = reinterpret_cast<uint32_t*>(c.base[rank] + t.count_off);
+    cnt[1] = cnt[0];  // keep the last step's touched-row count for inspection
+    cnt[0] = 0u;
+  }
+}
+
+int check_table(const PdjEmbTable* t) {
+  const int d = t->dim;
+  if (d < 4 || d > 128 || (d & (d - 1)) != 0) {
+    pdj_set_error("embedding: dim must be a power of two in 4..128 (got %d)", d);
+    return -1;
+  }
+  return 0;
+}
+
+template <typename... Args>
+int launch_emb(void (*kern)(Args...), int nblocks, int nthreads, int emulate, int nranks, cudaStream_t st,
+               Args... args) {
+  if (nblocks < 1) nblocks = 1;
+  if (nblocks > PDJ_MAX_BLOCKS) nblocks = PDJ_MAX_BLOCKS;
+  dim3 grid(nblocks, emulate ? nranks : 1);
+  if (emulate) {
+    void* argv[] = {(void*)&args...};
+    PDJ_CUDA_CHECK(cudaLaunchCooperativeKernel((const void*)kern, grid, dim3(nthreads), argv, 0, st));
+  } else {
+    kern<<<grid, nthreads, 0, st>>>(args...);
+    PDJ_CUDA_CHECK(cudaGetLastError());
+  }
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+int pdj_emb_lookup(const PdjComm* c, const PdjEmbTable* t, size_t ids_off, size_t out_deep_off, size_t out_wide_off,
+                   int B, int S, int barrier, int nblocks, int emulate, cudaStream_t st) {
+  if (check_table(t)) return -1;
+  return launch_emb(emb_lookup_kernel, nblocks, 256, emulate, c->nranks, st, *c, *t, ids_off, out_deep_off,
+                    out_wide_off, B, S, barrier);
+}
+
+int pdj_emb_push(const PdjComm* c, const PdjEmbTable* t, size_t ids_off, size_t gdeep_off, size_t gwide_off, int B,
+                 int S, int async_sgd, float lr, float grad_scale, int nblocks, int emulate, cudaStream_t st) {
+  if (check_table(t)) return -1;
+  return launch_emb(emb_push_kernel, nblocks, 256, emulate, c->nranks, st, *c, *t, ids_off, gdeep_off, gwide_off, B,
+                    S, async_sgd ? 1 : 0, lr, grad_scale);
+}
+
+int pdj_emb_apply(const PdjComm* c, const PdjEmbTable* t, int optimizer, float lr, float eps, int nblocks,
+                  int emulate, cudaStream_t st) {
+  if (check_table(t)) return -1;
+  if (nblocks < 1) nblocks = 1;
+  dim3 grid(nblocks, emulate ? c->nranks : 1);
+  emb_apply_kernel<<<grid, 256, 0, st>>>(*c, *t, optimizer, lr, eps);
+  PDJ_CUDA_CHECK(cudaGetLastError());
+  emb_reset_count_kernel<<<dim3(1, emulate ? c->nranks : 1), 32, 0, st>>>(*c, *t);
+  PDJ_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+}  // extern "C"

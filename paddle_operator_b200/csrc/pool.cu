@@ -22,14 +22,16 @@ __global__ void __launch_bounds__(256)
 maxpool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, uint8_t* __restrict__ idx,
                    int N, int H, int W, int C, int Ho, int Wo, int k, int s, int p) {
   const int c8 = C >> 3;
-  const size_t total = (size_t)N * Ho * Wo * c8;
-  const size_t stride = (size_t)gridDim.x * blockDim.x;
-  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
-    const int cv = (int)(i % c8);
-    size_t t = i / c8;
-    const int wo = (int)(t % Wo); t /= Wo;
-    const int ho = (int)(t % Ho);
-    const int n = (int)(t / Ho);
+  // 32-bit index arithmetic (the host rejects tensors with >= 2^32 vectors):
+  // 64-bit div/mod per element dominated the first version of this kernel.
+  const uint32_t total = (uint32_t)N * Ho * Wo * c8;
+  const uint32_t stride = gridDim.x * blockDim.x;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const int cv = (int)(i % (uint32_t)c8);
+    uint32_t t = i / (uint32_t)c8;
+    const int wo = (int)(t % (uint32_t)Wo); t /= (uint32_t)Wo;
+    const int ho = (int)(t % (uint32_t)Ho);
+    const int n = (int)(t / (uint32_t)Ho);
     float best[8];
     uint32_t arg[8];
 #pragma unroll
@@ -65,14 +67,14 @@ __global__ void __launch_bounds__(256)
 maxpool_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const uint8_t* __restrict__ idx,
                    __nv_bfloat16* __restrict__ dx, int N, int H, int W, int C, int Ho, int Wo, int k, int s, int p) {
   const int c8 = C >> 3;
-  const size_t total = (size_t)N * H * W * c8;
-  const size_t stride = (size_t)gridDim.x * blockDim.x;
-  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
-    const int cv = (int)(i % c8);
-    size_t t = i / c8;
-    const int w = (int)(t % W); t /= W;
-    const int h = (int)(t % H);
-    const int n = (int)(t / H);
+  const uint32_t total = (uint32_t)N * H * W * c8;
+  const uint32_t stride = gridDim.x * blockDim.x;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const int cv = (int)(i % (uint32_t)c8);
+    uint32_t t = i / (uint32_t)c8;
+    const int w = (int)(t % (uint32_t)W); t /= (uint32_t)W;
+    const int h = (int)(t % (uint32_t)H);
+    const int n = (int)(t / (uint32_t)H);
     float g[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) g[j] = 0.f;
@@ -127,6 +129,10 @@ int pdj_maxpool_fwd(const void* x, void* y, void* idx, int N, int H, int W, int 
     return -1;
   }
   const int Ho = (H + 2 * p - k) / s + 1, Wo = (W + 2 * p - k) / s + 1;
+  if ((size_t)N * H * W * (C / 8) >= 0xffffffffull) {
+    pdj_set_error("pdj_maxpool_fwd: tensor too large for 32-bit indexing");
+    return -1;
+  }
   maxpool_fwd_kernel<<<pool_grid((size_t)N * Ho * Wo * (C / 8)), 256, 0, st>>>(
       (const __nv_bfloat16*)x, (__nv_bfloat16*)y, (uint8_t*)idx, N, H, W, C, Ho, Wo, k, s, p);
   PDJ_CUDA_CHECK(cudaGetLastError());
@@ -140,6 +146,10 @@ int pdj_maxpool_bwd(const void* dy, const void* idx, void* dx, int N, int H, int
     return -1;
   }
   const int Ho = (H + 2 * p - k) / s + 1, Wo = (W + 2 * p - k) / s + 1;
+  if ((size_t)N * H * W * (C / 8) >= 0xffffffffull) {
+    pdj_set_error("pdj_maxpool_bwd: tensor too large for 32-bit indexing");
+    return -1;
+  }
   maxpool_bwd_kernel<<<pool_grid((size_t)N * H * W * (C / 8)), 256, 0, st>>>(
       (const __nv_bfloat16*)dy, (const uint8_t*)idx, (__nv_bfloat16*)dx, N, H, W, C, Ho, Wo, k, s, p);
   PDJ_CUDA_CHECK(cudaGetLastError());

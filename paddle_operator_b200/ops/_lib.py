@@ -26,6 +26,15 @@ class PdjComm(ctypes.Structure):
     ]
 
 
+class PdjEmbTable(ctypes.Structure):
+    _fields_ = [
+        ("deep_off", c_size_t), ("wide_off", c_size_t), ("gdeep_off", c_size_t), ("gwide_off", c_size_t),
+        ("acc_deep_off", c_size_t), ("acc_wide_off", c_size_t), ("flag_off", c_size_t), ("list_off", c_size_t),
+        ("count_off", c_size_t), ("rows_per_shard", ctypes.c_longlong), ("list_cap", ctypes.c_uint),
+        ("dim", c_int), ("has_wide", c_int),
+    ]
+
+
 class PdjError(RuntimeError):
     pass
 
@@ -58,6 +67,10 @@ def _declare(lib: ctypes.CDLL) -> None:
         "pdj_allreduce_bf16": (c_int, [POINTER(PdjComm), sz, sz, sz, c_float, c_int, c_int, c_int, c_int, st]),
         "pdj_alltoall": (c_int, [POINTER(PdjComm), sz, sz, sz, c_int, c_int, st]),
         "pdj_broadcast": (c_int, [POINTER(PdjComm), c_int, sz, sz, c_int, c_int, st]),
+        "pdj_emb_lookup": (c_int, [POINTER(PdjComm), POINTER(PdjEmbTable), sz, sz, sz, c_int, c_int, c_int, c_int, c_int, st]),
+        "pdj_emb_push": (c_int, [POINTER(PdjComm), POINTER(PdjEmbTable), sz, sz, sz, c_int, c_int, c_int, c_float, c_float,
+                                 c_int, c_int, st]),
+        "pdj_emb_apply": (c_int, [POINTER(PdjComm), POINTER(PdjEmbTable), c_int, c_float, c_float, c_int, c_int, st]),
         "pdj_bn_workspace_bytes": (sz, []),
         "pdj_bn_fwd": (c_int, [vp, vp, vp, c_int, c_int, vp, vp, c_float, c_float, vp, vp, vp, vp, c_int, vp, st]),
         "pdj_bn_bwd": (c_int, [vp, vp, vp, vp, vp, c_int, c_int, vp, vp, vp, vp, vp, c_int, vp, st]),

@@ -1,0 +1,177 @@
+"""PS mode: the parameter-server role as GPU-sharded embedding tables.
+
+`ShardedEmbedding` owns one shard of a row-sharded table (plus staging rows,
+Adagrad accumulators and the touched-row list) inside the symmetric arena of a
+`Communicator`, and exposes
+
+    deep, wide = emb(ids)          # pull: fused peer-memory gather (K2)
+    loss.backward()                # push + owner-side optimizer (K3), inside backward
+
+The dense part of the model is ordinary data parallelism (parallel/collective).
+
+Reference parity: PS mode = `spec.ps` present (controllers/paddlejob_helper.go:
+191-193); roles PSERVER/TRAINER (api/v1/paddlejob_types.go:44-48); what they do:
+docs/design-arch.md:7-9,49-74 ("trainers ... pull parameters ... push gradients;
+pservers update parameters", sync vs async SGD).  Mapping used here: shard j of
+the table lives on GPU j (one shard per trainer rank); `ps.replicas` PSERVER
+ranks still exist as processes for ordering/status, but the "server" is memory
+plus the owner-side half of the kernels.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Optional
+
+import torch
+
+from ..ops import _lib
+from ..ops._lib import PdjEmbTable, check
+from .symm import Communicator
+
+SGD, ADAGRAD = 0, 1
+
+
+def embedding_reference(table_deep, table_wide, ids):
+    """fp32 oracle: table_* are the FULL (unsharded) tables."""
+    deep = table_deep[ids]  # [B, S, D]
+    wide = table_wide[ids].sum(dim=1) if table_wide is not None else None
+    return deep, wide
+
+
+class ShardedEmbedding:
+    def __init__(self, comm: Communicator, num_rows: int, dim: int, max_batch: int, slots: int,
+                 has_wide: bool = True, optimizer: int = ADAGRAD, lr: float = 0.05, eps: float = 1e-6,
+                 async_sgd: bool = False, init_scale: float = 0.01, seed: int = 0, nblocks: int = 0):
+        self.comm, self.dim, self.slots, self.max_batch = comm, dim, slots, max_batch
+        self.nranks = comm.nranks
+        self.rows_per_shard = (num_rows + self.nranks - 1) // self.nranks
+        self.num_rows = self.rows_per_shard * self.nranks
+        self.has_wide, self.optimizer, self.lr, self.eps, self.async_sgd = has_wide, optimizer, lr, eps, async_sgd
+        self.nblocks = nblocks or 128
+        self.lib = _lib.load()
+        R, D = self.rows_per_shard, dim
+        a = comm.alloc
+        t = PdjEmbTable()
+        t.deep_off = a(R * D * 4)
+        t.wide_off = a(R * 4)
+        t.gdeep_off = a(R * D * 4)
+        t.gwide_off = a(R * 4)
+        t.acc_deep_off = a(R * D * 4)
+        t.acc_wide_off = a(R * 4)
+        t.flag_off = a(R * 4)
+        cap = min(R, max_batch * slots * self.nranks)
+        t.list_off = a(cap * 4)
+        t.count_off = a(256)
+        t.rows_per_shard, t.list_cap, t.dim, t.has_wide = R, cap, D, int(has_wide)
+        self.t = t
+        # per-step I/O buffers (also in the arena so the emulation can address every rank's)
+        self.ids_off = a(max_batch * slots * 8)
+        self.out_deep_off = a(max_batch * slots * D * 2)
+        self.out_wide_off = a(max_batch * 4)
+        self.gdeep_in_off = a(max_batch * slots * D * 2)
+        self.gwide_in_off = a(max_batch * 4)
+        self._init(init_scale, seed)
+
+    # -- views -----------------------------------------------------------------
+    def _ranks(self):
+        return range(self.nranks) if self.comm.emulate else [self.comm.rank]
+
+    def shard(self, rank: Optional[int] = None) -> torch.Tensor:
+        return self.comm.tensor(self.t.deep_off, (self.rows_per_shard, self.dim), torch.float32, rank)
+
+    def shard_wide(self, rank: Optional[int] = None) -> torch.Tensor:
+        return self.comm.tensor(self.t.wide_off, (self.rows_per_shard,), torch.float32, rank)
+
+    def _init(self, scale: float, seed: int) -> None:
+        for r in self._ranks():
+            g = torch.Generator(device=f"cuda:{self.comm.device}").manual_seed(seed * 1000 + r)
+            self.shard(r).copy_(torch.randn(self.rows_per_shard, self.dim, generator=g,
+                                            device=f"cuda:{self.comm.device}") * scale)
+            self.shard_wide(r).copy_(torch.randn(self.rows_per_shard, generator=g,
+                                                 device=f"cuda:{self.comm.device}") * scale)
+            for off, n in ((self.t.gdeep_off, self.rows_per_shard * self.dim), (self.t.gwide_off, self.rows_per_shard),
+                           (self.t.acc_deep_off, self.rows_per_shard * self.dim),
+                           (self.t.acc_wide_off, self.rows_per_shard), (self.t.flag_off, self.rows_per_shard),
+                           (self.t.count_off, 64)):
+                self.comm.tensor(off, (n,), torch.float32, r).zero_()
+
+    def full_tables(self):
+        """Gathers the whole table on this device (tests / checkpoints); needs the emulation
+        or peer mappings, both of which let any rank read any shard."""
+        deep = torch.empty(self.num_rows, self.dim, device=f"cuda:{self.comm.device}")
+        wide = torch.empty(self.num_rows, device=f"cuda:{self.comm.device}")
+        for r in range(self.nranks):
+            deep[r::self.nranks] = self.shard(r)
+            wide[r::self.nranks] = self.shard_wide(r)
+        return deep, wide
+
+    # -- raw kernel launches (rank-local unless emulated) -----------------------------
+    def ids_buffer(self, batch: int, rank: Optional[int] = None) -> torch.Tensor:
+        return self.comm.tensor(self.ids_off, (batch, self.slots), torch.int64, rank)
+
+    def lookup_raw(self, batch: int, barrier: bool = True, stream=None) -> None:
+        c = self.comm
+        check(self.lib.pdj_emb_lookup(ctypes.byref(c.comm_struct), ctypes.byref(self.t), self.ids_off,
+                                      self.out_deep_off, self.out_wide_off, batch, self.slots, int(barrier),
+                                      self.nblocks, int(c.emulate), c._stream(stream)), "emb_lookup")
+
+    def push_raw(self, batch: int, grad_scale: float = 1.0, stream=None) -> None:
+        c = self.comm
+        check(self.lib.pdj_emb_push(ctypes.byref(c.comm_struct), ctypes.byref(self.t), self.ids_off, self.gdeep_in_off,
+                                    self.gwide_in_off, batch, self.slots, int(self.async_sgd), self.lr, grad_scale,
+                                    self.nblocks, int(c.emulate), c._stream(stream)), "emb_push")
+        if not self.async_sgd:
+            check(self.lib.pdj_emb_apply(ctypes.byref(c.comm_struct), ctypes.byref(self.t), self.optimizer, self.lr,
+                                         self.eps, 4 * 148, int(c.emulate), c._stream(stream)), "emb_apply")
+
+    def out_deep(self, batch: int, rank: Optional[int] = None) -> torch.Tensor:
+        return self.comm.tensor(self.out_deep_off, (batch, self.slots * self.dim), torch.bfloat16, rank)
+
+    def out_wide(self, batch: int, rank: Optional[int] = None) -> torch.Tensor:
+        return self.comm.tensor(self.out_wide_off, (batch,), torch.float32, rank)
+
+    def grad_deep_in(self, batch: int, rank: Optional[int] = None) -> torch.Tensor:
+        return self.comm.tensor(self.gdeep_in_off, (batch, self.slots * self.dim), torch.bfloat16, rank)
+
+    def grad_wide_in(self, batch: int, rank: Optional[int] = None) -> torch.Tensor:
+        return self.comm.tensor(self.gwide_in_off, (batch,), torch.float32, rank)
+
+    def touched_last_step(self, rank: Optional[int] = None) -> int:
+        return int(self.comm.tensor(self.t.count_off, (2,), torch.int32, rank)[1].item())
+
+    # -- autograd face (one real rank) --------------------------------------------------
+    def __call__(self, ids: torch.Tensor):
+        """ids [B, S] int64 on this rank's device -> (deep bf16 [B, S*D], wide fp32 [B]).
+        The sparse optimizer step runs inside backward."""
+        return _LookupFn.apply(self, ids, torch.zeros((), device=ids.device, requires_grad=True))
+
+    def state_dict(self) -> dict:
+        r = self.comm.rank
+        return {"deep": self.shard(r).clone(), "wide": self.shard_wide(r).clone(),
+                "acc_deep": self.comm.tensor(self.t.acc_deep_off, (self.rows_per_shard, self.dim), torch.float32).clone(),
+                "acc_wide": self.comm.tensor(self.t.acc_wide_off, (self.rows_per_shard,), torch.float32).clone(),
+                "shard": r, "nshards": self.nranks}
+
+    def load_state_dict(self, sd: dict) -> None:
+        self.shard().copy_(sd["deep"])
+        self.shard_wide().copy_(sd["wide"])
+        self.comm.tensor(self.t.acc_deep_off, (self.rows_per_shard, self.dim), torch.float32).copy_(sd["acc_deep"])
+        self.comm.tensor(self.t.acc_wide_off, (self.rows_per_shard,), torch.float32).copy_(sd["acc_wide"])
+
+
+class _LookupFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, emb: ShardedEmbedding, ids: torch.Tensor, _anchor: torch.Tensor):
+        b = ids.shape[0]
+        emb.ids_buffer(b).copy_(ids)
+        emb.lookup_raw(b)
+        ctx.emb, ctx.batch = emb, b
+        return emb.out_deep(b), emb.out_wide(b)
+
+    @staticmethod
+    def backward(ctx, g_deep, g_wide):
+        emb, b = ctx.emb, ctx.batch
+        emb.grad_deep_in(b).copy_(g_deep)
+        emb.grad_wide_in(b).copy_(g_wide if g_wide is not None else torch.zeros(b, device=g_deep.device))
+        emb.push_raw(b)
+        return None, None, None
