@@ -139,7 +139,7 @@ def main() -> int:
     if args.workload == "wide_deep":
         from paddle_operator_b200.workloads import bench_wide_deep
 
-        return bench_wide_deep.run(args, rank, world, dev)
+        return bench_wide_deep.run(args, rank, world, dev, ClockSampler)
     from paddle_operator_b200.workloads import bench_resnet
 
     return bench_resnet.run(args, rank, world, dev, ClockSampler)

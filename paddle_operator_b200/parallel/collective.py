@@ -118,7 +118,7 @@ class CollectiveTrainer:
     def __init__(self, model: torch.nn.Module, loss_fn: Callable, example_inputs: tuple,
                  comm: Optional[Communicator] = None, lr: float = 0.1, momentum: float = 0.9,
                  weight_decay: float = 1e-4, bucket_bytes: int = 16 << 20, use_graph: bool = True,
-                 comm_blocks: int = 24, algo: Optional[int] = None):
+                 comm_blocks: int = 24, algo: Optional[int] = None, extra_kernels_per_step: int = 0):
         self.model = model
         self.loss_fn = loss_fn
         self.inputs = example_inputs
@@ -134,6 +134,7 @@ class CollectiveTrainer:
         self.algo = algo
         self.graph: Optional[torch.cuda.CUDAGraph] = None
         self.kernels_per_step = 0  # launches of OUR kernels per step (counted at capture/eager time)
+        self.extra_kernels_per_step = extra_kernels_per_step  # the job's own kernels outside modules (loss, embedding)
         self._count = 0
         self.comm_stream = torch.cuda.Stream(self.device) if self.comm is not None else None
         self._attach_masters()
@@ -229,14 +230,14 @@ class CollectiveTrainer:
 
     def _model_kernel_count(self) -> int:
         """Hand-written kernel launches per step inside the model (fused BN:
-        2 forward + 2 backward per layer) and the loss (1)."""
+        2 forward + 2 backward per layer, max-pool 1 + 1) plus what the job declares."""
         from ..ops.bn import FusedBnAct
 
         from ..ops.pool import FusedMaxPool2d
 
         n = sum(4 for m in self.model.modules() if isinstance(m, FusedBnAct))
         n += sum(2 for m in self.model.modules() if isinstance(m, FusedMaxPool2d))
-        return n + 1
+        return n + self.extra_kernels_per_step
 
     def step(self) -> torch.Tensor:
         """Runs one optimisation step on the current contents of the static

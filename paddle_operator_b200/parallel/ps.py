@@ -48,6 +48,7 @@ class ShardedEmbedding:
         self.num_rows = self.rows_per_shard * self.nranks
         self.has_wide, self.optimizer, self.lr, self.eps, self.async_sgd = has_wide, optimizer, lr, eps, async_sgd
         self.nblocks = nblocks or 128
+        self.grad_scale = 1.0  # trainers set 1/world so that summed pushes equal the global-batch mean
         self.lib = _lib.load()
         R, D = self.rows_per_shard, dim
         a = comm.alloc
@@ -173,5 +174,5 @@ class _LookupFn(torch.autograd.Function):
         emb, b = ctx.emb, ctx.batch
         emb.grad_deep_in(b).copy_(g_deep)
         emb.grad_wide_in(b).copy_(g_wide if g_wide is not None else torch.zeros(b, device=g_deep.device))
-        emb.push_raw(b)
+        emb.push_raw(b, emb.grad_scale)
         return None, None, None

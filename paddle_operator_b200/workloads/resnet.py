@@ -52,7 +52,7 @@ class ResNetJob:
         self.y = torch.zeros((batch,), dtype=torch.int64, device=self.device)
         self.trainer = CollectiveTrainer(model, _loss_fn, (self.x, self.y), comm=comm, lr=lr, momentum=momentum,
                                          weight_decay=weight_decay, use_graph=use_graph, bucket_bytes=bucket_bytes,
-                                         comm_blocks=comm_blocks, algo=algo)
+                                         comm_blocks=comm_blocks, algo=algo, extra_kernels_per_step=1)
         # host -> device staging (double buffered)
         self._stage_u8 = [torch.empty((batch, image, image, 3), dtype=torch.uint8, device=self.device)
                           for _ in range(2)]
