@@ -41,9 +41,9 @@ struct Acc8 {
 __global__ void barrier_kernel(PdjComm c) {
   const int rank = c.rank + blockIdx.y;
   PdjSignalPad* me = pdj_pad(c, rank);
-  const uint32_t e = me->epoch[blockIdx.x];
+  const uint32_t e = me->epoch[pdj_slot(c)];
   pdj_block_barrier(c, rank, e + 1);
-  if (threadIdx.x == 0) me->epoch[blockIdx.x] = e + 1;
+  if (threadIdx.x == 0) me->epoch[pdj_slot(c)] = e + 1;
 }
 
 // ---------------------------------------------------------------------------
@@ -56,7 +56,7 @@ __global__ void __launch_bounds__(512)
 allreduce_twoshot_kernel(PdjComm c, size_t in_off, size_t out_off, size_t n_vec, float scale) {
   const int rank = c.rank + blockIdx.y;
   PdjSignalPad* me = pdj_pad(c, rank);
-  const uint32_t e = me->epoch[blockIdx.x];
+  const uint32_t e = me->epoch[pdj_slot(c)];
   pdj_block_barrier(c, rank, e + 1);  // every rank's input is complete
 
   const size_t per = (n_vec + NR - 1) / NR;
@@ -97,7 +97,7 @@ allreduce_twoshot_kernel(PdjComm c, size_t in_off, size_t out_off, size_t n_vec,
     }
   }
   pdj_block_barrier(c, rank, e + 2);  // every peer's pushes into my output have landed
-  if (threadIdx.x == 0) me->epoch[blockIdx.x] = e + 2;
+  if (threadIdx.x == 0) me->epoch[pdj_slot(c)] = e + 2;
 }
 
 // One-shot all-reduce for latency-bound sizes: every rank pulls the whole
@@ -107,7 +107,7 @@ __global__ void __launch_bounds__(512)
 allreduce_oneshot_kernel(PdjComm c, size_t in_off, size_t out_off, size_t n_vec, float scale) {
   const int rank = c.rank + blockIdx.y;
   PdjSignalPad* me = pdj_pad(c, rank);
-  const uint32_t e = me->epoch[blockIdx.x];
+  const uint32_t e = me->epoch[pdj_slot(c)];
   pdj_block_barrier(c, rank, e + 1);
   const char* src[NR];
 #pragma unroll
@@ -130,7 +130,7 @@ allreduce_oneshot_kernel(PdjComm c, size_t in_off, size_t out_off, size_t n_vec,
     pdj_st16(dst + i * 16, acc.pack(scale));
   }
   pdj_block_barrier(c, rank, e + 2);  // peers are done reading my input
-  if (threadIdx.x == 0) me->epoch[blockIdx.x] = e + 2;
+  if (threadIdx.x == 0) me->epoch[pdj_slot(c)] = e + 2;
 }
 
 // NVLS all-reduce: the switch reduces (multimem.ld_reduce) and broadcasts
@@ -140,7 +140,7 @@ allreduce_nvls_kernel(PdjComm c, size_t in_off, size_t out_off, size_t n_vec, fl
   const int rank = c.rank + blockIdx.y;
   const int NR = c.nranks;
   PdjSignalPad* me = pdj_pad(c, rank);
-  const uint32_t e = me->epoch[blockIdx.x];
+  const uint32_t e = me->epoch[pdj_slot(c)];
   pdj_block_barrier(c, rank, e + 1);
   const size_t per = (n_vec + NR - 1) / NR;
   const size_t beg = (size_t)rank * per;
@@ -165,7 +165,7 @@ allreduce_nvls_kernel(PdjComm c, size_t in_off, size_t out_off, size_t n_vec, fl
                  : "memory");
   }
   pdj_block_barrier(c, rank, e + 2);
-  if (threadIdx.x == 0) me->epoch[blockIdx.x] = e + 2;
+  if (threadIdx.x == 0) me->epoch[pdj_slot(c)] = e + 2;
 }
 
 // ---------------------------------------------------------------------------
@@ -176,7 +176,7 @@ alltoall_kernel(PdjComm c, size_t in_off, size_t out_off, size_t chunk_vec) {
   const int rank = c.rank + blockIdx.y;
   const int NR = c.nranks;
   PdjSignalPad* me = pdj_pad(c, rank);
-  const uint32_t e = me->epoch[blockIdx.x];
+  const uint32_t e = me->epoch[pdj_slot(c)];
   pdj_block_barrier(c, rank, e + 1);  // peers' outputs are free to overwrite
   const char* in = c.base[rank] + in_off;
   const size_t stride = (size_t)gridDim.x * blockDim.x;
@@ -190,7 +190,7 @@ alltoall_kernel(PdjComm c, size_t in_off, size_t out_off, size_t chunk_vec) {
     pdj_st16(c.base[p] + out_off + ((size_t)rank * chunk_vec + within) * 16, v);
   }
   pdj_block_barrier(c, rank, e + 2);
-  if (threadIdx.x == 0) me->epoch[blockIdx.x] = e + 2;
+  if (threadIdx.x == 0) me->epoch[pdj_slot(c)] = e + 2;
 }
 
 // K6 broadcast: every non-root rank pulls the root's buffer (pull keeps the
@@ -199,7 +199,7 @@ __global__ void __launch_bounds__(512)
 broadcast_kernel(PdjComm c, int root, size_t off, size_t n_vec) {
   const int rank = c.rank + blockIdx.y;
   PdjSignalPad* me = pdj_pad(c, rank);
-  const uint32_t e = me->epoch[blockIdx.x];
+  const uint32_t e = me->epoch[pdj_slot(c)];
   pdj_block_barrier(c, rank, e + 1);
   if (rank != root) {
     const char* src = c.base[root] + off;
@@ -209,14 +209,14 @@ broadcast_kernel(PdjComm c, int root, size_t off, size_t n_vec) {
       pdj_st16(dst + i * 16, pdj_ld16(src + i * 16));
   }
   pdj_block_barrier(c, rank, e + 2);
-  if (threadIdx.x == 0) me->epoch[blockIdx.x] = e + 2;
+  if (threadIdx.x == 0) me->epoch[pdj_slot(c)] = e + 2;
 }
 
 template <typename... Args>
 int launch_comm(void (*kern)(Args...), int nblocks, int nthreads, int emulate, int nranks, cudaStream_t st,
                 Args... args) {
   if (nblocks < 1) nblocks = 1;
-  if (nblocks > PDJ_MAX_BLOCKS) nblocks = PDJ_MAX_BLOCKS;
+  if (nblocks > PDJ_CHANNEL_BLOCKS) nblocks = PDJ_CHANNEL_BLOCKS;
   dim3 grid(nblocks, emulate ? nranks : 1);
   if (emulate) {
     // All y-slices spin on one another: they must be co-resident.

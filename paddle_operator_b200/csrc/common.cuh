@@ -12,7 +12,12 @@
 #include <stdint.h>
 
 #define PDJ_MAX_RANKS 8
-#define PDJ_MAX_BLOCKS 256
+// The signal pad has PDJ_MAX_BLOCKS barrier slots, split into channels of
+// PDJ_CHANNEL_BLOCKS.  Kernels that may run concurrently on different streams
+// (a bucket all-reduce next to an embedding push) must use different channels:
+// a slot's epoch counter belongs to one kernel at a time.
+#define PDJ_MAX_BLOCKS 1024
+#define PDJ_CHANNEL_BLOCKS 256
 // Bytes reserved at the head of every rank's arena for the signal pad.
 #define PDJ_PAD_BYTES 65536
 // Spin-wait bound (ns).  A peer that never shows up turns into a trapped
@@ -35,6 +40,8 @@ static_assert(sizeof(PdjSignalPad) <= PDJ_PAD_BYTES, "signal pad too large");
 struct PdjComm {
   int nranks;
   int rank;
+  int pad_base;  // first barrier slot of this communicator view (channel * PDJ_CHANNEL_BLOCKS)
+  int reserved;
   char* base[PDJ_MAX_RANKS];
   char* mc_base;  // NVLS multicast mapping of the arena (nullptr when unavailable)
 };
@@ -75,14 +82,17 @@ __device__ __forceinline__ PdjSignalPad* pdj_pad(const PdjComm& c, int r) {
 // Barrier between block blockIdx.x of every rank.  `epoch` must be the same
 // on all ranks and strictly increasing per (block index) across kernels; the
 // kernels read it from pad->epoch[] so that CUDA-graph replays stay in step.
+__device__ __forceinline__ int pdj_slot(const PdjComm& c) { return c.pad_base + (int)blockIdx.x; }
+
 __device__ __forceinline__ void pdj_block_barrier(const PdjComm& c, int rank, uint32_t epoch) {
   __syncthreads();
   const int t = threadIdx.x;
+  const int slot = pdj_slot(c);
   if (t < c.nranks) {
     __threadfence_system();
-    pdj_st_release_sys(&pdj_pad(c, t)->flag[blockIdx.x][rank], epoch);
+    pdj_st_release_sys(&pdj_pad(c, t)->flag[slot][rank], epoch);
     PdjSignalPad* me = pdj_pad(c, rank);
-    const uint32_t* f = &me->flag[blockIdx.x][t];
+    const uint32_t* f = &me->flag[slot][t];
     const unsigned long long t0 = pdj_globaltimer();
     uint32_t spins = 0;
     while ((int32_t)(pdj_ld_acquire_sys(f) - epoch) < 0) {

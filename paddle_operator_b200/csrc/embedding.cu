@@ -64,7 +64,7 @@ emb_lookup_kernel(PdjComm c, PdjEmbTable t, size_t ids_off, size_t out_deep_off,
   const int rank = c.rank + blockIdx.y;
   const int NR = c.nranks;
   PdjSignalPad* me = pdj_pad(c, rank);
-  const uint32_t e = me->epoch[blockIdx.x];
+  const uint32_t e = me->epoch[pdj_slot(c)];
   if (do_barrier) pdj_block_barrier(c, rank, e + 1);  // owners finished applying the previous step
   const int D = t.dim;
   const int lpr = D >> 2;          // lanes per row
@@ -97,7 +97,7 @@ emb_lookup_kernel(PdjComm c, PdjEmbTable t, size_t ids_off, size_t out_deep_off,
       if (lane == 0) out_wide[b] = wide;
     }
   }
-  if (do_barrier && threadIdx.x == 0) me->epoch[blockIdx.x] = e + 1;
+  if (do_barrier && threadIdx.x == 0) me->epoch[pdj_slot(c)] = e + 1;
 }
 
 // Push.  mode 0 (sync): accumulate into the owner's staging rows and register
@@ -108,7 +108,7 @@ emb_push_kernel(PdjComm c, PdjEmbTable t, size_t ids_off, size_t gdeep_off, size
   const int rank = c.rank + blockIdx.y;
   const int NR = c.nranks;
   PdjSignalPad* me = pdj_pad(c, rank);
-  const uint32_t e = me->epoch[blockIdx.x];
+  const uint32_t e = me->epoch[pdj_slot(c)];
   const int D = t.dim;
   const int lpr = D >> 2, rpw = 32 / lpr;
   const int lane = threadIdx.x & 31;
@@ -146,7 +146,7 @@ emb_push_kernel(PdjComm c, PdjEmbTable t, size_t ids_off, size_t gdeep_off, size
   // All pushes of all ranks have landed once every block of every rank has
   // passed this barrier and the kernels have drained.
   pdj_block_barrier(c, rank, e + 1);
-  if (threadIdx.x == 0) me->epoch[blockIdx.x] = e + 1;
+  if (threadIdx.x == 0) me->epoch[pdj_slot(c)] = e + 1;
 }
 
 // Owner-side optimizer over the touched rows.  opt 0 = SGD, 1 = Adagrad.
@@ -223,7 +223,7 @@ template <typename... Args>
 int launch_emb(void (*kern)(Args...), int nblocks, int nthreads, int emulate, int nranks, cudaStream_t st,
                Args... args) {
   if (nblocks < 1) nblocks = 1;
-  if (nblocks > PDJ_MAX_BLOCKS) nblocks = PDJ_MAX_BLOCKS;
+  if (nblocks > PDJ_CHANNEL_BLOCKS) nblocks = PDJ_CHANNEL_BLOCKS;
   dim3 grid(nblocks, emulate ? nranks : 1);
   if (emulate) {
     void* argv[] = {(void*)&args...};

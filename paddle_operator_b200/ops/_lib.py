@@ -13,6 +13,9 @@ from ctypes import POINTER, c_char_p, c_float, c_int, c_int64, c_size_t, c_void_
 
 MAX_RANKS = 8
 PAD_BYTES = 65536
+MAX_BLOCKS = 1024        # barrier slots in the signal pad (csrc/common.cuh)
+CHANNEL_BLOCKS = 256     # slots per channel; concurrent comm kernels must use different channels
+NUM_CHANNELS = MAX_BLOCKS // CHANNEL_BLOCKS
 
 AR_TWOSHOT, AR_ONESHOT, AR_NVLS = 0, 1, 2
 
@@ -21,6 +24,8 @@ class PdjComm(ctypes.Structure):
     _fields_ = [
         ("nranks", c_int),
         ("rank", c_int),
+        ("pad_base", c_int),
+        ("reserved", c_int),
         ("base", c_void_p * MAX_RANKS),
         ("mc_base", c_void_p),
     ]

@@ -257,6 +257,66 @@ class CollectiveTrainer:
         else:
             self.hyper[0] = lr
 
+    # -- elastic re-form -----------------------------------------------------------
+    def reform(self, comm: Optional[Communicator]) -> None:
+        """Switches to a new communicator (new world size) without touching the
+        parameters, masters, momentum or BN statistics, which stay where they are
+        in HBM.  Only the gradient buffer moves (it lives in the arena) and the
+        step graph is captured again for the new pointers."""
+        torch.cuda.synchronize(self.device)
+        self.graph = None
+        self.comm = comm if (comm is not None and comm.nranks > 1) else None
+        self.world = comm.nranks if comm is not None else 1
+        self.comm_stream = torch.cuda.Stream(self.device) if self.comm is not None else None
+        flat = self.flat
+        flat.comm = self.comm
+        if self.comm is not None:
+            flat.grad_off = self.comm.alloc(flat.numel * 2)
+            flat.grad = self.comm.tensor(flat.grad_off, (flat.numel,), torch.bfloat16)
+        else:
+            flat.grad_off = 0
+            flat.grad = torch.zeros(flat.numel, dtype=torch.bfloat16, device=self.device)
+        flat.grad.zero_()
+        for b in flat.buckets:
+            b.gviews = []
+            for p in b.params:
+                pv, _, mv = flat.views[id(p)]
+                off = (pv.data_ptr() - flat.param.data_ptr()) // 2
+                gv = flat._view(flat.grad, off, p)
+                flat.views[id(p)] = (pv, gv, mv)
+                b.gviews.append(gv)
+        if self.use_graph:
+            self.capture(warmup=0)
+
+    def broadcast_state(self, root: int = 0, chunk_bytes: int = 32 << 20) -> None:
+        """K6: every rank ends up with the root's masters, momentum, hyper-parameters and
+        model buffers, moved GPU-to-GPU through the arena (no disk, no host)."""
+        if self.comm is None:
+            return
+        comm = self.comm
+        off = comm.alloc(chunk_bytes)
+        stage = comm.tensor(off, (chunk_bytes,), torch.uint8)
+        tensors = [self.flat.master, self.flat.momentum, self.hyper] + [b for _, b in self.model.named_buffers()]
+        for t in tensors:
+            flat = t.detach().reshape(-1).view(torch.uint8) if t.is_contiguous() else None
+            if flat is None:
+                flat = t.detach().contiguous().reshape(-1).view(torch.uint8)
+            n = flat.numel()
+            for s in range(0, n, chunk_bytes):
+                m = min(chunk_bytes, n - s)
+                padded = (m + 15) // 16 * 16
+                if comm.rank == root:
+                    stage[:m].copy_(flat[s:s + m])
+                comm.broadcast(root, off, padded)
+                if comm.rank != root:
+                    flat[s:s + m].copy_(stage[:m])
+                    if not t.is_contiguous():
+                        t.copy_(flat.view(t.dtype).view(t.shape))
+                comm.barrier()  # the stage is reused by the next chunk
+        with torch.no_grad():
+            self.flat.param.copy_(self.flat.master.to(torch.bfloat16))
+        torch.cuda.synchronize(self.device)
+
     # -- state (checkpoint / elastic re-shard) -------------------------------------
     def state_dict(self) -> dict:
         return {"master": self.flat.master, "momentum": self.flat.momentum, "hyper": self.hyper,

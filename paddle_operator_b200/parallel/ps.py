@@ -48,6 +48,7 @@ class ShardedEmbedding:
         self.num_rows = self.rows_per_shard * self.nranks
         self.has_wide, self.optimizer, self.lr, self.eps, self.async_sgd = has_wide, optimizer, lr, eps, async_sgd
         self.nblocks = nblocks or 128
+        self.cstruct = comm.channel_struct(1)  # never shares barrier slots with the dense all-reduce
         self.grad_scale = 1.0  # trainers set 1/world so that summed pushes equal the global-batch mean
         self.lib = _lib.load()
         R, D = self.rows_per_shard, dim
@@ -112,17 +113,17 @@ class ShardedEmbedding:
 
     def lookup_raw(self, batch: int, barrier: bool = True, stream=None) -> None:
         c = self.comm
-        check(self.lib.pdj_emb_lookup(ctypes.byref(c.comm_struct), ctypes.byref(self.t), self.ids_off,
+        check(self.lib.pdj_emb_lookup(ctypes.byref(self.cstruct), ctypes.byref(self.t), self.ids_off,
                                       self.out_deep_off, self.out_wide_off, batch, self.slots, int(barrier),
                                       self.nblocks, int(c.emulate), c._stream(stream)), "emb_lookup")
 
     def push_raw(self, batch: int, grad_scale: float = 1.0, stream=None) -> None:
         c = self.comm
-        check(self.lib.pdj_emb_push(ctypes.byref(c.comm_struct), ctypes.byref(self.t), self.ids_off, self.gdeep_in_off,
+        check(self.lib.pdj_emb_push(ctypes.byref(self.cstruct), ctypes.byref(self.t), self.ids_off, self.gdeep_in_off,
                                     self.gwide_in_off, batch, self.slots, int(self.async_sgd), self.lr, grad_scale,
                                     self.nblocks, int(c.emulate), c._stream(stream)), "emb_push")
         if not self.async_sgd:
-            check(self.lib.pdj_emb_apply(ctypes.byref(c.comm_struct), ctypes.byref(self.t), self.optimizer, self.lr,
+            check(self.lib.pdj_emb_apply(ctypes.byref(self.cstruct), ctypes.byref(self.t), self.optimizer, self.lr,
                                          self.eps, 4 * 148, int(c.emulate), c._stream(stream)), "emb_apply")
 
     def out_deep(self, batch: int, rank: Optional[int] = None) -> torch.Tensor:

@@ -162,6 +162,7 @@ class Communicator:
         self._comm = PdjComm()
         self._cursor = PAD_BYTES
         self._bases: list[int] = []
+        self._channels: dict[int, PdjComm] = {}
         self.has_multicast = False
 
     # -- construction -------------------------------------------------------
@@ -270,6 +271,7 @@ class Communicator:
         for i, b in enumerate(self._bases):
             self._comm.base[i] = b
         self._cursor = PAD_BYTES
+        self._channels.clear()
 
     # -- memory ---------------------------------------------------------------
     def alloc(self, nbytes: int, align: int = 256) -> int:
@@ -341,6 +343,21 @@ class Communicator:
     def comm_struct(self) -> PdjComm:
         return self._comm
 
+    def channel_struct(self, channel: int) -> PdjComm:
+        """A view of this communicator that uses barrier-slot channel `channel` of the signal
+        pad.  Kernels that may overlap on the GPU (e.g. a gradient all-reduce on a side stream
+        and an embedding push on the main stream) must not share a channel: each barrier slot's
+        epoch counter is owned by one kernel at a time.  Channel 0 is the default."""
+        if not 0 <= channel < _lib.NUM_CHANNELS:
+            raise ValueError(f"channel must be in [0, {_lib.NUM_CHANNELS})")
+        c = self._channels.get(channel)
+        if c is None:
+            c = PdjComm()
+            ctypes.pointer(c)[0] = self._comm
+            c.pad_base = channel * _lib.CHANNEL_BLOCKS
+            self._channels[channel] = c
+        return c
+
     def error_flags(self) -> list[int]:
         """Reads the timeout/error word of every local pad (debugging)."""
         import torch
@@ -349,7 +366,7 @@ class Communicator:
         out = []
         for r in ranks:
             pad = self.tensor(0, (PAD_BYTES // 4,), torch.int32, rank=r)
-            out.append(int(pad[256 * 8 + 256].item()))
+            out.append(int(pad[_lib.MAX_BLOCKS * 8 + _lib.MAX_BLOCKS].item()))
         return out
 
     def close(self) -> None:

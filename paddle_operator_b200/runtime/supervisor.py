@@ -113,6 +113,8 @@ class _Rank:
     log_path: str = ""
     started: bool = False
     done: bool = False
+    kill_at: float = 0.0   # monotonic deadline after which a terminating rank is SIGKILLed
+    grace: float = 30.0    # terminationGracePeriodSeconds
 
 
 class Supervisor:
@@ -204,12 +206,28 @@ class Supervisor:
                 r = self._ranks[key]
                 p = pods.get(key)
                 if p is None or p["metadata"].get("uid") != r.uid or p["metadata"].get("deletionTimestamp"):
-                    self._kill(r)
+                    # Graceful termination without blocking this loop: SIGTERM now, SIGKILL once the
+                    # pod's terminationGracePeriodSeconds (default 30, as in Kubernetes) has passed.
+                    alive = r.proc is not None and r.proc.poll() is None
+                    if alive and r.kill_at == 0.0:
+                        try:
+                            os.killpg(r.proc.pid, signal.SIGTERM)
+                        except (ProcessLookupError, PermissionError):
+                            pass
+                        r.kill_at = time.monotonic() + r.grace
+                        continue
+                    if alive and time.monotonic() < r.kill_at:
+                        continue
+                    if alive:
+                        self._kill(r, grace=0.0)
                     self._free_gpus(key)
                     del self._ranks[key]  # the work directory (log.txt) is kept for `pdj logs`
             for key, pod in pods.items():
                 if pod["metadata"].get("deletionTimestamp"):
                     continue
+                old = self._ranks.get(key)
+                if old is not None and old.uid != pod["metadata"].get("uid"):
+                    continue  # a previous incarnation of this name is still terminating
                 try:
                     self._sync_pod(key, pod)
                 except NotFound:
@@ -237,6 +255,7 @@ class Supervisor:
             r = _Rank(ns, name, pod["metadata"].get("uid", ""), workdir,
                       self._alloc_ip(bool(pod["spec"].get("hostNetwork"))), gpus or [])
             r.log_path = os.path.join(workdir, "log.txt")
+            r.grace = float(pod["spec"].get("terminationGracePeriodSeconds", 30))
             self._ranks[key] = r
             self._write_hosts()
             inits = [{"name": c["name"], "ready": False, "restartCount": 0,
@@ -408,12 +427,13 @@ class Supervisor:
         p = r.proc
         if p is None or p.poll() is not None:
             return
+        if grace > 0:
+            try:
+                os.killpg(p.pid, signal.SIGTERM)
+            except (ProcessLookupError, PermissionError):
+                pass
         try:
-            os.killpg(p.pid, signal.SIGTERM)
-        except (ProcessLookupError, PermissionError):
-            pass
-        try:
-            p.wait(grace)
+            p.wait(grace if grace > 0 else 0.001)
         except subprocess.TimeoutExpired:
             try:
                 os.killpg(p.pid, signal.SIGKILL)

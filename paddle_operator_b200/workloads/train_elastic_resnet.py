@@ -1,0 +1,229 @@
+"""Rank program for the elastic Collective-mode ResNet job
+(examples/resnet_elastic.yaml; the reference's deploy/elastic/resnet.yaml runs
+Paddle's train_fleet_dygraph_ckpt.py with /checkpoint on a shared host path).
+
+Membership goes through the etcd-compatible store named by
+PADDLE_ELASTIC_SERVER (runtime/elastic_agent.py).  Inside one *generation* the
+ranks train in lock-step.  When the desired world size changes (`pdj scale`,
+which the controller turns into pods created/deleted and an np update,
+controllers/paddlejob_elastic.go:41-55) or a member disappears, the ranks agree
+on a stop step, leave the collective together at that step, re-form the
+symmetric-memory group at the new size and continue from the same step:
+
+  * survivors keep parameters, momentum and BN statistics in HBM - nothing is
+    reloaded; only the gradient buffer (it lives in the arena) moves and the step
+    graph is re-captured;
+  * ranks that join receive the state from a survivor GPU-to-GPU (K6 broadcast
+    through the arena), not from disk;
+  * the checkpoint under /checkpoint is for whole-job restarts (every member
+    gone): the fresh generation's root loads it and broadcasts.
+
+`--cpu-dry-run` replaces the GPU job by a counter so that the membership
+protocol can be exercised with real processes on a machine without GPUs.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import signal
+import sys
+import time
+
+
+class _DryJob:
+    """Stands in for ResNetJob on CPU: the 'model state' is one float that every step increments."""
+
+    def __init__(self, step_time: float):
+        self.state = 0.0
+        self.step_time = step_time
+        self.world = 1
+
+    def reform(self, comm_key, rank, world):
+        self.world = world
+
+    def broadcast_state(self, etcd, prefix, gen, is_root):
+        key = f"{prefix}/dry-state/{gen}"
+        if is_root:
+            etcd.put(key, repr(self.state))
+        deadline = time.time() + 30
+        while time.time() < deadline:
+            kv = etcd.get(key)
+            if kv:
+                self.state = float(kv[0][1])
+                return
+            time.sleep(0.01)
+        raise TimeoutError("dry-run state broadcast")
+
+    def step(self):
+        time.sleep(self.step_time)
+        self.state += 1.0
+        return self.state
+
+    def state_dict(self):
+        return {"state": self.state}
+
+    def load_state_dict(self, sd):
+        self.state = sd["state"]
+
+
+def main() -> int:
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--batch", type=int, default=256)
+    ap.add_argument("--image", type=int, default=224)
+    ap.add_argument("--tiny", action="store_true")
+    ap.add_argument("--ckpt-every", type=int, default=50)
+    ap.add_argument("--report-every", type=int, default=5)
+    ap.add_argument("--cpu-dry-run", action="store_true")
+    ap.add_argument("--dry-step-time", type=float, default=0.02)
+    ap.add_argument("--fail-at-step", type=int, default=-1, help="fault injection: this rank SIGKILLs itself")
+    ap.add_argument("--fail-rank", type=int, default=-1)
+    args = ap.parse_args()
+    env = os.environ
+    dry = args.cpu_dry_run or env.get("PDJ_CPU_DRY_RUN") == "1"
+
+    from ..runtime.elastic_agent import ElasticAgent
+    from ..utils import checkpoint as ckpt
+
+    agent = ElasticAgent.from_env(ttl=int(env.get("PDJ_ELASTIC_TTL", "6")))
+    signal.signal(signal.SIGTERM, lambda *_: setattr(agent, "leaving", True))
+    root_dir = ckpt.checkpoint_root()
+    job_key = env.get("PDJ_JOB_KEY", agent.job_id)
+    trainer_id = int(env.get("PADDLE_TRAINER_ID", "0"))
+
+    t_boot = time.time()
+    if dry:
+        job = _DryJob(args.dry_step_time)
+        comm = None
+    else:
+        import torch
+
+        from ..parallel.symm import Communicator
+        from .resnet import ResNetJob
+
+        dev = int(env.get("LOCAL_RANK", env.get("PDJ_LOCAL_DEVICE", "0")))
+        torch.cuda.set_device(dev)
+        device = torch.device("cuda", dev)
+        # built for world 1 first; reform() binds it to each generation's communicator
+        job = ResNetJob(batch=args.batch, image=args.image, comm=None, device=device, tiny=args.tiny,
+                        num_classes=16 if args.tiny else 1000, use_graph=True)
+        with torch.no_grad():
+            job.x.copy_(torch.randn(job.x.shape, device=device).to(torch.bfloat16))
+            job.y.copy_(torch.randint(0, 16 if args.tiny else 1000, (args.batch,), device=device))
+        # warm cuDNN / allocator once so that later captures are quick
+        job.trainer.use_graph = False
+        job.trainer.step()
+        job.trainer.use_graph = True
+        torch.cuda.synchronize()
+        comm = None
+    agent.report("boot_seconds", round(time.time() - t_boot, 3))
+
+    m = agent.join()
+    step = 0
+    while True:
+        t_form = time.time()
+        is_root = (m.root == agent.host) or (m.root is None and m.rank == 0)
+        if dry:
+            job.reform(f"{job_key}-g{m.generation}", m.rank, m.world)
+            if m.fresh and is_root:
+                sd = ckpt.load_dp(root_dir)
+                if sd is not None:
+                    job.load_state_dict(sd["trainer"])
+                    step = int(sd["step"])
+            job.broadcast_state(agent.etcd, agent.prefix, m.generation, is_root)
+            if not is_root:
+                kv = None
+            # the step travels with the members record (live hand-over) or with the checkpoint (fresh)
+        else:
+            import torch
+
+            if comm is not None:
+                comm.close()
+                comm = None
+            if m.world > 1:
+                comm = Communicator.create(m.rank, m.world, dev, 256 << 20, key=f"{job_key}-g{m.generation}")
+            job.trainer.reform(comm)
+            job.comm, job.rank, job.world = comm, m.rank, m.world
+            if m.fresh and is_root:
+                sd = ckpt.load_dp(root_dir, map_location=device)
+                if sd is not None:
+                    job.trainer.load_state_dict(sd["trainer"])
+                    step = int(sd["step"])
+            root_rank = m.hosts.index(m.root) if m.root in m.hosts else 0
+            job.trainer.broadcast_state(root=root_rank)
+        # agree on the step this generation starts from
+        if is_root:
+            if m.step is not None:
+                step = int(m.step)
+            agent.publish_resume(m.generation, step, m.world)
+        else:
+            step = int(agent.wait_resume(m.generation)["step"])
+        agent.report(f"formed/{m.generation}", {"world": m.world, "rank": m.rank, "step": step,
+                                                  "form_seconds": round(time.time() - t_form, 3), "t": time.time()})
+        print(json.dumps({"event": "generation", "gen": m.generation, "rank": m.rank, "world": m.world, "step": step,
+                          "fresh": m.fresh, "form_seconds": round(time.time() - t_form, 3)}), flush=True)
+
+        # ---- train inside this generation ------------------------------------------
+        stop_at = None
+        t0, s0 = time.time(), step
+        while step < args.steps:
+            if args.fail_at_step == step + 1 and args.fail_rank == trainer_id and \
+                    int(env.get("PDJ_RESTART_COUNT", "0")) == 0:
+                os.kill(os.getpid(), signal.SIGKILL)  # fault injection
+            if dry:
+                loss = job.step()
+            else:
+                loss = float(job.step_device().item())  # one sync per step keeps host and device in lock-step
+            step += 1
+            if step % args.report_every == 0:
+                rate = (step - s0) * args.batch * m.world / max(1e-9, time.time() - t0)
+                agent.report("progress", {"gen": m.generation, "step": step, "world": m.world, "loss": loss,
+                                          "img_per_s": round(rate, 1), "t": time.time()})
+            if m.rank == 0 and args.ckpt_every > 0 and step % args.ckpt_every == 0:
+                ckpt.save_dp(root_dir, step, m.world, {"trainer": job.state_dict() if dry else job.trainer.state_dict(),
+                                                       "step": step})
+            stop_at = agent.should_stop(m, step)
+            if stop_at is not None:
+                if step > stop_at:
+                    raise RuntimeError(f"rank passed the agreed stop step ({step} > {stop_at})")
+                if step == stop_at:
+                    break
+        if step >= args.steps and stop_at is None:
+            break
+        if stop_at is None or step < stop_at:
+            break
+        # ---- re-form ----------------------------------------------------------------------
+        t_stop = time.time()
+        agent.report(f"stopped/{m.generation}", {"step": step, "t": t_stop})
+        if not dry:
+            import torch
+
+            torch.cuda.synchronize()
+        nm = agent.next_generation(m, step)
+        if nm is None:
+            print(json.dumps({"event": "leave", "gen": m.generation, "rank": m.rank, "step": step}), flush=True)
+            if comm is not None:
+                comm.close()
+            return 0
+        m = nm
+
+    # normal completion
+    if m.rank == 0:
+        ckpt.save_dp(root_dir, step, m.world, {"trainer": job.state_dict() if dry else job.trainer.state_dict(),
+                                               "step": step})
+    agent.report("done", {"step": step, "t": time.time()})
+    print(json.dumps({"event": "done", "rank": m.rank, "step": step}), flush=True)
+    if comm is not None:
+        import torch
+
+        torch.cuda.synchronize()
+        comm.barrier()
+        torch.cuda.synchronize()
+        comm.close()
+    agent.leave()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())
