@@ -39,7 +39,13 @@ def sync_etcd(etcd, path: str, np: str) -> bool:
 
 def sync_np(etcd, pdj: PaddleJob) -> Optional[str]:
     """Returns the new np (as a string) when the key was updated, else None."""
-    if pdj.status.mode != PaddleJobMode.COLLECTIVE.value or pdj.spec.worker is None:
+    if pdj.spec.worker is None or pdj.spec.ps is not None:
+        return None
+    # The reference syncs only while status.mode is Collective (paddlejob_elastic.go:45), and the
+    # mode flips to Single when an elastic job is scaled to one worker (helper.go:191-199), which
+    # leaves np stale at 2 and the last rank waiting for a peer that was deleted.  An elastic job
+    # without ps is collective by construction, so the sync also covers the one-worker case here.
+    if pdj.status.mode != PaddleJobMode.COLLECTIVE.value and pdj.spec.elastic is None:
         return None
     np = str(pdj.spec.worker.replicas)
     return np if sync_etcd(etcd, np_key(pdj.namespace, pdj.name), np) else None

@@ -142,7 +142,17 @@ def main() -> int:
     sizes = [int(x) for x in args.sizes.split(",")]
     gpus = None if not args.cpu_dry_run else list(range(max(sizes)))
     work = tempfile.mkdtemp(prefix="pdj-elastic-")
-    res = run(sizes, args.steps_per_phase, args.cpu_dry_run, args.batch, args.tiny, gpus, work, args.timeout)
+    try:
+        res = run(sizes, args.steps_per_phase, args.cpu_dry_run, args.batch, args.tiny, gpus, work, args.timeout)
+    except Exception:
+        # post-mortem: every rank's log
+        import glob
+
+        for f in sorted(glob.glob(os.path.join(work, "pods", "*", "*", "log.txt"))):
+            print(f"===== {f}", flush=True)
+            with open(f, errors="replace") as fh:
+                print(fh.read()[-3000:], flush=True)
+        raise
     print(json.dumps(res), flush=True)
     if args.out:
         with open(args.out, "w") as f:
