@@ -47,6 +47,49 @@ def save_dp(root: str, step: int, world: int, state: dict, rank: int = 0) -> Non
     _write_step(root, step, world)
 
 
+class AsyncSaver:
+    """Checkpoints without stalling the training loop: tensors are snapshotted to host memory
+    on the caller's thread (one device-to-host copy), the file is written by a background thread.
+    At most one save is in flight; a save requested while another runs is skipped (the next
+    interval will catch up), which keeps "overwrite the previous save" semantics."""
+
+    def __init__(self):
+        import threading
+
+        self._thread = None
+        self._lock = threading.Lock()
+
+    @staticmethod
+    def _to_host(obj):
+        import torch
+
+        if torch.is_tensor(obj):
+            return obj.detach().to("cpu", copy=True)
+        if isinstance(obj, dict):
+            return {k: AsyncSaver._to_host(v) for k, v in obj.items()}
+        if isinstance(obj, (list, tuple)):
+            return type(obj)(AsyncSaver._to_host(v) for v in obj)
+        return obj
+
+    def save_dp(self, root: str, step: int, world: int, state: dict, rank: int = 0) -> bool:
+        import threading
+
+        if rank != 0:
+            return False
+        with self._lock:
+            if self._thread is not None and self._thread.is_alive():
+                return False
+            snap = self._to_host(state)
+            self._thread = threading.Thread(target=save_dp, args=(root, step, world, snap, 0), daemon=True)
+            self._thread.start()
+            return True
+
+    def wait(self) -> None:
+        t = self._thread
+        if t is not None:
+            t.join()
+
+
 def save_ps_shard(root: str, idx: int, state: dict) -> None:
     os.makedirs(root, exist_ok=True)
     _atomic_save(state, os.path.join(root, f"ps-{idx}.pt"))

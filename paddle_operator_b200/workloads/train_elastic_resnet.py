@@ -119,6 +119,7 @@ def main() -> int:
         comm = None
     agent.report("boot_seconds", round(time.time() - t_boot, 3))
 
+    saver = ckpt.AsyncSaver()
     m = agent.join()
     step = 0
     while True:
@@ -132,8 +133,6 @@ def main() -> int:
                     job.load_state_dict(sd["trainer"])
                     step = int(sd["step"])
             job.broadcast_state(agent.etcd, agent.prefix, m.generation, is_root)
-            if not is_root:
-                kv = None
             # the step travels with the members record (live hand-over) or with the checkpoint (fresh)
         else:
             import torch
@@ -181,8 +180,8 @@ def main() -> int:
                 agent.report("progress", {"gen": m.generation, "step": step, "world": m.world, "loss": loss,
                                           "img_per_s": round(rate, 1), "t": time.time()})
             if m.rank == 0 and args.ckpt_every > 0 and step % args.ckpt_every == 0:
-                ckpt.save_dp(root_dir, step, m.world, {"trainer": job.state_dict() if dry else job.trainer.state_dict(),
-                                                       "step": step})
+                saver.save_dp(root_dir, step, m.world, {"trainer": job.state_dict() if dry else job.trainer.state_dict(),
+                                                        "step": step})
             stop_at = agent.should_stop(m, step)
             if stop_at is not None:
                 if step > stop_at:
@@ -209,6 +208,7 @@ def main() -> int:
         m = nm
 
     # normal completion
+    saver.wait()
     if m.rank == 0:
         ckpt.save_dp(root_dir, step, m.world, {"trainer": job.state_dict() if dry else job.trainer.state_dict(),
                                                "step": step})

@@ -112,6 +112,14 @@ def test_controller_np_sync_against_the_store(server, kind):
     etcd.put(key, "3")
     assert sync_np(etcd, job) == "4" and etcd.get(key) == [(key, "4")]
     assert sync_np(etcd, job) is None  # already in sync
+    from paddle_operator_b200.api.types import ResourceSpec
+
     job.status.mode = "PS"
+    job.spec.ps = ResourceSpec(replicas=2)
     job.spec.worker.replicas = 8
-    assert sync_np(etcd, job) is None and etcd.get(key) == [(key, "4")]  # Collective mode only
+    assert sync_np(etcd, job) is None and etcd.get(key) == [(key, "4")]  # never for PS jobs
+    # an elastic job scaled to ONE worker reports mode Single; np must still follow (see controller/elastic.py)
+    job.spec.ps = None
+    job.status.mode = "Single"
+    job.spec.worker.replicas = 1
+    assert sync_np(etcd, job) == "1"
