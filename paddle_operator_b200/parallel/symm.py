@@ -315,7 +315,9 @@ class Communicator:
             return AR_TWOSHOT
         if nbytes <= 256 << 10:
             return AR_ONESHOT
-        if self.has_multicast and not self.emulate:
+        # measured on B200 (profiles/): at 2 ranks the peer-to-peer two-shot beats the switch
+        # reduction at every size; NVLS pays off once there are more peers to pull from
+        if self.has_multicast and not self.emulate and self.nranks >= 4:
             return AR_NVLS
         return AR_TWOSHOT
 

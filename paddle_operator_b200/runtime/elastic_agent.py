@@ -310,7 +310,10 @@ class ElasticAgent:
 
     def report(self, key: str, value) -> None:
         """Progress / timing breadcrumbs for harnesses: /paddle/<job>/report/<host>/<key>."""
-        self.etcd.put(f"{self.prefix}/report/{self.host}/{key}", json.dumps(value))
+        try:
+            self.etcd.put(f"{self.prefix}/report/{self.host}/{key}", json.dumps(value))
+        except Exception:  # noqa: BLE001 - breadcrumbs are best effort; never take a rank down for one
+            pass
 
     def leave(self) -> None:
         self.leaving = True

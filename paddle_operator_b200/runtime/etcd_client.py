@@ -17,6 +17,7 @@ import base64
 import http.client
 import json
 import threading
+import time
 from typing import Callable, Optional
 
 from .etcd_store import prefix_range_end
@@ -47,7 +48,19 @@ class EtcdClient:
     def endpoints(self) -> list:
         return list(self._endpoints)
 
-    def _post(self, path: str, body: dict) -> dict:
+    def _post(self, path: str, body: dict, retries: int = 3) -> dict:
+        last: Optional[Exception] = None
+        for attempt in range(retries):
+            try:
+                return self._post_once(path, body)
+            except EtcdError as e:
+                if "no etcd endpoint reachable" not in str(e):
+                    raise
+                last = e
+                time.sleep(0.05 * (attempt + 1))
+        raise last  # type: ignore[misc]
+
+    def _post_once(self, path: str, body: dict) -> dict:
         last: Optional[Exception] = None
         for ep in self._endpoints:
             host, _, port = ep.partition(":")

@@ -252,7 +252,9 @@ class EtcdServer:
     def __init__(self, host: str = "127.0.0.1", port: int = 2379, store: Optional[EtcdStore] = None):
         self.store = store or EtcdStore()
         handler = type("Handler", (_Handler,), {"store": self.store})
-        self.httpd = ThreadingHTTPServer((host, port), handler)
+        # eight ranks keep-alive, watch and report at once: the default backlog of 5 resets connections
+        server_cls = type("Server", (ThreadingHTTPServer,), {"request_queue_size": 256})
+        self.httpd = server_cls((host, port), handler)
         self.httpd.daemon_threads = True
         self.host, self.port = self.httpd.server_address[:2]
         self._thread: Optional[threading.Thread] = None

@@ -114,7 +114,12 @@ def run(sizes: list, steps_per_phase: int, dry: bool, batch: int, tiny: bool, gp
                 start_step = max(r["progress"]["step"] for r in rep.values() if "progress" in r and r["progress"]["world"] == n)
                 rep = _wait_progress(etcd, prefix, n, start_step + steps_per_phase, timeout, after_gen=gen_seen - 1)
                 pr = [r["progress"] for r in rep.values() if "progress" in r and r["progress"]["world"] == n
-                      and r["progress"]["gen"] == gen_seen]
+                      and r["progress"]["gen"] >= gen_seen]
+                if max(p["gen"] for p in pr) != gen_seen:  # the job re-formed on its own (a rank failed and came back)
+                    result.setdefault("unplanned_reforms", []).append({"world": n, "from_gen": gen_seen,
+                                                                       "to_gen": max(p["gen"] for p in pr)})
+                    gen_seen = max(p["gen"] for p in pr)
+                    pr = [p for p in pr if p["gen"] == gen_seen]
                 cur_step = max(p["step"] for p in pr)
                 result["phases"].append({"world": n, "gen": gen_seen, "step": cur_step,
                                          "img_per_s": round(min(p["img_per_s"] for p in pr), 1),
