@@ -103,6 +103,16 @@ int pdj_emb_push(const struct PdjComm* c, const struct PdjEmbTable* t, size_t id
 int pdj_emb_apply(const struct PdjComm* c, const struct PdjEmbTable* t, int optimizer, float lr, float eps,
                   int nblocks, int emulate, cudaStream_t st);
 
+/* ---- tcgen05 / TMA fused linear layer (csrc/gemm_tcgen05.cu) -----------------
+ * out[M,N] = epilogue(A[M,K] . B[N,K]^T): bf16 operands (row pitches lda/ldb in
+ * elements, multiples of 8), fp32 accumulation in tensor memory, bf16 output with
+ * row pitch ldo.  Epilogue: + bias[N] (fp32, optional), ReLU (optional), zero where
+ * mask[M,N] <= 0 (bf16, optional; the ReLU derivative for the backward GEMM).
+ * The MLP of the Wide&Deep workload (deploy/examples/wide_and_deep.yaml). */
+int pdj_linear_block_n(int N);
+int pdj_linear_bf16(const void* a, const void* b, void* out, const float* bias, const void* mask, int M, int N, int K,
+                    int lda, int ldb, int ldo, int relu, cudaStream_t st);
+
 /* ---- ResNet-50 step kernels (csrc/bn_act.cu, csrc/optim_misc.cu) -----------
  * The workload of deploy/examples/resnet.yaml:13-19. NHWC bf16 activations
  * viewed as [M, C]; fp32 statistics. */

@@ -1,0 +1,95 @@
+"""Fused Linear(+bias)(+ReLU) on tcgen05 tensor cores (csrc/gemm_tcgen05.cu).
+
+    y = linear_act(x, weight, bias, relu=True)        # x [M,K] bf16, weight [N,K] bf16 -> y [M,N] bf16
+
+Forward and the input-gradient GEMM run on the hand-written TMA + tcgen05 kernel
+(the ReLU derivative is applied in the dX epilogue of the layer above, so no
+separate mask pass exists); the weight-gradient GEMM is a plain library GEMM.
+CPU tensors / other dtypes fall back to torch.  Reference parity: no counterpart
+in the reference (no compute code); the MLP of deploy/examples/wide_and_deep.yaml.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+
+from . import _lib
+
+
+def linear_bf16(a: torch.Tensor, b: torch.Tensor, bias: Optional[torch.Tensor] = None, relu: bool = False,
+                mask: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """out[M,N] = epilogue(a[M,K] @ b[N,K]^T).  a, b: bf16, last dim contiguous, row pitch a multiple of 8."""
+    assert a.is_cuda and a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16
+    assert a.dim() == 2 and b.dim() == 2 and a.shape[1] == b.shape[1]
+    if a.stride(1) != 1 or a.stride(0) % 8 != 0 or a.data_ptr() % 16 != 0:
+        a = _pad_rows(a)
+    if b.stride(1) != 1 or b.stride(0) % 8 != 0 or b.data_ptr() % 16 != 0:
+        b = _pad_rows(b)
+    m, k = a.shape
+    n = b.shape[0]
+    if out is None:
+        out = torch.empty((m, n), dtype=torch.bfloat16, device=a.device)
+    if bias is not None and bias.dtype != torch.float32:
+        bias = bias.float()
+    if mask is not None:
+        assert mask.shape == out.shape and mask.stride() == out.stride() and mask.dtype == torch.bfloat16
+    _lib.check(_lib.load().pdj_linear_bf16(a.data_ptr(), b.data_ptr(), out.data_ptr(), _lib.ptr(bias), _lib.ptr(mask),
+                                           m, n, k, a.stride(0), b.stride(0), out.stride(0), int(relu),
+                                           torch.cuda.current_stream().cuda_stream), "linear_bf16")
+    return out
+
+
+def _pad_rows(t: torch.Tensor) -> torch.Tensor:
+    """Copy into a buffer whose row pitch is a multiple of 8 elements (TMA needs 16-byte pitches)."""
+    r, c = t.shape
+    ld = (c + 7) // 8 * 8
+    buf = torch.zeros((r, ld), dtype=t.dtype, device=t.device)
+    buf[:, :c].copy_(t)
+    return buf[:, :c]
+
+
+class _LinearActFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, bias, relu, bias_f32):
+        y = linear_bf16(x, weight, bias_f32 if bias_f32 is not None else bias, relu=relu)
+        ctx.save_for_backward(x, weight, y if relu else None)
+        ctx.relu = relu
+        ctx.has_bias = bias is not None
+        ctx.bias_dtype = bias.dtype if bias is not None else None
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, weight, y = ctx.saved_tensors
+        dy = dy.contiguous()
+        dz = torch.where(y > 0, dy, torch.zeros((), dtype=dy.dtype, device=dy.device)) if ctx.relu else dy
+        dx = dw = db = None
+        if ctx.needs_input_grad[0]:
+            # dX[M,K] = dZ[M,N] @ W[N,K]  ==  dZ . (W^T)[K,N]^T : the B operand is W^T, K-major over N
+            dx = linear_bf16(dz, weight.t().contiguous())
+        if ctx.needs_input_grad[1]:
+            dw = dz.t().mm(x)
+        if ctx.has_bias and ctx.needs_input_grad[2]:
+            db = dz.float().sum(0).to(ctx.bias_dtype)
+        return dx, dw, db, None, None
+
+
+def linear_act(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] = None, relu: bool = False,
+               bias_f32: Optional[torch.Tensor] = None) -> torch.Tensor:
+    if x.is_cuda and x.dtype == torch.bfloat16 and weight.dtype == torch.bfloat16:
+        return _LinearActFn.apply(x, weight, bias, relu, bias_f32)
+    y = torch.nn.functional.linear(x, weight, bias)
+    return torch.relu(y) if relu else y
+
+
+class FusedLinear(torch.nn.Linear):
+    """nn.Linear whose CUDA bf16 forward / dgrad run on the tcgen05 kernel, with an optional fused ReLU."""
+
+    def __init__(self, in_features: int, out_features: int, relu: bool = False, bias: bool = True):
+        super().__init__(in_features, out_features, bias=bias)
+        self.relu = relu
+        self.bias_f32 = None  # a trainer may point this at its fp32 master copy
+
+    def forward(self, x):
+        return linear_act(x, self.weight, self.bias, self.relu, self.bias_f32)
