@@ -2,14 +2,16 @@
 //   out[M,N] = epilogue( A[M,K] . B[N,K]^T )       bf16 in, fp32 accumulate in TMEM, bf16 out
 //
 // Blackwell-native structure (sm_100a only):
-//   * operands arrive by TMA (cp.async.bulk.tensor.2d, 128-byte swizzle) into a
-//     4-stage shared-memory ring guarded by mbarriers;
+//   * persistent: one CTA per SM walks the output tiles; operands arrive by TMA
+//     (cp.async.bulk.tensor.2d, 128-byte swizzle) into a multi-stage shared-memory
+//     ring guarded by mbarriers;
 //   * one elected thread issues tcgen05.mma (cta_group::1, kind::f16, M=128,
-//     N=block_n, K=16) with the accumulator in tensor memory; tcgen05.commit
-//     releases ring slots and finally signals the epilogue;
+//     N=block_n, K=16) into one of two accumulator buffers in tensor memory;
+//     tcgen05.commit releases ring slots and signals the epilogue, which drains
+//     buffer i while the MMAs of tile i + 1 fill the other one;
 //   * four epilogue warps read the accumulator with tcgen05.ld (32 lanes x 32 bit
 //     x 16 columns), add the bias, apply ReLU and/or a ReLU-derivative mask, pack
-//     to bf16 and store.
+//     to bf16, stage the tile in shared memory and write it with one TMA store.
 // Out-of-range rows / columns / K tail are handled by TMA zero fill and guarded
 // stores, so M, N, K need no padding (only 16-byte aligned row pitches).
 //
@@ -17,22 +19,23 @@
 // GEMMs.  Reference parity: none (the reference has no compute code); workload of
 // deploy/examples/wide_and_deep.yaml.
 #include <cuda.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 #include "../../include/pdjob_b200.h"
 
 namespace {
 
-constexpr int BM = 128;          // rows of A per CTA = UMMA M
+constexpr int BM = 128;          // rows of A per tile = UMMA M
 constexpr int BK = 64;           // K per stage: 64 bf16 = one 128-byte swizzle row
 constexpr int UK = 16;           // K per tcgen05.mma for 16-bit inputs
-constexpr int STAGES = 4;
 constexpr int MAX_BN = 256;
-constexpr int A_STAGE_BYTES = BM * BK * 2;        // 16 KiB
-constexpr int B_STAGE_BYTES = MAX_BN * BK * 2;    // 32 KiB
-constexpr int TMEM_COLS = 256;
-constexpr int SMEM_BYTES = STAGES * (A_STAGE_BYTES + B_STAGE_BYTES) + 256 + 1024;  // + barriers + alignment slack
-constexpr int THREADS = 192;     // warp 0: TMA, warp 1: MMA + TMEM owner, warps 2-5: epilogue
+constexpr int MAX_STAGES = 6;
+constexpr int A_STAGE_BYTES = BM * BK * 2;  // 16 KiB
+constexpr int TMEM_COLS = 512;              // two accumulator buffers of up to 256 columns
+constexpr int EPI_WARPS = 8;                // two warps per TMEM lane quarter, each takes half of the columns
+constexpr int THREADS = 64 + 32 * EPI_WARPS; // warp 0: TMA, warp 1: MMA + TMEM owner, warps 2..9: epilogue
+constexpr int SMEM_LIMIT = 227 * 1024;
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -41,6 +44,9 @@ __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
 }
 __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   asm volatile(
@@ -60,6 +66,11 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map
       "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(dst),
       "l"(map), "r"(c0), "r"(c1), "r"(bar)
       : "memory");
+}
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, uint32_t src, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(map), "r"(src), "r"(c0),
+               "r"(c1)
+               : "memory");
 }
 // Shared-memory matrix descriptor: K-major tile, 128-byte swizzle, rows 128 B apart,
 // 8-row groups 1024 B apart (SBO), descriptor version 1 (sm_100).
@@ -86,33 +97,48 @@ __device__ __forceinline__ void umma_commit(uint32_t bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
 
+// Persistent: one CTA per SM walks tiles t = blockIdx.x, blockIdx.x + gridDim.x, ... (column tile
+// fastest, so CTAs running at the same time share A rows in L2).  The accumulator is double
+// buffered in TMEM: the epilogue of tile i overlaps the MMAs of tile i + 1.
+template <bool TMA_STORE>
 __global__ void __launch_bounds__(THREADS, 1)
 linear_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
-                      __nv_bfloat16* __restrict__ out, const float* __restrict__ bias,
-                      const __nv_bfloat16* __restrict__ mask, int M, int N, int K, int ldo, int block_n, int relu) {
+                      const __grid_constant__ CUtensorMap tma_o, __nv_bfloat16* __restrict__ out,
+                      const float* __restrict__ bias, const __nv_bfloat16* __restrict__ mask, int M, int N, int K,
+                      int ldo, int block_n, int stages, int relu) {
   extern __shared__ uint8_t smem_raw[];
-  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;  // SWIZZLE_128B wants 1024-byte alignment
+  const uint32_t raw = smem_u32(smem_raw);
+  const uint32_t base = (raw + 1023u) & ~1023u;  // SWIZZLE_128B wants 1024-byte alignment
+  const uint32_t b_stage_bytes = (uint32_t)block_n * BK * 2;
   const uint32_t a_smem = base;
-  const uint32_t b_smem = base + STAGES * A_STAGE_BYTES;
-  const uint32_t bars = b_smem + STAGES * B_STAGE_BYTES;
-  const uint32_t full0 = bars, empty0 = bars + 8 * STAGES, tmem_full = bars + 16 * STAGES, tmem_slot = tmem_full + 8;
-  uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
+  const uint32_t b_smem = a_smem + stages * A_STAGE_BYTES;
+  const uint32_t stage_out = b_smem + stages * b_stage_bytes;                    // [128][block_n] bf16 staging
+  const uint32_t bias_smem = stage_out + (TMA_STORE ? (uint32_t)BM * block_n * 2 : 0u);      // fp32 [block_n]
+  const uint32_t bars = bias_smem + MAX_BN * 4;
+  const uint32_t full0 = bars, empty0 = bars + 8 * MAX_STAGES;
+  const uint32_t tfull0 = bars + 16 * MAX_STAGES, tempty0 = tfull0 + 16, tmem_slot = tempty0 + 16;
+  uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(smem_raw + (tmem_slot - raw));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int m0 = blockIdx.x * BM, n0 = blockIdx.y * block_n;
+  const int tiles_n = (N + block_n - 1) / block_n;
+  const int total = ((M + BM - 1) / BM) * tiles_n;
   const int num_kb = (K + BK - 1) / BK;
 
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_a) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_b) : "memory");
+    if (TMA_STORE) asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_o) : "memory");
   }
   if (warp == 1) {
     if (lane == 0) {
-      for (int s = 0; s < STAGES; ++s) {
+      for (int s = 0; s < stages; ++s) {
         mbar_init(full0 + 8 * s, 1);
         mbar_init(empty0 + 8 * s, 1);
       }
-      mbar_init(tmem_full, 1);
+      for (int b = 0; b < 2; ++b) {
+        mbar_init(tfull0 + 8 * b, 1);
+        mbar_init(tempty0 + 8 * b, EPI_WARPS);  // one arrival per epilogue warp
+      }
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncwarp();
@@ -128,14 +154,17 @@ linear_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
   if (warp == 0) {
     // ===== TMA producer =====
     if (lane == 0) {
-      const uint32_t stage_bytes = (uint32_t)(BM + block_n) * BK * 2;
-      for (int kb = 0; kb < num_kb; ++kb) {
-        const int s = kb % STAGES;
-        const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
-        mbar_wait(empty0 + 8 * s, ph ^ 1u);
-        mbar_expect_tx(full0 + 8 * s, stage_bytes);
-        tma_load_2d(a_smem + s * A_STAGE_BYTES, &tma_a, kb * BK, m0, full0 + 8 * s);
-        tma_load_2d(b_smem + s * B_STAGE_BYTES, &tma_b, kb * BK, n0, full0 + 8 * s);
+      const uint32_t stage_bytes = (uint32_t)A_STAGE_BYTES + b_stage_bytes;
+      uint32_t it = 0;
+      for (int t = blockIdx.x; t < total; t += gridDim.x) {
+        const int m0 = (t / tiles_n) * BM, n0 = (t % tiles_n) * block_n;
+        for (int kb = 0; kb < num_kb; ++kb, ++it) {
+          const uint32_t s = it % (uint32_t)stages, ph = (it / (uint32_t)stages) & 1u;
+          mbar_wait(empty0 + 8 * s, ph ^ 1u);
+          mbar_expect_tx(full0 + 8 * s, stage_bytes);
+          tma_load_2d(a_smem + s * A_STAGE_BYTES, &tma_a, kb * BK, m0, full0 + 8 * s);
+          tma_load_2d(b_smem + s * b_stage_bytes, &tma_b, kb * BK, n0, full0 + 8 * s);
+        }
       }
     }
   } else if (warp == 1) {
@@ -143,68 +172,122 @@ linear_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
     if (lane == 0) {
       // instruction descriptor: D = f32, A = B = bf16, both K-major, N >> 3, M >> 4
       const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(block_n >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
-      for (int kb = 0; kb < num_kb; ++kb) {
-        const int s = kb % STAGES;
-        const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
-        mbar_wait(full0 + 8 * s, ph);
+      uint32_t it = 0, i = 0;
+      for (int t = blockIdx.x; t < total; t += gridDim.x, ++i) {
+        const uint32_t buf = i & 1u, aph = (i >> 1) & 1u;
+        mbar_wait(tempty0 + 8 * buf, aph ^ 1u);  // the epilogue has drained this accumulator
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const uint32_t tmem_d = tmem_base + buf * MAX_BN;
+        for (int kb = 0; kb < num_kb; ++kb, ++it) {
+          const uint32_t s = it % (uint32_t)stages, ph = (it / (uint32_t)stages) & 1u;
+          mbar_wait(full0 + 8 * s, ph);
+          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 #pragma unroll
-        for (int k = 0; k < BK / UK; ++k) {
-          const uint64_t da = umma_desc(a_smem + s * A_STAGE_BYTES + k * UK * 2);
-          const uint64_t db = umma_desc(b_smem + s * B_STAGE_BYTES + k * UK * 2);
-          umma_f16(tmem_base, da, db, idesc, (uint32_t)((kb | k) != 0));
+          for (int k = 0; k < BK / UK; ++k) {
+            const uint64_t da = umma_desc(a_smem + s * A_STAGE_BYTES + k * UK * 2);
+            const uint64_t db = umma_desc(b_smem + s * b_stage_bytes + k * UK * 2);
+            umma_f16(tmem_d, da, db, idesc, (uint32_t)((kb | k) != 0));
+          }
+          umma_commit(empty0 + 8 * s);  // slot is free once these MMAs have read it
         }
-        umma_commit(empty0 + 8 * s);  // slot is free once these MMAs have read it
+        umma_commit(tfull0 + 8 * buf);  // accumulator complete
       }
-      umma_commit(tmem_full);  // accumulator complete
     }
   } else {
-    // ===== epilogue: warps 2..5 own TMEM lane quarters (warp % 4) =====
-    mbar_wait(tmem_full, 0);
-    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    // ===== epilogue: warps 2..9.  Warp w reads TMEM lane quarter (w % 4) - a hardware rule -
+    // and the two warps of a quarter split the columns in halves. =====
     const int q = warp & 3;
-    const int row = m0 + q * 32 + lane;
-    const uint32_t taddr_row = tmem_base + ((uint32_t)(q * 32) << 16);
-    for (int c0 = 0; c0 < block_n; c0 += 16) {
-      uint32_t r[16];
-      asm volatile(
-          "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
-          : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-            "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
-          : "r"(taddr_row + (uint32_t)c0)
-          : "memory");
-      asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-      const int col = n0 + c0;
-      if (row < M && col < N) {
-        float v[16];
-#pragma unroll
-        for (int j = 0; j < 16; ++j) {
-          v[j] = __uint_as_float(r[j]);
-          if (bias != nullptr && col + j < N) v[j] += __ldg(bias + col + j);
-          if (relu) v[j] = fmaxf(v[j], 0.f);
+    const int half = (warp - 2) >> 2;           // 0: lower column half, 1: upper
+    const int et = threadIdx.x - 64;            // 0..255 within the epilogue group
+    const int ncols_half = ((block_n / 16 + 1) / 2) * 16;
+    const int c_begin = half * ncols_half;
+    const int c_end = (c_begin + ncols_half < block_n) ? c_begin + ncols_half : block_n;
+    float* bias_s = reinterpret_cast<float*>(smem_raw + (bias_smem - raw));
+    uint32_t i = 0;
+    for (int t = blockIdx.x; t < total; t += gridDim.x, ++i) {
+      const int m0 = (t / tiles_n) * BM, n0 = (t % tiles_n) * block_n;
+      const uint32_t buf = i & 1u, aph = (i >> 1) & 1u;
+      // bias slice of this column tile -> shared memory (overlaps the wait for the accumulator)
+      if (TMA_STORE && et == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+      asm volatile("bar.sync 1, %0;" ::"n"(32 * EPI_WARPS) : "memory");  // previous tile's bias / staging are free
+      for (int j = et; j < block_n; j += 32 * EPI_WARPS) bias_s[j] = (bias != nullptr && n0 + j < N) ? __ldg(bias + n0 + j) : 0.f;
+      asm volatile("bar.sync 1, %0;" ::"n"(32 * EPI_WARPS) : "memory");
+      mbar_wait(tfull0 + 8 * buf, aph);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      const int row = m0 + q * 32 + lane;
+      const uint32_t taddr_row = tmem_base + buf * MAX_BN + ((uint32_t)(q * 32) << 16);
+      for (int c0 = c_begin; c0 < c_end; c0 += 32) {
+        // two 16-column loads in flight, one wait
+        uint32_t r[32];
+        const bool second = c0 + 16 < c_end;
+        asm volatile(
+            "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+            : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+              "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+            : "r"(taddr_row + (uint32_t)c0)
+            : "memory");
+        if (second) {
+          asm volatile(
+              "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+              : "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+                "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+              : "r"(taddr_row + (uint32_t)c0 + 16u)
+              : "memory");
         }
-        __nv_bfloat16* o = out + (size_t)row * ldo + col;
-        if (mask != nullptr) {
-          const __nv_bfloat16* mk = mask + (size_t)row * ldo + col;
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 #pragma unroll
-          for (int j = 0; j < 16; ++j)
-            if (col + j < N && !(__bfloat162float(mk[j]) > 0.f)) v[j] = 0.f;
-        }
-        if (col + 16 <= N && (((size_t)row * ldo + col) & 7) == 0) {
+        for (int h = 0; h < 2; ++h) {
+          if (h == 1 && !second) break;
+          const int cc = c0 + 16 * h;
+          const int col = n0 + cc;
+          float v[16];
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            v[j] = __uint_as_float(r[16 * h + j]) + bias_s[cc + j];
+            if (relu) v[j] = fmaxf(v[j], 0.f);
+          }
+          if (mask != nullptr && row < M) {
+            const __nv_bfloat16* mk = mask + (size_t)row * ldo + col;
+#pragma unroll
+            for (int j = 0; j < 16; ++j)
+              if (col + j < N && !(__bfloat162float(mk[j]) > 0.f)) v[j] = 0.f;
+          }
           uint4 p0, p1;
           p0.x = pdj_f2_to_bf2(v[0], v[1]); p0.y = pdj_f2_to_bf2(v[2], v[3]);
           p0.z = pdj_f2_to_bf2(v[4], v[5]); p0.w = pdj_f2_to_bf2(v[6], v[7]);
           p1.x = pdj_f2_to_bf2(v[8], v[9]); p1.y = pdj_f2_to_bf2(v[10], v[11]);
           p1.z = pdj_f2_to_bf2(v[12], v[13]); p1.w = pdj_f2_to_bf2(v[14], v[15]);
-          reinterpret_cast<uint4*>(o)[0] = p0;
-          reinterpret_cast<uint4*>(o)[1] = p1;
-        } else {
+          if (TMA_STORE) {
+            const uint32_t dst = stage_out + (uint32_t)((q * 32 + lane) * block_n + cc) * 2;
+            asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(dst), "r"(p0.x), "r"(p0.y), "r"(p0.z), "r"(p0.w) : "memory");
+            asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(dst + 16), "r"(p1.x), "r"(p1.y), "r"(p1.z), "r"(p1.w) : "memory");
+          } else if (row < M && col < N) {
+            __nv_bfloat16* o = out + (size_t)row * ldo + col;
+            if (col + 16 <= N && (((size_t)row * ldo + col) & 7) == 0) {
+              reinterpret_cast<uint4*>(o)[0] = p0;
+              reinterpret_cast<uint4*>(o)[1] = p1;
+            } else {
 #pragma unroll
-          for (int j = 0; j < 16; ++j)
-            if (col + j < N) o[j] = __float2bfloat16(v[j]);
+              for (int j = 0; j < 16; ++j)
+                if (col + j < N) o[j] = __float2bfloat16(v[j]);
+            }
+          }
+        }
+      }
+      // this accumulator buffer may be overwritten by the MMA warp now
+      asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tempty0 + 8 * buf);
+      if (TMA_STORE) {
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy writes -> visible to the TMA engine
+        asm volatile("bar.sync 1, %0;" ::"n"(32 * EPI_WARPS) : "memory");
+        if (et == 0) {
+          tma_store_2d(&tma_o, stage_out, n0, m0);  // rows / columns beyond M, N are clipped by the tensor map
+          asm volatile("cp.async.bulk.commit_group;" ::: "memory");
         }
       }
     }
+    if (TMA_STORE && et == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
@@ -218,7 +301,7 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 EncodeTiledFn g_encode = nullptr;
 
-int make_map(CUtensorMap* map, const void* ptr, int rows, int cols, int ld_elems, int box_rows) {
+int make_map(CUtensorMap* map, const void* ptr, int rows, int cols, int ld_elems, int box_cols, int box_rows, bool swizzle) {
   if (g_encode == nullptr) {
     void* p = nullptr;
     cudaDriverEntryPointQueryResult q;
@@ -231,20 +314,21 @@ int make_map(CUtensorMap* map, const void* ptr, int rows, int cols, int ld_elems
   }
   const cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};       // innermost first
   const cuuint64_t strides[1] = {(cuuint64_t)ld_elems * 2};              // bytes, for dim 1
-  const cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)box_rows};
+  const cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
   const cuuint32_t estr[2] = {1, 1};
   CUresult r = g_encode(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
-                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE,
+                        CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
-    pdj_set_error("cuTensorMapEncodeTiled failed with CUresult %d (rows=%d cols=%d ld=%d box_rows=%d ptr=%p)", (int)r, rows,
-                  cols, ld_elems, box_rows, ptr);
+    pdj_set_error("cuTensorMapEncodeTiled failed with CUresult %d (rows=%d cols=%d ld=%d box=%dx%d ptr=%p)", (int)r, rows, cols,
+                  ld_elems, box_rows, box_cols, ptr);
     return (int)r;
   }
   return 0;
 }
 
 bool g_attr_set = false;
+int g_sms = 0;
 
 }  // namespace
 
@@ -267,16 +351,47 @@ int pdj_linear_bf16(const void* a, const void* b, void* out, const float* bias, 
     return -1;
   }
   const int bn = pdj_linear_block_n(N);
-  CUtensorMap ma, mb;
-  if (int r = make_map(&ma, a, M, K, lda, BM)) return r;
-  if (int r = make_map(&mb, b, N, K, ldb, bn)) return r;
+  // TMA store needs a 16-byte aligned output pitch; otherwise the epilogue stores directly.
+  // Measured on B200 (profiles/gemm_bench.py): staging + TMA store wins for narrow outputs (it frees
+  // the epilogue warps early), direct 32-byte stores win once the tile is 256 wide, where the staging
+  // buffer would cost a pipeline stage.  PDJ_GEMM_DIRECT_STORE / PDJ_GEMM_TMA_STORE override.
+  static const bool force_direct = getenv("PDJ_GEMM_DIRECT_STORE") != nullptr;
+  static const bool force_tma = getenv("PDJ_GEMM_TMA_STORE") != nullptr;
+  const bool tma_ok = (ldo % 8 == 0) && (((uintptr_t)out & 15) == 0);
+  const bool tma_store = tma_ok && !force_direct && (force_tma || bn < MAX_BN);
+  CUtensorMap ma, mb, mo;
+  if (int r = make_map(&ma, a, M, K, lda, BK, BM, true)) return r;
+  if (int r = make_map(&mb, b, N, K, ldb, BK, bn, true)) return r;
+  if (tma_store) {
+    if (int r = make_map(&mo, out, M, N, ldo, bn, BM, false)) return r;
+  } else {
+    mo = ma;
+  }
   if (!g_attr_set) {
-    PDJ_CUDA_CHECK(cudaFuncSetAttribute(linear_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    PDJ_CUDA_CHECK(cudaFuncSetAttribute(linear_tcgen05_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+    PDJ_CUDA_CHECK(cudaFuncSetAttribute(linear_tcgen05_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+    int dev = 0;
+    PDJ_CUDA_CHECK(cudaGetDevice(&dev));
+    PDJ_CUDA_CHECK(cudaDeviceGetAttribute(&g_sms, cudaDevAttrMultiProcessorCount, dev));
     g_attr_set = true;
   }
-  dim3 grid((M + BM - 1) / BM, (N + bn - 1) / bn);
-  linear_tcgen05_kernel<<<grid, THREADS, SMEM_BYTES, st>>>(ma, mb, (__nv_bfloat16*)out, bias, (const __nv_bfloat16*)mask, M,
-                                                            N, K, ldo, bn, relu);
+  const int stage_bytes = A_STAGE_BYTES + bn * BK * 2;
+  const int fixed = 1024 /*alignment*/ + 256 /*barriers*/ + MAX_BN * 4 /*bias slice*/ + (tma_store ? BM * bn * 2 : 0);
+  int stages = (SMEM_LIMIT - fixed) / stage_bytes;
+  if (stages > MAX_STAGES) stages = MAX_STAGES;
+  if (stages < 2) {
+    pdj_set_error("pdj_linear_bf16: tile does not fit in shared memory (block_n=%d)", bn);
+    return -1;
+  }
+  const int smem = fixed + stages * stage_bytes;
+  const int total = ((M + BM - 1) / BM) * ((N + bn - 1) / bn);
+  const int grid = total < g_sms ? total : g_sms;
+  if (tma_store)
+    linear_tcgen05_kernel<true><<<grid, THREADS, smem, st>>>(ma, mb, mo, (__nv_bfloat16*)out, bias, (const __nv_bfloat16*)mask,
+                                                            M, N, K, ldo, bn, stages, relu);
+  else
+    linear_tcgen05_kernel<false><<<grid, THREADS, smem, st>>>(ma, mb, mo, (__nv_bfloat16*)out, bias,
+                                                             (const __nv_bfloat16*)mask, M, N, K, ldo, bn, stages, relu);
   PDJ_CUDA_CHECK(cudaGetLastError());
   return 0;
 }

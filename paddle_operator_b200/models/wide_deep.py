@@ -20,11 +20,18 @@ SPARSE_SLOTS = 26
 
 class WideDeepDense(nn.Module):
     def __init__(self, emb_dim: int = 16, hidden=(400, 400, 400), slots: int = SPARSE_SLOTS,
-                 dense: int = DENSE_FEATURES):
+                 dense: int = DENSE_FEATURES, fused: bool = False):
         super().__init__()
         self.in_dim = slots * emb_dim + dense
         dims = [self.in_dim] + list(hidden)
-        self.layers = nn.ModuleList([nn.Linear(a, b) for a, b in zip(dims[:-1], dims[1:])])
+        if fused:
+            from ..ops.gemm import FusedLinear
+
+            # hidden layers on the tcgen05 kernel with bias + ReLU fused into the epilogue
+            self.layers = nn.ModuleList([FusedLinear(a, b, relu=True) for a, b in zip(dims[:-1], dims[1:])])
+        else:
+            self.layers = nn.ModuleList([nn.Linear(a, b) for a, b in zip(dims[:-1], dims[1:])])
+        self.fused = fused
         self.out = nn.Linear(dims[-1], 1)
         self.wide_dense = nn.Linear(dense, 1)
         for l in list(self.layers) + [self.out, self.wide_dense]:
@@ -35,7 +42,7 @@ class WideDeepDense(nn.Module):
         """deep_emb [B, slots*emb_dim], wide_sum [B] fp32, dense [B, 13] -> logits [B] fp32."""
         x = torch.cat([deep_emb, dense.to(deep_emb.dtype)], dim=1)
         for l in self.layers:
-            x = torch.relu(l(x))
+            x = l(x) if self.fused else torch.relu(l(x))
         deep = self.out(x).squeeze(1).float()
         wide = wide_sum + self.wide_dense(dense.to(self.wide_dense.weight.dtype)).squeeze(1).float()
         return deep + wide

@@ -65,7 +65,7 @@ class WideDeepJob:
                                     lr=sparse_lr, async_sgd=async_sgd, seed=seed, nblocks=emb_blocks or 148)
         self.emb.grad_scale = 1.0 / world
         torch.manual_seed(seed)
-        dense = WideDeepDense(emb_dim).to(self.device).to(torch.bfloat16)
+        dense = WideDeepDense(emb_dim, fused=True).to(self.device).to(torch.bfloat16)
         self.model = _Net(dense, self.emb).train()
         self.ids = torch.zeros((batch, SPARSE_SLOTS), dtype=torch.int64, device=self.device)
         self.dense_x = torch.zeros((batch, DENSE_FEATURES), dtype=torch.float32, device=self.device)
@@ -73,7 +73,9 @@ class WideDeepJob:
         self.trainer = CollectiveTrainer(self.model, _loss_fn, (self.ids, self.dense_x, self.labels),
                                          comm=comm if world > 1 else None, lr=lr, momentum=0.9, weight_decay=0.0,
                                          use_graph=use_graph, bucket_bytes=4 << 20, comm_blocks=8,
-                                         extra_kernels_per_step=3 if async_sgd else 4)
+                                         # embedding kernels + 2 tcgen05 GEMMs (forward, dX) per hidden layer
+                                         extra_kernels_per_step=(3 if async_sgd else 4) + 2 * len(dense.layers))
+        self._attach_bias_masters()
         self._copy_stream = torch.cuda.Stream(self.device)
         self._stage = [(torch.empty_like(self.ids), torch.empty_like(self.dense_x), torch.empty_like(self.labels))
                        for _ in range(2)]
@@ -84,6 +86,13 @@ class WideDeepJob:
         self._slot = 0
         self._loss_host = torch.zeros(64, dtype=torch.float32).pin_memory()
         self._loss_i = 0
+
+    def _attach_bias_masters(self) -> None:
+        from ..ops.gemm import FusedLinear
+
+        for m in self.model.modules():
+            if isinstance(m, FusedLinear) and m.bias is not None:
+                m.bias_f32 = self.trainer.flat.master_view(m.bias)
 
     @staticmethod
     def arena_bytes_needed(rows: int, dim: int, batch: int, world: int) -> int:
