@@ -87,8 +87,8 @@ struct PdjEmbTable {
   size_t gwide_off;
   size_t acc_deep_off;  /* Adagrad accumulators, same shapes */
   size_t acc_wide_off;
-  size_t flag_off;      /* u32 [rows_per_shard]: row already in the touched list */
-  size_t list_off;      /* u32 [list_cap] */
+  size_t flag_off;      /* u8 [rows_per_shard rounded up to 128]: row touched this step */
+  size_t list_off;      /* unused (kept for ABI stability) */
   size_t count_off;     /* u32 [2]: touched rows this step, last step */
   long long rows_per_shard;
   unsigned int list_cap;
@@ -148,6 +148,8 @@ int pdj_sgd_momentum(float* w, float* mom, const void* grad, void* param, size_t
                      const float* hyper, cudaStream_t st);
 int pdj_preprocess_u8(const void* in, void* out, size_t n_px, const float* mean3, const float* std3,
                       cudaStream_t st);
+/* out[c] = sum_r x[r, c] for row-major bf16 x with row pitch ld (the bias gradient of a linear layer). */
+int pdj_colsum_bf16(const void* x, float* out, int M, int N, int ld, cudaStream_t st);
 int pdj_softmax_xent(const void* logits, const int64_t* labels, void* dlogits, float* loss_sum, int rows,
                      int ncls, float grad_scale, cudaStream_t st);
 

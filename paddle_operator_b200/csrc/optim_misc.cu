@@ -118,6 +118,35 @@ softmax_xent_kernel(const __nv_bfloat16* __restrict__ logits, const int64_t* __r
   }
 }
 
+// Column sums of a row-major bf16 matrix: out[c] += sum_r x[r, c] (fp32, caller zeroes out).
+// The bias gradient of a linear layer.  One block takes ROWS rows; a thread owns two columns.
+constexpr int kColsumRows = 128;
+__global__ void __launch_bounds__(256)
+colsum_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ out, int M, int N, int ld) {
+  const int r0 = blockIdx.x * kColsumRows;
+  const int r1 = r0 + kColsumRows < M ? r0 + kColsumRows : M;
+  for (int c = 2 * threadIdx.x; c < N; c += 2 * blockDim.x) {
+    float a = 0.f, b = 0.f;
+    if (c + 1 < N && (ld & 1) == 0) {
+      for (int r = r0; r < r1; ++r) {
+        const uint32_t u = __ldg(reinterpret_cast<const uint32_t*>(x + (size_t)r * ld + c));
+        const float2 f = pdj_bf2_to_f2(u);
+        a += f.x;
+        b += f.y;
+      }
+      atomicAdd(out + c, a);
+      atomicAdd(out + c + 1, b);
+    } else {
+      for (int r = r0; r < r1; ++r) {
+        a += __bfloat162float(x[(size_t)r * ld + c]);
+        if (c + 1 < N) b += __bfloat162float(x[(size_t)r * ld + c + 1]);
+      }
+      atomicAdd(out + c, a);
+      if (c + 1 < N) atomicAdd(out + c + 1, b);
+    }
+  }
+}
+
 int grid_for(size_t n, int per_block) {
   size_t g = (n + per_block - 1) / per_block;
   if (g > 148 * 8) g = 148 * 8;
@@ -146,6 +175,14 @@ int pdj_preprocess_u8(const void* in, void* out, size_t n_px, const float* mean3
   preprocess_kernel<<<grid_for(n_px / 4 + 1, 256 * 4), 256, 0, st>>>((const uint8_t*)in, (__nv_bfloat16*)out, n_px,
                                                                      mean3[0], mean3[1], mean3[2], std3[0], std3[1],
                                                                      std3[2]);
+  PDJ_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+int pdj_colsum_bf16(const void* x, float* out, int M, int N, int ld, cudaStream_t st) {
+  if (M < 1 || N < 1) return 0;
+  PDJ_CUDA_CHECK(cudaMemsetAsync(out, 0, (size_t)N * sizeof(float), st));
+  colsum_kernel<<<(M + kColsumRows - 1) / kColsumRows, 256, 0, st>>>((const __nv_bfloat16*)x, out, M, N, ld);
   PDJ_CUDA_CHECK(cudaGetLastError());
   return 0;
 }

@@ -5,7 +5,10 @@ deep:  concat(emb[id_1..id_26], dense) -> 400 -> 400 -> 400 -> 1   (ReLU)
 logit = wide + deep; loss = binary cross-entropy with logits.
 
 The sparse parameters (w_wide, emb) are a `ShardedEmbedding` (parallel/ps.py);
-this module holds the dense part only.  Reference parity: the workload of
+this module holds the dense part only.  With `fused=True` the hidden tower is
+`ops.mlp.FusedMLP` (tcgen05 fused-linear kernels forward and backward) and the
+concatenated input is zero-padded to a multiple of 8 columns so that every
+operand row is 16-byte aligned for TMA.  Reference parity: the workload of
 deploy/examples/wide_and_deep*.yaml (Paddle's demo-wide-and-deep image); the
 reference contains no model code.
 """
@@ -22,30 +25,47 @@ class WideDeepDense(nn.Module):
     def __init__(self, emb_dim: int = 16, hidden=(400, 400, 400), slots: int = SPARSE_SLOTS,
                  dense: int = DENSE_FEATURES, fused: bool = False):
         super().__init__()
-        self.in_dim = slots * emb_dim + dense
+        self.fused = fused
+        self.raw_in = slots * emb_dim + dense
+        self.in_dim = (self.raw_in + 7) // 8 * 8 if fused else self.raw_in
         dims = [self.in_dim] + list(hidden)
         if fused:
-            from ..ops.gemm import FusedLinear
+            from ..ops.mlp import FusedMLP
 
-            # hidden layers on the tcgen05 kernel with bias + ReLU fused into the epilogue
-            self.layers = nn.ModuleList([FusedLinear(a, b, relu=True) for a, b in zip(dims[:-1], dims[1:])])
+            self.tower = FusedMLP(dims)
         else:
-            self.layers = nn.ModuleList([nn.Linear(a, b) for a, b in zip(dims[:-1], dims[1:])])
-        self.fused = fused
+            self.tower = _TorchMLP(dims)
         self.out = nn.Linear(dims[-1], 1)
         self.wide_dense = nn.Linear(dense, 1)
-        for l in list(self.layers) + [self.out, self.wide_dense]:
+        for l in list(self.tower.layers) + [self.out, self.wide_dense]:
             nn.init.normal_(l.weight, std=1.0 / (l.in_features ** 0.5))
             nn.init.zeros_(l.bias)
 
+    @property
+    def layers(self):
+        return self.tower.layers
+
     def forward(self, deep_emb: torch.Tensor, wide_sum: torch.Tensor, dense: torch.Tensor) -> torch.Tensor:
         """deep_emb [B, slots*emb_dim], wide_sum [B] fp32, dense [B, 13] -> logits [B] fp32."""
-        x = torch.cat([deep_emb, dense.to(deep_emb.dtype)], dim=1)
-        for l in self.layers:
-            x = l(x) if self.fused else torch.relu(l(x))
+        parts = [deep_emb, dense.to(deep_emb.dtype)]
+        if self.in_dim != self.raw_in:
+            parts.append(torch.zeros((deep_emb.shape[0], self.in_dim - self.raw_in), dtype=deep_emb.dtype,
+                                     device=deep_emb.device))
+        x = self.tower(torch.cat(parts, dim=1))
         deep = self.out(x).squeeze(1).float()
         wide = wide_sum + self.wide_dense(dense.to(self.wide_dense.weight.dtype)).squeeze(1).float()
         return deep + wide
+
+
+class _TorchMLP(nn.Module):
+    def __init__(self, dims):
+        super().__init__()
+        self.layers = nn.ModuleList([nn.Linear(a, b) for a, b in zip(dims[:-1], dims[1:])])
+
+    def forward(self, x):
+        for l in self.layers:
+            x = torch.relu(l(x))
+        return x
 
 
 def bce_with_logits(logits: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:

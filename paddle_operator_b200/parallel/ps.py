@@ -60,9 +60,10 @@ class ShardedEmbedding:
         t.gwide_off = a(R * 4)
         t.acc_deep_off = a(R * D * 4)
         t.acc_wide_off = a(R * 4)
-        t.flag_off = a(R * 4)
-        cap = min(R, max_batch * slots * self.nranks)
-        t.list_off = a(cap * 4)
+        self._flag_bytes = (R + 127) // 128 * 128
+        t.flag_off = a(self._flag_bytes)  # one byte per row: "touched this step"
+        cap = 0
+        t.list_off = 0
         t.count_off = a(256)
         t.rows_per_shard, t.list_cap, t.dim, t.has_wide = R, cap, D, int(has_wide)
         self.t = t
@@ -93,7 +94,7 @@ class ShardedEmbedding:
                                                  device=f"cuda:{self.comm.device}") * scale)
             for off, n in ((self.t.gdeep_off, self.rows_per_shard * self.dim), (self.t.gwide_off, self.rows_per_shard),
                            (self.t.acc_deep_off, self.rows_per_shard * self.dim),
-                           (self.t.acc_wide_off, self.rows_per_shard), (self.t.flag_off, self.rows_per_shard),
+                           (self.t.acc_wide_off, self.rows_per_shard), (self.t.flag_off, self._flag_bytes // 4),
                            (self.t.count_off, 64)):
                 self.comm.tensor(off, (n,), torch.float32, r).zero_()
 

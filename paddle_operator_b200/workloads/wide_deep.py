@@ -74,7 +74,8 @@ class WideDeepJob:
                                          comm=comm if world > 1 else None, lr=lr, momentum=0.9, weight_decay=0.0,
                                          use_graph=use_graph, bucket_bytes=4 << 20, comm_blocks=8,
                                          # embedding kernels + 2 tcgen05 GEMMs (forward, dX) per hidden layer
-                                         extra_kernels_per_step=(3 if async_sgd else 4) + 2 * len(dense.layers))
+                                         # embedding kernels + per hidden layer: forward GEMM, dX GEMM, bias colsum
+                                         extra_kernels_per_step=(3 if async_sgd else 4) + 3 * len(dense.layers))
         self._attach_bias_masters()
         self._copy_stream = torch.cuda.Stream(self.device)
         self._stage = [(torch.empty_like(self.ids), torch.empty_like(self.dense_x), torch.empty_like(self.labels))
@@ -88,11 +89,12 @@ class WideDeepJob:
         self._loss_i = 0
 
     def _attach_bias_masters(self) -> None:
-        from ..ops.gemm import FusedLinear
+        """The tcgen05 epilogue adds fp32 biases: point it at the trainer's master copies."""
+        from ..ops.mlp import FusedMLP
 
         for m in self.model.modules():
-            if isinstance(m, FusedLinear) and m.bias is not None:
-                m.bias_f32 = self.trainer.flat.master_view(m.bias)
+            if isinstance(m, FusedMLP):
+                m.bias_f32 = [self.trainer.flat.master_view(l.bias) for l in m.layers]
 
     @staticmethod
     def arena_bytes_needed(rows: int, dim: int, batch: int, world: int) -> int:

@@ -87,7 +87,7 @@ def test_push_update_matches_reference(nranks, opt):
                 # staging rows and flags are clean again
                 for r in range(nranks):
                     assert float(comm.tensor(emb.t.gdeep_off, (emb.rows_per_shard * D,), torch.float32, r).abs().max()) == 0.0
-                    assert int(comm.tensor(emb.t.flag_off, (emb.rows_per_shard,), torch.int32, r).sum()) == 0
+                    assert int(comm.tensor(emb.t.flag_off, (emb._flag_bytes,), torch.uint8, r).sum()) == 0
     finally:
         comm.close()
 

@@ -50,3 +50,33 @@ def test_linear_mask_epilogue_and_autograd():
     torch.testing.assert_close(x.grad.float(), xr.grad, atol=0.15, rtol=3e-2)
     torch.testing.assert_close(lin.weight.grad.float(), ref_lin.weight.grad, atol=0.5, rtol=3e-2)
     torch.testing.assert_close(lin.bias.grad.float(), ref_lin.bias.grad, atol=0.5, rtol=3e-2)
+
+
+def test_fused_mlp_matches_torch():
+    from paddle_operator_b200.ops.mlp import FusedMLP, colsum
+
+    torch.manual_seed(3)
+    x = torch.randn(1000, 400, device="cuda").to(torch.bfloat16)
+    torch.testing.assert_close(colsum(x), x.float().sum(0), atol=0.5, rtol=1e-2)
+    mlp = FusedMLP([432, 400, 400, 400]).cuda().to(torch.bfloat16)
+    ref = [torch.nn.Linear(a, b).cuda().float() for a, b in ((432, 400), (400, 400), (400, 400))]
+    with torch.no_grad():
+        for r, l in zip(ref, mlp.layers):
+            r.weight.copy_(l.weight.float())
+            r.bias.copy_(l.bias.float())
+    xi = (torch.randn(2048, 432, device="cuda") * 0.5).to(torch.bfloat16).requires_grad_(True)
+    xr = xi.detach().float().requires_grad_(True)
+    g = (torch.randn(2048, 400, device="cuda") * 0.1).to(torch.bfloat16)
+    y = mlp(xi)
+    y.backward(g)
+    h = xr
+    for r in ref:
+        h = torch.relu(r(h))
+    h.backward(g.float())
+    torch.testing.assert_close(y.float(), h, atol=0.08, rtol=3e-2)
+    torch.testing.assert_close(xi.grad.float(), xr.grad, atol=0.05, rtol=5e-2)
+    for r, l in zip(ref, mlp.layers):
+        # ReLU gates that sit within bf16 rounding of zero flip between the two paths; each flip moves a
+        # sum over 2048 rows by one gradient element (~0.1), hence the absolute tolerances
+        torch.testing.assert_close(l.weight.grad.float(), r.weight.grad, atol=1.0, rtol=5e-2)
+        torch.testing.assert_close(l.bias.grad.float(), r.bias.grad, atol=1.0, rtol=5e-2)
