@@ -1,0 +1,149 @@
+"""Turns the scratch captures in gpurun_out/ into the committed summaries in profiles/.
+
+  python profiles/summarize.py            # reads gpurun_out/*.ncu-rep, gpurun_out/launches*.csv
+
+* <name>.ncu.md      key metrics of every kernel instance in an `ncu --set full` report
+* <name>.launches.md per-kernel totals of an `ncu --metrics gpu__time_duration.sum,...` launch list
+* sass_evidence.txt  counts of the SASS mnemonics that prove tcgen05 / TMA / multimem code paths
+"""
+import collections
+import csv
+import io
+import os
+import re
+import subprocess
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+OUT = os.path.join(ROOT, "profiles")
+SCRATCH = os.path.join(ROOT, "gpurun_out")
+
+METRICS = [
+    ("gpu__time_duration.sum", "time"),
+    ("dram__bytes_read.sum", "dram rd"),
+    ("dram__bytes_write.sum", "dram wr"),
+    ("gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "dram %peak"),
+    ("sm__throughput.avg.pct_of_peak_sustained_elapsed", "sm %peak"),
+    ("sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active", "tensor %"),
+    ("sm__inst_executed_pipe_tensor.sum", "tensor inst"),
+    ("sm__warps_active.avg.pct_of_peak_sustained_active", "warps act %"),
+    ("launch__registers_per_thread", "regs"),
+    ("launch__grid_size", "grid"),
+    ("launch__block_size", "block"),
+    ("launch__shared_mem_per_block_dynamic", "dyn smem"),
+    ("lts__t_sector_hit_rate.pct", "L2 hit %"),
+]
+
+
+def short(name: str) -> str:
+    name = name.replace("void ", "").replace("<unnamed>::", "").replace("(anonymous namespace)::", "")
+    return re.sub(r"\(.*", "", name)[:70]
+
+
+def ncu_raw(rep: str):
+    r = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True)
+    rows = list(csv.reader(io.StringIO(r.stdout)))
+    if len(rows) < 3:
+        return None, None, []
+    return rows[0], rows[1], rows[2:]
+
+
+def summarize_rep(rep: str, title: str) -> None:
+    hdr, units, rows = ncu_raw(rep)
+    if hdr is None:
+        return
+    name = os.path.splitext(os.path.basename(rep))[0]
+    cols = [(hdr.index(m), lab, units[hdr.index(m)]) for m, lab in METRICS if m in hdr]
+    ki = hdr.index("Kernel Name")
+    with open(os.path.join(OUT, name + ".ncu.md"), "w") as f:
+        f.write(f"# {title}\n\nSource: `ncu --set full --clock-control none --import-source on` on a B200 "
+                f"(report `{os.path.basename(rep)}`, kept in scratch).  One row per profiled kernel instance.\n\n")
+        f.write("| kernel | " + " | ".join(f"{lab} [{u}]" if u else lab for _, lab, u in cols) + " |\n")
+        f.write("|---|" + "---|" * len(cols) + "\n")
+        for row in rows:
+            f.write("| `" + short(row[ki]) + "` | " + " | ".join(row[i] for i, _, _ in cols) + " |\n")
+
+
+def summarize_launches(path: str, title: str) -> None:
+    with open(path) as f:
+        lines = [l for l in f if not l.startswith("==")]
+    agg = collections.defaultdict(lambda: [0, 0.0, 0.0, 0.0])
+    for row in csv.DictReader(lines):
+        v = float(row["Metric Value"].replace(",", ""))
+        a = agg[short(row["Kernel Name"])]
+        m = row["Metric Name"]
+        if m == "gpu__time_duration.sum":
+            a[0] += 1
+            a[1] += v
+        elif m == "dram__bytes_read.sum":
+            a[2] += v
+        elif m == "dram__bytes_write.sum":
+            a[3] += v
+    tot = sum(a[1] for a in agg.values()) or 1.0
+    name = os.path.splitext(os.path.basename(path))[0]
+    ours = ("bn_", "maxpool", "sgd_momentum", "softmax_xent", "preprocess", "emb_", "linear_tcgen05", "colsum",
+            "allreduce", "alltoall", "broadcast", "barrier_kernel")
+    with open(os.path.join(OUT, name + ".launches.md"), "w") as f:
+        f.write(f"# {title}\n\nEvery kernel of one training step, serialised under ncu (cold caches: compare shares, "
+                f"not absolutes).  `*` = hand-written kernel of this repository.\n\n")
+        f.write(f"Total: {tot / 1e6:.3f} ms over {sum(a[0] for a in agg.values())} launches; hand-written kernels: "
+                f"{sum(a[1] for k, a in agg.items() if k.startswith(ours)) / tot * 100:.1f}% of the time, "
+                f"{sum(a[0] for k, a in agg.items() if k.startswith(ours))} launches.\n\n")
+        f.write("| share | launches | time [us] | dram read [MB] | dram write [MB] | kernel |\n|---|---|---|---|---|---|\n")
+        for k, a in sorted(agg.items(), key=lambda kv: -kv[1][1])[:40]:
+            star = "*" if k.startswith(ours) else ""
+            f.write(f"| {a[1] / tot * 100:.1f}% | {a[0]} | {a[1] / 1e3:.1f} | {a[2] / 1e6:.1f} | {a[3] / 1e6:.1f} | `{k}`{star} |\n")
+
+
+def sass_evidence() -> None:
+    lib = os.path.join(ROOT, "paddle_operator_b200", "lib", "libpdjob_b200.so")
+    if not os.path.exists(lib):
+        return
+    sass = subprocess.run(["cuobjdump", "-sass", lib], capture_output=True, text=True).stdout
+    cur, per = None, collections.defaultdict(collections.Counter)
+    pat = re.compile(r"\b(UTCHMMA|UTCQMMA|UTMALDG\.2D|UTMASTG\.2D|UBLKCP\S*|LDTM\S*|STTM\S*|UTCBAR\S*|UTCATOMSWS\S*|SYNCS\.\S+|"
+                     r"HMMA\S*|RED\.E\S*|REDG\S*|ATOMG\S*|LDG\.E\.128\S*|MULTIMEM\S*|ST\.E\.\S*SYS\S*|LD\.E\.\S*SYS\S*)")
+    for line in sass.splitlines():
+        m = re.search(r"Function : (\S+)", line)
+        if m:
+            cur = m.group(1)
+            continue
+        if cur:
+            for mm in pat.findall(line):
+                per[cur][mm.split(" ")[0]] += 1
+    ptx = subprocess.run(["cuobjdump", "-ptx", lib], capture_output=True, text=True).stdout
+    with open(os.path.join(OUT, "sass_evidence.txt"), "w") as f:
+        f.write("SASS mnemonic counts per kernel of libpdjob_b200.so (cuobjdump -sass, sm_100a).\n"
+                "UTCHMMA = tcgen05.mma, LDTM = tcgen05.ld, UTMALDG/UTMASTG = TMA tensor load/store, UTCBAR = tcgen05.commit,\n"
+                "SYNCS = mbarrier, RED/ATOM = peer reductions; multimem.* appears in SASS as *.MULTIMEM / MMLS forms.\n\n")
+        for fn, cnt in sorted(per.items()):
+            if not cnt:
+                continue
+            dem = subprocess.run(["c++filt", fn], capture_output=True, text=True).stdout.strip()
+            f.write(f"{short(dem)}\n    " + "  ".join(f"{k}={v}" for k, v in sorted(cnt.items())) + "\n")
+        f.write("\nPTX instruction families present (cuobjdump -ptx | grep -c):\n")
+        for key in ("tcgen05.mma", "tcgen05.ld", "tcgen05.alloc", "tcgen05.commit", "cp.async.bulk.tensor", "mbarrier.",
+                    "multimem.ld_reduce", "multimem.st", "red.relaxed.sys", "st.release.sys", "ld.acquire.sys"):
+            f.write(f"  {key:24s} {ptx.count(key)}\n")
+
+
+def main() -> int:
+    reps = {"prof_bn": "Fused BatchNorm kernels (ResNet-50 step, batch 256)",
+            "prof_gemm": "tcgen05 + TMA fused linear kernel (profiles/gemm_bench.py shapes)",
+            "prof_emb": "Sharded-embedding kernels and bias colsum (Wide&Deep step, batch 32768, 16.7 M rows)"}
+    for n, t in reps.items():
+        p = os.path.join(SCRATCH, n + ".ncu-rep")
+        if os.path.exists(p):
+            summarize_rep(p, t)
+    lists = {"launches2": "ResNet-50 step launch list (batch 256, one B200)",
+             "launches_wd2": "Wide&Deep step launch list (batch 32768, one B200)"}
+    for n, t in lists.items():
+        p = os.path.join(SCRATCH, n + ".csv")
+        if os.path.exists(p):
+            summarize_launches(p, t)
+    sass_evidence()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())
