@@ -21,6 +21,8 @@
 //
 // Everything is addressed by arena offsets so the same arguments are valid on
 // every rank; the single-GPU emulation runs all ranks in one cooperative launch.
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "../../include/pdjob_b200.h"
 
@@ -96,6 +98,112 @@ emb_lookup_kernel(PdjComm c, PdjEmbTable t, size_t ids_off, size_t out_deep_off,
       for (int o = 16; o > 0; o >>= 1) wide += __shfl_xor_sync(0xffffffffu, wide, o);
       if (lane == 0) out_wide[b] = wide;
     }
+  }
+  if (do_barrier && threadIdx.x == 0) me->epoch[pdj_slot(c)] = e + 1;
+}
+
+// TMA-fed lookup.  One warp per sample, double buffered: lane s asks the TMA engine for row
+// id[b, s] with one bulk copy (cp.async.bulk, 16-byte granularity, completion counted on an
+// mbarrier) straight from the owner GPU's HBM into this warp's shared-memory tile, for sample
+// b + stride while sample b is being converted.  26 x 64 B rows per sample and two samples per
+// warp are in flight without holding a single register, which is what a latency-bound gather
+// over NVLink (~2 us per access) needs.  SASS: UBLKCP + SYNCS.
+__device__ __forceinline__ uint32_t emb_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__global__ void __launch_bounds__(256)
+emb_lookup_tma_kernel(PdjComm c, PdjEmbTable t, size_t ids_off, size_t out_deep_off, size_t out_wide_off, int B, int S,
+                      int do_barrier) {
+  extern __shared__ __align__(128) uint8_t emb_sm[];
+  __shared__ __align__(8) uint64_t bars[8][2];
+  const int rank = c.rank + blockIdx.y;
+  const int NR = c.nranks;
+  PdjSignalPad* me = pdj_pad(c, rank);
+  const uint32_t e = me->epoch[pdj_slot(c)];
+  const int D = t.dim;
+  const uint32_t row_bytes = (uint32_t)D * 4u;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const uint32_t tile = emb_smem_u32(emb_sm) + (uint32_t)w * 2u * 32u * row_bytes;  // [2][32][row_bytes]
+  const uint32_t bar0 = emb_smem_u32(&bars[w][0]), bar1 = emb_smem_u32(&bars[w][1]);
+  if (lane == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar0));
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar1));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncwarp();
+  if (do_barrier) pdj_block_barrier(c, rank, e + 1);  // owners finished applying the previous step
+  const long long* ids = reinterpret_cast<const long long*>(c.base[rank] + ids_off);
+  __nv_bfloat16* out_deep = reinterpret_cast<__nv_bfloat16*>(c.base[rank] + out_deep_off);
+  float* out_wide = reinterpret_cast<float*>(c.base[rank] + out_wide_off);
+  const int warps = gridDim.x * 8;
+
+  auto issue = [&](int b, int buf) -> float {
+    const uint32_t bar = buf ? bar1 : bar0;
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // earlier generic reads of this buffer are done
+    if (lane == 0)
+      asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"((uint32_t)S * row_bytes) : "memory");
+    __syncwarp();
+    float wv = 0.f;
+    if (lane < S) {
+      const long long id = ids[(size_t)b * S + lane];
+      const int owner = (int)(id % NR);
+      const long long row = id / NR;
+      const char* src = c.base[owner] + t.deep_off + (size_t)row * row_bytes;
+      const uint32_t dst = tile + ((uint32_t)buf * 32u + (uint32_t)lane) * row_bytes;
+      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+                   "l"(src), "r"(row_bytes), "r"(bar)
+                   : "memory");
+      if (t.has_wide) wv = ld_f1(c.base[owner] + t.wide_off + (size_t)row * 4);
+    }
+    return wv;
+  };
+
+  uint32_t phase0 = 0, phase1 = 0;
+  int b = blockIdx.x * 8 + w;
+  int buf = 0;
+  float wv_cur = 0.f;
+  if (b < B) wv_cur = issue(b, 0);
+  for (; b < B; b += warps) {
+    const int nb = b + warps;
+    float wv_next = 0.f;
+    if (nb < B) wv_next = issue(nb, buf ^ 1);
+    {
+      const uint32_t bar = buf ? bar1 : bar0;
+      const uint32_t ph = buf ? phase1 : phase0;
+      asm volatile(
+          "{\n\t"
+          ".reg .pred p;\n\t"
+          "EW_%=:\n\t"
+          "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+          "@p bra ED_%=;\n\t"
+          "bra EW_%=;\n\t"
+          "ED_%=:\n\t"
+          "}" ::"r"(bar),
+          "r"(ph)
+          : "memory");
+      if (buf) phase1 ^= 1u; else phase0 ^= 1u;
+    }
+    if (lane < S) {
+      const uint32_t src = tile + ((uint32_t)buf * 32u + (uint32_t)lane) * row_bytes;
+      __nv_bfloat16* o = out_deep + ((size_t)b * S + lane) * D;
+      for (int k = 0; k < D; k += 8) {
+        float4 v0, v1;
+        asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v0.x), "=f"(v0.y), "=f"(v0.z), "=f"(v0.w) : "r"(src + k * 4));
+        asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v1.x), "=f"(v1.y), "=f"(v1.z), "=f"(v1.w) : "r"(src + k * 4 + 16));
+        uint4 p;
+        p.x = pdj_f2_to_bf2(v0.x, v0.y); p.y = pdj_f2_to_bf2(v0.z, v0.w);
+        p.z = pdj_f2_to_bf2(v1.x, v1.y); p.w = pdj_f2_to_bf2(v1.z, v1.w);
+        *reinterpret_cast<uint4*>(o + k) = p;
+      }
+    }
+    if (t.has_wide) {
+      float wide = wv_cur;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) wide += __shfl_xor_sync(0xffffffffu, wide, o);
+      if (lane == 0) out_wide[b] = wide;
+    }
+    __syncwarp();
+    wv_cur = wv_next;
+    buf ^= 1;
   }
   if (do_barrier && threadIdx.x == 0) me->epoch[pdj_slot(c)] = e + 1;
 }
@@ -247,16 +355,16 @@ int check_table(const PdjEmbTable* t) {
 }
 
 template <typename... Args>
-int launch_emb(void (*kern)(Args...), int nblocks, int nthreads, int emulate, int nranks, cudaStream_t st,
+int launch_emb(void (*kern)(Args...), int nblocks, int nthreads, size_t smem, int emulate, int nranks, cudaStream_t st,
                Args... args) {
   if (nblocks < 1) nblocks = 1;
   if (nblocks > PDJ_CHANNEL_BLOCKS) nblocks = PDJ_CHANNEL_BLOCKS;
   dim3 grid(nblocks, emulate ? nranks : 1);
   if (emulate) {
     void* argv[] = {(void*)&args...};
-    PDJ_CUDA_CHECK(cudaLaunchCooperativeKernel((const void*)kern, grid, dim3(nthreads), argv, 0, st));
+    PDJ_CUDA_CHECK(cudaLaunchCooperativeKernel((const void*)kern, grid, dim3(nthreads), argv, smem, st));
   } else {
-    kern<<<grid, nthreads, 0, st>>>(args...);
+    kern<<<grid, nthreads, smem, st>>>(args...);
     PDJ_CUDA_CHECK(cudaGetLastError());
   }
   return 0;
@@ -269,14 +377,25 @@ extern "C" {
 int pdj_emb_lookup(const PdjComm* c, const PdjEmbTable* t, size_t ids_off, size_t out_deep_off, size_t out_wide_off,
                    int B, int S, int barrier, int nblocks, int emulate, cudaStream_t st) {
   if (check_table(t)) return -1;
-  return launch_emb(emb_lookup_kernel, nblocks, 256, emulate, c->nranks, st, *c, *t, ids_off, out_deep_off,
+  static const bool no_tma = getenv("PDJ_EMB_NO_TMA") != nullptr;
+  if (!no_tma && t->dim >= 8 && t->dim <= 64 && S <= 32) {
+    const size_t smem = (size_t)8 * 2 * 32 * t->dim * 4;
+    static size_t attr_set_for = 0;
+    if (smem > 48 * 1024 && smem > attr_set_for) {
+      PDJ_CUDA_CHECK(cudaFuncSetAttribute(emb_lookup_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      attr_set_for = smem;
+    }
+    return launch_emb(emb_lookup_tma_kernel, nblocks, 256, smem, emulate, c->nranks, st, *c, *t, ids_off, out_deep_off,
+                      out_wide_off, B, S, barrier);
+  }
+  return launch_emb(emb_lookup_kernel, nblocks, 256, (size_t)0, emulate, c->nranks, st, *c, *t, ids_off, out_deep_off,
                     out_wide_off, B, S, barrier);
 }
 
 int pdj_emb_push(const PdjComm* c, const PdjEmbTable* t, size_t ids_off, size_t gdeep_off, size_t gwide_off, int B,
                  int S, int async_sgd, float lr, float grad_scale, int nblocks, int emulate, cudaStream_t st) {
   if (check_table(t)) return -1;
-  return launch_emb(emb_push_kernel, nblocks, 256, emulate, c->nranks, st, *c, *t, ids_off, gdeep_off, gwide_off, B,
+  return launch_emb(emb_push_kernel, nblocks, 256, (size_t)0, emulate, c->nranks, st, *c, *t, ids_off, gdeep_off, gwide_off, B,
                     S, async_sgd ? 1 : 0, lr, grad_scale);
 }
 

@@ -16,7 +16,7 @@ def _mk(nranks, rows=4096, dim=16, batch=96, slots=26, **kw):
 
 
 @pytest.mark.parametrize("nranks", [1, 2, 8])
-@pytest.mark.parametrize("dim", [8, 16, 64])
+@pytest.mark.parametrize("dim", [4, 8, 16, 64])
 def test_lookup_matches_reference(nranks, dim):
     from paddle_operator_b200.parallel.ps import embedding_reference
 
