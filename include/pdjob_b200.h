@@ -123,6 +123,14 @@ int pdj_bn_fwd(const void* x, const void* res, void* y, int M, int C, const floa
 int pdj_bn_bwd(const void* dy, const void* y, const void* x, void* dx, void* dres, int M, int C,
                const float* gamma, const float* mean_rstd, float* dgamma_dbeta, void* dgb_bf16, float* coef,
                int relu, void* workspace, cudaStream_t st);
+/* Variants with a 1-bit ReLU gate: forward also writes one byte per 8 elements (bit j = y_j > 0), backward
+ * reads that instead of y - 1/16 of the bytes on the two backward passes. */
+int pdj_bn_fwd_gate(const void* x, const void* res, void* y, void* gate, int M, int C, const float* gamma,
+                    const float* beta, float eps, float momentum, float* running_mean, float* running_var,
+                    float* mean_rstd, float* scale_shift, int relu, void* workspace, cudaStream_t st);
+int pdj_bn_bwd_gate(const void* dy, const void* y, const void* gate, const void* x, void* dx, void* dres, int M, int C,
+                    const float* gamma, const float* mean_rstd, float* dgamma_dbeta, void* dgb_bf16, float* coef,
+                    int relu, void* workspace, cudaStream_t st);
 /* No counterpart in the reference (it has no device code and no allocator
  * story).  Same result as pdj_bn_fwd, but takes no workspace and allocates
  * nothing: its block partials and tickets live in a file-scope device array of

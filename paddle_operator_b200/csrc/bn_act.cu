@@ -179,7 +179,10 @@ bn_stats_kernel(const __nv_bfloat16* __restrict__ x, int M, int C, const float* 
 template <bool RELU, bool RES>
 __global__ void __launch_bounds__(kThreads)
 bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ res,
-                __nv_bfloat16* __restrict__ y, size_t n_vec, int C, const float* __restrict__ scale_shift) {
+                __nv_bfloat16* __restrict__ y, size_t n_vec, int C, const float* __restrict__ scale_shift,
+                uint8_t* __restrict__ gate) {
+  // gate (optional, RELU only): one byte per 8-element vector, bit j = (y_j > 0).  The backward
+  // kernels read it instead of y: 1/16 of the bytes.
   const int c8 = C >> 3;
   const int cv = threadIdx.x % c8;  // 256 % c8 == 0 and the grid stride is a multiple of 256
   float sc[8], sh[8];
@@ -209,6 +212,16 @@ bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __rest
     }
     yv[i] = pack8(f);
     yv[i + stride] = pack8(g);
+    if (RELU && gate != nullptr) {
+      uint32_t b0 = 0, b1 = 0;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        b0 |= (f[j] > 0.f ? 1u : 0u) << j;
+        b1 |= (g[j] > 0.f ? 1u : 0u) << j;
+      }
+      gate[i] = (uint8_t)b0;
+      gate[i + stride] = (uint8_t)b1;
+    }
   }
   if (i < n_vec) {
     float f[8], p[8];
@@ -221,6 +234,12 @@ bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __rest
       if (RELU) f[j] = fmaxf(f[j], 0.f);
     }
     yv[i] = pack8(f);
+    if (RELU && gate != nullptr) {
+      uint32_t b0 = 0;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) b0 |= (f[j] > 0.f ? 1u : 0u) << j;
+      gate[i] = (uint8_t)b0;
+    }
   }
 }
 
@@ -235,7 +254,7 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
                      const float* __restrict__ mean_rstd, float* __restrict__ dgamma_dbeta /*[2][C] fp32*/,
                      __nv_bfloat16* __restrict__ dgb_bf16 /*[2][C] or null*/,
                      float* __restrict__ coef /*[3][C]*/, float* __restrict__ partial,
-                     unsigned int* __restrict__ counter, int cvt_max) {
+                     unsigned int* __restrict__ counter, int cvt_max, const uint8_t* __restrict__ gate) {
   const Tile t = make_tile(C, cvt_max);
   float mu[8], rs[8], acc[16];
 #pragma unroll
@@ -246,6 +265,7 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
     acc[8 + j] = 0.f;
   }
   const size_t row_bytes = (size_t)C * 2;
+  const int c8g = C >> 3;
   const size_t coff = (size_t)t.cv * 16;
   const char* dyp = reinterpret_cast<const char*>(dy) + coff;
   const char* yp = reinterpret_cast<const char*>(y) + coff;
@@ -258,10 +278,26 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
     const size_t o0 = (size_t)r * row_bytes, o1 = (size_t)(r + rstep) * row_bytes;
     const uint4 ud0 = ldg16(dyp + o0), ux0 = ldg16(xp + o0), ud1 = ldg16(dyp + o1), ux1 = ldg16(xp + o1);
     uint4 uy0, uy1;
-    if (RELU) { uy0 = ldg16(yp + o0); uy1 = ldg16(yp + o1); }
+    uint32_t gb0 = 0, gb1 = 0;
+    if (RELU) {
+      if (gate != nullptr) {
+        gb0 = __ldg(gate + (size_t)r * c8g + t.cv);
+        gb1 = __ldg(gate + (size_t)(r + rstep) * c8g + t.cv);
+      } else {
+        uy0 = ldg16(yp + o0);
+        uy1 = ldg16(yp + o1);
+      }
+    }
     float d[8], xx[8], yy[8];
     unpack8(ud0, d); unpack8(ux0, xx);
-    if (RELU) unpack8(uy0, yy);
+    if (RELU) {
+      if (gate != nullptr) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) yy[j] = (float)((gb0 >> j) & 1u);
+      } else {
+        unpack8(uy0, yy);
+      }
+    }
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       const float dz = RELU ? (yy[j] > 0.f ? d[j] : 0.f) : d[j];
@@ -269,7 +305,14 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
       acc[8 + j] = fmaf(dz, xx[j] - mu[j], acc[8 + j]);
     }
     unpack8(ud1, d); unpack8(ux1, xx);
-    if (RELU) unpack8(uy1, yy);
+    if (RELU) {
+      if (gate != nullptr) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) yy[j] = (float)((gb1 >> j) & 1u);
+      } else {
+        unpack8(uy1, yy);
+      }
+    }
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       const float dz = RELU ? (yy[j] > 0.f ? d[j] : 0.f) : d[j];
@@ -281,11 +324,22 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
     const size_t o = (size_t)r * row_bytes;
     const uint4 ud = ldg16(dyp + o), ux = ldg16(xp + o);
     uint4 uy;
-    if (RELU) uy = ldg16(yp + o);
+    uint32_t gb = 0;
+    if (RELU) {
+      if (gate != nullptr) gb = __ldg(gate + (size_t)r * c8g + t.cv);
+      else uy = ldg16(yp + o);
+    }
     float d[8], xx[8], yy[8];
     unpack8(ud, d);
     unpack8(ux, xx);
-    if (RELU) unpack8(uy, yy);
+    if (RELU) {
+      if (gate != nullptr) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) yy[j] = (float)((gb >> j) & 1u);
+      } else {
+        unpack8(uy, yy);
+      }
+    }
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       const float dz = RELU ? (yy[j] > 0.f ? d[j] : 0.f) : d[j];
@@ -320,7 +374,8 @@ template <bool RELU, bool WRITE_DZ>
 __global__ void __launch_bounds__(kThreads)
 bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ y,
                     const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ dx,
-                    __nv_bfloat16* __restrict__ dres, size_t n_vec, int C, const float* __restrict__ coef) {
+                    __nv_bfloat16* __restrict__ dres, size_t n_vec, int C, const float* __restrict__ coef,
+                    const uint8_t* __restrict__ gate) {
   const int c8 = C >> 3;
   const int cv = threadIdx.x % c8;
   float A[8], B[8], Cc[8];
@@ -339,11 +394,22 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* _
   for (size_t i = (size_t)blockIdx.x * kThreads + threadIdx.x; i < n_vec; i += stride) {
     const uint4 ud = ldg16(dyv + i), ux = ldg16(xv + i);
     uint4 uy;
-    if (RELU) uy = ldg16(yv + i);
+    uint32_t gb = 0;
+    if (RELU) {
+      if (gate != nullptr) gb = __ldg(gate + i);
+      else uy = ldg16(yv + i);
+    }
     float d[8], xx[8], yy[8], o[8];
     unpack8(ud, d);
     unpack8(ux, xx);
-    if (RELU) unpack8(uy, yy);
+    if (RELU) {
+      if (gate != nullptr) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) yy[j] = (float)((gb >> j) & 1u);
+      } else {
+        unpack8(uy, yy);
+      }
+    }
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       if (RELU) d[j] = yy[j] > 0.f ? d[j] : 0.f;
@@ -429,10 +495,22 @@ size_t pdj_bn_workspace_bytes() {
   return (size_t)PDJ_BN_MAX_ROW_BLOCKS * 2 * 2048 * sizeof(float) + 256;
 }
 
+int pdj_bn_fwd_gate(const void* x, const void* res, void* y, void* gate, int M, int C, const float* gamma,
+                    const float* beta, float eps, float momentum, float* running_mean, float* running_var,
+                    float* mean_rstd, float* scale_shift, int relu, void* workspace, cudaStream_t st);
+
 int pdj_bn_fwd(const void* x, const void* res, void* y, int M, int C, const float* gamma, const float* beta,
                float eps, float momentum, float* running_mean, float* running_var, float* mean_rstd,
                float* scale_shift, int relu, void* workspace, cudaStream_t st) {
+  return pdj_bn_fwd_gate(x, res, y, nullptr, M, C, gamma, beta, eps, momentum, running_mean, running_var, mean_rstd,
+                         scale_shift, relu, workspace, st);
+}
+
+int pdj_bn_fwd_gate(const void* x, const void* res, void* y, void* gate, int M, int C, const float* gamma,
+                    const float* beta, float eps, float momentum, float* running_mean, float* running_var,
+                    float* mean_rstd, float* scale_shift, int relu, void* workspace, cudaStream_t st) {
   if (check_shape(M, C)) return -1;
+  uint8_t* gate_out = reinterpret_cast<uint8_t*>(gate);
   float* partial = reinterpret_cast<float*>(reinterpret_cast<char*>(workspace) + 256);
   unsigned int* counter = reinterpret_cast<unsigned int*>(workspace);
   const int c8 = C / 8, cvt = c8 < knob_cvt() ? c8 : knob_cvt();
@@ -445,18 +523,31 @@ int pdj_bn_fwd(const void* x, const void* res, void* y, int M, int C, const floa
   const __nv_bfloat16* xb = (const __nv_bfloat16*)x;
   const __nv_bfloat16* rb = (const __nv_bfloat16*)res;
   __nv_bfloat16* yb = (__nv_bfloat16*)y;
-  if (relu && res) bn_apply_kernel<true, true><<<fg, kThreads, 0, st>>>(xb, rb, yb, n_vec, C, scale_shift);
-  else if (relu) bn_apply_kernel<true, false><<<fg, kThreads, 0, st>>>(xb, rb, yb, n_vec, C, scale_shift);
-  else if (res) bn_apply_kernel<false, true><<<fg, kThreads, 0, st>>>(xb, rb, yb, n_vec, C, scale_shift);
-  else bn_apply_kernel<false, false><<<fg, kThreads, 0, st>>>(xb, rb, yb, n_vec, C, scale_shift);
+  if (relu && res) bn_apply_kernel<true, true><<<fg, kThreads, 0, st>>>(xb, rb, yb, n_vec, C, scale_shift, gate_out);
+  else if (relu) bn_apply_kernel<true, false><<<fg, kThreads, 0, st>>>(xb, rb, yb, n_vec, C, scale_shift, gate_out);
+  else if (res) bn_apply_kernel<false, true><<<fg, kThreads, 0, st>>>(xb, rb, yb, n_vec, C, scale_shift, gate_out);
+  else bn_apply_kernel<false, false><<<fg, kThreads, 0, st>>>(xb, rb, yb, n_vec, C, scale_shift, gate_out);
   PDJ_CUDA_CHECK(cudaGetLastError());
   return 0;
 }
 
+int pdj_bn_bwd_gate(const void* dy, const void* y, const void* gate, const void* x, void* dx, void* dres, int M, int C,
+                    const float* gamma, const float* mean_rstd, float* dgamma_dbeta, void* dgb_bf16, float* coef,
+                    int relu, void* workspace, cudaStream_t st);
+
 int pdj_bn_bwd(const void* dy, const void* y, const void* x, void* dx, void* dres, int M, int C, const float* gamma,
                const float* mean_rstd, float* dgamma_dbeta, void* dgb_bf16, float* coef, int relu,
                void* workspace, cudaStream_t st) {
+  return pdj_bn_bwd_gate(dy, y, nullptr, x, dx, dres, M, C, gamma, mean_rstd, dgamma_dbeta, dgb_bf16, coef, relu,
+                         workspace, st);
+}
+
+// `gate` (from pdj_bn_fwd_gate) replaces y as the source of the ReLU derivative when given.
+int pdj_bn_bwd_gate(const void* dy, const void* y, const void* gate, const void* x, void* dx, void* dres, int M, int C,
+                    const float* gamma, const float* mean_rstd, float* dgamma_dbeta, void* dgb_bf16, float* coef,
+                    int relu, void* workspace, cudaStream_t st) {
   if (check_shape(M, C)) return -1;
+  const uint8_t* gate_in = reinterpret_cast<const uint8_t*>(gate);
   float* partial = reinterpret_cast<float*>(reinterpret_cast<char*>(workspace) + 256);
   unsigned int* counter = reinterpret_cast<unsigned int*>(workspace);
   const int c8 = C / 8, cvt = c8 < knob_cvt() ? c8 : knob_cvt();
@@ -469,27 +560,27 @@ int pdj_bn_bwd(const void* dy, const void* y, const void* x, void* dx, void* dre
   if (knob_bwd_unroll() == 2) {
     if (relu)
       bn_bwd_reduce_kernel<true, 2><<<g, kThreads, 0, st>>>(dyb, yb, xb, M, C, gamma, mean_rstd, dgamma_dbeta, dgb, coef,
-                                                            partial, counter, cm);
+                                                            partial, counter, cm, gate_in);
     else
       bn_bwd_reduce_kernel<false, 2><<<g, kThreads, 0, st>>>(dyb, yb, xb, M, C, gamma, mean_rstd, dgamma_dbeta, dgb,
-                                                             coef, partial, counter, cm);
+                                                             coef, partial, counter, cm, gate_in);
   } else {
     if (relu)
       bn_bwd_reduce_kernel<true, 1><<<g, kThreads, 0, st>>>(dyb, yb, xb, M, C, gamma, mean_rstd, dgamma_dbeta, dgb, coef,
-                                                            partial, counter, cm);
+                                                            partial, counter, cm, gate_in);
     else
       bn_bwd_reduce_kernel<false, 1><<<g, kThreads, 0, st>>>(dyb, yb, xb, M, C, gamma, mean_rstd, dgamma_dbeta, dgb,
-                                                             coef, partial, counter, cm);
+                                                             coef, partial, counter, cm, gate_in);
   }
   PDJ_CUDA_CHECK(cudaGetLastError());
   const size_t n_vec = (size_t)M * c8;
   const int fg = flat_grid(n_vec);
   __nv_bfloat16* dxb = (__nv_bfloat16*)dx;
   __nv_bfloat16* drb = (__nv_bfloat16*)dres;
-  if (relu && dres) bn_bwd_apply_kernel<true, true><<<fg, kThreads, 0, st>>>(dyb, yb, xb, dxb, drb, n_vec, C, coef);
-  else if (relu) bn_bwd_apply_kernel<true, false><<<fg, kThreads, 0, st>>>(dyb, yb, xb, dxb, drb, n_vec, C, coef);
-  else if (dres) bn_bwd_apply_kernel<false, true><<<fg, kThreads, 0, st>>>(dyb, yb, xb, dxb, drb, n_vec, C, coef);
-  else bn_bwd_apply_kernel<false, false><<<fg, kThreads, 0, st>>>(dyb, yb, xb, dxb, drb, n_vec, C, coef);
+  if (relu && dres) bn_bwd_apply_kernel<true, true><<<fg, kThreads, 0, st>>>(dyb, yb, xb, dxb, drb, n_vec, C, coef, gate_in);
+  else if (relu) bn_bwd_apply_kernel<true, false><<<fg, kThreads, 0, st>>>(dyb, yb, xb, dxb, drb, n_vec, C, coef, gate_in);
+  else if (dres) bn_bwd_apply_kernel<false, true><<<fg, kThreads, 0, st>>>(dyb, yb, xb, dxb, drb, n_vec, C, coef, gate_in);
+  else bn_bwd_apply_kernel<false, false><<<fg, kThreads, 0, st>>>(dyb, yb, xb, dxb, drb, n_vec, C, coef, gate_in);
   PDJ_CUDA_CHECK(cudaGetLastError());
   return 0;
 }
@@ -597,6 +688,7 @@ extern "C" int pdj_bn_fwd_noalloc(const void* x, const void* res, void* y, int M
 
   unsigned int* counter = reinterpret_cast<unsigned int*>(scratch);
   float* partial = reinterpret_cast<float*>(reinterpret_cast<char*>(scratch) + kNoAllocCounterBytes);
+  uint8_t* gate_out = nullptr;
   // Tickets must start at zero whatever the previous user of the array did.
   PDJ_CUDA_CHECK(cudaMemsetAsync(counter, 0, kNoAllocCounterBytes, st));
 
@@ -615,10 +707,10 @@ extern "C" int pdj_bn_fwd_noalloc(const void* x, const void* res, void* y, int M
   const __nv_bfloat16* xb = (const __nv_bfloat16*)x;
   const __nv_bfloat16* rb = (const __nv_bfloat16*)res;
   __nv_bfloat16* yb = (__nv_bfloat16*)y;
-  if (relu && res) bn_apply_kernel<true, true><<<(int)fg, kThreads, 0, st>>>(xb, rb, yb, n_vec, C, scale_shift);
-  else if (relu) bn_apply_kernel<true, false><<<(int)fg, kThreads, 0, st>>>(xb, rb, yb, n_vec, C, scale_shift);
-  else if (res) bn_apply_kernel<false, true><<<(int)fg, kThreads, 0, st>>>(xb, rb, yb, n_vec, C, scale_shift);
-  else bn_apply_kernel<false, false><<<(int)fg, kThreads, 0, st>>>(xb, rb, yb, n_vec, C, scale_shift);
+  if (relu && res) bn_apply_kernel<true, true><<<(int)fg, kThreads, 0, st>>>(xb, rb, yb, n_vec, C, scale_shift, gate_out);
+  else if (relu) bn_apply_kernel<true, false><<<(int)fg, kThreads, 0, st>>>(xb, rb, yb, n_vec, C, scale_shift, gate_out);
+  else if (res) bn_apply_kernel<false, true><<<(int)fg, kThreads, 0, st>>>(xb, rb, yb, n_vec, C, scale_shift, gate_out);
+  else bn_apply_kernel<false, false><<<(int)fg, kThreads, 0, st>>>(xb, rb, yb, n_vec, C, scale_shift, gate_out);
   PDJ_CUDA_CHECK(cudaGetLastError());
   return 0;
 }

@@ -65,10 +65,13 @@ class _BnActFn(torch.autograd.Function):
         beta = b32 if b32 is not None else (bias if bias.dtype == torch.float32 else bias.float())
         ws = _workspace(x.device)
         st = torch.cuda.current_stream().cuda_stream
-        _lib.check(lib.pdj_bn_fwd(x.data_ptr(), _lib.ptr(residual), y.data_ptr(), m, c, gamma.data_ptr(),
-                                  beta.data_ptr(), eps, momentum, _lib.ptr(running_mean), _lib.ptr(running_var),
-                                  stats.data_ptr(), stats[2:].data_ptr(), int(relu), ws.data_ptr(), st), "bn_fwd")
-        ctx.save_for_backward(x, y if relu else None, gamma, stats)
+        # ReLU derivative for the backward pass as one bit per element (instead of re-reading y)
+        gate = torch.empty(m * c // 8, dtype=torch.uint8, device=x.device) if relu else None
+        _lib.check(lib.pdj_bn_fwd_gate(x.data_ptr(), _lib.ptr(residual), y.data_ptr(), _lib.ptr(gate), m, c,
+                                       gamma.data_ptr(), beta.data_ptr(), eps, momentum, _lib.ptr(running_mean),
+                                       _lib.ptr(running_var), stats.data_ptr(), stats[2:].data_ptr(), int(relu),
+                                       ws.data_ptr(), st), "bn_fwd")
+        ctx.save_for_backward(x, gate, gamma, stats)
         ctx.relu = relu
         ctx.has_res = residual is not None
         ctx.wdtype = weight.dtype
@@ -77,7 +80,7 @@ class _BnActFn(torch.autograd.Function):
     @staticmethod
     def backward(ctx, dy):
         lib = _lib.load()
-        x, y, gamma, stats = ctx.saved_tensors
+        x, gate, gamma, stats = ctx.saved_tensors
         if not _is_nhwc(dy):
             dy = dy.contiguous(memory_format=torch.channels_last)
         n, c, h, w = x.shape
@@ -89,9 +92,9 @@ class _BnActFn(torch.autograd.Function):
         coef = torch.empty(3, c, dtype=torch.float32, device=x.device)
         ws = _workspace(x.device)
         st = torch.cuda.current_stream().cuda_stream
-        _lib.check(lib.pdj_bn_bwd(dy.data_ptr(), _lib.ptr(y), x.data_ptr(), dx.data_ptr(), _lib.ptr(dres), m, c,
-                                  gamma.data_ptr(), stats.data_ptr(), dgb.data_ptr(), _lib.ptr(dgb16), coef.data_ptr(),
-                                  int(ctx.relu), ws.data_ptr(), st), "bn_bwd")
+        _lib.check(lib.pdj_bn_bwd_gate(dy.data_ptr(), None, _lib.ptr(gate), x.data_ptr(), dx.data_ptr(), _lib.ptr(dres),
+                                       m, c, gamma.data_ptr(), stats.data_ptr(), dgb.data_ptr(), _lib.ptr(dgb16),
+                                       coef.data_ptr(), int(ctx.relu), ws.data_ptr(), st), "bn_bwd")
         if ctx.has_res and not ctx.relu:
             dres = dy  # no activation: the skip branch sees dy unchanged
         if dgb16 is not None:
