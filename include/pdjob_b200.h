@@ -156,6 +156,9 @@ int pdj_sgd_momentum(float* w, float* mom, const void* grad, void* param, size_t
                      const float* hyper, cudaStream_t st);
 int pdj_preprocess_u8(const void* in, void* out, size_t n_px, const float* mean3, const float* std3,
                       cudaStream_t st);
+/* uint8 NHWC image -> normalised bf16 in the stem's space-to-depth layout [N, H/2+3, W/2+3, 16] (border untouched). */
+int pdj_preprocess_u8_s2d(const void* in, void* out, int N, int H, int W, const float* mean3, const float* std3,
+                          cudaStream_t st);
 /* out[c] = sum_r x[r, c] for row-major bf16 x with row pitch ld (the bias gradient of a linear layer). */
 int pdj_colsum_bf16(const void* x, float* out, int M, int N, int ld, cudaStream_t st);
 int pdj_softmax_xent(const void* logits, const int64_t* labels, void* dlogits, float* loss_sum, int rows,

@@ -81,11 +81,38 @@ class Bottleneck(nn.Module):
         return self.bn3(self.conv3(y), identity)
 
 
+def stem_weight_to_s2d(w7: torch.Tensor) -> torch.Tensor:
+    """[O,3,7,7] stem weights -> the [O,16,4,4] weights of the equivalent stride-1 convolution over the
+    space-to-depth input (ops.optim.space_to_depth_reference):
+        W[o, (dy*2+dx)*3 + c, jy, jx] = w7[o, c, 2*jy + dy - 1, 2*jx + dx - 1]   (zero where out of range)."""
+    o = w7.shape[0]
+    w8 = w7.new_zeros((o, 3, 8, 8))
+    w8[:, :, 1:, 1:] = w7                                   # tap k of the 7x7 kernel sits at k + 1
+    w = w8.reshape(o, 3, 4, 2, 4, 2)                          # o c jy dy jx dx
+    w = w.permute(0, 3, 5, 1, 2, 4).reshape(o, 12, 4, 4)      # o (dy dx c) jy jx
+    out = w7.new_zeros((o, 16, 4, 4))
+    out[:, :12] = w
+    return out
+
+
+def stem_s2d_mask(out_channels: int) -> torch.Tensor:
+    """1 where an s2d stem weight corresponds to a real 7x7 tap, 0 for the structural zeros."""
+    return (stem_weight_to_s2d(torch.ones(out_channels, 3, 7, 7)) != 0).float()
+
+
 class ResNet(nn.Module):
-    def __init__(self, layers=(3, 4, 6, 3), num_classes: int = 1000, fused: bool = True, width: int = 64):
+    def __init__(self, layers=(3, 4, 6, 3), num_classes: int = 1000, fused: bool = True, width: int = 64,
+                 s2d_stem: bool = False):
         super().__init__()
         self.fused = fused
-        self.conv1 = nn.Conv2d(3, width, 7, stride=2, padding=3, bias=False)
+        self.s2d_stem = s2d_stem
+        if s2d_stem:
+            # The 7x7 / stride 2 / pad 3 stem as a 4x4 / stride 1 convolution over the space-to-depth
+            # input (16 channels, border baked into the input).  Same function, tensor-core friendly.
+            self.conv1 = nn.Conv2d(16, width, 4, stride=1, padding=0, bias=False)
+            self.register_buffer("stem_mask", stem_s2d_mask(width), persistent=False)
+        else:
+            self.conv1 = nn.Conv2d(3, width, 7, stride=2, padding=3, bias=False)
         self.bn1 = _bn(width, True, fused)
         self.maxpool = FusedMaxPool2d(3, 2, 1) if fused else nn.MaxPool2d(3, stride=2, padding=1)
         blocks = []
@@ -101,8 +128,19 @@ class ResNet(nn.Module):
         for m in self.modules():
             if isinstance(m, nn.Conv2d):
                 nn.init.kaiming_normal_(m.weight, mode="fan_out", nonlinearity="relu")
+        if s2d_stem:
+            w7 = torch.empty(width, 3, 7, 7)
+            nn.init.kaiming_normal_(w7, mode="fan_out", nonlinearity="relu")
+            with torch.no_grad():
+                self.conv1.weight.copy_(stem_weight_to_s2d(w7))
+            # gradients of the structurally-zero taps are dropped so the stem stays a 7x7 convolution
+            self.conv1.weight.register_hook(lambda g: g * self.stem_mask.to(g.dtype))
 
     def forward(self, x):
+        if self.s2d_stem and x.shape[1] == 3:
+            from ..ops.optim import space_to_depth_reference
+
+            x = space_to_depth_reference(x).contiguous(memory_format=torch.channels_last)
         x = self.bn1(self.conv1(x))
         x = self.maxpool(x)
         x = self.blocks(x)
@@ -110,13 +148,13 @@ class ResNet(nn.Module):
         return self.fc(x)
 
 
-def resnet50(num_classes: int = 1000, fused: bool = True) -> ResNet:
-    return ResNet((3, 4, 6, 3), num_classes, fused)
+def resnet50(num_classes: int = 1000, fused: bool = True, s2d_stem: bool = False) -> ResNet:
+    return ResNet((3, 4, 6, 3), num_classes, fused, s2d_stem=s2d_stem)
 
 
-def resnet_tiny(num_classes: int = 16, fused: bool = True) -> ResNet:
+def resnet_tiny(num_classes: int = 16, fused: bool = True, s2d_stem: bool = False) -> ResNet:
     """Two-stage, narrow variant for smoke tests."""
-    return ResNet((1, 1), num_classes, fused, width=16)
+    return ResNet((1, 1), num_classes, fused, width=16, s2d_stem=s2d_stem)
 
 
 def to_training_dtype(model: nn.Module, dtype=torch.bfloat16, bn_fp32: bool = False) -> nn.Module:

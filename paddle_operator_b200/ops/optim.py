@@ -85,3 +85,47 @@ def softmax_cross_entropy(logits: torch.Tensor, labels: torch.Tensor) -> torch.T
     if logits.is_cuda and logits.dtype == torch.bfloat16:
         return _SoftmaxXentFn.apply(logits, labels)
     return torch.nn.functional.cross_entropy(logits.float(), labels)
+
+
+# ---------------------------------------------------------------------------
+# Space-to-depth stem (see models/resnet.py): input layout helpers.
+S2D_CHANNELS = 16
+
+
+def s2d_shape(n: int, h: int, w: int) -> tuple:
+    """NHWC shape of the stem input for an n x h x w x 3 image batch."""
+    return (n, h // 2 + 3, w // 2 + 3, S2D_CHANNELS)
+
+
+def space_to_depth_reference(x_nchw: torch.Tensor) -> torch.Tensor:
+    """Plain-torch definition: [N,3,H,W] -> logical [N,16,H/2+3,W/2+3]; channel (dy*2+dx)*3+c of block
+    (by,bx) is pixel (2by+dy, 2bx+dx) channel c; blocks are offset by 2 (zero border 2 before, 1 after)."""
+    n, c, h, w = x_nchw.shape
+    assert c == 3 and h % 2 == 0 and w % 2 == 0
+    x = x_nchw.reshape(n, 3, h // 2, 2, w // 2, 2)            # n c by dy bx dx
+    x = x.permute(0, 3, 5, 1, 2, 4).reshape(n, 12, h // 2, w // 2)  # (dy dx c) by bx
+    out = x.new_zeros((n, S2D_CHANNELS, h // 2 + 3, w // 2 + 3))
+    out[:, :12, 2:2 + h // 2, 2:2 + w // 2] = x
+    return out
+
+
+def preprocess_u8_s2d(images_u8: torch.Tensor, mean=IMAGENET_MEAN, std=IMAGENET_STD, out=None) -> torch.Tensor:
+    """uint8 [N,H,W,3] -> normalised bf16 stem input, logical [N,16,H/2+3,W/2+3] in channels-last memory.
+    `out`, if given, is a contiguous bf16 [N,H/2+3,W/2+3,16] buffer whose border is already zero."""
+    n, h, w, c = images_u8.shape
+    assert c == 3 and images_u8.dtype == torch.uint8 and images_u8.is_contiguous()
+    if images_u8.is_cuda:
+        if out is None:
+            out = torch.zeros(s2d_shape(n, h, w), dtype=torch.bfloat16, device=images_u8.device)
+        assert out.is_contiguous() and tuple(out.shape) == s2d_shape(n, h, w)
+        m = (ctypes.c_float * 3)(*mean)
+        s = (ctypes.c_float * 3)(*std)
+        _lib.check(_lib.load().pdj_preprocess_u8_s2d(images_u8.data_ptr(), out.data_ptr(), n, h, w, m, s,
+                                                     torch.cuda.current_stream().cuda_stream), "preprocess_u8_s2d")
+        return out.permute(0, 3, 1, 2)
+    x = (images_u8.float() / 255.0 - torch.tensor(mean)) / torch.tensor(std)
+    y = space_to_depth_reference(x.permute(0, 3, 1, 2)).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    if out is not None:
+        out.copy_(y.permute(0, 2, 3, 1))
+        return out.permute(0, 3, 1, 2)
+    return y

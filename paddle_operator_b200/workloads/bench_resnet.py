@@ -161,7 +161,9 @@ def run(args, rank: int, world: int, dev, ClockSampler) -> int:
         "data": "synthetic (random uint8 224x224 images, random labels; random-init weights)",
         "impl": args.impl,
         "config": {
-            "model": "ResNet-50 v1.5, NHWC, SGD momentum 0.9 wd 1e-4, fp32 master weights",
+            "model": "ResNet-50 v1.5, NHWC, SGD momentum 0.9 wd 1e-4, fp32 master weights"
+                     + (" (7x7 stem evaluated as the equivalent 4x4 conv over space-to-depth input)"
+                        if getattr(job, "s2d", False) else ""),
             "global_batch": batch * world,
             "per_gpu_batch": batch,
             "seq_len": None,

@@ -35,11 +35,13 @@ class ResNetJob:
     def __init__(self, batch: int = 256, image: int = 224, num_classes: int = 1000, comm: Optional[Communicator] = None,
                  device: Optional[torch.device] = None, lr: float = 0.1, momentum: float = 0.9,
                  weight_decay: float = 1e-4, use_graph: bool = True, tiny: bool = False, seed: int = 0,
-                 bucket_bytes: int = 16 << 20, comm_blocks: int = 24, algo: Optional[int] = None):
+                 bucket_bytes: int = 16 << 20, comm_blocks: int = 24, algo: Optional[int] = None,
+                 s2d_stem: bool = True):
         self.device = device or torch.device("cuda", torch.cuda.current_device())
         self.batch, self.image = batch, image
         torch.manual_seed(seed)  # identical initial weights on every rank
-        model = (resnet_tiny if tiny else resnet50)(num_classes=num_classes, fused=True)
+        self.s2d = s2d_stem and image % 2 == 0
+        model = (resnet_tiny if tiny else resnet50)(num_classes=num_classes, fused=True, s2d_stem=self.s2d)
         model = to_training_dtype(model.to(self.device), torch.bfloat16)
         model.train()
         self.model = model
@@ -47,7 +49,9 @@ class ResNetJob:
         self.rank = comm.rank if comm else 0
         self.world = comm.nranks if comm else 1
         # static device inputs of the captured step
-        self._x_nhwc = torch.zeros((batch, image, image, 3), dtype=torch.bfloat16, device=self.device)
+        # (space-to-depth stem: [N, image/2+3, image/2+3, 16] with a zero border, see ops/optim.py)
+        in_shape = pdj_optim.s2d_shape(batch, image, image) if self.s2d else (batch, image, image, 3)
+        self._x_nhwc = torch.zeros(in_shape, dtype=torch.bfloat16, device=self.device)
         self.x = self._x_nhwc.permute(0, 3, 1, 2)
         self.y = torch.zeros((batch,), dtype=torch.int64, device=self.device)
         self.trainer = CollectiveTrainer(model, _loss_fn, (self.x, self.y), comm=comm, lr=lr, momentum=momentum,
@@ -76,7 +80,11 @@ class ResNetJob:
     def prepare(self) -> None:
         """Fills the static inputs with noise and captures the step graph."""
         with torch.no_grad():
-            self.x.copy_(torch.randn(self.x.shape, device=self.device).to(torch.bfloat16))
+            if self.s2d:  # noise in the interior only: the border is the convolution's zero padding
+                self._x_nhwc[:, 2:-1, 2:-1, :12].copy_(
+                    torch.randn((self.batch, self.image // 2, self.image // 2, 12), device=self.device).to(torch.bfloat16))
+            else:
+                self.x.copy_(torch.randn(self.x.shape, device=self.device).to(torch.bfloat16))
             self.y.copy_(torch.randint(0, 1000 if self.model.fc.out_features >= 1000 else self.model.fc.out_features,
                                        (self.batch,), device=self.device))
         self.trainer.capture()
@@ -99,7 +107,10 @@ class ResNetJob:
             self._stage_y[s].copy_(labels, non_blocking=True)
             self._copied[s].record(self._copy_stream)
         main.wait_event(self._copied[s])
-        pdj_optim.preprocess_u8_nhwc(self._stage_u8[s], out=self._x_nhwc)
+        if self.s2d:
+            pdj_optim.preprocess_u8_s2d(self._stage_u8[s], out=self._x_nhwc)
+        else:
+            pdj_optim.preprocess_u8_nhwc(self._stage_u8[s], out=self._x_nhwc)
         self.y.copy_(self._stage_y[s])
         self._consumed[s].record(main)
         loss = self.step_device()

@@ -109,7 +109,11 @@ def main() -> int:
         job = ResNetJob(batch=args.batch, image=args.image, comm=None, device=device, tiny=args.tiny,
                         num_classes=16 if args.tiny else 1000, use_graph=True)
         with torch.no_grad():
-            job.x.copy_(torch.randn(job.x.shape, device=device).to(torch.bfloat16))
+            if job.s2d:
+                job._x_nhwc[:, 2:-1, 2:-1, :12].copy_(torch.randn((args.batch, args.image // 2, args.image // 2, 12),
+                                                                  device=device).to(torch.bfloat16))
+            else:
+                job.x.copy_(torch.randn(job.x.shape, device=device).to(torch.bfloat16))
             job.y.copy_(torch.randint(0, 16 if args.tiny else 1000, (args.batch,), device=device))
         # warm cuDNN / allocator once so that later captures are quick
         job.trainer.use_graph = False

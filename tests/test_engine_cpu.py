@@ -47,3 +47,36 @@ def test_state_dict_roundtrip_cpu():
     tr.load_state_dict(sd)
     l2 = float(tr.step())
     assert abs(l1 - l2) < 1e-6
+
+
+def test_space_to_depth_stem_is_the_same_convolution():
+    """7x7/2/pad3 over the image == 4x4/1/pad0 over the space-to-depth input with re-arranged weights."""
+    from paddle_operator_b200.models.resnet import stem_s2d_mask, stem_weight_to_s2d
+    from paddle_operator_b200.ops.optim import preprocess_u8_s2d, space_to_depth_reference
+
+    torch.manual_seed(0)
+    x = torch.randn(2, 3, 32, 48, dtype=torch.float64)
+    w7 = torch.randn(5, 3, 7, 7, dtype=torch.float64)
+    ref = torch.nn.functional.conv2d(x, w7, stride=2, padding=3)
+    got = torch.nn.functional.conv2d(space_to_depth_reference(x), stem_weight_to_s2d(w7))
+    assert got.shape == ref.shape
+    torch.testing.assert_close(got, ref, atol=1e-10, rtol=1e-10)
+    assert int(stem_s2d_mask(5).sum()) == 5 * 3 * 49
+    # the uint8 pre-processing path (CPU branch) produces that layout
+    img = torch.randint(0, 256, (2, 8, 12, 3), dtype=torch.uint8)
+    y = preprocess_u8_s2d(img)
+    assert y.shape == (2, 16, 7, 9) and float(y[:, 12:].abs().max()) == 0.0 and float(y[:, :, :2].abs().max()) == 0.0
+
+
+def test_s2d_model_trains_and_keeps_structural_zeros():
+    torch.manual_seed(0)
+    model = to_training_dtype(resnet_tiny(num_classes=8, fused=True, s2d_stem=True), torch.bfloat16).train()
+    x = torch.randn(4, 3, 32, 32).to(torch.bfloat16)
+    y = torch.randint(0, 8, (4,))
+    tr = CollectiveTrainer(model, _loss, (x, y), lr=0.05, use_graph=False)
+    l0 = float(tr.step())
+    for _ in range(5):
+        l1 = float(tr.step())
+    assert l1 < l0
+    w = model.conv1.weight.float()
+    assert float((w * (1 - model.stem_mask)).abs().max()) == 0.0

@@ -105,6 +105,17 @@ def test_preprocess_u8(dev):
     torch.testing.assert_close(y.permute(0, 2, 3, 1).float(), ref, atol=2e-2, rtol=1e-2)
 
 
+def test_preprocess_u8_s2d(dev):
+    from paddle_operator_b200.ops.optim import IMAGENET_MEAN, IMAGENET_STD, preprocess_u8_s2d, space_to_depth_reference
+
+    x = torch.randint(0, 256, (3, 16, 20, 3), dtype=torch.uint8, device=dev)
+    y = preprocess_u8_s2d(x)
+    norm = (x.float() / 255.0 - torch.tensor(IMAGENET_MEAN, device=dev)) / torch.tensor(IMAGENET_STD, device=dev)
+    ref = space_to_depth_reference(norm.permute(0, 3, 1, 2))
+    assert y.shape == ref.shape == (3, 16, 11, 13)
+    torch.testing.assert_close(y.float(), ref, atol=2e-2, rtol=1e-2)
+
+
 def test_softmax_xent(dev):
     from paddle_operator_b200.ops.optim import softmax_cross_entropy
 
