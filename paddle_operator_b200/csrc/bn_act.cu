@@ -49,6 +49,16 @@ __device__ __forceinline__ uint4 pack8(const float* f) {
   return o;
 }
 __device__ __forceinline__ uint4 ldg16(const void* p) { return __ldg(reinterpret_cast<const uint4*>(p)); }
+// Same load as an ordered (volatile) asm statement: the compiler keeps a batch of these in program
+// order ahead of the arithmetic that consumes them, which is what puts several loads in flight per
+// thread in the reduction kernels (with plain __ldg the loads were sunk next to their uses).
+__device__ __forceinline__ uint4 ldg16_ordered(const void* p) {
+  uint4 v;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "l"(p));
+  return v;
+}
 
 // Block-level reduction of 16 per-thread accumulators over the threads that
 // share a channel-vector, then one partial row per block:
@@ -131,7 +141,7 @@ bn_stats_kernel(const __nv_bfloat16* __restrict__ x, int M, int C, const float* 
   for (; r + (U - 1) * rs < M; r += U * rs) {
     uint4 u[U];
 #pragma unroll
-    for (int k = 0; k < U; ++k) u[k] = ldg16(xp + (size_t)(r + k * rs) * row_bytes);
+    for (int k = 0; k < U; ++k) u[k] = ldg16_ordered(xp + (size_t)(r + k * rs) * row_bytes);
 #pragma unroll
     for (int k = 0; k < U; ++k) {
       float f[8];
@@ -276,7 +286,8 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
   const int rstep = t.row_step;
   for (; U == 2 && r + rstep < M; r += 2 * rstep) {
     const size_t o0 = (size_t)r * row_bytes, o1 = (size_t)(r + rstep) * row_bytes;
-    const uint4 ud0 = ldg16(dyp + o0), ux0 = ldg16(xp + o0), ud1 = ldg16(dyp + o1), ux1 = ldg16(xp + o1);
+    const uint4 ud0 = ldg16_ordered(dyp + o0), ux0 = ldg16_ordered(xp + o0), ud1 = ldg16_ordered(dyp + o1),
+                ux1 = ldg16_ordered(xp + o1);
     uint4 uy0, uy1;
     uint32_t gb0 = 0, gb1 = 0;
     if (RELU) {

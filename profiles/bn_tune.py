@@ -50,10 +50,10 @@ if __name__ == "__main__":
     if len(sys.argv) > 1 and sys.argv[1] == "child":
         child()
     else:
-        for cvt in (4, 8, 16, 32):
-            for bps in (2, 4, 6):
-                for ub in (1, 2):
-                    env = dict(os.environ, PDJ_BN_BLOCKS_PER_SM=str(bps), PDJ_BN_STATS_UNROLL="1", PDJ_BN_BWD_UNROLL=str(ub),
+        for cvt in (4,):
+            for bps in (2, 4):
+                for us, ub in ((1, 1), (2, 1), (4, 1), (2, 2), (4, 2)):
+                    env = dict(os.environ, PDJ_BN_BLOCKS_PER_SM=str(bps), PDJ_BN_STATS_UNROLL=str(us), PDJ_BN_BWD_UNROLL=str(ub),
                                PDJ_BN_MIN_ROWS="4", PDJ_BN_CVT=str(cvt))
                     r = subprocess.run([sys.executable, __file__, "child"], env=env, capture_output=True, text=True)
-                    print(f"cvt={cvt} bps={bps} bwd_unroll={ub}: {r.stdout.strip()[-400:]} {r.stderr.strip()[-200:]}", flush=True)
+                    print(f"cvt={cvt} bps={bps} stats_unroll={us} bwd_unroll={ub}: {r.stdout.strip()[-400:]} {r.stderr.strip()[-200:]}", flush=True)
