@@ -41,7 +41,7 @@ struct PdjComm {
   int nranks;
   int rank;
   int pad_base;  // first barrier slot of this communicator view (channel * PDJ_CHANNEL_BLOCKS)
-  int reserved;
+  int spin_timeout_ms;  // 0 = PDJ_SPIN_TIMEOUT_NS; elastic jobs lower it to detect a lost peer sooner
   char* base[PDJ_MAX_RANKS];
   char* mc_base;  // NVLS multicast mapping of the arena (nullptr when unavailable)
 };
@@ -94,9 +94,11 @@ __device__ __forceinline__ void pdj_block_barrier(const PdjComm& c, int rank, ui
     PdjSignalPad* me = pdj_pad(c, rank);
     const uint32_t* f = &me->flag[slot][t];
     const unsigned long long t0 = pdj_globaltimer();
+    const unsigned long long limit =
+        c.spin_timeout_ms > 0 ? (unsigned long long)c.spin_timeout_ms * 1000000ULL : PDJ_SPIN_TIMEOUT_NS;
     uint32_t spins = 0;
     while ((int32_t)(pdj_ld_acquire_sys(f) - epoch) < 0) {
-      if (((++spins) & 0x3ff) == 0 && pdj_globaltimer() - t0 > PDJ_SPIN_TIMEOUT_NS) {
+      if (((++spins) & 0x3ff) == 0 && pdj_globaltimer() - t0 > limit) {
         me->error = 1u + (uint32_t)t;
         __threadfence_system();
         __trap();

@@ -25,7 +25,7 @@ class PdjComm(ctypes.Structure):
         ("nranks", c_int),
         ("rank", c_int),
         ("pad_base", c_int),
-        ("reserved", c_int),
+        ("spin_timeout_ms", c_int),
         ("base", c_void_p * MAX_RANKS),
         ("mc_base", c_void_p),
     ]

@@ -267,6 +267,8 @@ class Communicator:
         lib = self.lib
         self._comm.nranks = self.nranks
         self._comm.rank = self.rank
+        # how long a device-side barrier waits for a peer before trapping (0 = the 8 s default)
+        self._comm.spin_timeout_ms = int(os.environ.get("PDJ_SPIN_TIMEOUT_MS", "0"))
         self._bases = [lib.pdj_arena_ptr(ctypes.c_void_p(a)) for a in self._arenas]
         for i, b in enumerate(self._bases):
             self._comm.base[i] = b

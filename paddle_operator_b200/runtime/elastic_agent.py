@@ -41,6 +41,7 @@ class Membership:
     root: Optional[str] = None   # member that holds valid state (None: start from the checkpoint / scratch)
     step: Optional[int] = None   # step at which this generation starts (None: taken from the checkpoint)
     fresh: bool = False          # no live predecessor generation: state comes from disk, not from a peer
+    incs: dict = field(default_factory=dict)  # host -> process incarnation the generation was formed with
 
 
 class ElasticAgent:
@@ -163,7 +164,7 @@ class ElasticAgent:
         if self.host not in rec["hosts"] or rec["incs"].get(self.host) != self.inc:
             return None
         return Membership(gen, rec["hosts"].index(self.host), len(rec["hosts"]), list(rec["hosts"]), rec.get("root"),
-                          rec.get("step"), bool(rec.get("fresh")))
+                          rec.get("step"), bool(rec.get("fresh")), dict(rec.get("incs") or {}))
 
     def _generation_alive(self, rec: dict) -> bool:
         incs = self.node_incs()
@@ -228,7 +229,7 @@ class ElasticAgent:
             np, nodes, incs = self.np(), self.nodes(), self.node_incs()
             if len(nodes) >= np > 0:
                 members = nodes[:np]
-                stay = [h for h in m.hosts if h in members]
+                stay = [h for h in m.hosts if h in members and (not m.incs.get(h) or incs.get(h) == m.incs[h])]
                 if not stay:
                     self.leave()
                     return None
@@ -274,6 +275,9 @@ class ElasticAgent:
         np, nodes = self.np(), set(self.nodes())
         if any(h not in nodes for h in m.hosts):
             return True  # a member's lease expired
+        live = self.node_incs()
+        if any(m.incs.get(h) and live.get(h) != m.incs[h] for h in m.hosts):
+            return True  # a member died and was restarted under the same name: it holds no state
         if np < m.world:
             return True
         if np > m.world and len(nodes) >= np:

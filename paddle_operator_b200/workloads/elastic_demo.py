@@ -134,6 +134,56 @@ def run(sizes: list, steps_per_phase: int, dry: bool, batch: int, tiny: bool, gp
     return result
 
 
+def run_failure(n: int, fail_rank: int, fail_step: int, batch: int, tiny: bool, gpus, work_root: str, timeout: float,
+                dry: bool = False, spin_timeout_ms: int = 2000) -> dict:
+    """Fault injection: rank `fail_rank` SIGKILLs itself at `fail_step`.  On GPUs its peers are
+    inside a collective, trap after the spin time-out and exit; the supervisor restarts every rank
+    (restartPolicy OnFailure), the job re-forms as a fresh generation and resumes from /checkpoint.
+    Reports the seconds from the last progress of the failed generation to the first progress of the
+    new one, and the steps that had to be redone."""
+    ckpt_dir = os.path.join(work_root, "checkpoint")
+    os.makedirs(ckpt_dir, exist_ok=True)
+    rank_args = ["--steps", "100000", "--batch", str(batch), "--report-every", "1", "--ckpt-every", "10",
+                 "--fail-rank", str(fail_rank), "--fail-at-step", str(fail_step)]
+    if tiny:
+        rank_args += ["--tiny", "--image", "64"]
+    if dry:
+        rank_args += ["--cpu-dry-run"]
+    doc = job_doc(n, rank_args, gpu=not dry)
+    doc["spec"]["worker"]["template"]["spec"]["volumes"][0]["hostPath"]["path"] = ckpt_dir
+    with EtcdServer("127.0.0.1", 0) as srv:
+        etcd = EtcdClient(srv.endpoint)
+        cluster = LocalCluster(etcd=etcd, gpus=gpus, work_root=os.path.join(work_root, "pods"),
+                               extra_env={"PDJ_ELASTIC_TTL": "3", "PDJ_SPIN_TIMEOUT_MS": str(spin_timeout_ms)})
+        prefix = f"/paddle/default-{JOB}"
+        with cluster:
+            cluster.apply(doc)
+            last_old, first_new = None, None
+            deadline = time.time() + timeout
+            while time.time() < deadline and first_new is None:
+                for r in _reports(etcd, prefix).values():
+                    p = r.get("progress")
+                    if not p or p["world"] != n:
+                        continue
+                    if p["gen"] == 0 and (last_old is None or p["t"] > last_old["t"]):
+                        last_old = p
+                    if p["gen"] > 0 and p["step"] > 0:
+                        first_new = p
+                time.sleep(0.02)
+            restarts = sum((p["status"].get("containerStatuses") or [{}])[0].get("restartCount", 0)
+                           for p in cluster.pods(JOB))
+            phase = cluster.get(JOB).status.phase
+            cluster.delete(JOB)
+            cluster.wait_deleted(JOB, timeout=60)
+    if first_new is None or last_old is None:
+        raise TimeoutError("the job did not recover from the injected failure")
+    return {"world": n, "failed_rank": fail_rank, "failed_at_step": fail_step, "last_step_before": last_old["step"],
+            "resumed_generation": first_new["gen"], "resumed_at_step": first_new["step"],
+            "steps_redone": max(0, last_old["step"] - first_new["step"] + 1),
+            "recovery_seconds": round(first_new["t"] - last_old["t"], 3), "spin_timeout_ms": spin_timeout_ms,
+            "rank_restarts": restarts, "job_phase_after": phase}
+
+
 def main() -> int:
     ap = argparse.ArgumentParser()
     ap.add_argument("--sizes", default="8,4,8")
@@ -143,12 +193,18 @@ def main() -> int:
     ap.add_argument("--cpu-dry-run", action="store_true")
     ap.add_argument("--timeout", type=float, default=240.0)
     ap.add_argument("--out", default="")
+    ap.add_argument("--fail-rank", type=int, default=-1, help="fault injection instead of a rescale: rank to kill")
+    ap.add_argument("--fail-step", type=int, default=25)
     args = ap.parse_args()
     sizes = [int(x) for x in args.sizes.split(",")]
     gpus = None if not args.cpu_dry_run else list(range(max(sizes)))
     work = tempfile.mkdtemp(prefix="pdj-elastic-")
     try:
-        res = run(sizes, args.steps_per_phase, args.cpu_dry_run, args.batch, args.tiny, gpus, work, args.timeout)
+        if args.fail_rank >= 0:
+            res = run_failure(sizes[0], args.fail_rank, args.fail_step, args.batch, args.tiny, gpus, work, args.timeout,
+                              dry=args.cpu_dry_run)
+        else:
+            res = run(sizes, args.steps_per_phase, args.cpu_dry_run, args.batch, args.tiny, gpus, work, args.timeout)
     except Exception:
         # post-mortem: every rank's log
         import glob

@@ -21,3 +21,13 @@ def test_rescale_4_2_4_keeps_the_step():
         assert abs(p["loss"] - p["step"]) < 1e-6 or p["loss"] <= p["step"], p
     assert res["events"] == ["Scaled: scaled replicas to 2", "Scaled: scaled replicas to 4"]
     assert res["job_phase"] in ("Running", "Starting", "Pending")
+
+
+def test_killed_rank_is_restarted_and_state_is_handed_over():
+    """SIGKILL one rank mid-run (dry-run trainers do not block on a collective, so the survivors notice the
+    expired lease, stop together, and re-form with the restarted rank without going back to the checkpoint)."""
+    work = tempfile.mkdtemp(prefix="pdj-elastic-fail-")
+    res = elastic_demo.run_failure(3, fail_rank=1, fail_step=15, batch=1, tiny=True, gpus=[0, 1, 2], work_root=work,
+                                   timeout=90, dry=True)
+    assert res["resumed_generation"] >= 1 and res["rank_restarts"] >= 1
+    assert res["steps_redone"] <= 1 and res["recovery_seconds"] < 30
