@@ -394,6 +394,30 @@ def cmd_etcd(args) -> int:
     return etcd_server.main()
 
 
+def cmd_crd(args) -> int:
+    """The CustomResourceDefinition the reference generates (config/crd/bases/...paddlejobs.yaml), reduced to
+    what is PaddleJob-specific: names, scope, printer columns, status subresource and the top-level schema
+    (PodTemplateSpec is left open instead of being inlined three times)."""
+    import yaml
+
+    from .api import loader
+    from .api.types import GROUP, KIND, SHORT_NAME, VERSION
+
+    crd = {"apiVersion": "apiextensions.k8s.io/v1", "kind": "CustomResourceDefinition",
+           "metadata": {"name": f"paddlejobs.{GROUP}"},
+           "spec": {"group": GROUP, "scope": "Namespaced",
+                    "names": {"kind": KIND, "listKind": KIND + "List", "plural": "paddlejobs", "singular": "paddlejob",
+                              "shortNames": [SHORT_NAME]},
+                    "versions": [{"name": VERSION, "served": True, "storage": True, "subresources": {"status": {}},
+                                  "additionalPrinterColumns": [
+                                      {"name": "Status", "type": "string", "jsonPath": ".status.phase"},
+                                      {"name": "Mode", "type": "string", "jsonPath": ".status.mode"},
+                                      {"name": "Age", "type": "date", "jsonPath": ".metadata.creationTimestamp"}],
+                                  "schema": {"openAPIV3Schema": loader.openapi_schema()}}]}}
+    print(yaml.safe_dump(crd, sort_keys=False))
+    return 0
+
+
 def cmd_client_demo(args) -> int:
     """Create, get, list, delete a PaddleJob through the API - what client/client.go of the
     reference demonstrates with controller-runtime's client ("not an SDK", client/README.MD:3)."""
@@ -468,6 +492,8 @@ def main(argv=None) -> int:
                                                            name=None, output="")))
     p = client_parser("client-demo", "CRUD round trip through the API")
     p.set_defaults(fn=cmd_client_demo)
+    p = sub.add_parser("crd", help="print the PaddleJob schema (the generated CRD's top level) as YAML")
+    p.set_defaults(fn=cmd_crd)
     p = sub.add_parser("etcd", help="run the etcd-compatible store")
     p.add_argument("--listen", default="127.0.0.1:2379")
     p.set_defaults(fn=cmd_etcd)

@@ -551,3 +551,24 @@ def test_status_written_only_on_change():
     for _ in range(3):
         env.r.reconcile("default", "j")
     assert env.store.get("PaddleJob", "default", "j")["metadata"]["resourceVersion"] == rv
+
+
+def test_legacy_hostport_manager_semantics_and_crd():
+    """third_party/hostport-allocator of the reference: N ports per job, comma annotation, release."""
+    from paddle_operator_b200.controller.hostport import (LEGACY_HOSTPORT_ANNOTATION, LEGACY_PORTNUM_ANNOTATION,
+                                                          format_annotation)
+
+    a = HostPortAllocator(30000, 30000 + 200, block=1)
+    ports = a.allocate_many(3)
+    assert len(set(ports)) == 3 and all(30000 <= p <= 30200 for p in ports)
+    assert parse_annotation(format_annotation(ports)) == ports
+    assert LEGACY_PORTNUM_ANNOTATION == "hostport-manager/portnum" and LEGACY_HOSTPORT_ANNOTATION == "hostport-manager/hostport"
+    for p in ports:
+        assert a.release(p)
+    small = HostPortAllocator(30000, 30002, block=1)
+    with pytest.raises(RuntimeError):
+        small.allocate_many(5)
+    schema = loader.openapi_schema()
+    assert schema["properties"]["spec"]["properties"]["worker"]["required"] == ["replicas"]
+    assert set(schema["properties"]["status"]["properties"]) >= {"phase", "mode", "ps", "worker", "heter", "elastic",
+                                                                  "startTime", "completionTime", "observedGeneration"}
