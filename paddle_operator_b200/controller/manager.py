@@ -11,13 +11,13 @@ Two ways to drive it:
 """
 from __future__ import annotations
 
-import heapq
 import logging
 import threading
 import time
 from typing import Optional
 
 from ..api.types import KIND
+from ..utils import trace
 from .gang import GangScheduler
 from .reconciler import PaddleJobReconciler, Result
 from .store import ObjectStore
@@ -86,7 +86,8 @@ class ControllerManager:
     def _process(self, key: tuple) -> Result:
         self.reconcile_count += 1
         try:
-            res = self.reconciler.reconcile(*key)
+            with trace.span("reconcile", namespace=key[0], job=key[1]):
+                res = self.reconciler.reconcile(*key)
         except Exception as e:  # noqa: BLE001 - like controller-runtime: log, back off, retry
             self.reconcile_errors += 1
             log.exception("reconcile %s/%s failed: %s", key[0], key[1], e)

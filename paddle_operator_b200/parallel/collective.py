@@ -21,6 +21,7 @@ from typing import Callable, Optional
 import torch
 
 from ..ops import optim as pdj_optim
+from ..utils import trace
 from .symm import AR_NVLS, AR_ONESHOT, AR_TWOSHOT, Communicator
 
 
@@ -180,8 +181,9 @@ class CollectiveTrainer:
         algo = self.algo if self.algo is not None else self.comm.pick_algo(n * 2)
         if algo == AR_ONESHOT:
             algo = AR_TWOSHOT  # in-place
-        self.comm.all_reduce_bf16(off, off, n, scale=1.0 / self.world, algo=algo, nblocks=self.comm_blocks,
-                                  stream=self.comm_stream)
+        with trace.span("bucket_allreduce", bytes=n * 2, algo=int(algo)):
+            self.comm.all_reduce_bf16(off, off, n, scale=1.0 / self.world, algo=algo, nblocks=self.comm_blocks,
+                                      stream=self.comm_stream)
         self._count += 1
         done = torch.cuda.Event()
         done.record(self.comm_stream)

@@ -572,3 +572,18 @@ def test_legacy_hostport_manager_semantics_and_crd():
     assert schema["properties"]["spec"]["properties"]["worker"]["required"] == ["replicas"]
     assert set(schema["properties"]["status"]["properties"]) >= {"phase", "mode", "ps", "worker", "heter", "elastic",
                                                                   "startTime", "completionTime", "observedGeneration"}
+
+
+def test_trace_spans_cover_reconcile_passes(tmp_path):
+    from paddle_operator_b200.utils import trace
+
+    trace.enable()
+    n0 = len(trace.events())
+    env = Env(init_image="", supervisor=False)
+    env.apply(_job("t", ps=None, worker=1))
+    env.mgr.run_until_idle()
+    evs = [e for e in trace.events()[n0:] if e["name"] == "reconcile"]
+    assert evs and evs[0]["args"]["job"] == "t" and evs[0]["dur"] >= 0
+    out = trace.flush(str(tmp_path / "trace.json"))
+    import json as _json
+    assert _json.load(open(out))["traceEvents"]
