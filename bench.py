@@ -66,10 +66,20 @@ class ClockSampler:
         self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
         self.p = None
 
+    @staticmethod
+    def gpus_in_use() -> str:
+        """Only the GPUs this job runs on: idle neighbours on a bigger box sit
+        at idle clocks and would drag the median down."""
+        world = int(os.environ.get("WORLD_SIZE", "1"))
+        visible = [v.strip() for v in os.environ.get("CUDA_VISIBLE_DEVICES", "").split(",") if v.strip()]
+        ids = visible[:world] if visible else [str(i) for i in range(world)]
+        return ",".join(ids)
+
     def start(self):
         try:
-            self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                       "-lms", "100"], stdout=self.f, stderr=subprocess.DEVNULL)
+            self.p = subprocess.Popen(["nvidia-smi", "-i", self.gpus_in_use(), f"--query-gpu={self.Q}",
+                                       "--format=csv,noheader,nounits", "-lms", "50"],
+                                      stdout=self.f, stderr=subprocess.DEVNULL)
         except OSError:
             self.p = None
 
