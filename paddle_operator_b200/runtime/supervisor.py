@@ -70,7 +70,9 @@ SCRIPT_MODULES = {
 
 
 def resolve_command(container: dict) -> Optional[list[str]]:
-    cmd = list(container.get("command") or []) + list(container.get("args") or [])
+    # Kubernetes semantics: `command` replaces the image's entrypoint, `args` are appended to
+    # whichever of the two is in effect.
+    cmd = list(container.get("command") or [])
     if not cmd:
         image = container.get("image", "")
         for pat, argv in IMAGE_COMMANDS.items():
@@ -79,6 +81,7 @@ def resolve_command(container: dict) -> Optional[list[str]]:
                 break
     if not cmd:
         return None
+    cmd += [str(a) for a in container.get("args") or []]
     # `python -m paddle.distributed.launch script.py ...` -> the local workload for that script
     if len(cmd) >= 4 and cmd[1] == "-m" and cmd[2] == "paddle.distributed.launch":
         script = os.path.basename(cmd[3])

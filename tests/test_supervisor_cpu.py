@@ -121,3 +121,23 @@ def test_command_resolution():
     c = resolve_command({"image": "x", "command": ["python"], "args": ["-m", "paddle.distributed.launch", "train_fleet.py"]})
     assert c[1:] == ["-m", "paddle_operator_b200.workloads.train_resnet"]
     assert resolve_command({"image": "unknown"}) is None
+    # args without a command are appended to the image's registered entrypoint
+    c = resolve_command({"image": "local/pdjob-b200:wide-and-deep", "args": ["--emb-dim", 32]})
+    assert c[1:] == ["-m", "paddle_operator_b200.workloads.train_wide_deep", "--emb-dim", "32"]
+    assert resolve_command({"image": "unknown", "args": ["--x"]}) is None
+
+
+def test_every_example_manifest_loads_and_resolves():
+    import glob
+
+    from paddle_operator_b200.api import loader
+
+    files = sorted(glob.glob(os.path.join(ROOT, "examples", "*.yaml")))
+    assert len(files) >= 10
+    for f in files:
+        job = loader.load_paddlejob(f)
+        for res in (job.spec.ps, job.spec.worker, job.spec.heter):
+            if res is None:
+                continue
+            c0 = res.template["spec"]["containers"][0]
+            assert resolve_command(c0), (f, c0)
