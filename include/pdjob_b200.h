@@ -112,6 +112,21 @@ int pdj_emb_apply(const struct PdjComm* c, const struct PdjEmbTable* t, int opti
 int pdj_linear_block_n(int N);
 int pdj_linear_bf16(const void* a, const void* b, void* out, const float* bias, const void* mask, int M, int N, int K,
                     int lda, int ldb, int ldo, int relu, cudaStream_t st);
+/* 1x1 convolution over NHWC activations as a GEMM on the same tcgen05 pipeline, with the
+ * per-channel sum / sum of squares of the (bf16-rounded) output accumulated in the epilogue:
+ *   out[M,N] = A[M,K] . B[N,K]^T,   partial[p][0][n] = sum_m out, partial[p][1][n] = sum_m out^2
+ * for p < pdj_conv1x1_partial_rows(M, N) (fp32; pass partial = NULL to skip the statistics).
+ * N must be a multiple of 64.  Feed `partial` to pdj_bn_fwd_pre: the BatchNorm that follows then
+ * needs no statistics pass over the activation.  ResNet-50's bottleneck 1x1 convolutions
+ * (deploy/examples/resnet.yaml workload). */
+int pdj_conv1x1_partial_rows(int M, int N);
+int pdj_conv1x1_bf16(const void* a, const void* b, void* out, float* partial, int M, int N, int K, int lda, int ldb,
+                     int ldo, cudaStream_t st);
+/* out[M,N] = addend[M,N] + A[M,K] . B[N,K]^T on the same kernel (the addend box is fetched by TMA into
+ * the epilogue's staging buffer; out may alias addend).  The input-gradient GEMM of a bottleneck's
+ * first 1x1 convolution with the skip connection's gradient folded in. */
+int pdj_conv1x1_add_bf16(const void* a, const void* b, const void* addend, void* out, int M, int N, int K, int lda,
+                         int ldb, int ldc, int ldo, cudaStream_t st);
 
 /* ---- ResNet-50 step kernels (csrc/bn_act.cu, csrc/optim_misc.cu) -----------
  * The workload of deploy/examples/resnet.yaml:13-19. NHWC bf16 activations
@@ -131,6 +146,11 @@ int pdj_bn_fwd_gate(const void* x, const void* res, void* y, void* gate, int M, 
 int pdj_bn_bwd_gate(const void* dy, const void* y, const void* gate, const void* x, void* dx, void* dres, int M, int C,
                     const float* gamma, const float* mean_rstd, float* dgamma_dbeta, void* dgb_bf16, float* coef,
                     int relu, void* workspace, cudaStream_t st);
+/* Forward with the statistics pre-reduced to `nb` partial rows ([nb][2][C] fp32) by the kernel that
+ * produced x (pdj_conv1x1_bf16): finalisation + apply only. */
+int pdj_bn_fwd_pre(const void* x, const void* res, void* y, void* gate, int M, int C, const float* gamma,
+                   const float* beta, float eps, float momentum, float* running_mean, float* running_var,
+                   float* mean_rstd, float* scale_shift, int relu, const float* partial, int nb, cudaStream_t st);
 /* No counterpart in the reference (it has no device code and no allocator
  * story).  Same result as pdj_bn_fwd, but takes no workspace and allocates
  * nothing: its block partials and tickets live in a file-scope device array of

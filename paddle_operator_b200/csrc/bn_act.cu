@@ -121,6 +121,29 @@ __device__ __forceinline__ bool sum_partials(const float* partial, int C, int ch
   return true;
 }
 
+// Per-channel epilogue of the statistics pass: mean / rstd, the fused scale and shift of the
+// apply pass, and the running statistics (unbiased variance, like torch).
+__device__ __forceinline__ void finalize_channel(int ch, float s, float q, int M, int C, const float* __restrict__ gamma,
+                                                 const float* __restrict__ beta, float eps, float momentum,
+                                                 float* __restrict__ running_mean, float* __restrict__ running_var,
+                                                 float* __restrict__ mean_rstd, float* __restrict__ scale_shift) {
+  const float inv_m = 1.f / (float)M;
+  const float mean = s * inv_m;
+  float var = q * inv_m - mean * mean;
+  var = var < 0.f ? 0.f : var;
+  const float rstd = rsqrtf(var + eps);
+  mean_rstd[ch] = mean;
+  mean_rstd[C + ch] = rstd;
+  const float sc = gamma[ch] * rstd;
+  scale_shift[ch] = sc;
+  scale_shift[C + ch] = beta[ch] - mean * sc;
+  if (running_mean != nullptr) {
+    const float unbiased = M > 1 ? var * ((float)M / (float)(M - 1)) : var;
+    running_mean[ch] = (1.f - momentum) * running_mean[ch] + momentum * mean;
+    running_var[ch] = (1.f - momentum) * running_var[ch] + momentum * unbiased;
+  }
+}
+
 // ---- forward --------------------------------------------------------------
 template <int U>
 __global__ void __launch_bounds__(kThreads)
@@ -165,25 +188,24 @@ bn_stats_kernel(const __nv_bfloat16* __restrict__ x, int M, int C, const float* 
   if (!reduce_and_publish(t, C, acc, partial, counter)) return;
   // Last block of this channel tile: finalise its channels.
   const int nch = t.cvt * 8;
-  const float inv_m = 1.f / (float)M;
   float s, q;
   if (sum_partials(partial, C, blockIdx.y * nch, nch, gridDim.x, s, q)) {
-    const int ch = blockIdx.y * nch + threadIdx.x;
-    const float mean = s * inv_m;
-    float var = q * inv_m - mean * mean;
-    var = var < 0.f ? 0.f : var;
-    const float rstd = rsqrtf(var + eps);
-    mean_rstd[ch] = mean;
-    mean_rstd[C + ch] = rstd;
-    const float sc = gamma[ch] * rstd;
-    scale_shift[ch] = sc;
-    scale_shift[C + ch] = beta[ch] - mean * sc;
-    if (running_mean != nullptr) {
-      const float unbiased = M > 1 ? var * ((float)M / (float)(M - 1)) : var;
-      running_mean[ch] = (1.f - momentum) * running_mean[ch] + momentum * mean;
-      running_var[ch] = (1.f - momentum) * running_var[ch] + momentum * unbiased;
-    }
+    finalize_channel(blockIdx.y * nch + threadIdx.x, s, q, M, C, gamma, beta, eps, momentum, running_mean, running_var,
+                     mean_rstd, scale_shift);
   }
+}
+
+// Statistics already reduced to `nb` partial rows by the producer of x (the 1x1-convolution GEMM
+// of gemm_tcgen05.cu writes them from its epilogue): only the finalisation is left.  8 channels per
+// block, 32 threads per channel.
+__global__ void __launch_bounds__(kThreads)
+bn_finalize_kernel(const float* __restrict__ partial, unsigned int nb, int M, int C, const float* __restrict__ gamma,
+                   const float* __restrict__ beta, float eps, float momentum, float* __restrict__ running_mean,
+                   float* __restrict__ running_var, float* __restrict__ mean_rstd, float* __restrict__ scale_shift) {
+  float s, q;
+  if (sum_partials(partial, C, blockIdx.x * 8, 8, nb, s, q))
+    finalize_channel(blockIdx.x * 8 + threadIdx.x, s, q, M, C, gamma, beta, eps, momentum, running_mean, running_var,
+                     mean_rstd, scale_shift);
 }
 
 template <bool RELU, bool RES>
@@ -497,6 +519,21 @@ int flat_grid(size_t n_vec) {
   return (int)want;
 }
 
+int launch_apply(const void* x, const void* res, void* y, uint8_t* gate_out, int M, int C, const float* scale_shift,
+                 int relu, cudaStream_t st) {
+  const size_t n_vec = (size_t)M * (C / 8);
+  const int fg = flat_grid(n_vec);
+  const __nv_bfloat16* xb = (const __nv_bfloat16*)x;
+  const __nv_bfloat16* rb = (const __nv_bfloat16*)res;
+  __nv_bfloat16* yb = (__nv_bfloat16*)y;
+  if (relu && res) bn_apply_kernel<true, true><<<fg, kThreads, 0, st>>>(xb, rb, yb, n_vec, C, scale_shift, gate_out);
+  else if (relu) bn_apply_kernel<true, false><<<fg, kThreads, 0, st>>>(xb, rb, yb, n_vec, C, scale_shift, gate_out);
+  else if (res) bn_apply_kernel<false, true><<<fg, kThreads, 0, st>>>(xb, rb, yb, n_vec, C, scale_shift, gate_out);
+  else bn_apply_kernel<false, false><<<fg, kThreads, 0, st>>>(xb, rb, yb, n_vec, C, scale_shift, gate_out);
+  PDJ_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
 }  // namespace
 
 extern "C" {
@@ -529,17 +566,23 @@ int pdj_bn_fwd_gate(const void* x, const void* res, void* y, void* gate, int M, 
   launch_stats(g, st, (const __nv_bfloat16*)x, M, C, gamma, beta, eps, momentum, running_mean, running_var, mean_rstd,
                scale_shift, partial, counter, knob_cvt());
   PDJ_CUDA_CHECK(cudaGetLastError());
-  const size_t n_vec = (size_t)M * c8;
-  const int fg = flat_grid(n_vec);
-  const __nv_bfloat16* xb = (const __nv_bfloat16*)x;
-  const __nv_bfloat16* rb = (const __nv_bfloat16*)res;
-  __nv_bfloat16* yb = (__nv_bfloat16*)y;
-  if (relu && res) bn_apply_kernel<true, true><<<fg, kThreads, 0, st>>>(xb, rb, yb, n_vec, C, scale_shift, gate_out);
-  else if (relu) bn_apply_kernel<true, false><<<fg, kThreads, 0, st>>>(xb, rb, yb, n_vec, C, scale_shift, gate_out);
-  else if (res) bn_apply_kernel<false, true><<<fg, kThreads, 0, st>>>(xb, rb, yb, n_vec, C, scale_shift, gate_out);
-  else bn_apply_kernel<false, false><<<fg, kThreads, 0, st>>>(xb, rb, yb, n_vec, C, scale_shift, gate_out);
+  return launch_apply(x, res, y, gate_out, M, C, scale_shift, relu, st);
+}
+
+// Same as pdj_bn_fwd_gate, but the per-channel sums come from `partial` ([nb][2][C] fp32: sum, sum
+// of squares; written by pdj_conv1x1_bf16) instead of a pass over x.
+int pdj_bn_fwd_pre(const void* x, const void* res, void* y, void* gate, int M, int C, const float* gamma,
+                   const float* beta, float eps, float momentum, float* running_mean, float* running_var,
+                   float* mean_rstd, float* scale_shift, int relu, const float* partial, int nb, cudaStream_t st) {
+  if (check_shape(M, C)) return -1;
+  if (partial == nullptr || nb < 1) {
+    pdj_set_error("pdj_bn_fwd_pre: no partial sums (nb=%d)", nb);
+    return -1;
+  }
+  bn_finalize_kernel<<<C / 8, kThreads, 0, st>>>(partial, (unsigned int)nb, M, C, gamma, beta, eps, momentum, running_mean,
+                                                running_var, mean_rstd, scale_shift);
   PDJ_CUDA_CHECK(cudaGetLastError());
-  return 0;
+  return launch_apply(x, res, y, reinterpret_cast<uint8_t*>(gate), M, C, scale_shift, relu, st);
 }
 
 int pdj_bn_bwd_gate(const void* dy, const void* y, const void* gate, const void* x, void* dx, void* dres, int M, int C,

@@ -97,6 +97,57 @@ __device__ __forceinline__ void umma_commit(uint32_t bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
 
+// Shared-memory ring + accumulator hand-off barriers of one CTA.
+struct Pipe {
+  uint32_t a_smem, b_smem, b_stage_bytes;
+  uint32_t full0, empty0;      // per ring slot: TMA -> MMA, MMA -> TMA
+  uint32_t tfull0, tempty0;    // per accumulator buffer: MMA -> epilogue, epilogue -> MMA
+  int stages;
+};
+
+// TMA producer (one thread): walks this CTA's tiles and keeps the ring full.
+__device__ __forceinline__ void producer_loop(const CUtensorMap* tma_a, const CUtensorMap* tma_b, const Pipe& p, int total,
+                                              int tiles_n, int block_n, int num_kb) {
+  const uint32_t stage_bytes = (uint32_t)A_STAGE_BYTES + p.b_stage_bytes;
+  uint32_t it = 0;
+  for (int t = blockIdx.x; t < total; t += gridDim.x) {
+    const int m0 = (t / tiles_n) * BM, n0 = (t % tiles_n) * block_n;
+    for (int kb = 0; kb < num_kb; ++kb, ++it) {
+      const uint32_t s = it % (uint32_t)p.stages, ph = (it / (uint32_t)p.stages) & 1u;
+      mbar_wait(p.empty0 + 8 * s, ph ^ 1u);
+      mbar_expect_tx(p.full0 + 8 * s, stage_bytes);
+      tma_load_2d(p.a_smem + s * A_STAGE_BYTES, tma_a, kb * BK, m0, p.full0 + 8 * s);
+      tma_load_2d(p.b_smem + s * p.b_stage_bytes, tma_b, kb * BK, n0, p.full0 + 8 * s);
+    }
+  }
+}
+
+// MMA issuer (one thread): tile i accumulates into TMEM buffer i & 1.
+__device__ __forceinline__ void mma_loop(const Pipe& p, uint32_t tmem_base, int total, int block_n, int num_kb) {
+  // instruction descriptor: D = f32, A = B = bf16, both K-major, N >> 3, M >> 4
+  const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(block_n >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+  uint32_t it = 0, i = 0;
+  for (int t = blockIdx.x; t < total; t += gridDim.x, ++i) {
+    const uint32_t buf = i & 1u, aph = (i >> 1) & 1u;
+    mbar_wait(p.tempty0 + 8 * buf, aph ^ 1u);  // the epilogue has drained this accumulator
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_d = tmem_base + buf * MAX_BN;
+    for (int kb = 0; kb < num_kb; ++kb, ++it) {
+      const uint32_t s = it % (uint32_t)p.stages, ph = (it / (uint32_t)p.stages) & 1u;
+      mbar_wait(p.full0 + 8 * s, ph);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+#pragma unroll
+      for (int k = 0; k < BK / UK; ++k) {
+        const uint64_t da = umma_desc(p.a_smem + s * A_STAGE_BYTES + k * UK * 2);
+        const uint64_t db = umma_desc(p.b_smem + s * p.b_stage_bytes + k * UK * 2);
+        umma_f16(tmem_d, da, db, idesc, (uint32_t)((kb | k) != 0));
+      }
+      umma_commit(p.empty0 + 8 * s);  // slot is free once these MMAs have read it
+    }
+    umma_commit(p.tfull0 + 8 * buf);  // accumulator complete
+  }
+}
+
 // Persistent: one CTA per SM walks tiles t = blockIdx.x, blockIdx.x + gridDim.x, ... (column tile
 // fastest, so CTAs running at the same time share A rows in L2).  The accumulator is double
 // buffered in TMEM: the epilogue of tile i overlaps the MMAs of tile i + 1.
@@ -150,49 +201,12 @@ linear_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const uint32_t tmem_base = *tmem_slot_ptr;
+  const Pipe pipe{a_smem, b_smem, b_stage_bytes, full0, empty0, tfull0, tempty0, stages};
 
   if (warp == 0) {
-    // ===== TMA producer =====
-    if (lane == 0) {
-      const uint32_t stage_bytes = (uint32_t)A_STAGE_BYTES + b_stage_bytes;
-      uint32_t it = 0;
-      for (int t = blockIdx.x; t < total; t += gridDim.x) {
-        const int m0 = (t / tiles_n) * BM, n0 = (t % tiles_n) * block_n;
-        for (int kb = 0; kb < num_kb; ++kb, ++it) {
-          const uint32_t s = it % (uint32_t)stages, ph = (it / (uint32_t)stages) & 1u;
-          mbar_wait(empty0 + 8 * s, ph ^ 1u);
-          mbar_expect_tx(full0 + 8 * s, stage_bytes);
-          tma_load_2d(a_smem + s * A_STAGE_BYTES, &tma_a, kb * BK, m0, full0 + 8 * s);
-          tma_load_2d(b_smem + s * b_stage_bytes, &tma_b, kb * BK, n0, full0 + 8 * s);
-        }
-      }
-    }
+    if (lane == 0) producer_loop(&tma_a, &tma_b, pipe, total, tiles_n, block_n, num_kb);
   } else if (warp == 1) {
-    // ===== MMA issuer =====
-    if (lane == 0) {
-      // instruction descriptor: D = f32, A = B = bf16, both K-major, N >> 3, M >> 4
-      const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(block_n >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
-      uint32_t it = 0, i = 0;
-      for (int t = blockIdx.x; t < total; t += gridDim.x, ++i) {
-        const uint32_t buf = i & 1u, aph = (i >> 1) & 1u;
-        mbar_wait(tempty0 + 8 * buf, aph ^ 1u);  // the epilogue has drained this accumulator
-        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        const uint32_t tmem_d = tmem_base + buf * MAX_BN;
-        for (int kb = 0; kb < num_kb; ++kb, ++it) {
-          const uint32_t s = it % (uint32_t)stages, ph = (it / (uint32_t)stages) & 1u;
-          mbar_wait(full0 + 8 * s, ph);
-          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-#pragma unroll
-          for (int k = 0; k < BK / UK; ++k) {
-            const uint64_t da = umma_desc(a_smem + s * A_STAGE_BYTES + k * UK * 2);
-            const uint64_t db = umma_desc(b_smem + s * b_stage_bytes + k * UK * 2);
-            umma_f16(tmem_d, da, db, idesc, (uint32_t)((kb | k) != 0));
-          }
-          umma_commit(empty0 + 8 * s);  // slot is free once these MMAs have read it
-        }
-        umma_commit(tfull0 + 8 * buf);  // accumulator complete
-      }
-    }
+    if (lane == 0) mma_loop(pipe, tmem_base, total, block_n, num_kb);
   } else {
     // ===== epilogue: warps 2..9.  Warp w reads TMEM lane quarter (w % 4) - a hardware rule -
     // and the two warps of a quarter split the columns in halves. =====
@@ -296,6 +310,253 @@ linear_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// 1x1 convolution (NHWC) = GEMM over [N*H*W, Cin] x [Cout, Cin]^T, fused with the per-channel
+// sum / sum-of-squares that the following training-mode BatchNorm needs, so the activation is not
+// read a second time for its statistics.
+//
+// These layers are HBM-bound (K is as small as 64), so the epilogue is built for store bandwidth:
+//   * the 8 epilogue warps form two groups of four (one warp per TMEM lane quarter); group g drains
+//     accumulator buffer g, i.e. the groups work on alternate tiles in parallel;
+//   * a tile leaves as 64-column boxes: TMEM -> registers -> bf16 -> 128-byte-swizzled shared
+//     memory (conflict-free 16-byte stores) -> one TMA store per box, two boxes in flight per group;
+//   * while the TMA engine reads a box, the group sums its columns from the same staging buffer
+//     (values exactly as stored, i.e. bf16-rounded) and folds them into per-thread accumulators.
+// The grid is a multiple of the column-tile count, so a CTA always works on the same channel
+// range and the sums stay in registers until the end; each (CTA, group) then writes one row
+//   partial[p][0][c] = sum, partial[p][1][c] = sum of squares,   p = (cta / tiles_n) * 2 + group
+// which is the layout bn_act.cu's finalisation consumes.  Fixed schedule => bit-reproducible.
+constexpr int BOX_N = 64;                       // columns per staged box: 64 bf16 = one swizzle row
+constexpr int BOX_BYTES = BM * BOX_N * 2;       // 16 KiB
+constexpr int SW_STAGING_BYTES = 4 * BOX_BYTES; // 2 groups x 2 boxes
+constexpr int SW_SCRATCH_BYTES = 2 * 2 * 4 * BOX_N * 4;  // [group][sum|sq][warp][64] fp32
+
+// MODE_ADD: out = addend + A.B^T instead (no statistics).  The addend box is fetched by TMA into the
+// staging buffer one box ahead, summed in place with the accumulator, and stored from there - the
+// residual-gradient add of a bottleneck block folded into the input-gradient GEMM of its first conv.
+constexpr int MODE_PLAIN = 0, MODE_STATS = 1, MODE_ADD = 2;
+
+template <int MODE>
+__global__ void __launch_bounds__(THREADS, 1)
+conv1x1_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
+                       const __grid_constant__ CUtensorMap tma_o, const __grid_constant__ CUtensorMap tma_c,
+                       float* __restrict__ partial, int M, int N, int K, int block_n, int stages) {
+  constexpr bool STATS = MODE == MODE_STATS;
+  constexpr bool ADD = MODE == MODE_ADD;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  const uint32_t base = (raw + 1023u) & ~1023u;
+  const uint32_t b_stage_bytes = (uint32_t)block_n * BK * 2;
+  const uint32_t a_smem = base;
+  const uint32_t b_smem = a_smem + stages * A_STAGE_BYTES;
+  const uint32_t staging = b_smem + stages * b_stage_bytes;  // 1024-aligned: every term is a multiple of 1024
+  const uint32_t scratch = staging + SW_STAGING_BYTES;
+  const uint32_t bars = scratch + SW_SCRATCH_BYTES;
+  const uint32_t full0 = bars, empty0 = bars + 8 * MAX_STAGES;
+  const uint32_t tfull0 = bars + 16 * MAX_STAGES, tempty0 = tfull0 + 16, tmem_slot = tempty0 + 16;
+  const uint32_t abar0 = tmem_slot + 16;  // [group][staging buffer]: addend box has landed (MODE_ADD)
+  uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(smem_raw + (tmem_slot - raw));
+  float* scratch_f = reinterpret_cast<float*>(smem_raw + (scratch - raw));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int tiles_n = N / block_n;
+  const int total = ((M + BM - 1) / BM) * tiles_n;
+  const int num_kb = (K + BK - 1) / BK;
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_a) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_b) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_o) : "memory");
+    if (ADD) asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_c) : "memory");
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      for (int s = 0; s < stages; ++s) {
+        mbar_init(full0 + 8 * s, 1);
+        mbar_init(empty0 + 8 * s, 1);
+      }
+      for (int b = 0; b < 2; ++b) {
+        mbar_init(tfull0 + 8 * b, 1);
+        mbar_init(tempty0 + 8 * b, 4);  // the four warps of the group that owns the buffer
+      }
+      for (int b = 0; b < 4; ++b) mbar_init(abar0 + 8 * b, 1);
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(TMEM_COLS)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem_base = *tmem_slot_ptr;
+  const Pipe pipe{a_smem, b_smem, b_stage_bytes, full0, empty0, tfull0, tempty0, stages};
+
+  if (warp == 0) {
+    if (lane == 0) producer_loop(&tma_a, &tma_b, pipe, total, tiles_n, block_n, num_kb);
+  } else if (warp == 1) {
+    if (lane == 0) mma_loop(pipe, tmem_base, total, block_n, num_kb);
+  } else {
+    const int g = (warp - 2) >> 2;               // epilogue group = accumulator buffer it drains
+    const int q = warp & 3;                      // TMEM lane quarter this warp may read
+    const int gw = (warp - 2) & 3;               // warp index within the group
+    const int gt = gw * 32 + lane;               // thread index within the group, 0..127
+    const int row = q * 32 + lane;               // accumulator row handled by this thread
+    const uint32_t bar_id = 1 + g;
+    const uint32_t stg0 = staging + (uint32_t)g * 2 * BOX_BYTES;
+    float* sc_sum = scratch_f + g * (2 * 4 * BOX_N);
+    float* sc_sq = sc_sum + 4 * BOX_N;
+    const int nboxes = block_n / BOX_N;
+    const int n0 = ((int)blockIdx.x % tiles_n) * block_n;   // fixed per CTA: gridDim.x % tiles_n == 0
+    float acc_s[MAX_BN / BOX_N], acc_q[MAX_BN / BOX_N];
+#pragma unroll
+    for (int b = 0; b < MAX_BN / BOX_N; ++b) acc_s[b] = acc_q[b] = 0.f;
+    uint32_t bc = 0;  // boxes staged by this group so far
+    if (ADD && gt == 0) {
+      const long long t0 = (long long)blockIdx.x + (long long)g * gridDim.x;
+      if (t0 < total) {  // addend of the group's first box
+        mbar_expect_tx(abar0 + 8 * (g * 2), BOX_BYTES);
+        tma_load_2d(stg0, &tma_c, n0, (int)(t0 / tiles_n) * BM, abar0 + 8 * (g * 2));
+      }
+    }
+    for (uint32_t i = g;; i += 2) {
+      const long long t = (long long)blockIdx.x + (long long)i * gridDim.x;
+      if (t >= total) break;
+      const int m0 = (int)(t / tiles_n) * BM;
+      const uint32_t aph = (i >> 1) & 1u;
+      mbar_wait(tfull0 + 8 * g, aph);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      const uint32_t taddr_row = tmem_base + (uint32_t)g * MAX_BN + ((uint32_t)(q * 32) << 16);
+#pragma unroll
+      for (int b = 0; b < MAX_BN / BOX_N; ++b) {
+        if (b >= nboxes) break;
+        const uint32_t sbi = bc & 1u, use = bc >> 1;
+        const uint32_t stg = stg0 + sbi * BOX_BYTES;
+        ++bc;
+        if (ADD) {
+          // the addend box was requested one box ago, after the last store out of this buffer had been read
+          mbar_wait(abar0 + 8 * (g * 2 + sbi), use & 1u);
+        } else {
+          // (A) the TMA store that last read this staging buffer (two boxes ago) has finished reading
+          if (gt == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+          asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
+        }
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          uint32_t r[32];
+          const uint32_t ta = taddr_row + (uint32_t)(b * BOX_N + h * 32);
+          asm volatile(
+              "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+              : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+                "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+              : "r"(ta)
+              : "memory");
+          asm volatile(
+              "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+              : "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+                "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+              : "r"(ta + 16u)
+              : "memory");
+          asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {  // four 16-byte chunks = 32 columns
+            const uint32_t chunk = (uint32_t)(h * 4 + c);
+            const uint32_t dst = stg + (uint32_t)row * 128u + ((chunk ^ ((uint32_t)row & 7u)) << 4);
+            float v[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[8 * c + j]);
+            if (ADD) {
+              uint4 cv;
+              asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(cv.x), "=r"(cv.y), "=r"(cv.z), "=r"(cv.w) : "r"(dst));
+              const float2 a0 = pdj_bf2_to_f2(cv.x), a1 = pdj_bf2_to_f2(cv.y), a2 = pdj_bf2_to_f2(cv.z), a3 = pdj_bf2_to_f2(cv.w);
+              v[0] += a0.x; v[1] += a0.y; v[2] += a1.x; v[3] += a1.y;
+              v[4] += a2.x; v[5] += a2.y; v[6] += a3.x; v[7] += a3.y;
+            }
+            const uint32_t p0 = pdj_f2_to_bf2(v[0], v[1]);
+            const uint32_t p1 = pdj_f2_to_bf2(v[2], v[3]);
+            const uint32_t p2 = pdj_f2_to_bf2(v[4], v[5]);
+            const uint32_t p3 = pdj_f2_to_bf2(v[6], v[7]);
+            asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(dst), "r"(p0), "r"(p1), "r"(p2), "r"(p3) : "memory");
+          }
+        }
+        if (b == nboxes - 1) {
+          // accumulator fully read: hand the TMEM buffer back to the MMA warp
+          asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+          __syncwarp();
+          if (lane == 0) mbar_arrive(tempty0 + 8 * g);
+        }
+        // (B) box staged: make the generic-proxy writes visible to the TMA engine, then store
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
+        if (gt == 0) {
+          tma_store_2d(&tma_o, stg, n0 + b * BOX_N, m0);  // rows beyond M are clipped by the tensor map
+          asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+          if (ADD) {
+            // request the next box's addend into the other buffer once the store out of it (the previous
+            // box) has been read; the store just issued may still be in flight
+            int nrow = m0, ncol = n0 + (b + 1) * BOX_N;
+            bool more = b + 1 < nboxes;
+            if (!more) {
+              const long long t2 = t + 2ll * gridDim.x;
+              more = t2 < total;
+              nrow = (int)(t2 / tiles_n) * BM;
+              ncol = n0;
+            }
+            if (more) {
+              asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+              const uint32_t nb_ = abar0 + 8 * (g * 2 + (sbi ^ 1u));
+              mbar_expect_tx(nb_, BOX_BYTES);
+              tma_load_2d(stg0 + (sbi ^ 1u) * BOX_BYTES, &tma_c, ncol, nrow, nb_);
+            }
+          }
+        }
+        if (STATS) {
+          // column pair `lane` of rows gw*32 .. gw*32+31, read back exactly as stored
+          float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
+          const uint32_t chunk = (uint32_t)lane >> 2, word = ((uint32_t)lane & 3u) << 2;
+#pragma unroll 8
+          for (int rr = 0; rr < 32; ++rr) {
+            const uint32_t r2 = (uint32_t)(gw * 32 + rr);
+            uint32_t v;
+            asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(stg + r2 * 128u + ((chunk ^ (r2 & 7u)) << 4) + word));
+            const float2 f = pdj_bf2_to_f2(v);
+            s0 += f.x;
+            s1 += f.y;
+            q0 = fmaf(f.x, f.x, q0);
+            q1 = fmaf(f.y, f.y, q1);
+          }
+          sc_sum[gw * BOX_N + 2 * lane] = s0;
+          sc_sum[gw * BOX_N + 2 * lane + 1] = s1;
+          sc_sq[gw * BOX_N + 2 * lane] = q0;
+          sc_sq[gw * BOX_N + 2 * lane + 1] = q1;
+          // (C) the four row-quarter partials of this box are in shared memory
+          asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
+          if (gt < BOX_N) {
+            acc_s[b] += (sc_sum[gt] + sc_sum[BOX_N + gt]) + (sc_sum[2 * BOX_N + gt] + sc_sum[3 * BOX_N + gt]);
+            acc_q[b] += (sc_sq[gt] + sc_sq[BOX_N + gt]) + (sc_sq[2 * BOX_N + gt] + sc_sq[3 * BOX_N + gt]);
+          }
+        }
+      }
+    }
+    if (STATS && gt < BOX_N) {
+      const size_t p = (size_t)((int)blockIdx.x / tiles_n) * 2 + g;
+#pragma unroll
+      for (int b = 0; b < MAX_BN / BOX_N; ++b) {
+        if (b >= nboxes) break;
+        partial[(p * 2 + 0) * N + n0 + b * BOX_N + gt] = acc_s[b];
+        partial[(p * 2 + 1) * N + n0 + b * BOX_N + gt] = acc_q[b];
+      }
+    }
+    if (gt == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 1) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
+  }
+}
+
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -329,6 +590,59 @@ int make_map(CUtensorMap* map, const void* ptr, int rows, int cols, int ld_elems
 
 bool g_attr_set = false;
 int g_sms = 0;
+
+int ensure_init() {
+  if (g_attr_set) return 0;
+  PDJ_CUDA_CHECK(cudaFuncSetAttribute(linear_tcgen05_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+  PDJ_CUDA_CHECK(cudaFuncSetAttribute(linear_tcgen05_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+  PDJ_CUDA_CHECK(cudaFuncSetAttribute(conv1x1_tcgen05_kernel<MODE_PLAIN>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+  PDJ_CUDA_CHECK(cudaFuncSetAttribute(conv1x1_tcgen05_kernel<MODE_STATS>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+  PDJ_CUDA_CHECK(cudaFuncSetAttribute(conv1x1_tcgen05_kernel<MODE_ADD>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+  int dev = 0;
+  PDJ_CUDA_CHECK(cudaGetDevice(&dev));
+  PDJ_CUDA_CHECK(cudaDeviceGetAttribute(&g_sms, cudaDevAttrMultiProcessorCount, dev));
+  g_attr_set = true;
+  return 0;
+}
+
+// Column tile of the 1x1-convolution kernel: the widest of 256/192/128/64 that divides N and still
+// fills the last wave of the persistent grid to 85 % (the 7x7 layers have too few row tiles for
+// 256-wide tiles); failing that, the candidate with the fullest last wave.
+int conv_block_n(int M, int N, int sms) {
+  const int tiles_m = (M + BM - 1) / BM;
+  int best = 0;
+  double best_eff = -1.0;
+  for (int bn = MAX_BN; bn >= BOX_N; bn -= BOX_N) {
+    if (N % bn != 0) continue;
+    const long long tiles = (long long)tiles_m * (N / bn);
+    const long long waves = (tiles + sms - 1) / sms;
+    const double eff = (double)tiles / (double)(waves * sms);
+    if (eff >= 0.85) return bn;
+    if (eff > best_eff) { best_eff = eff; best = bn; }
+  }
+  return best;
+}
+
+int sm_count_cached() {
+  if (g_sms == 0) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess ||
+        cudaDeviceGetAttribute(&g_sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || g_sms <= 0)
+      g_sms = 148;
+  }
+  return g_sms;
+}
+
+// Persistent grid: as many CTAs as SMs (or tiles), rounded down to a multiple of the column-tile
+// count so that every CTA stays on one channel range.
+int conv_grid(int M, int N, int bn, int sms) {
+  const int tiles_n = N / bn;
+  const long long total = (long long)((M + BM - 1) / BM) * tiles_n;
+  long long g = total < sms ? total : sms;
+  g -= g % tiles_n;
+  if (g < tiles_n) g = tiles_n;
+  return (int)g;
+}
 
 }  // namespace
 
@@ -367,14 +681,7 @@ int pdj_linear_bf16(const void* a, const void* b, void* out, const float* bias, 
   } else {
     mo = ma;
   }
-  if (!g_attr_set) {
-    PDJ_CUDA_CHECK(cudaFuncSetAttribute(linear_tcgen05_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
-    PDJ_CUDA_CHECK(cudaFuncSetAttribute(linear_tcgen05_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
-    int dev = 0;
-    PDJ_CUDA_CHECK(cudaGetDevice(&dev));
-    PDJ_CUDA_CHECK(cudaDeviceGetAttribute(&g_sms, cudaDevAttrMultiProcessorCount, dev));
-    g_attr_set = true;
-  }
+  if (int r = ensure_init()) return r;
   const int stage_bytes = A_STAGE_BYTES + bn * BK * 2;
   const int fixed = 1024 /*alignment*/ + 256 /*barriers*/ + MAX_BN * 4 /*bias slice*/ + (tma_store ? BM * bn * 2 : 0);
   int stages = (SMEM_LIMIT - fixed) / stage_bytes;
@@ -394,6 +701,66 @@ int pdj_linear_bf16(const void* a, const void* b, void* out, const float* bias, 
                                                              (const __nv_bfloat16*)mask, M, N, K, ldo, bn, stages, relu);
   PDJ_CUDA_CHECK(cudaGetLastError());
   return 0;
+}
+
+int pdj_conv1x1_partial_rows(int M, int N) {
+  if (M < 1 || N < BOX_N || N % BOX_N != 0) return 0;
+  const int sms = sm_count_cached();
+  const int bn = conv_block_n(M, N, sms);
+  return 2 * conv_grid(M, N, bn, sms) / (N / bn);
+}
+
+static int launch_conv1x1(const void* a, const void* b, const void* addend, void* out, float* partial, int M, int N, int K,
+                          int lda, int ldb, int ldc, int ldo, cudaStream_t st) {
+  const int bn = (M >= 1 && N >= BOX_N && N % BOX_N == 0) ? conv_block_n(M, N, sm_count_cached()) : 0;
+  if (M < 1 || K < 1 || bn == 0 || lda % 8 != 0 || ldb % 8 != 0 || ldo % 8 != 0 || ((uintptr_t)a & 15) ||
+      ((uintptr_t)b & 15) || ((uintptr_t)out & 15) || (addend != nullptr && (ldc % 8 != 0 || ((uintptr_t)addend & 15)))) {
+    pdj_set_error("pdj_conv1x1: need M,K >= 1, N a multiple of 64, 16-byte aligned operands and row pitches that are "
+                  "multiples of 8 elements (N=%d lda=%d ldb=%d ldc=%d ldo=%d)", N, lda, ldb, ldc, ldo);
+    return -1;
+  }
+  if (int r = ensure_init()) return r;
+  CUtensorMap ma, mb, mo, mc;
+  if (int r = make_map(&ma, a, M, K, lda, BK, BM, true)) return r;
+  if (int r = make_map(&mb, b, N, K, ldb, BK, bn, true)) return r;
+  if (int r = make_map(&mo, out, M, N, ldo, BOX_N, BM, true)) return r;
+  if (addend != nullptr) {
+    if (int r = make_map(&mc, addend, M, N, ldc, BOX_N, BM, true)) return r;
+  } else {
+    mc = mo;
+  }
+  const int stage_bytes = A_STAGE_BYTES + bn * BK * 2;
+  const int fixed = 1024 /*alignment*/ + 256 /*barriers*/ + SW_STAGING_BYTES + SW_SCRATCH_BYTES;
+  int stages = (SMEM_LIMIT - fixed) / stage_bytes;
+  if (stages > MAX_STAGES) stages = MAX_STAGES;
+  if (stages < 2) {
+    pdj_set_error("pdj_conv1x1: tile does not fit in shared memory (block_n=%d)", bn);
+    return -1;
+  }
+  const int smem = fixed + stages * stage_bytes;
+  const int grid = conv_grid(M, N, bn, g_sms);
+  if (addend != nullptr)
+    conv1x1_tcgen05_kernel<MODE_ADD><<<grid, THREADS, smem, st>>>(ma, mb, mo, mc, nullptr, M, N, K, bn, stages);
+  else if (partial != nullptr)
+    conv1x1_tcgen05_kernel<MODE_STATS><<<grid, THREADS, smem, st>>>(ma, mb, mo, mc, partial, M, N, K, bn, stages);
+  else
+    conv1x1_tcgen05_kernel<MODE_PLAIN><<<grid, THREADS, smem, st>>>(ma, mb, mo, mc, nullptr, M, N, K, bn, stages);
+  PDJ_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+int pdj_conv1x1_bf16(const void* a, const void* b, void* out, float* partial, int M, int N, int K, int lda, int ldb,
+                     int ldo, cudaStream_t st) {
+  return launch_conv1x1(a, b, nullptr, out, partial, M, N, K, lda, ldb, 0, ldo, st);
+}
+
+int pdj_conv1x1_add_bf16(const void* a, const void* b, const void* addend, void* out, int M, int N, int K, int lda,
+                         int ldb, int ldc, int ldo, cudaStream_t st) {
+  if (addend == nullptr) {
+    pdj_set_error("pdj_conv1x1_add_bf16: addend is NULL");
+    return -1;
+  }
+  return launch_conv1x1(a, b, addend, out, nullptr, M, N, K, lda, ldb, ldc, ldo, st);
 }
 
 }  // extern "C"

@@ -16,6 +16,7 @@ import torch
 import torch.nn as nn
 
 from ..ops.bn import FusedBnAct
+from ..ops.conv import conv1x1_dual, conv1x1_stats
 from ..ops.pool import FusedMaxPool2d
 
 
@@ -58,9 +59,11 @@ def _bn(channels, relu, fused, zero_init=False):
 class Bottleneck(nn.Module):
     expansion = 4
 
-    def __init__(self, inplanes: int, planes: int, stride: int, fused: bool):
+    def __init__(self, inplanes: int, planes: int, stride: int, fused: bool, gemm_1x1: bool = False):
         super().__init__()
         out = planes * self.expansion
+        # stride-1 1x1 convolutions on the tcgen05 GEMM with BN statistics in its epilogue (ops/conv.py)
+        self.gemm_1x1 = fused and gemm_1x1
         self.conv1 = nn.Conv2d(inplanes, planes, 1, bias=False)
         self.bn1 = _bn(planes, True, fused)
         self.conv2 = nn.Conv2d(planes, planes, 3, stride=stride, padding=1, bias=False)
@@ -72,8 +75,34 @@ class Bottleneck(nn.Module):
             self.downsample = nn.Conv2d(inplanes, out, 1, stride=stride, bias=False)
             self.bn_ds = _bn(out, False, fused)
 
+    def pdj_kernels_per_step(self) -> int:
+        """Upper bound on the launches of the tcgen05 1x1-convolution kernel in this block per step (bf16 CUDA
+        training; layers below ops.conv.MIN_OUTPUT_BYTES keep the library forward)."""
+        if not self.gemm_1x1:
+            return 0
+        convs = [self.conv1, self.conv3]
+        if self.downsample is not None and self.downsample.stride == (1, 1):
+            convs.append(self.downsample)
+        n = sum(1 for c in convs if c.out_channels % 64 == 0 and c.in_channels % 8 == 0)
+        if self.conv1.in_channels % 64 == 0:
+            n += 1  # conv1's input-gradient GEMM with the skip / shortcut gradient folded in
+        return n
+
     def forward(self, x):
         identity = x
+        if self.gemm_1x1:
+            if self.downsample is None:
+                # the skip connection's gradient comes back through conv1's backward (one fused GEMM + add)
+                y, p, identity = conv1x1_stats(x, self.conv1.weight, carry_skip=True)
+            else:
+                # conv1 and the projection shortcut read the same input: their input gradients are summed in
+                # conv1's dgrad GEMM
+                y, p, d, pd = conv1x1_dual(x, self.conv1.weight, self.downsample.weight, self.downsample.stride[0])
+                identity = self.bn_ds(d, partial=pd)
+            y = self.bn1(y, partial=p)
+            y = self.bn2(self.conv2(y))
+            y, p = conv1x1_stats(y, self.conv3.weight)
+            return self.bn3(y, identity, partial=p)
         y = self.bn1(self.conv1(x))
         y = self.bn2(self.conv2(y))
         if self.downsample is not None:
@@ -102,9 +131,10 @@ def stem_s2d_mask(out_channels: int) -> torch.Tensor:
 
 class ResNet(nn.Module):
     def __init__(self, layers=(3, 4, 6, 3), num_classes: int = 1000, fused: bool = True, width: int = 64,
-                 s2d_stem: bool = False):
+                 s2d_stem: bool = False, gemm_1x1: bool = False):
         super().__init__()
         self.fused = fused
+        self.gemm_1x1 = fused and gemm_1x1
         self.s2d_stem = s2d_stem
         if s2d_stem:
             # The 7x7 / stride 2 / pad 3 stem as a 4x4 / stride 1 convolution over the space-to-depth
@@ -120,7 +150,7 @@ class ResNet(nn.Module):
         for i, n in enumerate(layers):
             planes = width * (2 ** i)
             for j in range(n):
-                blocks.append(Bottleneck(inplanes, planes, (1 if i == 0 else 2) if j == 0 else 1, fused))
+                blocks.append(Bottleneck(inplanes, planes, (1 if i == 0 else 2) if j == 0 else 1, fused, gemm_1x1))
                 inplanes = planes * Bottleneck.expansion
         self.blocks = nn.Sequential(*blocks)
         self.avgpool = nn.AdaptiveAvgPool2d(1)
@@ -148,13 +178,13 @@ class ResNet(nn.Module):
         return self.fc(x)
 
 
-def resnet50(num_classes: int = 1000, fused: bool = True, s2d_stem: bool = False) -> ResNet:
-    return ResNet((3, 4, 6, 3), num_classes, fused, s2d_stem=s2d_stem)
+def resnet50(num_classes: int = 1000, fused: bool = True, s2d_stem: bool = False, gemm_1x1: bool = False) -> ResNet:
+    return ResNet((3, 4, 6, 3), num_classes, fused, s2d_stem=s2d_stem, gemm_1x1=gemm_1x1)
 
 
-def resnet_tiny(num_classes: int = 16, fused: bool = True, s2d_stem: bool = False) -> ResNet:
-    """Two-stage, narrow variant for smoke tests."""
-    return ResNet((1, 1), num_classes, fused, width=16, s2d_stem=s2d_stem)
+def resnet_tiny(num_classes: int = 16, fused: bool = True, s2d_stem: bool = False, gemm_1x1: bool = False) -> ResNet:
+    """Two-stage, narrow variant for smoke tests (width 16: conv3 of each block is wide enough for the GEMM path)."""
+    return ResNet((1, 1), num_classes, fused, width=16, s2d_stem=s2d_stem, gemm_1x1=gemm_1x1)
 
 
 def to_training_dtype(model: nn.Module, dtype=torch.bfloat16, bn_fp32: bool = False) -> nn.Module:

@@ -48,7 +48,7 @@ def _is_nhwc(t: torch.Tensor) -> bool:
 
 class _BnActFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, weight, bias, residual, running_mean, running_var, relu, eps, momentum, w32, b32):
+    def forward(ctx, x, weight, bias, residual, running_mean, running_var, relu, eps, momentum, w32, b32, partial=None):
         lib = _lib.load()
         assert x.is_cuda and x.dtype == torch.bfloat16
         if not _is_nhwc(x):
@@ -67,10 +67,18 @@ class _BnActFn(torch.autograd.Function):
         st = torch.cuda.current_stream().cuda_stream
         # ReLU derivative for the backward pass as one bit per element (instead of re-reading y)
         gate = torch.empty(m * c // 8, dtype=torch.uint8, device=x.device) if relu else None
-        _lib.check(lib.pdj_bn_fwd_gate(x.data_ptr(), _lib.ptr(residual), y.data_ptr(), _lib.ptr(gate), m, c,
-                                       gamma.data_ptr(), beta.data_ptr(), eps, momentum, _lib.ptr(running_mean),
-                                       _lib.ptr(running_var), stats.data_ptr(), stats[2:].data_ptr(), int(relu),
-                                       ws.data_ptr(), st), "bn_fwd")
+        if partial is not None:
+            # the producer of x (ops.conv.conv1x1_stats) already reduced the statistics to a few rows
+            assert partial.dtype == torch.float32 and partial.dim() == 3 and partial.shape[1:] == (2, c)
+            _lib.check(lib.pdj_bn_fwd_pre(x.data_ptr(), _lib.ptr(residual), y.data_ptr(), _lib.ptr(gate), m, c,
+                                          gamma.data_ptr(), beta.data_ptr(), eps, momentum, _lib.ptr(running_mean),
+                                          _lib.ptr(running_var), stats.data_ptr(), stats[2:].data_ptr(), int(relu),
+                                          partial.data_ptr(), partial.shape[0], st), "bn_fwd_pre")
+        else:
+            _lib.check(lib.pdj_bn_fwd_gate(x.data_ptr(), _lib.ptr(residual), y.data_ptr(), _lib.ptr(gate), m, c,
+                                           gamma.data_ptr(), beta.data_ptr(), eps, momentum, _lib.ptr(running_mean),
+                                           _lib.ptr(running_var), stats.data_ptr(), stats[2:].data_ptr(), int(relu),
+                                           ws.data_ptr(), st), "bn_fwd")
         ctx.save_for_backward(x, gate, gamma, stats)
         ctx.relu = relu
         ctx.has_res = residual is not None
@@ -101,15 +109,17 @@ class _BnActFn(torch.autograd.Function):
             dgamma, dbeta = dgb16[0], dgb16[1]
         else:
             dgamma, dbeta = dgb[0].to(ctx.wdtype), dgb[1].to(ctx.wdtype)
-        return dx, dgamma, dbeta, dres, None, None, None, None, None, None, None
+        return dx, dgamma, dbeta, dres, None, None, None, None, None, None, None, None
 
 
 def bn_act(x, weight, bias, residual: Optional[torch.Tensor] = None, running_mean=None, running_var=None,
-           relu: bool = True, eps: float = 1e-5, momentum: float = 0.1, weight_f32=None, bias_f32=None):
-    """y = relu?(BN_train(x) + residual?).  CUDA bf16 -> hand-written kernels."""
+           relu: bool = True, eps: float = 1e-5, momentum: float = 0.1, weight_f32=None, bias_f32=None,
+           partial: Optional[torch.Tensor] = None):
+    """y = relu?(BN_train(x) + residual?).  CUDA bf16 -> hand-written kernels.  `partial` ([rows, 2, C]
+    fp32 sums / sums of squares from ops.conv.conv1x1_stats) replaces the statistics pass over x."""
     if x.is_cuda:
         return _BnActFn.apply(x, weight, bias, residual, running_mean, running_var, relu, eps, momentum,
-                              weight_f32, bias_f32)
+                              weight_f32, bias_f32, partial)
     # CPU path (tests, plumbing): plain PyTorch.
     y = torch.nn.functional.batch_norm(x.float(), running_mean, running_var, weight.float(), bias.float(), True,
                                        momentum, eps)
@@ -135,10 +145,10 @@ class FusedBnAct(torch.nn.Module):
         self.register_buffer("running_mean", torch.zeros(channels))
         self.register_buffer("running_var", torch.ones(channels))
 
-    def forward(self, x, residual=None):
+    def forward(self, x, residual=None, partial=None):
         if self.training:
             return bn_act(x, self.weight, self.bias, residual, self.running_mean, self.running_var, self.relu,
-                          self.eps, self.momentum, self.weight_f32, self.bias_f32)
+                          self.eps, self.momentum, self.weight_f32, self.bias_f32, partial)
         y = torch.nn.functional.batch_norm(x.float(), self.running_mean, self.running_var, self.weight.float(),
                                            self.bias.float(), False, self.momentum, self.eps)
         if residual is not None:

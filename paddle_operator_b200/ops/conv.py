@@ -1,0 +1,219 @@
+"""1x1 convolution on the tcgen05 GEMM pipeline, fused with BatchNorm statistics.
+
+A stride-1 1x1 convolution over a channels-last activation is the GEMM
+[N*H*W, Cin] x [Cout, Cin]^T.  `conv1x1_stats` runs it on the hand-written
+TMA + tcgen05 kernel (csrc/gemm_tcgen05.cu::conv1x1_tcgen05_kernel) whose
+epilogue also accumulates the per-channel sum and sum of squares of the output,
+so the training-mode BatchNorm that follows (ops.bn, `partial=`) skips its
+statistics pass - one full read of the activation per layer.
+
+    y, partial = conv1x1_stats(x, weight)          # x NHWC bf16, weight [Cout, Cin, 1, 1] bf16
+    z = bn(y, residual, partial=partial)           # FusedBnAct
+
+Backward: input and weight gradients are plain library convolutions
+(aten.convolution_backward), exactly what autograd would have run.
+
+Reference parity: none - the reference launches a user image that runs the
+ResNet of deploy/examples/resnet.yaml:13-19; this is part of the compute layer
+the runtime owns.
+"""
+from __future__ import annotations
+
+import os
+from typing import Optional, Tuple
+
+import torch
+import torch.nn.functional as F
+
+from . import _lib
+
+
+# The fusion pays where the output does not fit in L2 (126 MB): below that the separate statistics
+# pass reads the activation from L2 right after the convolution wrote it, and costs little.
+MIN_OUTPUT_BYTES = int(float(os.environ.get("PDJ_CONV1X1_MIN_MB", "150")) * (1 << 20))
+
+
+def conv1x1_eligible(x: torch.Tensor, weight: torch.Tensor, stride=1, padding=0, min_bytes: int = 0) -> bool:
+    """True when the hand-written kernel can take this convolution."""
+    if min_bytes and x.numel() // x.shape[1] * weight.shape[0] * 2 < min_bytes:
+        return False
+    s = stride if isinstance(stride, int) else (stride[0] if stride[0] == stride[1] else -1)
+    p = padding if isinstance(padding, int) else (padding[0] if padding[0] == padding[1] else -1)
+    return (x.is_cuda and x.dtype == torch.bfloat16 and weight.dtype == torch.bfloat16 and x.dim() == 4
+            and weight.dim() == 4 and weight.shape[2] == 1 and weight.shape[3] == 1 and s == 1 and p == 0
+            and weight.shape[0] % 64 == 0 and weight.shape[1] % 8 == 0
+            and x.is_contiguous(memory_format=torch.channels_last))
+
+
+def conv1x1_gemm(x2: torch.Tensor, w2: torch.Tensor, stats: bool = True,
+                 out: Optional[torch.Tensor] = None) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
+    """out[M,N] = x2[M,K] @ w2[N,K]^T on the kernel; also the [rows, 2, N] fp32 partial sums when `stats`."""
+    lib = _lib.load()
+    m, k = x2.shape
+    n = w2.shape[0]
+    assert x2.stride(1) == 1 and w2.stride(1) == 1 and w2.shape[1] == k
+    if out is None:
+        out = torch.empty((m, n), dtype=torch.bfloat16, device=x2.device)
+    partial = None
+    if stats:
+        rows = lib.pdj_conv1x1_partial_rows(m, n)
+        if rows < 1:
+            raise ValueError(f"conv1x1: unsupported shape M={m} N={n}")
+        partial = torch.empty((rows, 2, n), dtype=torch.float32, device=x2.device)
+    _lib.check(lib.pdj_conv1x1_bf16(x2.data_ptr(), w2.data_ptr(), out.data_ptr(), _lib.ptr(partial), m, n, k,
+                                    x2.stride(0), w2.stride(0), out.stride(0),
+                                    torch.cuda.current_stream().cuda_stream), "conv1x1_bf16")
+    return out, partial
+
+
+def conv1x1_gemm_add(a2: torch.Tensor, b2: torch.Tensor, addend2: torch.Tensor,
+                     out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """out[M,N] = addend2[M,N] + a2[M,K] @ b2[N,K]^T on the kernel (out may be addend2 itself)."""
+    m, k = a2.shape
+    n = b2.shape[0]
+    assert a2.stride(1) == 1 and b2.stride(1) == 1 and b2.shape[1] == k and addend2.shape == (m, n)
+    assert addend2.stride(1) == 1
+    if out is None:
+        out = torch.empty((m, n), dtype=torch.bfloat16, device=a2.device)
+    _lib.check(_lib.load().pdj_conv1x1_add_bf16(a2.data_ptr(), b2.data_ptr(), addend2.data_ptr(), out.data_ptr(), m, n, k,
+                                                a2.stride(0), b2.stride(0), addend2.stride(0), out.stride(0),
+                                                torch.cuda.current_stream().cuda_stream), "conv1x1_add_bf16")
+    return out
+
+
+def _rows(t: torch.Tensor) -> torch.Tensor:
+    """[N,C,H,W] channels-last -> its storage as [N*H*W, C] (a view)."""
+    n, c, h, w = t.shape
+    v = t.permute(0, 2, 3, 1).reshape(n * h * w, c)
+    assert v.data_ptr() == t.data_ptr()
+    return v
+
+
+class _Conv1x1StatsFn(torch.autograd.Function):
+    """y = conv1x1(x, weight) with BN partial sums; with `carry_skip` the input is also handed through as a
+    third output, so that the gradient of whatever consumes it (the block's skip connection) arrives in
+    the same backward call and is folded into the input-gradient GEMM instead of a separate add pass."""
+
+    @staticmethod
+    def forward(ctx, x, weight, carry_skip, use_gemm):
+        n, c, h, w = x.shape
+        o = weight.shape[0]
+        if use_gemm:
+            y = torch.empty((n, o, h, w), dtype=x.dtype, device=x.device, memory_format=torch.channels_last)
+            _, partial = conv1x1_gemm(_rows(x), weight.reshape(o, c), stats=True, out=_rows(y))
+            ctx.mark_non_differentiable(partial)
+        else:  # library forward (small layers); the fused skip-gradient backward below still applies
+            y, partial = F.conv2d(x, weight), None
+        ctx.save_for_backward(x, weight)
+        ctx.carry_skip = carry_skip
+        if carry_skip:
+            return y, partial, x.view_as(x)
+        return y, partial
+
+    @staticmethod
+    def backward(ctx, dy, _dpartial, dskip=None):
+        x, weight = ctx.saved_tensors
+        if not dy.is_contiguous(memory_format=torch.channels_last):
+            dy = dy.contiguous(memory_format=torch.channels_last)
+        o, c = weight.shape[0], weight.shape[1]
+        fuse = (ctx.carry_skip and dskip is not None and ctx.needs_input_grad[0] and c % 64 == 0 and o % 8 == 0)
+        dx, dw, _ = torch.ops.aten.convolution_backward(
+            dy, x, weight, None, [1, 1], [0, 0], [1, 1], False, [0, 0], 1,
+            [ctx.needs_input_grad[0] and not fuse, ctx.needs_input_grad[1], False])
+        if fuse:
+            if not dskip.is_contiguous(memory_format=torch.channels_last):
+                dskip = dskip.contiguous(memory_format=torch.channels_last)
+            # dX[M,Cin] = dskip + dY[M,Cout] @ W[Cout,Cin]: the B operand is W^T, K-major over Cout
+            wt = weight.reshape(o, c).t().contiguous()
+            dx = torch.empty_like(x, memory_format=torch.channels_last)
+            conv1x1_gemm_add(_rows(dy), wt, _rows(dskip), out=_rows(dx))
+        elif ctx.carry_skip and dskip is not None and dx is not None:
+            dx = dx + dskip
+        elif ctx.carry_skip and dskip is not None:
+            dx = dskip
+        return dx, dw, None, None
+
+
+def conv1x1_stats(x: torch.Tensor, weight: torch.Tensor, carry_skip: bool = False):
+    """1x1 / stride 1 convolution; returns (y, partial sums for the following BatchNorm) or, with
+    `carry_skip`, (y, partial, x') where x' is x for the skip connection (see _Conv1x1StatsFn).
+    `partial` is None where the forward ran in the library (shapes the kernel does not take, or outputs
+    below MIN_OUTPUT_BYTES); the fused skip-gradient backward is used whenever the transposed GEMM fits."""
+    fwd = conv1x1_eligible(x, weight, min_bytes=MIN_OUTPUT_BYTES)
+    bwd = carry_skip and _dgrad_eligible(x, weight)
+    if fwd or bwd:
+        out = _Conv1x1StatsFn.apply(x, weight, bool(bwd), bool(fwd))
+        return (out[0], out[1], x) if (carry_skip and not bwd) else out
+    y = F.conv2d(x, weight)
+    return (y, None, x) if carry_skip else (y, None)
+
+
+class _Conv1x1DualFn(torch.autograd.Function):
+    """The two 1x1 convolutions that read the input of a down-sampling bottleneck: conv1 (stride 1) and the
+    projection shortcut (stride s).  Their input gradients are summed inside one GEMM: the shortcut's
+    dgrad comes from the library, conv1's dgrad runs on the tcgen05 kernel with that tensor as addend."""
+
+    @staticmethod
+    def forward(ctx, x, w1, w_ds, stride, gemm1, gemm_ds):
+        n, c, h, w = x.shape
+        o1 = w1.shape[0]
+        if gemm1:
+            y1 = torch.empty((n, o1, h, w), dtype=x.dtype, device=x.device, memory_format=torch.channels_last)
+            _, p1 = conv1x1_gemm(_rows(x), w1.reshape(o1, c), stats=True, out=_rows(y1))
+            ctx.mark_non_differentiable(p1)
+        else:
+            y1, p1 = F.conv2d(x, w1), None
+        if gemm_ds:
+            od = w_ds.shape[0]
+            yd = torch.empty((n, od, h, w), dtype=x.dtype, device=x.device, memory_format=torch.channels_last)
+            _, pd = conv1x1_gemm(_rows(x), w_ds.reshape(od, c), stats=True, out=_rows(yd))
+            ctx.mark_non_differentiable(pd)
+        else:
+            yd, pd = F.conv2d(x, w_ds, stride=stride), None
+        ctx.save_for_backward(x, w1, w_ds)
+        ctx.stride = stride
+        return y1, p1, yd, pd
+
+    @staticmethod
+    def backward(ctx, dy1, _dp1, dyd, _dpd):
+        x, w1, w_ds = ctx.saved_tensors
+        cl = torch.channels_last
+        dy1 = dy1 if dy1.is_contiguous(memory_format=cl) else dy1.contiguous(memory_format=cl)
+        dyd = dyd if dyd.is_contiguous(memory_format=cl) else dyd.contiguous(memory_format=cl)
+        s = ctx.stride
+        need_x = ctx.needs_input_grad[0]
+        g, dwd, _ = torch.ops.aten.convolution_backward(dyd, x, w_ds, None, [s, s], [0, 0], [1, 1], False, [0, 0], 1,
+                                                        [need_x, ctx.needs_input_grad[2], False])
+        _, dw1, _ = torch.ops.aten.convolution_backward(dy1, x, w1, None, [1, 1], [0, 0], [1, 1], False, [0, 0], 1,
+                                                        [False, ctx.needs_input_grad[1], False])
+        dx = None
+        if need_x:
+            o1, c = w1.shape[0], w1.shape[1]
+            g = g if g.is_contiguous(memory_format=cl) else g.contiguous(memory_format=cl)
+            wt = w1.reshape(o1, c).t().contiguous()
+            conv1x1_gemm_add(_rows(dy1), wt, _rows(g), out=_rows(g))  # in place: g += dY1 @ W1
+            dx = g
+        return dx, dw1, dwd, None, None, None
+
+
+def conv1x1_dual(x: torch.Tensor, w1: torch.Tensor, w_ds: torch.Tensor, stride: int):
+    """(conv1(x), partial1, shortcut(x), partial_ds) for a down-sampling bottleneck; None partials where the
+    forward ran in the library.  Falls back to two plain convolutions when conv1's dgrad GEMM does not fit."""
+    if _dgrad_eligible(x, w1) and w_ds.dim() == 4 and w_ds.shape[2] == 1 and w_ds.shape[3] == 1:
+        gemm1 = conv1x1_eligible(x, w1, min_bytes=MIN_OUTPUT_BYTES)
+        gemm_ds = stride == 1 and conv1x1_eligible(x, w_ds, min_bytes=MIN_OUTPUT_BYTES)
+        return _Conv1x1DualFn.apply(x, w1, w_ds, int(stride), bool(gemm1), bool(gemm_ds))
+    y1, p1 = conv1x1_stats(x, w1)
+    if stride == 1:
+        yd, pd = conv1x1_stats(x, w_ds)
+    else:
+        yd, pd = F.conv2d(x, w_ds, stride=stride), None
+    return y1, p1, yd, pd
+
+
+def _dgrad_eligible(x: torch.Tensor, weight: torch.Tensor) -> bool:
+    """dX = dskip + dY @ W as a GEMM with N = Cin, K = Cout."""
+    return (x.is_cuda and x.dtype == torch.bfloat16 and weight.dtype == torch.bfloat16 and x.dim() == 4
+            and weight.dim() == 4 and weight.shape[2] == 1 and weight.shape[3] == 1
+            and weight.shape[1] % 64 == 0 and weight.shape[0] % 8 == 0
+            and x.is_contiguous(memory_format=torch.channels_last))

@@ -239,6 +239,8 @@ class CollectiveTrainer:
 
         n = sum(4 for m in self.model.modules() if isinstance(m, FusedBnAct))
         n += sum(2 for m in self.model.modules() if isinstance(m, FusedMaxPool2d))
+        # modules that launch further hand-written kernels say how many (e.g. the tcgen05 1x1 convolutions)
+        n += sum(int(m.pdj_kernels_per_step()) for m in self.model.modules() if hasattr(m, "pdj_kernels_per_step"))
         return n + self.extra_kernels_per_step
 
     def step(self) -> torch.Tensor:

@@ -36,12 +36,16 @@ class ResNetJob:
                  device: Optional[torch.device] = None, lr: float = 0.1, momentum: float = 0.9,
                  weight_decay: float = 1e-4, use_graph: bool = True, tiny: bool = False, seed: int = 0,
                  bucket_bytes: int = 16 << 20, comm_blocks: int = 24, algo: Optional[int] = None,
-                 s2d_stem: bool = True):
+                 s2d_stem: bool = True, gemm_1x1: Optional[bool] = None):
         self.device = device or torch.device("cuda", torch.cuda.current_device())
+        if gemm_1x1 is None:  # stride-1 1x1 convolutions on the tcgen05 GEMM with fused BN statistics
+            gemm_1x1 = os.environ.get("PDJ_RESNET_GEMM_1X1", "1") == "1"
+        self.gemm_1x1 = gemm_1x1
         self.batch, self.image = batch, image
         torch.manual_seed(seed)  # identical initial weights on every rank
         self.s2d = s2d_stem and image % 2 == 0
-        model = (resnet_tiny if tiny else resnet50)(num_classes=num_classes, fused=True, s2d_stem=self.s2d)
+        model = (resnet_tiny if tiny else resnet50)(num_classes=num_classes, fused=True, s2d_stem=self.s2d,
+                                                    gemm_1x1=gemm_1x1)
         model = to_training_dtype(model.to(self.device), torch.bfloat16)
         model.train()
         self.model = model

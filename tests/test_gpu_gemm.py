@@ -5,6 +5,14 @@ import torch
 pytestmark = pytest.mark.gpu
 
 
+@pytest.fixture(autouse=True)
+def _conv_gemm_for_every_size(monkeypatch):
+    """The product only routes outputs larger than L2 through the 1x1-convolution GEMM; the tests use small shapes."""
+    from paddle_operator_b200.ops import conv as conv_ops
+
+    monkeypatch.setattr(conv_ops, "MIN_OUTPUT_BYTES", 0)
+
+
 @pytest.mark.parametrize("m,n,k", [(128, 128, 64), (256, 400, 400), (1000, 400, 432), (4096, 1, 400), (77, 24, 40),
                                    (32768, 400, 400), (513, 1000, 2048)])
 @pytest.mark.parametrize("relu,use_bias", [(False, False), (True, True)])
@@ -80,3 +88,127 @@ def test_fused_mlp_matches_torch():
         # sum over 2048 rows by one gradient element (~0.1), hence the absolute tolerances
         torch.testing.assert_close(l.weight.grad.float(), r.weight.grad, atol=1.0, rtol=5e-2)
         torch.testing.assert_close(l.bias.grad.float(), r.bias.grad, atol=1.0, rtol=5e-2)
+
+
+# ---- 1x1 convolution GEMM with BatchNorm statistics in the epilogue (ops/conv.py) ----------------
+@pytest.mark.gpu
+@pytest.mark.parametrize("n,hw,cin,cout", [(4, 14, 64, 64), (2, 28, 256, 128), (3, 7, 128, 512), (2, 9, 72, 192),
+                                           (8, 56, 64, 256)])
+def test_conv1x1_stats_matches_conv2d(n, hw, cin, cout):
+    from paddle_operator_b200.ops import conv as conv_ops
+
+    torch.manual_seed(cin + cout)
+    x = torch.randn(n, cin, hw, hw, device="cuda", dtype=torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    w = (torch.randn(cout, cin, 1, 1, device="cuda", dtype=torch.bfloat16) * 0.1).contiguous(memory_format=torch.channels_last)
+    assert conv_ops.conv1x1_eligible(x, w)
+    y, partial = conv_ops.conv1x1_stats(x, w)
+    ref = torch.nn.functional.conv2d(x.float(), w.float())
+    assert y.shape == ref.shape and y.is_contiguous(memory_format=torch.channels_last)
+    torch.testing.assert_close(y.float(), ref, atol=2e-2, rtol=2e-2)
+    # the partial rows add up to the sums of the values as stored (bf16-rounded)
+    yf = y.float()
+    s_ref, q_ref = yf.sum(dim=(0, 2, 3)), (yf * yf).sum(dim=(0, 2, 3))
+    torch.testing.assert_close(partial[:, 0].sum(0), s_ref, atol=1e-4 * float(yf.abs().sum(dim=(0, 2, 3)).max()), rtol=1e-3)
+    torch.testing.assert_close(partial[:, 1].sum(0), q_ref, atol=1e-3, rtol=1e-3)
+    # bit-reproducible
+    y2, partial2 = conv_ops.conv1x1_stats(x, w)
+    assert torch.equal(y, y2) and torch.equal(partial, partial2)
+
+
+@pytest.mark.gpu
+def test_conv1x1_bn_chain_matches_reference_forward_backward():
+    from paddle_operator_b200.ops import bn as bn_ops
+    from paddle_operator_b200.ops import conv as conv_ops
+
+    torch.manual_seed(5)
+    n, hw, cin, cout = 4, 14, 64, 128
+    x = torch.randn(n, cin, hw, hw, device="cuda", dtype=torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    res = torch.randn(n, cout, hw, hw, device="cuda", dtype=torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    w = (torch.randn(cout, cin, 1, 1, device="cuda", dtype=torch.bfloat16) * 0.1).contiguous(memory_format=torch.channels_last)
+    gamma = torch.rand(cout, device="cuda") + 0.5
+    beta = torch.randn(cout, device="cuda") * 0.1
+    xa, wa, ga, ba = (t.clone().requires_grad_(True) for t in (x, w, gamma, beta))
+    rm, rv = torch.zeros(cout, device="cuda"), torch.ones(cout, device="cuda")
+    y, partial = conv_ops.conv1x1_stats(xa, wa)
+    z = bn_ops.bn_act(y, ga, ba, res, rm, rv, relu=True, partial=partial)
+    # same chain with the statistics pass over y (the path without fusion): identical statistics source values
+    xb, wb, gb, bb = (t.clone().requires_grad_(True) for t in (x, w, gamma, beta))
+    rm2, rv2 = torch.zeros(cout, device="cuda"), torch.ones(cout, device="cuda")
+    y_b = torch.nn.functional.conv2d(xb, wb)
+    z_b = bn_ops.bn_act(y_b, gb, bb, res, rm2, rv2, relu=True)
+    torch.testing.assert_close(z.float(), z_b.float(), atol=3e-2, rtol=3e-2)
+    torch.testing.assert_close(rm, rm2, atol=1e-3, rtol=1e-3)
+    torch.testing.assert_close(rv, rv2, atol=1e-3, rtol=1e-3)
+    # fp32 oracle
+    ref = bn_ops.bn_act_reference(torch.nn.functional.conv2d(x.float(), w.float()), gamma, beta, res, relu=True)
+    torch.testing.assert_close(z.float(), ref, atol=6e-2, rtol=6e-2)
+    g = torch.randn_like(z)
+    z.backward(g)
+    z_b.backward(g)
+    torch.testing.assert_close(xa.grad.float(), xb.grad.float(), atol=3e-2, rtol=3e-2)
+    torch.testing.assert_close(wa.grad.float(), wb.grad.float(), atol=0.3, rtol=5e-2)
+    torch.testing.assert_close(ga.grad, gb.grad, atol=0.5, rtol=5e-2)
+
+
+@pytest.mark.parametrize("n,hw,cin,cout", [(4, 14, 64, 16), (2, 28, 256, 64), (3, 7, 512, 128), (2, 9, 192, 72)])
+def test_conv1x1_skip_gradient_is_folded_into_dgrad(n, hw, cin, cout):
+    """y = conv(x) + skip path on x: the fused backward (one GEMM with addend) equals autograd's conv dgrad + add."""
+    from paddle_operator_b200.ops import conv as conv_ops
+
+    torch.manual_seed(cin * 3 + cout)
+    x = torch.randn(n, cin, hw, hw, device="cuda", dtype=torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    w = (torch.randn(cout, cin, 1, 1, device="cuda", dtype=torch.bfloat16) * 0.1).contiguous(memory_format=torch.channels_last)
+    gy = torch.randn(n, cout, hw, hw, device="cuda", dtype=torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    gs = torch.randn(n, cin, hw, hw, device="cuda", dtype=torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    xa, wa = x.clone().requires_grad_(True), w.clone().requires_grad_(True)
+    y, partial, skip = conv_ops.conv1x1_stats(xa, wa, carry_skip=True)
+    assert skip.data_ptr() == xa.data_ptr()
+    torch.autograd.backward([y, skip], [gy, gs])
+    xb, wb = x.float().requires_grad_(True), w.float().requires_grad_(True)
+    yb = torch.nn.functional.conv2d(xb, wb)
+    torch.autograd.backward([yb, xb * 1.0], [gy.float(), gs.float()])
+    torch.testing.assert_close(y.float(), yb, atol=3e-2, rtol=3e-2)
+    torch.testing.assert_close(xa.grad.float(), xb.grad, atol=4e-2, rtol=3e-2)
+    torch.testing.assert_close(wa.grad.float(), wb.grad, atol=0.25, rtol=5e-2)
+
+
+def test_conv1x1_gemm_add_in_place():
+    from paddle_operator_b200.ops import conv as conv_ops
+
+    torch.manual_seed(11)
+    m, n, k = 1000, 320, 136
+    a = (torch.randn(m, k, device="cuda") * 0.3).to(torch.bfloat16)
+    b = (torch.randn(n, k, device="cuda") * 0.3).to(torch.bfloat16)
+    c = torch.randn(m, n, device="cuda").to(torch.bfloat16)
+    ref = c.float() + a.float() @ b.float().t()
+    out = conv_ops.conv1x1_gemm_add(a, b, c)
+    torch.testing.assert_close(out.float(), ref, atol=6e-2, rtol=2e-2)
+    c2 = c.clone()
+    conv_ops.conv1x1_gemm_add(a, b, c2, out=c2)
+    assert torch.equal(c2, out)
+
+
+@pytest.mark.parametrize("stride,cin,c1,cd", [(2, 64, 32, 128), (1, 64, 64, 256), (2, 256, 128, 512)])
+def test_conv1x1_dual_backward_sums_both_input_gradients(stride, cin, c1, cd):
+    from paddle_operator_b200.ops import conv as conv_ops
+
+    torch.manual_seed(cin + c1 + cd + stride)
+    n, hw = 3, 12
+    cl = torch.channels_last
+    x = torch.randn(n, cin, hw, hw, device="cuda", dtype=torch.bfloat16).contiguous(memory_format=cl)
+    w1 = (torch.randn(c1, cin, 1, 1, device="cuda", dtype=torch.bfloat16) * 0.1).contiguous(memory_format=cl)
+    wd = (torch.randn(cd, cin, 1, 1, device="cuda", dtype=torch.bfloat16) * 0.1).contiguous(memory_format=cl)
+    xa, w1a, wda = (t.clone().requires_grad_(True) for t in (x, w1, wd))
+    y1, p1, yd, pd = conv_ops.conv1x1_dual(xa, w1a, wda, stride)
+    xb, w1b, wdb = (t.float().requires_grad_(True) for t in (x, w1, wd))
+    r1 = torch.nn.functional.conv2d(xb, w1b)
+    rd = torch.nn.functional.conv2d(xb, wdb, stride=stride)
+    torch.testing.assert_close(y1.float(), r1, atol=3e-2, rtol=3e-2)
+    torch.testing.assert_close(yd.float(), rd, atol=3e-2, rtol=3e-2)
+    g1 = torch.randn_like(y1)
+    gd = torch.randn_like(yd)
+    torch.autograd.backward([y1, yd], [g1, gd])
+    torch.autograd.backward([r1, rd], [g1.float(), gd.float()])
+    torch.testing.assert_close(xa.grad.float(), xb.grad, atol=6e-2, rtol=3e-2)
+    torch.testing.assert_close(w1a.grad.float(), w1b.grad, atol=0.25, rtol=5e-2)
+    torch.testing.assert_close(wda.grad.float(), wdb.grad, atol=0.25, rtol=5e-2)

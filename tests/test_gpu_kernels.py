@@ -231,15 +231,23 @@ def test_alltoall_broadcast_barrier(comms, nranks):
 
 
 # ---------------------------------------------------------------------------
-def test_resnet_fused_matches_torch(dev):
-    """Few-step loss parity: fused model + engine vs stock torch modules + torch SGD."""
+@pytest.mark.parametrize("gemm_1x1", [False, True])
+def test_resnet_fused_matches_torch(dev, gemm_1x1, monkeypatch):
+    """Few-step loss parity: fused model + engine vs stock torch modules + torch SGD.  With gemm_1x1 the
+    64-channel 1x1 convolutions of the tiny model run on the tcgen05 kernel with fused BN statistics."""
     from paddle_operator_b200.models.resnet import resnet_tiny, to_training_dtype
     from paddle_operator_b200.ops.optim import softmax_cross_entropy
     from paddle_operator_b200.parallel.collective import CollectiveTrainer
 
     torch.manual_seed(0)
-    ref = resnet_tiny(num_classes=16, fused=False).to(dev).float().train()
-    fused = resnet_tiny(num_classes=16, fused=True).to(dev)
+    from paddle_operator_b200.models.resnet import ResNet
+    from paddle_operator_b200.ops import conv as conv_ops
+
+    monkeypatch.setattr(conv_ops, "MIN_OUTPUT_BYTES", 0)  # small activations: take the GEMM path anyway
+    # two blocks per stage, so that the second one has a plain skip connection (fused dgrad + add path)
+    layers = (2, 2) if gemm_1x1 else (1, 1)
+    ref = ResNet(layers, 16, fused=False, width=16).to(dev).float().train()
+    fused = ResNet(layers, 16, fused=True, width=16, gemm_1x1=gemm_1x1).to(dev)
     with torch.no_grad():
         for pf, pr in zip(fused.parameters(), ref.parameters()):
             pf.copy_(pr)
