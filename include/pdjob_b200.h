@@ -127,6 +127,13 @@ int pdj_conv1x1_bf16(const void* a, const void* b, void* out, float* partial, in
  * first 1x1 convolution with the skip connection's gradient folded in. */
 int pdj_conv1x1_add_bf16(const void* a, const void* b, const void* addend, void* out, int M, int N, int K, int lda,
                          int ldb, int ldc, int ldo, cudaStream_t st);
+/* ResNet stem on the same pipeline: the 7x7 / stride-2 convolution expressed as a 4x4 / stride-1
+ * convolution (16 -> 64 channels) over the space-to-depth input x[N][Ho+3][Wo+3][16] (see
+ * pdj_preprocess_u8_s2d); w[64][4][4][16] bf16, out[N][Ho][Wo][64] bf16, Wo <= 128.  The A operand is read
+ * through a TMA tensor map with overlapping pixel windows: no im2col buffer.  `partial` as above, with
+ * pdj_stem_s2d_partial_rows(N * Ho) rows (NULL to skip). */
+int pdj_stem_s2d_partial_rows(int n_rows);
+int pdj_stem_s2d_fwd(const void* x, const void* w, void* out, float* partial, int N, int Ho, int Wo, cudaStream_t st);
 
 /* ---- ResNet-50 step kernels (csrc/bn_act.cu, csrc/optim_misc.cu) -----------
  * The workload of deploy/examples/resnet.yaml:13-19. NHWC bf16 activations

@@ -72,6 +72,17 @@ __device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, uint32_t sr
                "r"(c1)
                : "memory");
 }
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map, int c0, int c1, int c2, uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(dst),
+      "l"(map), "r"(c0), "r"(c1), "r"(c2), "r"(bar)
+      : "memory");
+}
+__device__ __forceinline__ void tma_store_3d(const CUtensorMap* map, uint32_t src, int c0, int c1, int c2) {
+  asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(map), "r"(src), "r"(c0),
+               "r"(c1), "r"(c2)
+               : "memory");
+}
 // Shared-memory matrix descriptor: K-major tile, 128-byte swizzle, rows 128 B apart,
 // 8-row groups 1024 B apart (SBO), descriptor version 1 (sm_100).
 __device__ __forceinline__ uint64_t umma_desc(uint32_t smem_addr) {
@@ -336,13 +347,21 @@ constexpr int SW_SCRATCH_BYTES = 2 * 2 * 4 * BOX_N * 4;  // [group][sum|sq][warp
 // residual-gradient add of a bottleneck block folded into the input-gradient GEMM of its first conv.
 constexpr int MODE_PLAIN = 0, MODE_STATS = 1, MODE_ADD = 2;
 
-template <int MODE>
+//
+// WIN (the ResNet stem): the same pipeline as a 4x4 / stride-1 convolution over the space-to-depth input
+// [n][Hi][Wi][16].  One tile = one output row (n, y) of up to 128 pixels; its A operand for K block jy is
+// the 3-D TMA box {64 elements, 128 pixels, row n*Hi + y + jy} of a tensor map whose pixel stride is 16
+// elements - consecutive pixels' 64-element windows (4 taps x 16 channels) overlap in memory, so no
+// im2col buffer exists anywhere.  Pixels beyond Wo are zero-filled on load and clipped on store.
+template <int MODE, bool WIN>
 __global__ void __launch_bounds__(THREADS, 1)
 conv1x1_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                        const __grid_constant__ CUtensorMap tma_o, const __grid_constant__ CUtensorMap tma_c,
-                       float* __restrict__ partial, int M, int N, int K, int block_n, int stages) {
+                       float* __restrict__ partial, int M, int N, int K, int block_n, int stages, int win_ho,
+                       int win_hi) {
   constexpr bool STATS = MODE == MODE_STATS;
   constexpr bool ADD = MODE == MODE_ADD;
+  static_assert(!(WIN && ADD), "the stem has no addend mode");
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
   const uint32_t base = (raw + 1023u) & ~1023u;
@@ -360,7 +379,7 @@ conv1x1_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_c
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int tiles_n = N / block_n;
-  const int total = ((M + BM - 1) / BM) * tiles_n;
+  const int total = WIN ? M : ((M + BM - 1) / BM) * tiles_n;  // WIN: M counts output rows, one tile each
   const int num_kb = (K + BK - 1) / BK;
 
   if (warp == 0 && lane == 0) {
@@ -394,7 +413,24 @@ conv1x1_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_c
   const Pipe pipe{a_smem, b_smem, b_stage_bytes, full0, empty0, tfull0, tempty0, stages};
 
   if (warp == 0) {
-    if (lane == 0) producer_loop(&tma_a, &tma_b, pipe, total, tiles_n, block_n, num_kb);
+    if (lane == 0) {
+      if (WIN) {
+        const uint32_t stage_bytes = (uint32_t)A_STAGE_BYTES + b_stage_bytes;
+        uint32_t it = 0;
+        for (int t = blockIdx.x; t < total; t += gridDim.x) {
+          const int xrow = (t / win_ho) * win_hi + (t % win_ho);  // first input row of output row t
+          for (int kb = 0; kb < num_kb; ++kb, ++it) {
+            const uint32_t s = it % (uint32_t)stages, ph = (it / (uint32_t)stages) & 1u;
+            mbar_wait(empty0 + 8 * s, ph ^ 1u);
+            mbar_expect_tx(full0 + 8 * s, stage_bytes);
+            tma_load_3d(a_smem + s * A_STAGE_BYTES, &tma_a, 0, 0, xrow + kb, full0 + 8 * s);
+            tma_load_2d(b_smem + s * b_stage_bytes, &tma_b, kb * BK, 0, full0 + 8 * s);
+          }
+        }
+      } else {
+        producer_loop(&tma_a, &tma_b, pipe, total, tiles_n, block_n, num_kb);
+      }
+    }
   } else if (warp == 1) {
     if (lane == 0) mma_loop(pipe, tmem_base, total, block_n, num_kb);
   } else {
@@ -490,7 +526,8 @@ conv1x1_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_c
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
         if (gt == 0) {
-          tma_store_2d(&tma_o, stg, n0 + b * BOX_N, m0);  // rows beyond M are clipped by the tensor map
+          if (WIN) tma_store_3d(&tma_o, stg, b * BOX_N, 0, (int)t);  // pixels beyond Wo are clipped
+          else tma_store_2d(&tma_o, stg, n0 + b * BOX_N, m0);        // rows beyond M are clipped by the tensor map
           asm volatile("cp.async.bulk.commit_group;" ::: "memory");
           if (ADD) {
             // request the next box's addend into the other buffer once the store out of it (the previous
@@ -588,6 +625,31 @@ int make_map(CUtensorMap* map, const void* ptr, int rows, int cols, int ld_elems
   return 0;
 }
 
+// 3-D map {d0 contiguous elements, d1 with stride s1 bytes, d2 with stride s2 bytes}, 128-byte swizzle.
+int make_map3(CUtensorMap* map, const void* ptr, uint64_t d0, uint64_t d1, uint64_t d2, uint64_t s1, uint64_t s2, int b0,
+              int b1) {
+  if (g_encode == nullptr) {
+    CUtensorMap dummy;
+    static __nv_bfloat16 probe[64];
+    (void)make_map(&dummy, probe, 1, 64, 64, 64, 1, false);  // resolves the driver entry point
+    if (g_encode == nullptr) return -1;
+  }
+  const cuuint64_t dims[3] = {d0, d1, d2};
+  const cuuint64_t strides[2] = {s1, s2};
+  const cuuint32_t box[3] = {(cuuint32_t)b0, (cuuint32_t)b1, 1};
+  const cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = g_encode(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(ptr), dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    pdj_set_error("cuTensorMapEncodeTiled (3-D) failed with CUresult %d (dims %llu x %llu x %llu, strides %llu, %llu)", (int)r,
+                  (unsigned long long)d0, (unsigned long long)d1, (unsigned long long)d2, (unsigned long long)s1,
+                  (unsigned long long)s2);
+    return (int)r;
+  }
+  return 0;
+}
+
 bool g_attr_set = false;
 int g_sms = 0;
 
@@ -595,9 +657,11 @@ int ensure_init() {
   if (g_attr_set) return 0;
   PDJ_CUDA_CHECK(cudaFuncSetAttribute(linear_tcgen05_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
   PDJ_CUDA_CHECK(cudaFuncSetAttribute(linear_tcgen05_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
-  PDJ_CUDA_CHECK(cudaFuncSetAttribute(conv1x1_tcgen05_kernel<MODE_PLAIN>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
-  PDJ_CUDA_CHECK(cudaFuncSetAttribute(conv1x1_tcgen05_kernel<MODE_STATS>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
-  PDJ_CUDA_CHECK(cudaFuncSetAttribute(conv1x1_tcgen05_kernel<MODE_ADD>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+  PDJ_CUDA_CHECK(cudaFuncSetAttribute(conv1x1_tcgen05_kernel<MODE_PLAIN, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+  PDJ_CUDA_CHECK(cudaFuncSetAttribute(conv1x1_tcgen05_kernel<MODE_STATS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+  PDJ_CUDA_CHECK(cudaFuncSetAttribute(conv1x1_tcgen05_kernel<MODE_ADD, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+  PDJ_CUDA_CHECK(cudaFuncSetAttribute(conv1x1_tcgen05_kernel<MODE_PLAIN, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+  PDJ_CUDA_CHECK(cudaFuncSetAttribute(conv1x1_tcgen05_kernel<MODE_STATS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
   int dev = 0;
   PDJ_CUDA_CHECK(cudaGetDevice(&dev));
   PDJ_CUDA_CHECK(cudaDeviceGetAttribute(&g_sms, cudaDevAttrMultiProcessorCount, dev));
@@ -740,11 +804,49 @@ static int launch_conv1x1(const void* a, const void* b, const void* addend, void
   const int smem = fixed + stages * stage_bytes;
   const int grid = conv_grid(M, N, bn, g_sms);
   if (addend != nullptr)
-    conv1x1_tcgen05_kernel<MODE_ADD><<<grid, THREADS, smem, st>>>(ma, mb, mo, mc, nullptr, M, N, K, bn, stages);
+    conv1x1_tcgen05_kernel<MODE_ADD, false><<<grid, THREADS, smem, st>>>(ma, mb, mo, mc, nullptr, M, N, K, bn, stages, 0, 0);
   else if (partial != nullptr)
-    conv1x1_tcgen05_kernel<MODE_STATS><<<grid, THREADS, smem, st>>>(ma, mb, mo, mc, partial, M, N, K, bn, stages);
+    conv1x1_tcgen05_kernel<MODE_STATS, false><<<grid, THREADS, smem, st>>>(ma, mb, mo, mc, partial, M, N, K, bn, stages, 0, 0);
   else
-    conv1x1_tcgen05_kernel<MODE_PLAIN><<<grid, THREADS, smem, st>>>(ma, mb, mo, mc, nullptr, M, N, K, bn, stages);
+    conv1x1_tcgen05_kernel<MODE_PLAIN, false><<<grid, THREADS, smem, st>>>(ma, mb, mo, mc, nullptr, M, N, K, bn, stages, 0, 0);
+  PDJ_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+int pdj_stem_s2d_partial_rows(int n_rows) {
+  if (n_rows < 1) return 0;
+  const int sms = sm_count_cached();
+  return 2 * (n_rows < sms ? n_rows : sms);
+}
+
+// ResNet stem: 4x4 / stride-1 convolution, 16 -> 64 channels, over the space-to-depth input
+// x[N][Ho+3][Wo+3][16] (ops/optim.py), weights w[64][4][4][16] (channels-last memory of [64,16,4,4]),
+// out[N][Ho][Wo][64]; optional BN partial sums as in pdj_conv1x1_bf16 (pdj_stem_s2d_partial_rows(N*Ho) rows).
+int pdj_stem_s2d_fwd(const void* x, const void* w, void* out, float* partial, int N, int Ho, int Wo, cudaStream_t st) {
+  if (N < 1 || Ho < 1 || Wo < 1 || Wo > BM || ((uintptr_t)x & 15) || ((uintptr_t)w & 15) || ((uintptr_t)out & 15) ||
+      (long long)N * (Ho + 3) >= (1ll << 31)) {
+    pdj_set_error("pdj_stem_s2d_fwd: need 1 <= Wo <= 128 and 16-byte aligned tensors (N=%d Ho=%d Wo=%d)", N, Ho, Wo);
+    return -1;
+  }
+  if (int r = ensure_init()) return r;
+  const int Hi = Ho + 3, Wi = Wo + 3, C = 16, O = 64, Kc = 4 * 4 * C;
+  CUtensorMap ma, mb, mo;
+  // pixel stride 16 elements, window 64 elements: overlapping rows of the same buffer
+  if (int r = make_map3(&ma, x, 64, (uint64_t)Wo, (uint64_t)N * Hi, (uint64_t)C * 2, (uint64_t)Wi * C * 2, 64, BM)) return r;
+  if (int r = make_map(&mb, w, O, Kc, Kc, BK, O, true)) return r;
+  if (int r = make_map3(&mo, out, 64, (uint64_t)Wo, (uint64_t)N * Ho, (uint64_t)O * 2, (uint64_t)Wo * O * 2, 64, BM)) return r;
+  const int bn = O;
+  const int stage_bytes = A_STAGE_BYTES + bn * BK * 2;
+  const int fixed = 1024 + 256 + SW_STAGING_BYTES + SW_SCRATCH_BYTES;
+  int stages = (SMEM_LIMIT - fixed) / stage_bytes;
+  if (stages > MAX_STAGES) stages = MAX_STAGES;
+  const int smem = fixed + stages * stage_bytes;
+  const int rows = N * Ho;
+  const int grid = rows < g_sms ? rows : g_sms;
+  if (partial != nullptr)
+    conv1x1_tcgen05_kernel<MODE_STATS, true><<<grid, THREADS, smem, st>>>(ma, mb, mo, mo, partial, rows, O, Kc, bn, stages, Ho, Hi);
+  else
+    conv1x1_tcgen05_kernel<MODE_PLAIN, true><<<grid, THREADS, smem, st>>>(ma, mb, mo, mo, nullptr, rows, O, Kc, bn, stages, Ho, Hi);
   PDJ_CUDA_CHECK(cudaGetLastError());
   return 0;
 }

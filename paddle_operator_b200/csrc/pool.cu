@@ -63,51 +63,59 @@ maxpool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restric
   }
 }
 
+// One block per input row (n, h): the window rows that cover h are the same for the whole block, and the
+// only per-element index arithmetic left is w / cv from the thread index.  K, S, P > 0 are compile-time for
+// the ResNet stem pool (3, 2, 1), which turns the window bounds into shifts; K = 0 is the generic version.
+template <int K, int S, int P>
 __global__ void __launch_bounds__(256)
 maxpool_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const uint8_t* __restrict__ idx,
-                   __nv_bfloat16* __restrict__ dx, int N, int H, int W, int C, int Ho, int Wo, int k, int s, int p) {
+                   __nv_bfloat16* __restrict__ dx, int H, int W, int C, int Ho, int Wo, int k_rt, int s_rt, int p_rt) {
+  const int k = K > 0 ? K : k_rt, s = K > 0 ? S : s_rt, p = K > 0 ? P : p_rt;
   const int c8 = C >> 3;
-  const uint32_t total = (uint32_t)N * H * W * c8;
-  const uint32_t stride = gridDim.x * blockDim.x;
-  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
-    const int cv = (int)(i % (uint32_t)c8);
-    uint32_t t = i / (uint32_t)c8;
-    const int w = (int)(t % (uint32_t)W); t /= (uint32_t)W;
-    const int h = (int)(t % (uint32_t)H);
-    const int n = (int)(t / (uint32_t)H);
-    float g[8];
-#pragma unroll
-    for (int j = 0; j < 8; ++j) g[j] = 0.f;
-    // windows (ho, wo) with ho*s - p <= h <= ho*s - p + k - 1
-    int ho_lo = h + p - k + 1;
-    ho_lo = ho_lo <= 0 ? 0 : (ho_lo + s - 1) / s;
-    int ho_hi = (h + p) / s;
-    if (ho_hi > Ho - 1) ho_hi = Ho - 1;
+  const int h = (int)(blockIdx.x % (uint32_t)H);
+  const int n = (int)(blockIdx.x / (uint32_t)H);
+  // windows ho with ho*s - p <= h <= ho*s - p + k - 1
+  int ho_lo = h + p - k + 1;
+  ho_lo = ho_lo <= 0 ? 0 : (ho_lo + s - 1) / s;
+  int ho_hi = (h + p) / s;
+  if (ho_hi > Ho - 1) ho_hi = Ho - 1;
+  const int row_items = W * c8;
+  const uint4* dyv = reinterpret_cast<const uint4*>(dy);
+  const uint2* idv = reinterpret_cast<const uint2*>(idx);
+  uint4* dxv = reinterpret_cast<uint4*>(dx) + ((size_t)n * H + h) * row_items;
+  for (int it = threadIdx.x; it < row_items; it += 256) {
+    const int w = it / c8, cv = it - w * c8;
     int wo_lo = w + p - k + 1;
     wo_lo = wo_lo <= 0 ? 0 : (wo_lo + s - 1) / s;
     int wo_hi = (w + p) / s;
     if (wo_hi > Wo - 1) wo_hi = Wo - 1;
+    float g[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) g[j] = 0.f;
     for (int ho = ho_lo; ho <= ho_hi; ++ho) {
       const int kh = h - (ho * s - p);
+      const size_t orow = ((size_t)n * Ho + ho) * Wo;
       for (int wo = wo_lo; wo <= wo_hi; ++wo) {
-        const int kw = w - (wo * s - p);
-        const uint32_t code = (uint32_t)(kh * k + kw);
-        const size_t o = (((size_t)n * Ho + ho) * Wo + wo) * c8 + cv;
-        const uint2 a = __ldg(reinterpret_cast<const uint2*>(idx) + o);
-        const uint4 u = __ldg(reinterpret_cast<const uint4*>(dy) + o);
+        const uint32_t code = (uint32_t)(kh * k + (w - (wo * s - p)));
+        const size_t o = (orow + wo) * c8 + cv;
+        const uint2 a = __ldg(idv + o);
+        const uint4 u = __ldg(dyv + o);
         float f[8];
         unpack8p(u, f);
+        // byte j of the arg-max word equals `code` <=> this input element won window (ho, wo)
+        const uint32_t pat = code * 0x01010101u;
+        const uint32_t x0 = a.x ^ pat, x1 = a.y ^ pat;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const uint32_t aj = ((j < 4 ? a.x : a.y) >> ((j & 3) * 8)) & 0xffu;
-          if (aj == code) g[j] += f[j];
+        for (int j = 0; j < 4; ++j) {
+          if (((x0 >> (8 * j)) & 0xffu) == 0u) g[j] += f[j];
+          if (((x1 >> (8 * j)) & 0xffu) == 0u) g[4 + j] += f[4 + j];
         }
       }
     }
     uint4 out;
     out.x = pdj_f2_to_bf2(g[0], g[1]); out.y = pdj_f2_to_bf2(g[2], g[3]);
     out.z = pdj_f2_to_bf2(g[4], g[5]); out.w = pdj_f2_to_bf2(g[6], g[7]);
-    reinterpret_cast<uint4*>(dx)[i] = out;
+    dxv[it] = out;
   }
 }
 
@@ -150,8 +158,13 @@ int pdj_maxpool_bwd(const void* dy, const void* idx, void* dx, int N, int H, int
     pdj_set_error("pdj_maxpool_bwd: tensor too large for 32-bit indexing");
     return -1;
   }
-  maxpool_bwd_kernel<<<pool_grid((size_t)N * H * W * (C / 8)), 256, 0, st>>>(
-      (const __nv_bfloat16*)dy, (const uint8_t*)idx, (__nv_bfloat16*)dx, N, H, W, C, Ho, Wo, k, s, p);
+  const unsigned int rows = (unsigned int)N * (unsigned int)H;
+  if (k == 3 && s == 2 && p == 1)
+    maxpool_bwd_kernel<3, 2, 1><<<rows, 256, 0, st>>>((const __nv_bfloat16*)dy, (const uint8_t*)idx, (__nv_bfloat16*)dx, H, W,
+                                                      C, Ho, Wo, k, s, p);
+  else
+    maxpool_bwd_kernel<0, 0, 0><<<rows, 256, 0, st>>>((const __nv_bfloat16*)dy, (const uint8_t*)idx, (__nv_bfloat16*)dx, H, W,
+                                                      C, Ho, Wo, k, s, p);
   PDJ_CUDA_CHECK(cudaGetLastError());
   return 0;
 }

@@ -16,7 +16,7 @@ import torch
 import torch.nn as nn
 
 from ..ops.bn import FusedBnAct
-from ..ops.conv import conv1x1_dual, conv1x1_stats
+from ..ops.conv import conv1x1_dual, conv1x1_stats, stem_s2d_conv
 from ..ops.pool import FusedMaxPool2d
 
 
@@ -171,7 +171,12 @@ class ResNet(nn.Module):
             from ..ops.optim import space_to_depth_reference
 
             x = space_to_depth_reference(x).contiguous(memory_format=torch.channels_last)
-        x = self.bn1(self.conv1(x))
+        if self.s2d_stem and self.gemm_1x1:
+            # stem on the tcgen05 pipeline (TMA windows over the space-to-depth input), BN statistics fused
+            x, p = stem_s2d_conv(x, self.conv1.weight)
+            x = self.bn1(x, partial=p)
+        else:
+            x = self.bn1(self.conv1(x))
         x = self.maxpool(x)
         x = self.blocks(x)
         x = torch.flatten(self.avgpool(x), 1)

@@ -89,6 +89,11 @@ def _rows(t: torch.Tensor) -> torch.Tensor:
     return v
 
 
+def _wgrad_1x1(dy: torch.Tensor, x: torch.Tensor, weight: torch.Tensor) -> torch.Tensor:
+    """dW[Cout,Cin,1,1] = dY^T[Cout,M] @ X[M,Cin] (library GEMM)."""
+    return torch.mm(_rows(dy).t(), _rows(x)).view(weight.shape)
+
+
 class _Conv1x1StatsFn(torch.autograd.Function):
     """y = conv1x1(x, weight) with BN partial sums; with `carry_skip` the input is also handed through as a
     third output, so that the gradient of whatever consumes it (the block's skip connection) arrives in
@@ -117,9 +122,13 @@ class _Conv1x1StatsFn(torch.autograd.Function):
             dy = dy.contiguous(memory_format=torch.channels_last)
         o, c = weight.shape[0], weight.shape[1]
         fuse = (ctx.carry_skip and dskip is not None and ctx.needs_input_grad[0] and c % 64 == 0 and o % 8 == 0)
-        dx, dw, _ = torch.ops.aten.convolution_backward(
-            dy, x, weight, None, [1, 1], [0, 0], [1, 1], False, [0, 0], 1,
-            [ctx.needs_input_grad[0] and not fuse, ctx.needs_input_grad[1], False])
+        if fuse:
+            # weight gradient as a plain library GEMM dY^T @ X (a wgrad-only cuDNN call picks a far slower kernel)
+            dx, dw = None, (_wgrad_1x1(dy, x, weight) if ctx.needs_input_grad[1] else None)
+        else:
+            dx, dw, _ = torch.ops.aten.convolution_backward(
+                dy, x, weight, None, [1, 1], [0, 0], [1, 1], False, [0, 0], 1,
+                [ctx.needs_input_grad[0], ctx.needs_input_grad[1], False])
         if fuse:
             if not dskip.is_contiguous(memory_format=torch.channels_last):
                 dskip = dskip.contiguous(memory_format=torch.channels_last)
@@ -184,8 +193,7 @@ class _Conv1x1DualFn(torch.autograd.Function):
         need_x = ctx.needs_input_grad[0]
         g, dwd, _ = torch.ops.aten.convolution_backward(dyd, x, w_ds, None, [s, s], [0, 0], [1, 1], False, [0, 0], 1,
                                                         [need_x, ctx.needs_input_grad[2], False])
-        _, dw1, _ = torch.ops.aten.convolution_backward(dy1, x, w1, None, [1, 1], [0, 0], [1, 1], False, [0, 0], 1,
-                                                        [False, ctx.needs_input_grad[1], False])
+        dw1 = _wgrad_1x1(dy1, x, w1) if ctx.needs_input_grad[1] else None
         dx = None
         if need_x:
             o1, c = w1.shape[0], w1.shape[1]
@@ -217,3 +225,46 @@ def _dgrad_eligible(x: torch.Tensor, weight: torch.Tensor) -> bool:
             and weight.dim() == 4 and weight.shape[2] == 1 and weight.shape[3] == 1
             and weight.shape[1] % 64 == 0 and weight.shape[0] % 8 == 0
             and x.is_contiguous(memory_format=torch.channels_last))
+
+
+# ---- ResNet stem: 4x4 / stride-1 convolution over the space-to-depth input -------------------------------
+def stem_s2d_eligible(x: torch.Tensor, weight: torch.Tensor) -> bool:
+    return (x.is_cuda and x.dtype == torch.bfloat16 and weight.dtype == torch.bfloat16 and x.dim() == 4
+            and tuple(weight.shape) == (64, 16, 4, 4) and x.shape[1] == 16 and 4 <= x.shape[3] <= 131
+            and x.is_contiguous(memory_format=torch.channels_last)
+            and weight.is_contiguous(memory_format=torch.channels_last))
+
+
+class _StemS2dFn(torch.autograd.Function):
+    """y = conv2d(x, weight) for the [64,16,4,4] stem over x[N,16,Ho+3,Wo+3] on the tcgen05 pipeline
+    (csrc/gemm_tcgen05.cu, WIN mode), with the BN partial sums from its epilogue."""
+
+    @staticmethod
+    def forward(ctx, x, weight):
+        lib = _lib.load()
+        n, _, hi, wi = x.shape
+        ho, wo = hi - 3, wi - 3
+        y = torch.empty((n, 64, ho, wo), dtype=x.dtype, device=x.device, memory_format=torch.channels_last)
+        partial = torch.empty((lib.pdj_stem_s2d_partial_rows(n * ho), 2, 64), dtype=torch.float32, device=x.device)
+        _lib.check(lib.pdj_stem_s2d_fwd(x.data_ptr(), weight.data_ptr(), y.data_ptr(), partial.data_ptr(), n, ho, wo,
+                                        torch.cuda.current_stream().cuda_stream), "stem_s2d_fwd")
+        ctx.save_for_backward(x, weight)
+        ctx.mark_non_differentiable(partial)
+        return y, partial
+
+    @staticmethod
+    def backward(ctx, dy, _dpartial):
+        x, weight = ctx.saved_tensors
+        if not dy.is_contiguous(memory_format=torch.channels_last):
+            dy = dy.contiguous(memory_format=torch.channels_last)
+        dx, dw, _ = torch.ops.aten.convolution_backward(
+            dy, x, weight, None, [1, 1], [0, 0], [1, 1], False, [0, 0], 1,
+            [ctx.needs_input_grad[0], ctx.needs_input_grad[1], False])
+        return dx, dw
+
+
+def stem_s2d_conv(x: torch.Tensor, weight: torch.Tensor):
+    """(y, partial) for the space-to-depth stem; library convolution (partial = None) when not eligible."""
+    if stem_s2d_eligible(x, weight):
+        return _StemS2dFn.apply(x, weight)
+    return F.conv2d(x, weight), None

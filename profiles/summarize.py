@@ -137,7 +137,8 @@ def main() -> int:
         p = os.path.join(SCRATCH, n + ".ncu-rep")
         if os.path.exists(p):
             summarize_rep(p, t)
-    lists = {"launches3": "ResNet-50 step launch list (batch 256, one B200)",
+    lists = {"launches3": "ResNet-50 step launch list (batch 256, one B200) - before the 1x1-convolution GEMM",
+             "launches4": "ResNet-50 step launch list (batch 256, one B200)",
              "launches_wd2": "Wide&Deep step launch list (batch 32768, one B200)"}
     for n, t in lists.items():
         p = os.path.join(SCRATCH, n + ".csv")

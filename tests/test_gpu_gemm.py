@@ -212,3 +212,29 @@ def test_conv1x1_dual_backward_sums_both_input_gradients(stride, cin, c1, cd):
     torch.testing.assert_close(xa.grad.float(), xb.grad, atol=6e-2, rtol=3e-2)
     torch.testing.assert_close(w1a.grad.float(), w1b.grad, atol=0.25, rtol=5e-2)
     torch.testing.assert_close(wda.grad.float(), wdb.grad, atol=0.25, rtol=5e-2)
+
+
+@pytest.mark.parametrize("n,img", [(2, 64), (3, 224), (1, 40)])
+def test_stem_s2d_conv_matches_conv2d(n, img):
+    """4x4 stem over the space-to-depth input through TMA windows == F.conv2d; partial sums == sums of y."""
+    from paddle_operator_b200.ops import conv as conv_ops
+
+    torch.manual_seed(img)
+    hi = img // 2 + 3
+    x = torch.randn(n, 16, hi, hi, device="cuda", dtype=torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    w = (torch.randn(64, 16, 4, 4, device="cuda", dtype=torch.bfloat16) * 0.1).contiguous(memory_format=torch.channels_last)
+    assert conv_ops.stem_s2d_eligible(x, w)
+    xa, wa = x.clone().requires_grad_(True), w.clone().requires_grad_(True)
+    y, partial = conv_ops.stem_s2d_conv(xa, wa)
+    ref = torch.nn.functional.conv2d(x.float(), w.float())
+    assert y.shape == ref.shape
+    torch.testing.assert_close(y.float(), ref, atol=5e-2, rtol=3e-2)
+    yf = y.float()
+    torch.testing.assert_close(partial[:, 0].sum(0), yf.sum(dim=(0, 2, 3)), atol=1e-4 * float(yf.abs().sum(dim=(0, 2, 3)).max()),
+                               rtol=1e-3)
+    torch.testing.assert_close(partial[:, 1].sum(0), (yf * yf).sum(dim=(0, 2, 3)), atol=1e-3, rtol=1e-3)
+    g = torch.randn_like(y)
+    y.backward(g)
+    wb = w.float().requires_grad_(True)
+    torch.nn.functional.conv2d(x.float(), wb).backward(g.float())
+    torch.testing.assert_close(wa.grad.float(), wb.grad, atol=0.5, rtol=5e-2)
