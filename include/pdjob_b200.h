@@ -134,6 +134,12 @@ int pdj_conv1x1_add_bf16(const void* a, const void* b, const void* addend, void*
  * pdj_stem_s2d_partial_rows(N * Ho) rows (NULL to skip). */
 int pdj_stem_s2d_partial_rows(int n_rows);
 int pdj_stem_s2d_fwd(const void* x, const void* w, void* out, float* partial, int N, int Ho, int Wo, cudaStream_t st);
+/* Weight gradient of the stem: dw[64][4][4][16] bf16 from x and dy[N][Ho][Wo][64]; a persistent tcgen05 kernel
+ * (MN-major operands straight from the NHWC tensors, one output row per k-step, X rows reused from a
+ * shared-memory ring) plus a fixed-order reduction of the per-CTA partials in `ws`
+ * (pdj_stem_s2d_wgrad_ws_bytes() bytes). */
+int pdj_stem_s2d_wgrad_ws_bytes(void);
+int pdj_stem_s2d_wgrad(const void* x, const void* dy, void* dw, void* ws, int N, int Ho, int Wo, cudaStream_t st);
 
 /* ---- ResNet-50 step kernels (csrc/bn_act.cu, csrc/optim_misc.cu) -----------
  * The workload of deploy/examples/resnet.yaml:13-19. NHWC bf16 activations

@@ -594,6 +594,177 @@ conv1x1_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_c
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Weight gradient of the ResNet stem (4x4 / stride 1, 16 -> 64 channels over the space-to-depth input):
+//   dW[o][jy][jx][c] = sum over (n, y, x) of dY[n][y][x][o] * X[n][y + jy][x + jx][c]
+// i.e. D[64, 256] = dY^T . im2col(X) with a reduction over every output pixel (3.2 M at batch 256) -
+// a shape the library handles with 48 CTAs.  Here it is one persistent tcgen05 kernel:
+//   * a k-step is one output row: the A operand is the dY row tile [pixels][64 channels], the B operand
+//     for tap row jy is the X window tile of input row y + jy ([pixels][64 = 4 taps x 16 channels], the
+//     same overlapping TMA windows as the forward).  Both are MN-major for the MMA (the contiguous
+//     dimension is M / N, the reduction runs over the rows of the tile), 128-byte swizzle;
+//   * X row tiles live in a ring and are reused by the four output rows that need them, so each step
+//     fetches one X tile and one dY tile;
+//   * tcgen05.mma M=64, N=64, four accumulators (one per jy) of 64 TMEM columns, fp32, kept for the whole
+//     kernel; at the end each CTA writes its [64][256] partial and a second kernel adds the partials in
+//     a fixed order (bit-reproducible) and casts to bf16.
+constexpr int WG_RX = 8, WG_RY = 4;   // ring depths: X row tiles, dY row tiles
+constexpr int WG_CHUNK = 28;          // output rows per work unit (3 halo X rows per unit)
+constexpr int WG_THREADS = 192;       // warp 0: TMA, warp 1: MMA, warps 2..5: epilogue
+
+// MN-major operand tile: rows = reduction index (128 B each, 64 elements of M or N), 8-row groups 1024 B apart.
+__device__ __forceinline__ uint64_t umma_desc_mn(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);
+  d |= (uint64_t)1 << 16;                 // leading byte offset: distance between 64-element groups (a single group here)
+  d |= (uint64_t)(1024 >> 4) << 32;       // stride byte offset: next group of 8 reduction rows
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;                 // SWIZZLE_128B
+  return d;
+}
+
+__global__ void __launch_bounds__(WG_THREADS, 1)
+stem_wgrad_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constant__ CUtensorMap tma_dy,
+                          float* __restrict__ partial, int n_img, int Ho, int Hi, int kp /* pixels per tile, % 16 == 0 */) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  const uint32_t base = (raw + 1023u) & ~1023u;
+  const uint32_t tile = (uint32_t)kp * 128u;
+  const uint32_t x_smem = base, dy_smem = x_smem + WG_RX * tile;
+  const uint32_t bars = dy_smem + WG_RY * tile;
+  const uint32_t xfull = bars, xempty = xfull + 8 * WG_RX, yfull = xempty + 8 * WG_RX, yempty = yfull + 8 * WG_RY;
+  const uint32_t done = yempty + 8 * WG_RY, tmem_slot = done + 8;
+  uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(smem_raw + (tmem_slot - raw));
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int upi = (Ho + WG_CHUNK - 1) / WG_CHUNK;  // units per image
+  const int units = n_img * upi;
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_x) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_dy) : "memory");
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      for (int i = 0; i < WG_RX; ++i) { mbar_init(xfull + 8 * i, 1); mbar_init(xempty + 8 * i, 1); }
+      for (int i = 0; i < WG_RY; ++i) { mbar_init(yfull + 8 * i, 1); mbar_init(yempty + 8 * i, 1); }
+      mbar_init(done, 1);
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(256) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem_base = *tmem_slot_ptr;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      uint32_t ix = 0, iy = 0;
+      for (int u = blockIdx.x; u < units; u += gridDim.x) {
+        const int n = u / upi, y0 = (u % upi) * WG_CHUNK;
+        const int rows = (Ho - y0) < WG_CHUNK ? (Ho - y0) : WG_CHUNK;
+        for (int r = 0; r < rows + 3; ++r, ++ix) {
+          const uint32_t s = ix % WG_RX, ph = (ix / WG_RX) & 1u;
+          mbar_wait(xempty + 8 * s, ph ^ 1u);
+          mbar_expect_tx(xfull + 8 * s, tile);
+          tma_load_3d(x_smem + s * tile, &tma_x, 0, 0, n * Hi + y0 + r, xfull + 8 * s);
+          if (r >= 3) {  // the dY row that becomes computable with this X row
+            const uint32_t sy = iy % WG_RY, phy = (iy / WG_RY) & 1u;
+            mbar_wait(yempty + 8 * sy, phy ^ 1u);
+            mbar_expect_tx(yfull + 8 * sy, tile);
+            tma_load_3d(dy_smem + sy * tile, &tma_dy, 0, 0, n * Ho + y0 + (r - 3), yfull + 8 * sy);
+            ++iy;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      // D = f32, A = B = bf16, both MN-major (bits 15, 16), N = 64, M = 64
+      const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) | ((64u >> 3) << 17) | ((64u >> 4) << 24);
+      const int ksteps = kp / 16;
+      uint32_t ix = 0, iy = 0;
+      for (int u = blockIdx.x; u < units; u += gridDim.x) {
+        const int y0 = (u % upi) * WG_CHUNK;
+        const int rows = (Ho - y0) < WG_CHUNK ? (Ho - y0) : WG_CHUNK;
+        for (int r = 0; r < 3; ++r) mbar_wait(xfull + 8 * ((ix + r) % WG_RX), ((ix + r) / WG_RX) & 1u);
+        for (int j = 0; j < rows; ++j, ++iy) {
+          mbar_wait(xfull + 8 * ((ix + j + 3) % WG_RX), ((ix + j + 3) / WG_RX) & 1u);
+          const uint32_t sy = iy % WG_RY;
+          mbar_wait(yfull + 8 * sy, (iy / WG_RY) & 1u);
+          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+#pragma unroll
+          for (int jy = 0; jy < 4; ++jy) {
+            const uint32_t xs = (ix + j + jy) % WG_RX;
+            for (int k = 0; k < ksteps; ++k) {
+              const uint64_t da = umma_desc_mn(dy_smem + sy * tile + (uint32_t)k * 2048u);
+              const uint64_t db = umma_desc_mn(x_smem + xs * tile + (uint32_t)k * 2048u);
+              umma_f16(tmem_base + (uint32_t)jy * 64u, da, db, idesc, (uint32_t)((iy | (uint32_t)k) != 0u));
+            }
+          }
+          umma_commit(yempty + 8 * sy);
+          umma_commit(xempty + 8 * ((ix + j) % WG_RX));       // input row y0 + j has served its last output row
+          if (j == rows - 1)
+            for (int r = 1; r <= 3; ++r) umma_commit(xempty + 8 * ((ix + j + r) % WG_RX));  // bottom halo rows
+        }
+        ix += rows + 3;
+      }
+      umma_commit(done);
+    }
+  } else {
+    // epilogue: M = 64 accumulators occupy lanes 0..15 of each 32-lane TMEM quarter: row 16 * q + lane
+    const int q = warp & 3;
+    mbar_wait(done, 0);
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    float* dst = partial + ((size_t)blockIdx.x * 64 + (size_t)(16 * q + lane)) * 256;
+    const bool has_work = (int)blockIdx.x < units;
+    for (int c0 = 0; c0 < 256; c0 += 16) {
+      uint32_t r[16];
+      asm volatile(
+          "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+          : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+            "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+          : "r"(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0)
+          : "memory");
+      asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+      if (lane < 16) {
+#pragma unroll
+        for (int v = 0; v < 4; ++v) {
+          float4 o;
+          o.x = has_work ? __uint_as_float(r[4 * v + 0]) : 0.f;
+          o.y = has_work ? __uint_as_float(r[4 * v + 1]) : 0.f;
+          o.z = has_work ? __uint_as_float(r[4 * v + 2]) : 0.f;
+          o.w = has_work ? __uint_as_float(r[4 * v + 3]) : 0.f;
+          reinterpret_cast<float4*>(dst + c0)[v] = o;
+        }
+      }
+    }
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 1) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(256) : "memory");
+  }
+}
+
+// dw[i] = sum over the CTAs' partials, fixed order, cast to bf16.
+__global__ void __launch_bounds__(256)
+stem_wgrad_reduce_kernel(const float* __restrict__ partial, int nparts, __nv_bfloat16* __restrict__ dw) {
+  const int i = blockIdx.x * 256 + threadIdx.x;  // 64 * 256 outputs
+  float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+  int p = 0;
+  for (; p + 3 < nparts; p += 4) {
+    a0 += partial[(size_t)p * 16384 + i];
+    a1 += partial[(size_t)(p + 1) * 16384 + i];
+    a2 += partial[(size_t)(p + 2) * 16384 + i];
+    a3 += partial[(size_t)(p + 3) * 16384 + i];
+  }
+  for (; p < nparts; ++p) a0 += partial[(size_t)p * 16384 + i];
+  dw[i] = __float2bfloat16((a0 + a1) + (a2 + a3));
+}
+
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -847,6 +1018,37 @@ int pdj_stem_s2d_fwd(const void* x, const void* w, void* out, float* partial, in
     conv1x1_tcgen05_kernel<MODE_STATS, true><<<grid, THREADS, smem, st>>>(ma, mb, mo, mo, partial, rows, O, Kc, bn, stages, Ho, Hi);
   else
     conv1x1_tcgen05_kernel<MODE_PLAIN, true><<<grid, THREADS, smem, st>>>(ma, mb, mo, mo, nullptr, rows, O, Kc, bn, stages, Ho, Hi);
+  PDJ_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+int pdj_stem_s2d_wgrad_ws_bytes(void) { return sm_count_cached() * 64 * 256 * (int)sizeof(float); }
+
+// dw[64][4][4][16] (bf16, channels-last memory of the [64,16,4,4] weight) = gradient of pdj_stem_s2d_fwd with
+// respect to w, given x[N][Ho+3][Wo+3][16] and dy[N][Ho][Wo][64].  `ws`: pdj_stem_s2d_wgrad_ws_bytes() bytes.
+int pdj_stem_s2d_wgrad(const void* x, const void* dy, void* dw, void* ws, int N, int Ho, int Wo, cudaStream_t st) {
+  if (N < 1 || Ho < 1 || Wo < 1 || Wo > BM || ((uintptr_t)x & 15) || ((uintptr_t)dy & 15) || ws == nullptr ||
+      (long long)N * (Ho + 3) >= (1ll << 31)) {
+    pdj_set_error("pdj_stem_s2d_wgrad: need 1 <= Wo <= 128, 16-byte aligned tensors and a workspace (N=%d Ho=%d Wo=%d)", N, Ho, Wo);
+    return -1;
+  }
+  if (int r = ensure_init()) return r;
+  static bool attr = false;
+  if (!attr) {
+    PDJ_CUDA_CHECK(cudaFuncSetAttribute(stem_wgrad_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+    attr = true;
+  }
+  const int Hi = Ho + 3, Wi = Wo + 3, C = 16, O = 64;
+  const int kp = (Wo + 15) / 16 * 16;
+  CUtensorMap mx, my;
+  if (int r = make_map3(&mx, x, 64, (uint64_t)Wo, (uint64_t)N * Hi, (uint64_t)C * 2, (uint64_t)Wi * C * 2, 64, kp)) return r;
+  if (int r = make_map3(&my, dy, 64, (uint64_t)Wo, (uint64_t)N * Ho, (uint64_t)O * 2, (uint64_t)Wo * O * 2, 64, kp)) return r;
+  const int units = N * ((Ho + WG_CHUNK - 1) / WG_CHUNK);
+  const int grid = units < g_sms ? units : g_sms;
+  const int smem = 1024 + 512 + (WG_RX + WG_RY) * kp * 128;
+  stem_wgrad_tcgen05_kernel<<<grid, WG_THREADS, smem, st>>>(mx, my, (float*)ws, N, Ho, Hi, kp);
+  PDJ_CUDA_CHECK(cudaGetLastError());
+  stem_wgrad_reduce_kernel<<<64, 256, 0, st>>>((const float*)ws, grid, (__nv_bfloat16*)dw);
   PDJ_CUDA_CHECK(cudaGetLastError());
   return 0;
 }

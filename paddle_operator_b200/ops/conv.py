@@ -257,9 +257,17 @@ class _StemS2dFn(torch.autograd.Function):
         x, weight = ctx.saved_tensors
         if not dy.is_contiguous(memory_format=torch.channels_last):
             dy = dy.contiguous(memory_format=torch.channels_last)
-        dx, dw, _ = torch.ops.aten.convolution_backward(
-            dy, x, weight, None, [1, 1], [0, 0], [1, 1], False, [0, 0], 1,
-            [ctx.needs_input_grad[0], ctx.needs_input_grad[1], False])
+        dx = dw = None
+        if ctx.needs_input_grad[0]:  # not the case in training (x is the image batch)
+            dx, _, _ = torch.ops.aten.convolution_backward(dy, x, weight, None, [1, 1], [0, 0], [1, 1], False, [0, 0], 1,
+                                                           [True, False, False])
+        if ctx.needs_input_grad[1]:
+            lib = _lib.load()
+            n, _, hi, wi = x.shape
+            dw = torch.empty_like(weight, memory_format=torch.channels_last)
+            ws = torch.empty(lib.pdj_stem_s2d_wgrad_ws_bytes(), dtype=torch.uint8, device=x.device)
+            _lib.check(lib.pdj_stem_s2d_wgrad(x.data_ptr(), dy.data_ptr(), dw.data_ptr(), ws.data_ptr(), n, hi - 3, wi - 3,
+                                              torch.cuda.current_stream().cuda_stream), "stem_s2d_wgrad")
         return dx, dw
 
 
