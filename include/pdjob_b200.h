@@ -131,8 +131,8 @@ int pdj_conv1x1_add_bf16(const void* a, const void* b, const void* addend, void*
  * convolution (16 -> 64 channels) over the space-to-depth input x[N][Ho+3][Wo+3][16] (see
  * pdj_preprocess_u8_s2d); w[64][4][4][16] bf16, out[N][Ho][Wo][64] bf16, Wo <= 128.  The A operand is read
  * through a TMA tensor map with overlapping pixel windows: no im2col buffer.  `partial` as above, with
- * pdj_stem_s2d_partial_rows(N * Ho) rows (NULL to skip). */
-int pdj_stem_s2d_partial_rows(int n_rows);
+ * pdj_stem_s2d_partial_rows(N, Ho) rows (NULL to skip). */
+int pdj_stem_s2d_partial_rows(int N, int Ho);
 int pdj_stem_s2d_fwd(const void* x, const void* w, void* out, float* partial, int N, int Ho, int Wo, cudaStream_t st);
 /* Weight gradient of the stem: dw[64][4][4][16] bf16 from x and dy[N][Ho][Wo][64]; a persistent tcgen05 kernel
  * (MN-major operands straight from the NHWC tensors, one output row per k-step, X rows reused from a

@@ -346,6 +346,7 @@ constexpr int SW_SCRATCH_BYTES = 2 * 2 * 4 * BOX_N * 4;  // [group][sum|sq][warp
 // staging buffer one box ahead, summed in place with the accumulator, and stored from there - the
 // residual-gradient add of a bottleneck block folded into the input-gradient GEMM of its first conv.
 constexpr int MODE_PLAIN = 0, MODE_STATS = 1, MODE_ADD = 2;
+constexpr int WIN_CHUNK = 28;  // WIN: output rows per work unit (3 halo input rows per unit)
 
 //
 // WIN (the ResNet stem): the same pipeline as a 4x4 / stride-1 convolution over the space-to-depth input
@@ -368,7 +369,7 @@ conv1x1_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_c
   const uint32_t b_stage_bytes = (uint32_t)block_n * BK * 2;
   const uint32_t a_smem = base;
   const uint32_t b_smem = a_smem + stages * A_STAGE_BYTES;
-  const uint32_t staging = b_smem + stages * b_stage_bytes;  // 1024-aligned: every term is a multiple of 1024
+  const uint32_t staging = b_smem + (WIN ? 4u : (uint32_t)stages) * b_stage_bytes;  // 1024-aligned (WIN: all 4 weight k-blocks resident)
   const uint32_t scratch = staging + SW_STAGING_BYTES;
   const uint32_t bars = scratch + SW_SCRATCH_BYTES;
   const uint32_t full0 = bars, empty0 = bars + 8 * MAX_STAGES;
@@ -380,6 +381,8 @@ conv1x1_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_c
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int tiles_n = N / block_n;
   const int total = WIN ? M : ((M + BM - 1) / BM) * tiles_n;  // WIN: M counts output rows, one tile each
+  const int win_upi = WIN ? (win_ho + WIN_CHUNK - 1) / WIN_CHUNK : 1;   // work units (row chunks) per image
+  const int win_units = WIN ? (M / win_ho) * win_upi : 0;
   const int num_kb = (K + BK - 1) / BK;
 
   if (warp == 0 && lane == 0) {
@@ -415,16 +418,19 @@ conv1x1_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_c
   if (warp == 0) {
     if (lane == 0) {
       if (WIN) {
-        const uint32_t stage_bytes = (uint32_t)A_STAGE_BYTES + b_stage_bytes;
-        uint32_t it = 0;
-        for (int t = blockIdx.x; t < total; t += gridDim.x) {
-          const int xrow = (t / win_ho) * win_hi + (t % win_ho);  // first input row of output row t
-          for (int kb = 0; kb < num_kb; ++kb, ++it) {
-            const uint32_t s = it % (uint32_t)stages, ph = (it / (uint32_t)stages) & 1u;
+        // weights: all four k-blocks once
+        mbar_expect_tx(abar0, 4u * b_stage_bytes);
+        for (int kb = 0; kb < 4; ++kb) tma_load_2d(b_smem + kb * b_stage_bytes, &tma_b, kb * BK, 0, abar0);
+        // input rows: a ring; output row y needs rows y .. y+3, so one new row per tile within a unit
+        uint32_t ix = 0;
+        for (int u = blockIdx.x; u < win_units; u += gridDim.x) {
+          const int n = u / win_upi, y0 = (u % win_upi) * WIN_CHUNK;
+          const int rows = (win_ho - y0) < WIN_CHUNK ? (win_ho - y0) : WIN_CHUNK;
+          for (int r = 0; r < rows + 3; ++r, ++ix) {
+            const uint32_t s = ix % (uint32_t)stages, ph = (ix / (uint32_t)stages) & 1u;
             mbar_wait(empty0 + 8 * s, ph ^ 1u);
-            mbar_expect_tx(full0 + 8 * s, stage_bytes);
-            tma_load_3d(a_smem + s * A_STAGE_BYTES, &tma_a, 0, 0, xrow + kb, full0 + 8 * s);
-            tma_load_2d(b_smem + s * b_stage_bytes, &tma_b, kb * BK, 0, full0 + 8 * s);
+            mbar_expect_tx(full0 + 8 * s, A_STAGE_BYTES);
+            tma_load_3d(a_smem + s * A_STAGE_BYTES, &tma_a, 0, 0, n * win_hi + y0 + r, full0 + 8 * s);
           }
         }
       } else {
@@ -432,7 +438,43 @@ conv1x1_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_c
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) mma_loop(pipe, tmem_base, total, block_n, num_kb);
+    if (lane == 0) {
+      if (WIN) {
+        const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(block_n >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+        const uint32_t S = (uint32_t)stages;
+        mbar_wait(abar0, 0);
+        uint32_t ix = 0, i = 0;
+        for (int u = blockIdx.x; u < win_units; u += gridDim.x) {
+          const int y0 = (u % win_upi) * WIN_CHUNK;
+          const int rows = (win_ho - y0) < WIN_CHUNK ? (win_ho - y0) : WIN_CHUNK;
+          for (int r = 0; r < 3; ++r) mbar_wait(full0 + 8 * ((ix + r) % S), ((ix + r) / S) & 1u);
+          for (int j = 0; j < rows; ++j, ++i) {
+            const uint32_t buf = i & 1u, aph = (i >> 1) & 1u;
+            mbar_wait(tempty0 + 8 * buf, aph ^ 1u);
+            mbar_wait(full0 + 8 * ((ix + j + 3) % S), ((ix + j + 3) / S) & 1u);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint32_t tmem_d = tmem_base + buf * MAX_BN;
+#pragma unroll
+            for (int kb = 0; kb < 4; ++kb) {
+              const uint32_t slot = (ix + j + kb) % S;
+#pragma unroll
+              for (int k = 0; k < BK / UK; ++k) {
+                const uint64_t da = umma_desc(a_smem + slot * A_STAGE_BYTES + k * UK * 2);
+                const uint64_t db = umma_desc(b_smem + kb * b_stage_bytes + k * UK * 2);
+                umma_f16(tmem_d, da, db, idesc, (uint32_t)((kb | k) != 0));
+              }
+            }
+            umma_commit(empty0 + 8 * ((ix + j) % S));  // input row y0 + j has served its last output row
+            if (j == rows - 1)
+              for (int r = 1; r <= 3; ++r) umma_commit(empty0 + 8 * ((ix + j + r) % S));
+            umma_commit(tfull0 + 8 * buf);
+          }
+          ix += rows + 3;
+        }
+      } else {
+        mma_loop(pipe, tmem_base, total, block_n, num_kb);
+      }
+    }
   } else {
     const int g = (warp - 2) >> 2;               // epilogue group = accumulator buffer it drains
     const int q = warp & 3;                      // TMEM lane quarter this warp may read
@@ -456,9 +498,20 @@ conv1x1_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_c
         tma_load_2d(stg0, &tma_c, n0, (int)(t0 / tiles_n) * BM, abar0 + 8 * (g * 2));
       }
     }
-    for (uint32_t i = g;; i += 2) {
-      const long long t = (long long)blockIdx.x + (long long)i * gridDim.x;
-      if (t >= total) break;
+    int wu = blockIdx.x, wj = 0;  // WIN: unit and row within it of CTA-local tile i
+    for (uint32_t i = 0;; ++i) {
+      long long t;
+      if (WIN) {
+        if (wu >= win_units) break;
+        const int y0 = (wu % win_upi) * WIN_CHUNK;
+        const int rows = (win_ho - y0) < WIN_CHUNK ? (win_ho - y0) : WIN_CHUNK;
+        t = (long long)(wu / win_upi) * win_ho + y0 + wj;  // output row index
+        if (++wj == rows) { wj = 0; wu += gridDim.x; }
+      } else {
+        t = (long long)blockIdx.x + (long long)i * gridDim.x;
+        if (t >= total) break;
+      }
+      if ((i & 1u) != (uint32_t)g) continue;  // the other group's tile
       const int m0 = (int)(t / tiles_n) * BM;
       const uint32_t aph = (i >> 1) & 1u;
       mbar_wait(tfull0 + 8 * g, aph);
@@ -984,10 +1037,12 @@ static int launch_conv1x1(const void* a, const void* b, const void* addend, void
   return 0;
 }
 
-int pdj_stem_s2d_partial_rows(int n_rows) {
-  if (n_rows < 1) return 0;
-  const int sms = sm_count_cached();
-  return 2 * (n_rows < sms ? n_rows : sms);
+static int stem_units(int N, int Ho) { return N * ((Ho + WIN_CHUNK - 1) / WIN_CHUNK); }
+
+int pdj_stem_s2d_partial_rows(int N, int Ho) {
+  if (N < 1 || Ho < 1) return 0;
+  const int sms = sm_count_cached(), units = stem_units(N, Ho);
+  return 2 * (units < sms ? units : sms);
 }
 
 // ResNet stem: 4x4 / stride-1 convolution, 16 -> 64 channels, over the space-to-depth input
@@ -1007,13 +1062,11 @@ int pdj_stem_s2d_fwd(const void* x, const void* w, void* out, float* partial, in
   if (int r = make_map(&mb, w, O, Kc, Kc, BK, O, true)) return r;
   if (int r = make_map3(&mo, out, 64, (uint64_t)Wo, (uint64_t)N * Ho, (uint64_t)O * 2, (uint64_t)Wo * O * 2, 64, BM)) return r;
   const int bn = O;
-  const int stage_bytes = A_STAGE_BYTES + bn * BK * 2;
-  const int fixed = 1024 + 256 + SW_STAGING_BYTES + SW_SCRATCH_BYTES;
-  int stages = (SMEM_LIMIT - fixed) / stage_bytes;
-  if (stages > MAX_STAGES) stages = MAX_STAGES;
-  const int smem = fixed + stages * stage_bytes;
+  const int stages = MAX_STAGES;  // input-row ring
+  const int smem = 1024 + 256 + SW_STAGING_BYTES + SW_SCRATCH_BYTES + stages * A_STAGE_BYTES + 4 * bn * BK * 2;
   const int rows = N * Ho;
-  const int grid = rows < g_sms ? rows : g_sms;
+  const int units = stem_units(N, Ho);
+  const int grid = units < g_sms ? units : g_sms;
   if (partial != nullptr)
     conv1x1_tcgen05_kernel<MODE_STATS, true><<<grid, THREADS, smem, st>>>(ma, mb, mo, mo, partial, rows, O, Kc, bn, stages, Ho, Hi);
   else

@@ -81,7 +81,7 @@ def _declare(lib: ctypes.CDLL) -> None:
         "pdj_conv1x1_partial_rows": (c_int, [c_int, c_int]),
         "pdj_conv1x1_bf16": (c_int, [vp, vp, vp, vp, c_int, c_int, c_int, c_int, c_int, c_int, st]),
         "pdj_conv1x1_add_bf16": (c_int, [vp, vp, vp, vp, c_int, c_int, c_int, c_int, c_int, c_int, c_int, st]),
-        "pdj_stem_s2d_partial_rows": (c_int, [c_int]),
+        "pdj_stem_s2d_partial_rows": (c_int, [c_int, c_int]),
         "pdj_stem_s2d_fwd": (c_int, [vp, vp, vp, vp, c_int, c_int, c_int, st]),
         "pdj_stem_s2d_wgrad_ws_bytes": (c_int, []),
         "pdj_stem_s2d_wgrad": (c_int, [vp, vp, vp, vp, c_int, c_int, c_int, st]),

@@ -245,7 +245,7 @@ class _StemS2dFn(torch.autograd.Function):
         n, _, hi, wi = x.shape
         ho, wo = hi - 3, wi - 3
         y = torch.empty((n, 64, ho, wo), dtype=x.dtype, device=x.device, memory_format=torch.channels_last)
-        partial = torch.empty((lib.pdj_stem_s2d_partial_rows(n * ho), 2, 64), dtype=torch.float32, device=x.device)
+        partial = torch.empty((lib.pdj_stem_s2d_partial_rows(n, ho), 2, 64), dtype=torch.float32, device=x.device)
         _lib.check(lib.pdj_stem_s2d_fwd(x.data_ptr(), weight.data_ptr(), y.data_ptr(), partial.data_ptr(), n, ho, wo,
                                         torch.cuda.current_stream().cuda_stream), "stem_s2d_fwd")
         ctx.save_for_backward(x, weight)

@@ -81,7 +81,7 @@ def summarize_launches(path: str, title: str) -> None:
             a[3] += v
     tot = sum(a[1] for a in agg.values()) or 1.0
     name = os.path.splitext(os.path.basename(path))[0]
-    ours = ("bn_", "maxpool", "sgd_momentum", "softmax_xent", "preprocess", "emb_", "linear_tcgen05", "colsum",
+    ours = ("bn_", "maxpool", "sgd_momentum", "softmax_xent", "preprocess", "emb_", "linear_tcgen05", "colsum", "conv1x1_tcgen05", "stem_wgrad",
             "allreduce", "alltoall", "broadcast", "barrier_kernel")
     with open(os.path.join(OUT, name + ".launches.md"), "w") as f:
         f.write(f"# {title}\n\nEvery kernel of one training step, serialised under ncu (cold caches: compare shares, "
@@ -138,7 +138,8 @@ def main() -> int:
         if os.path.exists(p):
             summarize_rep(p, t)
     lists = {"launches3": "ResNet-50 step launch list (batch 256, one B200) - before the 1x1-convolution GEMM",
-             "launches4": "ResNet-50 step launch list (batch 256, one B200)",
+             "launches4": "ResNet-50 step launch list (batch 256, one B200) - first version of the 1x1-convolution GEMM",
+             "launches5": "ResNet-50 step launch list (batch 256, one B200)",
              "launches_wd2": "Wide&Deep step launch list (batch 32768, one B200)"}
     for n, t in lists.items():
         p = os.path.join(SCRATCH, n + ".csv")
