@@ -823,6 +823,48 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 EncodeTiledFn g_encode = nullptr;
 
+// cuTensorMapEncodeTiled is a driver call and needs a current context.  A thread that has only made
+// context-free runtime calls so far (an autograd worker entering backward) has none: bind the primary
+// context of its current device.
+int ensure_current_context() {
+  typedef CUresult (*GetCur)(CUcontext*);
+  typedef CUresult (*SetCur)(CUcontext);
+  typedef CUresult (*Retain)(CUcontext*, CUdevice);
+  typedef CUresult (*DevGet)(CUdevice*, int);
+  static GetCur get_cur = nullptr;
+  static SetCur set_cur = nullptr;
+  static Retain retain = nullptr;
+  static DevGet dev_get = nullptr;
+  if (get_cur == nullptr) {
+    void *a = nullptr, *b = nullptr, *c = nullptr, *d = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuCtxGetCurrent", &a, cudaEnableDefault, &q) != cudaSuccess || a == nullptr ||
+        cudaGetDriverEntryPoint("cuCtxSetCurrent", &b, cudaEnableDefault, &q) != cudaSuccess || b == nullptr ||
+        cudaGetDriverEntryPoint("cuDevicePrimaryCtxRetain", &c, cudaEnableDefault, &q) != cudaSuccess || c == nullptr ||
+        cudaGetDriverEntryPoint("cuDeviceGet", &d, cudaEnableDefault, &q) != cudaSuccess || d == nullptr) {
+      pdj_set_error("driver context entry points are unavailable");
+      return -1;
+    }
+    set_cur = reinterpret_cast<SetCur>(b);
+    retain = reinterpret_cast<Retain>(c);
+    dev_get = reinterpret_cast<DevGet>(d);
+    get_cur = reinterpret_cast<GetCur>(a);
+  }
+  CUcontext ctx = nullptr;
+  if (get_cur(&ctx) == CUDA_SUCCESS && ctx != nullptr) return 0;
+  int dev = 0;
+  PDJ_CUDA_CHECK(cudaGetDevice(&dev));
+  CUdevice cudev;
+  CUresult r = dev_get(&cudev, dev);
+  if (r == CUDA_SUCCESS) r = retain(&ctx, cudev);
+  if (r == CUDA_SUCCESS) r = set_cur(ctx);
+  if (r != CUDA_SUCCESS) {
+    pdj_set_error("could not bind the primary context of device %d to this thread (CUresult %d)", dev, (int)r);
+    return (int)r;
+  }
+  return 0;
+}
+
 int make_map(CUtensorMap* map, const void* ptr, int rows, int cols, int ld_elems, int box_cols, int box_rows, bool swizzle) {
   if (g_encode == nullptr) {
     void* p = nullptr;
@@ -834,6 +876,7 @@ int make_map(CUtensorMap* map, const void* ptr, int rows, int cols, int ld_elems
     }
     g_encode = reinterpret_cast<EncodeTiledFn>(p);
   }
+  if (int r = ensure_current_context()) return r;
   const cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};       // innermost first
   const cuuint64_t strides[1] = {(cuuint64_t)ld_elems * 2};              // bytes, for dim 1
   const cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
@@ -858,6 +901,7 @@ int make_map3(CUtensorMap* map, const void* ptr, uint64_t d0, uint64_t d1, uint6
     (void)make_map(&dummy, probe, 1, 64, 64, 64, 1, false);  // resolves the driver entry point
     if (g_encode == nullptr) return -1;
   }
+  if (int r = ensure_current_context()) return r;
   const cuuint64_t dims[3] = {d0, d1, d2};
   const cuuint64_t strides[2] = {s1, s2};
   const cuuint32_t box[3] = {(cuuint32_t)b0, (cuuint32_t)b1, 1};
@@ -933,6 +977,11 @@ int conv_grid(int M, int N, int bn, int sms) {
 }
 
 }  // namespace
+
+int pdj_tma_map_2d_bf16(void* map_out, const void* ptr, int rows, int cols, int ld_elems, int box_cols, int box_rows,
+                        int swizzle128) {
+  return make_map(reinterpret_cast<CUtensorMap*>(map_out), ptr, rows, cols, ld_elems, box_cols, box_rows, swizzle128 != 0);
+}
 
 extern "C" {
 
