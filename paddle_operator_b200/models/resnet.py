@@ -75,19 +75,6 @@ class Bottleneck(nn.Module):
             self.downsample = nn.Conv2d(inplanes, out, 1, stride=stride, bias=False)
             self.bn_ds = _bn(out, False, fused)
 
-    def pdj_kernels_per_step(self) -> int:
-        """Upper bound on the launches of the tcgen05 1x1-convolution kernel in this block per step (bf16 CUDA
-        training; layers below ops.conv.MIN_OUTPUT_BYTES keep the library forward)."""
-        if not self.gemm_1x1:
-            return 0
-        convs = [self.conv1, self.conv3]
-        if self.downsample is not None and self.downsample.stride == (1, 1):
-            convs.append(self.downsample)
-        n = sum(1 for c in convs if c.out_channels % 64 == 0 and c.in_channels % 8 == 0)
-        if self.conv1.in_channels % 64 == 0:
-            n += 1  # conv1's input-gradient GEMM with the skip / shortcut gradient folded in
-        return n
-
     def forward(self, x):
         identity = x
         if self.gemm_1x1:

@@ -30,6 +30,13 @@ from . import _lib
 
 # The fusion pays where the output does not fit in L2 (126 MB): below that the separate statistics
 # pass reads the activation from L2 right after the convolution wrote it, and costs little.
+_launches = [0]  # kernel launches issued from this module (the trainer reports launches per step)
+
+
+def launch_count() -> int:
+    return _launches[0]
+
+
 MIN_OUTPUT_BYTES = int(float(os.environ.get("PDJ_CONV1X1_MIN_MB", "150")) * (1 << 20))
 
 
@@ -63,6 +70,7 @@ def conv1x1_gemm(x2: torch.Tensor, w2: torch.Tensor, stats: bool = True,
     _lib.check(lib.pdj_conv1x1_bf16(x2.data_ptr(), w2.data_ptr(), out.data_ptr(), _lib.ptr(partial), m, n, k,
                                     x2.stride(0), w2.stride(0), out.stride(0),
                                     torch.cuda.current_stream().cuda_stream), "conv1x1_bf16")
+    _launches[0] += 1
     return out, partial
 
 
@@ -78,6 +86,7 @@ def conv1x1_gemm_add(a2: torch.Tensor, b2: torch.Tensor, addend2: torch.Tensor,
     _lib.check(_lib.load().pdj_conv1x1_add_bf16(a2.data_ptr(), b2.data_ptr(), addend2.data_ptr(), out.data_ptr(), m, n, k,
                                                 a2.stride(0), b2.stride(0), addend2.stride(0), out.stride(0),
                                                 torch.cuda.current_stream().cuda_stream), "conv1x1_add_bf16")
+    _launches[0] += 1
     return out
 
 
@@ -248,6 +257,7 @@ class _StemS2dFn(torch.autograd.Function):
         partial = torch.empty((lib.pdj_stem_s2d_partial_rows(n, ho), 2, 64), dtype=torch.float32, device=x.device)
         _lib.check(lib.pdj_stem_s2d_fwd(x.data_ptr(), weight.data_ptr(), y.data_ptr(), partial.data_ptr(), n, ho, wo,
                                         torch.cuda.current_stream().cuda_stream), "stem_s2d_fwd")
+        _launches[0] += 1
         ctx.save_for_backward(x, weight)
         ctx.mark_non_differentiable(partial)
         return y, partial
@@ -268,6 +278,7 @@ class _StemS2dFn(torch.autograd.Function):
             ws = torch.empty(lib.pdj_stem_s2d_wgrad_ws_bytes(), dtype=torch.uint8, device=x.device)
             _lib.check(lib.pdj_stem_s2d_wgrad(x.data_ptr(), dy.data_ptr(), dw.data_ptr(), ws.data_ptr(), n, hi - 3, wi - 3,
                                               torch.cuda.current_stream().cuda_stream), "stem_s2d_wgrad")
+            _launches[0] += 2  # the tcgen05 kernel and the reduction of its per-CTA partials
         return dx, dw
 
 

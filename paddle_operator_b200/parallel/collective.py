@@ -191,8 +191,9 @@ class CollectiveTrainer:
 
     # -- one step ---------------------------------------------------------------
     def _step_body(self) -> None:
-        from ..ops import bn as _bn  # noqa: F401  (kernels counted through module counters)
+        from ..ops import conv as _conv
 
+        conv0 = _conv.launch_count()
         for b in self.flat.buckets:
             b.pending = len(b.params)
             b.event = None
@@ -207,6 +208,7 @@ class CollectiveTrainer:
         pdj_optim.sgd_momentum_(self.flat.master, self.flat.momentum, self.flat.grad, self.flat.param, self.hyper,
                                 self.flat.numel)
         self._count += 1
+        self._count += _conv.launch_count() - conv0  # tcgen05 convolution kernels launched by the model this step
         self.loss.copy_(loss.detach().float())
 
     def capture(self, warmup: int = 2) -> None:
@@ -239,8 +241,6 @@ class CollectiveTrainer:
 
         n = sum(4 for m in self.model.modules() if isinstance(m, FusedBnAct))
         n += sum(2 for m in self.model.modules() if isinstance(m, FusedMaxPool2d))
-        # modules that launch further hand-written kernels say how many (e.g. the tcgen05 1x1 convolutions)
-        n += sum(int(m.pdj_kernels_per_step()) for m in self.model.modules() if hasattr(m, "pdj_kernels_per_step"))
         return n + self.extra_kernels_per_step
 
     def step(self) -> torch.Tensor:
