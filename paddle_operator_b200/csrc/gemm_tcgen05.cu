@@ -30,7 +30,7 @@ constexpr int BM = 128;          // rows of A per tile = UMMA M
 constexpr int BK = 64;           // K per stage: 64 bf16 = one 128-byte swizzle row
 constexpr int UK = 16;           // K per tcgen05.mma for 16-bit inputs
 constexpr int MAX_BN = 256;
-constexpr int MAX_STAGES = 6;
+constexpr int MAX_STAGES = 8;   // barrier slots; the operand ring of a launch uses up to this many
 constexpr int A_STAGE_BYTES = BM * BK * 2;  // 16 KiB
 constexpr int TMEM_COLS = 512;              // two accumulator buffers of up to 256 columns
 constexpr int EPI_WARPS = 8;                // two warps per TMEM lane quarter, each takes half of the columns
@@ -1111,7 +1111,7 @@ int pdj_stem_s2d_fwd(const void* x, const void* w, void* out, float* partial, in
   if (int r = make_map(&mb, w, O, Kc, Kc, BK, O, true)) return r;
   if (int r = make_map3(&mo, out, 64, (uint64_t)Wo, (uint64_t)N * Ho, (uint64_t)O * 2, (uint64_t)Wo * O * 2, 64, BM)) return r;
   const int bn = O;
-  const int stages = MAX_STAGES;  // input-row ring
+  const int stages = 7;  // input-row ring: four rows in use by a tile, three being fetched
   const int smem = 1024 + 256 + SW_STAGING_BYTES + SW_SCRATCH_BYTES + stages * A_STAGE_BYTES + 4 * bn * BK * 2;
   const int rows = N * Ho;
   const int units = stem_units(N, Ho);

@@ -131,6 +131,8 @@ def main() -> int:
     reps = {"prof_bn": "Fused BatchNorm kernels (ResNet-50 step, batch 256)",
             "prof_gemm": "tcgen05 + TMA fused linear kernel (profiles/gemm_bench.py shapes)",
             "prof_emb": "Sharded-embedding kernels and bias colsum (Wide&Deep step, batch 32768, 16.7 M rows)",
+            "prof_conv": "tcgen05 convolution kernels (1x1 + BN statistics, dgrad + skip add, stem forward / wgrad) and "
+                         "TMA-streamed BN reductions on ResNet-50 layer shapes, batch 256 (profiles/run_conv_kernels.py)",
             "prof_collectives": "Fused all-reduce / all-to-all kernel bodies, 8 ranks emulated on one GPU "
                                 "(cooperative launch; bandwidths here are HBM-local, NVLink numbers are in r1/sweep_n8.json)"}
     for n, t in reps.items():
