@@ -60,7 +60,7 @@ __device__ __forceinline__ uint32_t atom_add_sys(uint32_t* p, uint32_t v) {
 }
 
 // One warp per sample: S slots, D floats per row, D/4 lanes per row.
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(1024)
 emb_lookup_kernel(PdjComm c, PdjEmbTable t, size_t ids_off, size_t out_deep_off, size_t out_wide_off, int B, int S,
                   int do_barrier) {
   const int rank = c.rank + blockIdx.y;
@@ -110,11 +110,11 @@ emb_lookup_kernel(PdjComm c, PdjEmbTable t, size_t ids_off, size_t out_deep_off,
 // over NVLink (~2 us per access) needs.  SASS: UBLKCP + SYNCS.
 __device__ __forceinline__ uint32_t emb_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(1024)
 emb_lookup_tma_kernel(PdjComm c, PdjEmbTable t, size_t ids_off, size_t out_deep_off, size_t out_wide_off, int B, int S,
                       int do_barrier) {
   extern __shared__ __align__(128) uint8_t emb_sm[];
-  __shared__ __align__(8) uint64_t bars[8][2];
+  __shared__ __align__(8) uint64_t bars[32][2];  // one pair per warp, up to 1024 threads
   const int rank = c.rank + blockIdx.y;
   const int NR = c.nranks;
   PdjSignalPad* me = pdj_pad(c, rank);
@@ -134,7 +134,8 @@ emb_lookup_tma_kernel(PdjComm c, PdjEmbTable t, size_t ids_off, size_t out_deep_
   const long long* ids = reinterpret_cast<const long long*>(c.base[rank] + ids_off);
   __nv_bfloat16* out_deep = reinterpret_cast<__nv_bfloat16*>(c.base[rank] + out_deep_off);
   float* out_wide = reinterpret_cast<float*>(c.base[rank] + out_wide_off);
-  const int warps = gridDim.x * 8;
+  const int wpb = (int)(blockDim.x >> 5);
+  const int warps = gridDim.x * wpb;
 
   auto issue = [&](int b, int buf) -> float {
     const uint32_t bar = buf ? bar1 : bar0;
@@ -158,7 +159,7 @@ emb_lookup_tma_kernel(PdjComm c, PdjEmbTable t, size_t ids_off, size_t out_deep_
   };
 
   uint32_t phase0 = 0, phase1 = 0;
-  int b = blockIdx.x * 8 + w;
+  int b = blockIdx.x * wpb + w;
   int buf = 0;
   float wv_cur = 0.f;
   if (b < B) wv_cur = issue(b, 0);
@@ -210,7 +211,7 @@ emb_lookup_tma_kernel(PdjComm c, PdjEmbTable t, size_t ids_off, size_t out_deep_
 
 // Push.  mode 0 (sync): accumulate into the owner's staging rows and register
 // the row; mode 1 (async SGD): apply w -= lr * g on the owner directly.
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(1024)
 emb_push_kernel(PdjComm c, PdjEmbTable t, size_t ids_off, size_t gdeep_off, size_t gwide_off, int B, int S, int mode,
                 float lr, float grad_scale) {
   const int rank = c.rank + blockIdx.y;
@@ -378,25 +379,36 @@ int pdj_emb_lookup(const PdjComm* c, const PdjEmbTable* t, size_t ids_off, size_
                    int B, int S, int barrier, int nblocks, int emulate, cudaStream_t st) {
   if (check_table(t)) return -1;
   static const bool no_tma = getenv("PDJ_EMB_NO_TMA") != nullptr;
+  // Random 64-byte row gathers are latency-bound: what matters is rows in flight per SM.  With one block
+  // per SM (the barrier-slot budget of a channel) that means many warps per block: 32 warps, two samples
+  // in flight each.  The single-GPU emulation keeps small blocks so that all ranks stay co-resident.
+  static const int knob_threads = getenv("PDJ_EMB_THREADS") ? atoi(getenv("PDJ_EMB_THREADS")) : 1024;
+  int threads = emulate ? 256 : knob_threads;
+  if (threads < 32 || threads > 1024 || threads % 32 != 0) threads = 256;
   if (!no_tma && t->dim >= 8 && t->dim <= 64 && S <= 32) {
-    const size_t smem = (size_t)8 * 2 * 32 * t->dim * 4;
+    const size_t per_warp = (size_t)2 * 32 * t->dim * 4;
+    while ((size_t)(threads / 32) * per_warp > 160 * 1024 && threads > 32) threads -= 32;
+    const size_t smem = (size_t)(threads / 32) * per_warp;
     static size_t attr_set_for = 0;
     if (smem > 48 * 1024 && smem > attr_set_for) {
       PDJ_CUDA_CHECK(cudaFuncSetAttribute(emb_lookup_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
       attr_set_for = smem;
     }
-    return launch_emb(emb_lookup_tma_kernel, nblocks, 256, smem, emulate, c->nranks, st, *c, *t, ids_off, out_deep_off,
+    return launch_emb(emb_lookup_tma_kernel, nblocks, threads, smem, emulate, c->nranks, st, *c, *t, ids_off, out_deep_off,
                       out_wide_off, B, S, barrier);
   }
-  return launch_emb(emb_lookup_kernel, nblocks, 256, (size_t)0, emulate, c->nranks, st, *c, *t, ids_off, out_deep_off,
+  return launch_emb(emb_lookup_kernel, nblocks, threads, (size_t)0, emulate, c->nranks, st, *c, *t, ids_off, out_deep_off,
                     out_wide_off, B, S, barrier);
 }
 
 int pdj_emb_push(const PdjComm* c, const PdjEmbTable* t, size_t ids_off, size_t gdeep_off, size_t gwide_off, int B,
                  int S, int async_sgd, float lr, float grad_scale, int nblocks, int emulate, cudaStream_t st) {
   if (check_table(t)) return -1;
-  return launch_emb(emb_push_kernel, nblocks, 256, (size_t)0, emulate, c->nranks, st, *c, *t, ids_off, gdeep_off, gwide_off, B,
-                    S, async_sgd ? 1 : 0, lr, grad_scale);
+  static const int knob_threads = getenv("PDJ_EMB_THREADS") ? atoi(getenv("PDJ_EMB_THREADS")) : 1024;
+  int threads = emulate ? 256 : knob_threads;
+  if (threads < 32 || threads > 1024 || threads % 32 != 0) threads = 256;
+  return launch_emb(emb_push_kernel, nblocks, threads, (size_t)0, emulate, c->nranks, st, *c, *t, ids_off, gdeep_off, gwide_off,
+                    B, S, async_sgd ? 1 : 0, lr, grad_scale);
 }
 
 int pdj_emb_apply(const PdjComm* c, const PdjEmbTable* t, int optimizer, float lr, float eps, int nblocks,

@@ -143,7 +143,8 @@ def main() -> int:
              "launches4": "ResNet-50 step launch list (batch 256, one B200) - first version of the 1x1-convolution GEMM",
              "launches5": "ResNet-50 step launch list (batch 256, one B200) - before the TMA-streamed BN reductions",
              "launches6": "ResNet-50 step launch list (batch 256, one B200)",
-             "launches_wd2": "Wide&Deep step launch list (batch 32768, one B200)"}
+             "launches_wd2": "Wide&Deep step launch list (batch 32768, one B200) - 256-thread embedding blocks",
+             "launches_wd3": "Wide&Deep step launch list (batch 32768, one B200)"}
     for n, t in lists.items():
         p = os.path.join(SCRATCH, n + ".csv")
         if os.path.exists(p):

@@ -80,3 +80,41 @@ def test_s2d_model_trains_and_keeps_structural_zeros():
     assert l1 < l0
     w = model.conv1.weight.float()
     assert float((w * (1 - model.stem_mask)).abs().max()) == 0.0
+
+
+def test_resnet_gemm_1x1_falls_back_to_library_convolutions_on_cpu():
+    """The tcgen05 convolution paths are CUDA/bf16 only: on CPU the same module graph must compute exactly
+    what the plain model computes (same parameters, same outputs, same gradients)."""
+    import torch
+
+    from paddle_operator_b200.models.resnet import ResNet
+
+    torch.manual_seed(0)
+    a = ResNet((2, 1), 8, fused=True, width=16, gemm_1x1=False).train()
+    b = ResNet((2, 1), 8, fused=True, width=16, gemm_1x1=True).train()
+    b.load_state_dict(a.state_dict())
+    x = torch.randn(2, 3, 32, 32)
+    ya, yb = a(x), b(x)
+    assert torch.allclose(ya, yb, atol=1e-5)
+    ya.sum().backward()
+    yb.sum().backward()
+    for (n, pa), (_, pb) in zip(a.named_parameters(), b.named_parameters()):
+        assert torch.allclose(pa.grad, pb.grad, atol=1e-4), n
+
+
+def test_conv_ops_eligibility_rules():
+    import torch
+
+    from paddle_operator_b200.ops import conv as conv_ops
+
+    x = torch.randn(2, 64, 8, 8).contiguous(memory_format=torch.channels_last)
+    w = torch.randn(128, 64, 1, 1)
+    assert not conv_ops.conv1x1_eligible(x, w)            # CPU / fp32
+    y, partial = conv_ops.conv1x1_stats(x, w)
+    assert partial is None and y.shape == (2, 128, 8, 8)
+    y, partial, skip = conv_ops.conv1x1_stats(x, w, carry_skip=True)
+    assert partial is None and skip is x
+    y1, p1, yd, pd = conv_ops.conv1x1_dual(x, w, torch.randn(256, 64, 1, 1), 2)
+    assert p1 is None and pd is None and yd.shape == (2, 256, 4, 4)
+    ys, ps = conv_ops.stem_s2d_conv(torch.randn(1, 16, 19, 19), torch.randn(64, 16, 4, 4))
+    assert ps is None and ys.shape == (1, 64, 16, 16)

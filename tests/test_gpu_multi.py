@@ -2,6 +2,7 @@
 rendezvous, peer mappings, NVLS multicast, every collective against NCCL, and a short
 data-parallel ResNet run whose ranks must agree on the loss."""
 import json
+import re
 import os
 import subprocess
 import sys
@@ -36,13 +37,11 @@ def test_data_parallel_resnet_ranks_agree():
                   "16", "--steps", "12", "--log-every", "12")
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     rows = []
-    for l in r.stdout.splitlines():  # two ranks share stdout: keep the lines that are whole JSON objects
-        l = l.strip()
-        if l.startswith("{") and l.endswith("}"):
-            try:
-                rows.append(json.loads(l))
-            except ValueError:
-                pass
+    for m in re.findall(r"\{[^{}]*\}", r.stdout):  # two ranks share stdout: their lines may interleave or abut
+        try:
+            rows.append(json.loads(m))
+        except ValueError:
+            pass
     last = {x["rank"]: x for x in rows if x.get("step") == 12}
     assert len(last) >= 1, r.stdout[-1500:]
     # every rank sees a different batch but holds identical weights after the fused all-reduce
