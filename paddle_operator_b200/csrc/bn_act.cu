@@ -197,7 +197,7 @@ bn_stats_kernel(const __nv_bfloat16* __restrict__ x, int M, int C, const float* 
 }
 
 // Statistics already reduced to `nb` partial rows by the producer of x (the 1x1-convolution GEMM
-// of gemm_tcgen05.cu writes them from its epilogue): only the finalisation is left.  8 channels per
+// of conv_tcgen05.cu writes them from its epilogue): only the finalisation is left.  8 channels per
 // block, 32 threads per channel.
 __global__ void __launch_bounds__(kThreads)
 bn_finalize_kernel(const float* __restrict__ partial, unsigned int nb, int M, int C, const float* __restrict__ gamma,

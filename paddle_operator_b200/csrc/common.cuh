@@ -129,6 +129,6 @@ __device__ __forceinline__ uint32_t pdj_f2_to_bf2(float a, float b) {
 // Host: last error text (thread-local), see pdj_last_error().
 void pdj_set_error(const char* fmt, ...);
 // Host: encodes a 2-D bf16 TMA tensor map (CUtensorMap, 128 bytes at `map_out`) for a row-major
-// [rows, cols] tensor with a row pitch of ld_elems; box = box_rows x box_cols.  Defined in gemm_tcgen05.cu.
+// [rows, cols] tensor with a row pitch of ld_elems; box = box_rows x box_cols.  Defined in tma_util.cu.
 int pdj_tma_map_2d_bf16(void* map_out, const void* ptr, int rows, int cols, int ld_elems, int box_cols, int box_rows,
                         int swizzle128);

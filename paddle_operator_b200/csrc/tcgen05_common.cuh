@@ -1,0 +1,154 @@
+// Device-side building blocks shared by the tcgen05 kernels (gemm_tcgen05.cu, conv_tcgen05.cu): mbarrier /
+// TMA / tcgen05 PTX wrappers, the shared-memory operand ring and the TMA-producer / MMA-issuer loops of the
+// persistent GEMM pipeline, plus the host helpers of tma_util.cu.  sm_100a only.
+#pragma once
+#include <cuda.h>
+#include <stdint.h>
+
+#include "common.cuh"
+
+namespace pdj_tc {
+
+constexpr int BM = 128;          // rows of A per tile = UMMA M
+constexpr int BK = 64;           // K per stage: 64 bf16 = one 128-byte swizzle row
+constexpr int UK = 16;           // K per tcgen05.mma for 16-bit inputs
+constexpr int MAX_BN = 256;
+constexpr int MAX_STAGES = 8;   // barrier slots; the operand ring of a launch uses up to this many
+constexpr int A_STAGE_BYTES = BM * BK * 2;  // 16 KiB
+constexpr int TMEM_COLS = 512;              // two accumulator buffers of up to 256 columns
+constexpr int EPI_WARPS = 8;                // two warps per TMEM lane quarter, each takes half of the columns
+constexpr int THREADS = 64 + 32 * EPI_WARPS; // warp 0: TMA, warp 1: MMA + TMEM owner, warps 2..9: epilogue
+constexpr int SMEM_LIMIT = 227 * 1024;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "WAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE_%=;\n\t"
+      "bra WAIT_%=;\n\t"
+      "DONE_%=:\n\t"
+      "}" ::"r"(bar),
+      "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(dst),
+      "l"(map), "r"(c0), "r"(c1), "r"(bar)
+      : "memory");
+}
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, uint32_t src, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(map), "r"(src), "r"(c0),
+               "r"(c1)
+               : "memory");
+}
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map, int c0, int c1, int c2, uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(dst),
+      "l"(map), "r"(c0), "r"(c1), "r"(c2), "r"(bar)
+      : "memory");
+}
+__device__ __forceinline__ void tma_store_3d(const CUtensorMap* map, uint32_t src, int c0, int c1, int c2) {
+  asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(map), "r"(src), "r"(c0),
+               "r"(c1), "r"(c2)
+               : "memory");
+}
+// Shared-memory matrix descriptor: K-major tile, 128-byte swizzle, rows 128 B apart,
+// 8-row groups 1024 B apart (SBO), descriptor version 1 (sm_100).
+__device__ __forceinline__ uint64_t umma_desc(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);   // start address, bits [0,14)
+  d |= (uint64_t)1 << 16;                        // leading byte offset (unused for swizzled K-major), bits [16,30)
+  d |= (uint64_t)(1024 >> 4) << 32;              // stride byte offset, bits [32,46)
+  d |= (uint64_t)1 << 46;                        // version
+  d |= (uint64_t)2 << 61;                        // SWIZZLE_128B
+  return d;
+}
+__device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "}" ::"r"(tmem_d),
+      "l"(da), "l"(db), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+
+// Shared-memory ring + accumulator hand-off barriers of one CTA.
+struct Pipe {
+  uint32_t a_smem, b_smem, b_stage_bytes;
+  uint32_t full0, empty0;      // per ring slot: TMA -> MMA, MMA -> TMA
+  uint32_t tfull0, tempty0;    // per accumulator buffer: MMA -> epilogue, epilogue -> MMA
+  int stages;
+};
+
+// TMA producer (one thread): walks this CTA's tiles and keeps the ring full.
+__device__ __forceinline__ void producer_loop(const CUtensorMap* tma_a, const CUtensorMap* tma_b, const Pipe& p, int total,
+                                              int tiles_n, int block_n, int num_kb) {
+  const uint32_t stage_bytes = (uint32_t)A_STAGE_BYTES + p.b_stage_bytes;
+  uint32_t it = 0;
+  for (int t = blockIdx.x; t < total; t += gridDim.x) {
+    const int m0 = (t / tiles_n) * BM, n0 = (t % tiles_n) * block_n;
+    for (int kb = 0; kb < num_kb; ++kb, ++it) {
+      const uint32_t s = it % (uint32_t)p.stages, ph = (it / (uint32_t)p.stages) & 1u;
+      mbar_wait(p.empty0 + 8 * s, ph ^ 1u);
+      mbar_expect_tx(p.full0 + 8 * s, stage_bytes);
+      tma_load_2d(p.a_smem + s * A_STAGE_BYTES, tma_a, kb * BK, m0, p.full0 + 8 * s);
+      tma_load_2d(p.b_smem + s * p.b_stage_bytes, tma_b, kb * BK, n0, p.full0 + 8 * s);
+    }
+  }
+}
+
+// MMA issuer (one thread): tile i accumulates into TMEM buffer i & 1.
+__device__ __forceinline__ void mma_loop(const Pipe& p, uint32_t tmem_base, int total, int block_n, int num_kb) {
+  // instruction descriptor: D = f32, A = B = bf16, both K-major, N >> 3, M >> 4
+  const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(block_n >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+  uint32_t it = 0, i = 0;
+  for (int t = blockIdx.x; t < total; t += gridDim.x, ++i) {
+    const uint32_t buf = i & 1u, aph = (i >> 1) & 1u;
+    mbar_wait(p.tempty0 + 8 * buf, aph ^ 1u);  // the epilogue has drained this accumulator
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_d = tmem_base + buf * MAX_BN;
+    for (int kb = 0; kb < num_kb; ++kb, ++it) {
+      const uint32_t s = it % (uint32_t)p.stages, ph = (it / (uint32_t)p.stages) & 1u;
+      mbar_wait(p.full0 + 8 * s, ph);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+#pragma unroll
+      for (int k = 0; k < BK / UK; ++k) {
+        const uint64_t da = umma_desc(p.a_smem + s * A_STAGE_BYTES + k * UK * 2);
+        const uint64_t db = umma_desc(p.b_smem + s * p.b_stage_bytes + k * UK * 2);
+        umma_f16(tmem_d, da, db, idesc, (uint32_t)((kb | k) != 0));
+      }
+      umma_commit(p.empty0 + 8 * s);  // slot is free once these MMAs have read it
+    }
+    umma_commit(p.tfull0 + 8 * buf);  // accumulator complete
+  }
+}
+
+}  // namespace pdj_tc
+
+// ---- host helpers (tma_util.cu) ---------------------------------------------------------------
+// Tensor-map encoders (cuTensorMapEncodeTiled through the runtime's driver entry point; they bind the
+// primary context first when the calling thread has none) and the cached SM count.
+int pdj_tc_make_map(CUtensorMap* map, const void* ptr, int rows, int cols, int ld_elems, int box_cols, int box_rows,
+                    bool swizzle);
+int pdj_tc_make_map3(CUtensorMap* map, const void* ptr, uint64_t d0, uint64_t d1, uint64_t d2, uint64_t s1, uint64_t s2,
+                     int b0, int b1);
+int pdj_tc_sm_count();

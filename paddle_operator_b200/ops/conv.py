@@ -2,7 +2,7 @@
 
 A stride-1 1x1 convolution over a channels-last activation is the GEMM
 [N*H*W, Cin] x [Cout, Cin]^T.  `conv1x1_stats` runs it on the hand-written
-TMA + tcgen05 kernel (csrc/gemm_tcgen05.cu::conv1x1_tcgen05_kernel) whose
+TMA + tcgen05 kernel (csrc/conv_tcgen05.cu::conv1x1_tcgen05_kernel) whose
 epilogue also accumulates the per-channel sum and sum of squares of the output,
 so the training-mode BatchNorm that follows (ops.bn, `partial=`) skips its
 statistics pass - one full read of the activation per layer.
@@ -246,7 +246,7 @@ def stem_s2d_eligible(x: torch.Tensor, weight: torch.Tensor) -> bool:
 
 class _StemS2dFn(torch.autograd.Function):
     """y = conv2d(x, weight) for the [64,16,4,4] stem over x[N,16,Ho+3,Wo+3] on the tcgen05 pipeline
-    (csrc/gemm_tcgen05.cu, WIN mode), with the BN partial sums from its epilogue."""
+    (csrc/conv_tcgen05.cu, WIN mode), with the BN partial sums from its epilogue."""
 
     @staticmethod
     def forward(ctx, x, weight):
