@@ -230,6 +230,36 @@ def test_alltoall_broadcast_barrier(comms, nranks):
     assert all(e == 0 for e in comm.error_flags())
 
 
+def test_device_barrier_and_allreduce_stress(comms):
+    """a stress test of the device barrier.  500 back-to-back barriers and 200 in-place
+    all-reduces of changing sizes on 8 emulated ranks, no host synchronisation in between: a lost or
+    reordered flag would either trap (spin timeout -> CUDA error) or leave a wrong sum / an error flag."""
+    from paddle_operator_b200.parallel.symm import AR_ONESHOT, AR_TWOSHOT
+
+    comm = comms(8)
+    comm.reset_allocations()
+    n_max = 1 << 16
+    a = comm.alloc(n_max * 2)
+    b = comm.alloc(n_max * 2)
+    for _ in range(500):
+        comm.barrier()
+    torch.manual_seed(3)
+    for it in range(200):
+        n = 8 * (1 + (it * 37) % 4096)
+        for r in range(comm.nranks):
+            comm.tensor(a, (n,), torch.bfloat16, rank=r).fill_(float(r + 1 + it % 3))
+        algo = AR_TWOSHOT if it % 2 == 0 else AR_ONESHOT
+        out = a if algo == AR_TWOSHOT else b
+        comm.all_reduce_bf16(a, out, n, scale=1.0 / comm.nranks, algo=algo, nblocks=8)  # 64 co-resident blocks
+        if it % 20 == 19:  # sum over r of (r + 1 + k) / 8 = 4.5 + k
+            exp = 4.5 + it % 3
+            for r in (0, comm.nranks - 1):
+                got = comm.tensor(out, (n,), torch.bfloat16, rank=r).float()
+                assert torch.all(got == exp), (it, r, float(got[0]), exp)
+    torch.cuda.synchronize()
+    assert all(e == 0 for e in comm.error_flags())
+
+
 # ---------------------------------------------------------------------------
 @pytest.mark.parametrize("gemm_1x1", [False, True])
 def test_resnet_fused_matches_torch(dev, gemm_1x1, monkeypatch):
