@@ -194,6 +194,16 @@ int pdj_preprocess_u8_s2d(const void* in, void* out, int N, int H, int W, const 
                           cudaStream_t st);
 /* out[c] = sum_r x[r, c] for row-major bf16 x with row pitch ld (the bias gradient of a linear layer). */
 int pdj_colsum_bf16(const void* x, float* out, int M, int N, int ld, cudaStream_t st);
+/* Wide&Deep head in one pass (one warp per sample): z = h . w_out + b_out + wide_sum + dense . w_d + b_d,
+ * loss[b] = BCE-with-logits(z, labels[b]), dlogit[b] = (sigmoid(z) - labels[b]) * grad_scale.  h bf16 [B,N]
+ * (row pitch ld), w_out / w_d / biases bf16 (biases may be NULL), dense fp32 [B,Dd], wide_sum fp32 or NULL.
+ * pdj_wd_head_dz then forms the gradient entering the top ReLU layer, mask applied:
+ * dz[b,j] = h[b,j] > 0 ? dlogit[b] * w_out[j] : 0. */
+int pdj_wd_head(const void* h, int ld, const void* w_out, const void* b_out, const float* wide_sum, const float* dense,
+                const void* w_d, const void* b_d, const float* labels, float* loss, float* dlogit, int B, int N, int Dd,
+                float grad_scale, cudaStream_t st);
+int pdj_wd_head_dz(const float* dlogit, const void* w_out, const void* h, int ldh, void* dz, int ldz, int B, int N,
+                   cudaStream_t st);
 int pdj_softmax_xent(const void* logits, const int64_t* labels, void* dlogits, float* loss_sum, int rows,
                      int ncls, float grad_scale, cudaStream_t st);
 

@@ -186,6 +186,65 @@ colsum_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ out, int 
   }
 }
 
+// ---- Wide&Deep head: output layer + wide part + binary cross-entropy in one pass -------------------
+// One warp per sample:
+//   z = h[b,:] . w_out + b_out + wide_sum[b] + dense[b,:] . w_d + b_d
+//   loss[b] = max(z,0) - z*y + log1p(exp(-|z|)),   dlogit[b] = (sigmoid(z) - y) * grad_scale
+// replacing the gemv, bias adds, sigmoid / log-sigmoid / mean chain and their backward (about fifteen
+// launches of a few microseconds each in a 1 ms step).
+__global__ void __launch_bounds__(256)
+wd_head_kernel(const __nv_bfloat16* __restrict__ h, int ld, const __nv_bfloat16* __restrict__ w_out,
+               const __nv_bfloat16* __restrict__ b_out, const float* __restrict__ wide_sum,
+               const float* __restrict__ dense, const __nv_bfloat16* __restrict__ w_d,
+               const __nv_bfloat16* __restrict__ b_d, const float* __restrict__ labels, float* __restrict__ loss,
+               float* __restrict__ dlogit, int B, int N, int Dd, float grad_scale) {
+  const int lane = threadIdx.x & 31;
+  const int warps = (gridDim.x * blockDim.x) >> 5;
+  const float bias = (b_out ? __bfloat162float(b_out[0]) : 0.f) + (b_d ? __bfloat162float(b_d[0]) : 0.f);
+  for (int b = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; b < B; b += warps) {
+    const __nv_bfloat16* hr = h + (size_t)b * ld;
+    float acc = 0.f;
+    for (int c = 2 * lane; c + 1 < N; c += 64) {  // N is even (checked on the host)
+      const float2 hv = pdj_bf2_to_f2(__ldg(reinterpret_cast<const uint32_t*>(hr + c)));
+      const float2 wv = pdj_bf2_to_f2(__ldg(reinterpret_cast<const uint32_t*>(w_out + c)));
+      acc = fmaf(hv.x, wv.x, acc);
+      acc = fmaf(hv.y, wv.y, acc);
+    }
+    if (lane < Dd) acc = fmaf(dense[(size_t)b * Dd + lane], __bfloat162float(w_d[lane]), acc);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if (lane == 0) {
+      const float z = acc + bias + (wide_sum ? wide_sum[b] : 0.f);
+      const float y = labels[b];
+      const float e = __expf(-fabsf(z));
+      loss[b] = fmaxf(z, 0.f) - z * y + log1pf(e);
+      const float sig = z >= 0.f ? 1.f / (1.f + e) : e / (1.f + e);
+      dlogit[b] = (sig - y) * grad_scale;
+    }
+  }
+}
+
+// dz[b,j] = (h[b,j] > 0) ? dlogit[b] * w_out[j] : 0  - the gradient entering the top ReLU layer, mask applied.
+__global__ void __launch_bounds__(256)
+wd_head_dz_kernel(const float* __restrict__ dlogit, const __nv_bfloat16* __restrict__ w_out,
+                  const __nv_bfloat16* __restrict__ h, int ldh, __nv_bfloat16* __restrict__ dz, int ldz, int B, int N8) {
+  const size_t total = (size_t)B * N8;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int b = (int)(i / N8), v = (int)(i % N8);
+    const uint4 hv = __ldg(reinterpret_cast<const uint4*>(h + (size_t)b * ldh) + v);
+    const uint4 wv = __ldg(reinterpret_cast<const uint4*>(w_out) + v);
+    const float g = dlogit[b];
+    const uint32_t hh[4] = {hv.x, hv.y, hv.z, hv.w}, ww[4] = {wv.x, wv.y, wv.z, wv.w};
+    uint32_t o[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float2 hf = pdj_bf2_to_f2(hh[k]), wf = pdj_bf2_to_f2(ww[k]);
+      o[k] = pdj_f2_to_bf2(hf.x > 0.f ? g * wf.x : 0.f, hf.y > 0.f ? g * wf.y : 0.f);
+    }
+    reinterpret_cast<uint4*>(dz + (size_t)b * ldz)[v] = make_uint4(o[0], o[1], o[2], o[3]);
+  }
+}
+
 int grid_for(size_t n, int per_block) {
   size_t g = (n + per_block - 1) / per_block;
   if (g > 148 * 8) g = 148 * 8;
@@ -239,6 +298,34 @@ int pdj_colsum_bf16(const void* x, float* out, int M, int N, int ld, cudaStream_
   if (M < 1 || N < 1) return 0;
   PDJ_CUDA_CHECK(cudaMemsetAsync(out, 0, (size_t)N * sizeof(float), st));
   colsum_kernel<<<(M + kColsumRows - 1) / kColsumRows, 256, 0, st>>>((const __nv_bfloat16*)x, out, M, N, ld);
+  PDJ_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+int pdj_wd_head(const void* h, int ld, const void* w_out, const void* b_out, const float* wide_sum, const float* dense,
+                const void* w_d, const void* b_d, const float* labels, float* loss, float* dlogit, int B, int N, int Dd,
+                float grad_scale, cudaStream_t st) {
+  if (B < 1 || N < 2 || N % 2 != 0 || ld % 2 != 0 || Dd < 0 || Dd > 32 || ((uintptr_t)h & 3) || ((uintptr_t)w_out & 3)) {
+    pdj_set_error("pdj_wd_head: need even N and ld, at most 32 dense features, 4-byte aligned rows (N=%d ld=%d Dd=%d)", N, ld, Dd);
+    return -1;
+  }
+  wd_head_kernel<<<grid_for((size_t)B * 32, 256), 256, 0, st>>>(
+      (const __nv_bfloat16*)h, ld, (const __nv_bfloat16*)w_out, (const __nv_bfloat16*)b_out, wide_sum, dense,
+      (const __nv_bfloat16*)w_d, (const __nv_bfloat16*)b_d, labels, loss, dlogit, B, N, Dd, grad_scale);
+  PDJ_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+int pdj_wd_head_dz(const float* dlogit, const void* w_out, const void* h, int ldh, void* dz, int ldz, int B, int N,
+                   cudaStream_t st) {
+  if (B < 1 || N < 8 || N % 8 != 0 || ldh % 8 != 0 || ldz % 8 != 0 || ((uintptr_t)h & 15) || ((uintptr_t)dz & 15) ||
+      ((uintptr_t)w_out & 15)) {
+    pdj_set_error("pdj_wd_head_dz: need N, ldh, ldz multiples of 8 and 16-byte aligned tensors (N=%d)", N);
+    return -1;
+  }
+  wd_head_dz_kernel<<<grid_for((size_t)B * (N / 8), 256), 256, 0, st>>>(dlogit, (const __nv_bfloat16*)w_out,
+                                                                     (const __nv_bfloat16*)h, ldh, (__nv_bfloat16*)dz, ldz,
+                                                                     B, N / 8);
   PDJ_CUDA_CHECK(cudaGetLastError());
   return 0;
 }

@@ -45,13 +45,30 @@ class WideDeepDense(nn.Module):
     def layers(self):
         return self.tower.layers
 
-    def forward(self, deep_emb: torch.Tensor, wide_sum: torch.Tensor, dense: torch.Tensor) -> torch.Tensor:
-        """deep_emb [B, slots*emb_dim], wide_sum [B] fp32, dense [B, 13] -> logits [B] fp32."""
+    def _tower_input(self, deep_emb: torch.Tensor, dense: torch.Tensor) -> torch.Tensor:
         parts = [deep_emb, dense.to(deep_emb.dtype)]
         if self.in_dim != self.raw_in:
             parts.append(torch.zeros((deep_emb.shape[0], self.in_dim - self.raw_in), dtype=deep_emb.dtype,
                                      device=deep_emb.device))
-        x = self.tower(torch.cat(parts, dim=1))
+        return torch.cat(parts, dim=1)
+
+    def loss(self, deep_emb: torch.Tensor, wide_sum: torch.Tensor, dense: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
+        """Mean BCE-with-logits of forward(...) against labels.  On CUDA bf16 with the fused tower the output
+        layer, the wide part and the loss run as one kernel (ops/wd_head.py), forward and backward."""
+        from ..ops.wd_head import head_bce_loss
+
+        x_in = self._tower_input(deep_emb, dense)
+        fused_head = (self.fused and x_in.is_cuda and x_in.dtype == torch.bfloat16
+                      and self.out.weight.dtype == torch.bfloat16 and self.out.in_features % 8 == 0)
+        if not fused_head:
+            return bce_with_logits(self.forward(deep_emb, wide_sum, dense), labels)
+        h = self.tower(x_in, top_grad_masked=True)
+        return head_bce_loss(h, self.out.weight, self.out.bias, wide_sum, dense, self.wide_dense.weight,
+                             self.wide_dense.bias, labels)
+
+    def forward(self, deep_emb: torch.Tensor, wide_sum: torch.Tensor, dense: torch.Tensor) -> torch.Tensor:
+        """deep_emb [B, slots*emb_dim], wide_sum [B] fp32, dense [B, 13] -> logits [B] fp32."""
+        x = self.tower(self._tower_input(deep_emb, dense))
         deep = self.out(x).squeeze(1).float()
         wide = wide_sum + self.wide_dense(dense.to(self.wide_dense.weight.dtype)).squeeze(1).float()
         return deep + wide

@@ -96,6 +96,8 @@ def _declare(lib: ctypes.CDLL) -> None:
         "pdj_sgd_momentum": (c_int, [vp, vp, vp, vp, sz, sz, vp, st]),
         "pdj_preprocess_u8": (c_int, [vp, vp, sz, fp, fp, st]),
         "pdj_preprocess_u8_s2d": (c_int, [vp, vp, c_int, c_int, c_int, fp, fp, st]),
+        "pdj_wd_head": (c_int, [vp, c_int, vp, vp, vp, vp, vp, vp, vp, vp, vp, c_int, c_int, c_int, c_float, st]),
+        "pdj_wd_head_dz": (c_int, [vp, vp, vp, c_int, vp, c_int, c_int, c_int, st]),
         "pdj_colsum_bf16": (c_int, [vp, vp, c_int, c_int, c_int, st]),
         "pdj_softmax_xent": (c_int, [vp, vp, vp, vp, c_int, c_int, c_float, st]),
     }

@@ -31,7 +31,7 @@ def colsum(x: torch.Tensor) -> torch.Tensor:
 
 class _FusedMLPFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, n_layers, *params):
+    def forward(ctx, x, n_layers, top_grad_masked, *params):
         ws = params[:n_layers]
         bs = params[n_layers:2 * n_layers]
         b32 = params[2 * n_layers:]
@@ -41,6 +41,7 @@ class _FusedMLPFn(torch.autograd.Function):
             hs.append(linear_bf16(hs[-1], ws[l], bias, relu=True))
         ctx.save_for_backward(*hs, *ws)
         ctx.n = n_layers
+        ctx.top_grad_masked = top_grad_masked
         ctx.bias_dtypes = [b.dtype for b in bs]
         return hs[-1]
 
@@ -49,7 +50,10 @@ class _FusedMLPFn(torch.autograd.Function):
         n = ctx.n
         saved = ctx.saved_tensors
         hs, ws = saved[:n + 1], saved[n + 1:]
-        dz = torch.where(hs[n] > 0, dy, torch.zeros((), dtype=dy.dtype, device=dy.device)).contiguous()
+        if ctx.top_grad_masked:  # the consumer already zeroed dy where the top activation is zero (ops.wd_head)
+            dz = dy.contiguous()
+        else:
+            dz = torch.where(hs[n] > 0, dy, torch.zeros((), dtype=dy.dtype, device=dy.device)).contiguous()
         dws, dbs = [None] * n, [None] * n
         dx = None
         for l in range(n, 0, -1):  # layer l maps hs[l-1] -> hs[l] with ws[l-1]
@@ -59,7 +63,7 @@ class _FusedMLPFn(torch.autograd.Function):
                 dz = linear_bf16(dz, ws[l - 1].t().contiguous(), mask=hs[l - 1])
             elif ctx.needs_input_grad[0]:
                 dx = linear_bf16(dz, ws[0].t().contiguous())
-        return (dx, None, *dws, *dbs, *([None] * n))
+        return (dx, None, None, *dws, *dbs, *([None] * n))
 
 
 class FusedMLP(torch.nn.Module):
@@ -71,11 +75,13 @@ class FusedMLP(torch.nn.Module):
         self.layers = torch.nn.ModuleList([torch.nn.Linear(a, b) for a, b in zip(dims[:-1], dims[1:])])
         self.bias_f32 = [None] * len(self.layers)  # a trainer may point these at fp32 master copies
 
-    def forward(self, x):
+    def forward(self, x, top_grad_masked: bool = False):
+        """`top_grad_masked`: the gradient that will arrive for the output is already zero wherever the output
+        is zero (a fused consumer applied the ReLU derivative), so backward skips its own mask pass."""
         if x.is_cuda and x.dtype == torch.bfloat16 and self.layers[0].weight.dtype == torch.bfloat16:
             ws = [l.weight for l in self.layers]
             bs = [l.bias for l in self.layers]
-            return _FusedMLPFn.apply(x, len(ws), *ws, *bs, *self.bias_f32)
+            return _FusedMLPFn.apply(x, len(ws), bool(top_grad_masked), *ws, *bs, *self.bias_f32)
         for l in self.layers:
             x = torch.relu(l(x))
         return x

@@ -39,9 +39,13 @@ class _Net(torch.nn.Module):
         deep, wide = self._emb[0](ids)
         return self.dense(deep, wide, dense_x)
 
+    def loss(self, ids, dense_x, labels):
+        deep, wide = self._emb[0](ids)
+        return self.dense.loss(deep, wide, dense_x, labels)
+
 
 def _loss_fn(model, ids, dense_x, labels):
-    return bce_with_logits(model(ids, dense_x), labels)
+    return model.loss(ids, dense_x, labels)
 
 
 class WideDeepJob:
@@ -75,7 +79,7 @@ class WideDeepJob:
                                          use_graph=use_graph, bucket_bytes=4 << 20, comm_blocks=8,
                                          # embedding kernels + 2 tcgen05 GEMMs (forward, dX) per hidden layer
                                          # embedding kernels + per hidden layer: forward GEMM, dX GEMM, bias colsum
-                                         extra_kernels_per_step=(3 if async_sgd else 4) + 3 * len(dense.layers))
+                                         extra_kernels_per_step=(3 if async_sgd else 4) + 3 * len(dense.layers) + 2)  # + fused head / loss, its dz
         self._attach_bias_masters()
         self._copy_stream = torch.cuda.Stream(self.device)
         self._stage = [(torch.empty_like(self.ids), torch.empty_like(self.dense_x), torch.empty_like(self.labels))
