@@ -82,7 +82,7 @@ def summarize_launches(path: str, title: str) -> None:
             a[3] += v
     tot = sum(a[1] for a in agg.values()) or 1.0
     name = os.path.splitext(os.path.basename(path))[0]
-    ours = ("bn_", "maxpool", "sgd_momentum", "softmax_xent", "preprocess", "emb_", "linear_tcgen05", "colsum", "conv1x1_tcgen05", "stem_wgrad",
+    ours = ("bn_", "maxpool", "sgd_momentum", "softmax_xent", "preprocess", "emb_", "linear_tcgen05", "colsum", "wd_head", "conv1x1_tcgen05", "stem_wgrad",
             "allreduce", "alltoall", "broadcast", "barrier_kernel")
     with open(os.path.join(OUT, name + ".launches.md"), "w") as f:
         f.write(f"# {title}\n\nEvery kernel of one training step, serialised under ncu (cold caches: compare shares, "
@@ -155,7 +155,8 @@ def main() -> int:
              "launches5": "ResNet-50 step launch list (batch 256, one B200) - before the TMA-streamed BN reductions",
              "launches6": "ResNet-50 step launch list (batch 256, one B200)",
              "launches_wd2": "Wide&Deep step launch list (batch 32768, one B200) - 256-thread embedding blocks",
-             "launches_wd3": "Wide&Deep step launch list (batch 32768, one B200)"}
+             "launches_wd3": "Wide&Deep step launch list (batch 32768, one B200) - before the fused head / loss kernel",
+             "launches_wd4": "Wide&Deep step launch list (batch 32768, one B200)"}
     for n, t in lists.items():
         p = os.path.join(SCRATCH, n + ".csv")
         if os.path.exists(p):
