@@ -195,7 +195,8 @@ def build_cluster(args, extra_env=None):
     if getattr(args, "gpus", None) is not None:
         gpus = [int(x) for x in args.gpus.split(",") if x != ""]
     return LocalCluster(scheduling=args.scheduling, init_image=args.initImage, port_range=args.port_range, etcd=etcd,
-                        namespace=args.namespace, gpus=gpus, work_root=args.work_root, extra_env=extra_env)
+                        namespace=args.namespace, gpus=gpus, work_root=args.work_root, extra_env=extra_env,
+                        state_dir=getattr(args, "state_dir", "") or None)
 
 
 def add_manager_flags(p: argparse.ArgumentParser) -> None:
@@ -212,6 +213,9 @@ def add_manager_flags(p: argparse.ArgumentParser) -> None:
     p.add_argument("--api-bind-address", default="127.0.0.1:8079", help="Address of the REST API the CLI talks to.")
     p.add_argument("--work-root", default="/tmp/pdjob", help="Where rank work directories and logs live.")
     p.add_argument("--gpus", default=None, help="Comma list of GPU indices in the pool (default: all visible).")
+    p.add_argument("--state-dir", default="",
+                   help="Keep PaddleJobs (spec and status) in this directory and reload them on start - what the API "
+                        "server's storage does for the reference.  Empty: jobs live only as long as the manager.")
     for z in ("--zap-devel", "--zap-encoder", "--zap-log-level", "--zap-stacktrace-level"):
         p.add_argument(z, nargs="?", const="true", default=None, help="zap logging flag (accepted for compatibility)")
 
@@ -248,6 +252,8 @@ def cmd_manager(args) -> int:
         binds[b] = ep
         endpoints.append(ep)
         log.info("%s endpoint on %s", name, ep.url)
+    if cluster.persister is not None:
+        log.info("state directory %s: %d job(s) restored", cluster.persister.state_dir, cluster.restored)
     log.info("starting manager")
     cluster.start()
     stop = threading.Event()

@@ -107,6 +107,27 @@ class ObjectStore:
             self._notify("ADDED", obj)
             return copy.deepcopy(obj)
 
+    def restore(self, obj: dict) -> dict:
+        """Re-inserts an object exactly as it was persisted (uid, generation, creation time, finalizers, a pending
+        deletionTimestamp and its status are kept; only the resourceVersion is new).  Used by controller.persist
+        when a manager starts on a state directory left by a previous one."""
+        obj = copy.deepcopy(obj)
+        meta = obj.setdefault("metadata", {})
+        meta.setdefault("namespace", "default")
+        if not meta.get("name"):
+            raise StoreError("metadata.name is required")
+        key = self.key_of(obj)
+        with self._lock:
+            if key in self._objs:
+                raise AlreadyExists(f"{key[0]} {key[1]}/{key[2]} already exists")
+            meta["uid"] = meta.get("uid") or str(uuid.uuid4())
+            meta["resourceVersion"] = self._next_rv()
+            meta["generation"] = int(meta.get("generation") or 1)
+            meta["creationTimestamp"] = meta.get("creationTimestamp") or _now()
+            self._objs[key] = obj
+            self._notify("ADDED", obj)
+            return copy.deepcopy(obj)
+
     def get(self, kind: str, namespace: str, name: str) -> dict:
         with self._lock:
             obj = self._objs.get((kind, namespace or "default", name))

@@ -23,8 +23,16 @@ class LocalCluster:
                  port_range: str = "35000,65000", etcd=None, namespace: str = "", gpus: Optional[list] = None,
                  work_root: str = "/tmp/pdjob", batch: bool = True, isolate_gpus: bool = True,
                  extra_env: Optional[dict] = None, supervisor: bool = True, gang_capacity: Optional[dict] = None,
-                 priorities: Optional[dict] = None):
+                 priorities: Optional[dict] = None, state_dir: Optional[str] = None):
         self.store = ObjectStore()
+        # durable PaddleJobs (spec + status), reloaded when a manager starts on the same directory
+        self.persister = None
+        if state_dir:
+            from ..controller.persist import StorePersister
+
+            self.persister = StorePersister(self.store, state_dir)
+            self.restored = self.persister.load()
+            self.persister.start()
         self.recorder = EventRecorder(self.store)
         self.supervisor = Supervisor(self.store, work_root=work_root, gpus=gpus, isolate_gpus=isolate_gpus,
                                      extra_env=extra_env) if supervisor else None
@@ -55,6 +63,8 @@ class LocalCluster:
         self.manager.close()
         if self.supervisor:
             self.supervisor.stop()
+        if self.persister:
+            self.persister.stop()  # the jobs stay on disk for the next manager
         self._started = False
 
     def __enter__(self):

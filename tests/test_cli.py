@@ -140,3 +140,50 @@ def test_run_one_shot(tmp_path):
     r = _pdj("run", "-f", "examples/env_dump.yaml", "--work-root", str(tmp_path), "--gpus", "0", "--timeout", "90",
              "--etcd", "embedded")
     assert "env-dump Completed" in r.stdout and "NAME" in r.stdout
+
+
+def _start_manager(tmp_path, tag, state_dir):
+    ready = tmp_path / f"ready-{tag}.json"
+    p = subprocess.Popen(PDJ + ["manager", "--api-bind-address", "127.0.0.1:0", "--metrics-bind-address", "0",
+                                "--health-probe-bind-address", "0", "--work-root", str(tmp_path / "work"),
+                                "--gpus", "0,1", "--state-dir", state_dir, "--ready-file", str(ready)],
+                         env=dict(ENV, PDJ_ENV_DUMP_SLEEP="0.1"), cwd=ROOT, stderr=subprocess.PIPE, text=True)
+    deadline = time.time() + 60
+    while not ready.exists() and time.time() < deadline:
+        assert p.poll() is None, p.stderr.read()
+        time.sleep(0.05)
+    return json.load(open(ready))["api"], p
+
+
+def _stop(p):
+    p.terminate()
+    try:
+        p.wait(20)
+    except subprocess.TimeoutExpired:
+        p.kill()
+
+
+def test_manager_restart_keeps_jobs_with_state_dir(tmp_path):
+    """`pdj manager --state-dir`: a finished job is still listed, with its status, by the next manager process."""
+    state = str(tmp_path / "state")
+    url, p = _start_manager(tmp_path, "a", state)
+    try:
+        _pdj("apply", "-f", "examples/env_dump.yaml", server=url)
+        deadline = time.time() + 60
+        while time.time() < deadline and "Completed" not in _pdj("get", "pdj", server=url).stdout:
+            time.sleep(0.2)
+        assert "Completed" in _pdj("get", "pdj", server=url).stdout
+    finally:
+        _stop(p)
+    assert os.path.exists(os.path.join(state, "paddlejobs", "default", "env-dump.json"))
+    url, p = _start_manager(tmp_path, "b", state)
+    try:
+        out = _pdj("get", "pdj", server=url).stdout
+        assert out.strip().splitlines()[1].split()[:3] == ["env-dump", "Completed", "PS"]
+        st = json.loads(_pdj("get", "pdj", "env-dump", "-o", "json", server=url).stdout)["status"]
+        assert st["phase"] == "Completed" and st["completionTime"]
+        time.sleep(1.0)  # the controller has reconciled it by now: still finished, no pods re-created
+        assert "Completed" in _pdj("get", "pdj", server=url).stdout
+        assert "env-dump-worker-0" not in _pdj("get", "pods", server=url).stdout
+    finally:
+        _stop(p)

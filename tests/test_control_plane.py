@@ -587,3 +587,67 @@ def test_trace_spans_cover_reconcile_passes(tmp_path):
     out = trace.flush(str(tmp_path / "trace.json"))
     import json as _json
     assert _json.load(open(out))["traceEvents"]
+
+
+def test_jobs_and_status_survive_a_manager_restart(tmp_path):
+    """--state-dir: a PaddleJob and its status are reloaded by the next manager (the reference gets this from
+    the API server's storage); finished jobs stay finished; deleting a job removes its file."""
+    import json as _json
+
+    from paddle_operator_b200.runtime.cluster import LocalCluster
+
+    state = str(tmp_path / "state")
+    c1 = LocalCluster(supervisor=False, init_image="", state_dir=state)
+    c1.apply(os.path.join(EXAMPLES, "wide_and_deep.yaml"))
+    c1.manager.run_until_idle()
+    job = c1.get("wide-ande-deep")
+    assert len(job.status.ps.refs) == 2 and len(job.status.worker.refs) == 2 and job.status.mode == "PS"
+    # mark it Completed the way the supervisor would: every pod Succeeded
+    for pod in c1.store.list("Pod", "default"):
+        pod["status"] = {"phase": "Succeeded"}
+        c1.store.update_status(pod)
+    c1.manager.run_until_idle()
+    assert c1.get("wide-ande-deep").status.phase == "Completed"
+    uid = c1.store.get("PaddleJob", "default", "wide-ande-deep")["metadata"]["uid"]
+    path = c1.persister.path_of("PaddleJob", "default", "wide-ande-deep")
+    on_disk = _json.load(open(path))
+    assert on_disk["status"]["phase"] == "Completed" and on_disk["status"]["mode"] == "PS"
+    assert set(on_disk["status"]) >= {"phase", "mode", "ps", "worker"}
+    c1.stop()
+
+    c2 = LocalCluster(supervisor=False, init_image="", state_dir=state)
+    assert c2.restored == 1
+    job2 = c2.get("wide-ande-deep")
+    assert job2.status.phase == "Completed" and job2.status.mode == "PS"
+    assert c2.store.get("PaddleJob", "default", "wide-ande-deep")["metadata"]["uid"] == uid
+    c2.manager.enqueue("default", "wide-ande-deep")
+    c2.manager.run_until_idle()
+    assert c2.get("wide-ande-deep").status.phase == "Completed"  # sticky: nothing is re-run
+    c2.delete("wide-ande-deep")
+    c2.manager.run_until_idle()
+    assert c2.store.try_get("PaddleJob", "default", "wide-ande-deep") is None
+    assert not os.path.exists(path)
+    c2.stop()
+
+    c3 = LocalCluster(supervisor=False, init_image="", state_dir=state)
+    assert c3.restored == 0 and c3.list_jobs() == []
+    c3.stop()
+
+
+def test_running_job_is_recreated_from_its_persisted_spec(tmp_path):
+    from paddle_operator_b200.runtime.cluster import LocalCluster
+
+    state = str(tmp_path / "state")
+    c1 = LocalCluster(supervisor=False, init_image="", state_dir=state)
+    c1.apply(os.path.join(EXAMPLES, "resnet.yaml"))
+    c1.manager.run_until_idle()
+    name = c1.list_jobs()[0].metadata.name
+    n_pods = len(c1.store.list("Pod", "default"))
+    assert n_pods >= 2
+    c1.stop()
+    c2 = LocalCluster(supervisor=False, init_image="", state_dir=state)
+    assert c2.restored == 1 and c2.store.list("Pod", "default") == []  # children are not persisted ...
+    c2.manager.enqueue("default", name)
+    c2.manager.run_until_idle()
+    assert len(c2.store.list("Pod", "default")) == n_pods             # ... the reconciler brings them back
+    c2.stop()
