@@ -343,12 +343,55 @@ def cmd_get(args) -> int:
     if args.resource not in RESOURCES:
         raise SystemExit(f"error: the server doesn't have a resource type {args.resource!r}")
     ns = args.namespace or "default"
-    if args.name:
-        items = [c.req("GET", _path(args.resource, ns, args.name))]
-    else:
-        items = c.req("GET", _path(args.resource, ns)).get("items", [])
+    def fetch():
+        if args.name:
+            return [c.req("GET", _path(args.resource, ns, args.name))]
+        return c.req("GET", _path(args.resource, ns)).get("items", [])
+
+    items = fetch()
     print_objects(args.resource, items, args.output)
+    if not getattr(args, "watch", False):
+        return 0
+    # -w: like `kubectl get -w`, print again whenever something observable changed (polling the API)
+    def sig(objs):
+        return [(o["metadata"]["name"], o["metadata"].get("resourceVersion"), json.dumps(o.get("status"), sort_keys=True))
+                for o in objs]
+
+    last = sig(items)
+    deadline = time.monotonic() + args.watch_timeout if args.watch_timeout > 0 else None
+    try:
+        while deadline is None or time.monotonic() < deadline:
+            time.sleep(args.watch_interval)
+            items = fetch()
+            cur = sig(items)
+            if cur != last:
+                print_objects(args.resource, items, args.output)
+                sys.stdout.flush()
+                last = cur
+    except KeyboardInterrupt:
+        pass
     return 0
+
+
+def cmd_wait(args) -> int:
+    """`pdj wait pdj NAME --for Completed[,Failed]`: block until the job reaches one of the phases
+    (exit 0), or the timeout passes (exit 1) - the `kubectl wait --for=jsonpath=...` users script around."""
+    c = Client(args.server)
+    ns = args.namespace or "default"
+    wanted = [p.strip() for p in args.for_phase.split(",") if p.strip()]
+    deadline = time.monotonic() + args.timeout
+    phase = ""
+    while time.monotonic() < deadline:
+        try:
+            phase = (c.req("GET", _path("pdj", ns, args.name)).get("status") or {}).get("phase", "")
+        except SystemExit:
+            phase = "<deleted>"
+        if phase in wanted:
+            print(f"paddlejob.batch.paddlepaddle.org/{args.name} condition met: {phase}")
+            return 0
+        time.sleep(0.2)
+    print(f"error: timed out waiting for {args.name} to be {' or '.join(wanted)} (it is {phase or 'unknown'})", file=sys.stderr)
+    return 1
 
 
 def cmd_describe(args) -> int:
@@ -389,8 +432,28 @@ def cmd_scale(args) -> int:
 
 def cmd_logs(args) -> int:
     c = Client(args.server)
-    sys.stdout.write(c.req("GET", _path("pods", args.namespace or "default", args.pod, "log"), raw=True))
-    return 0
+    ns = args.namespace or "default"
+    text = c.req("GET", _path("pods", ns, args.pod, "log"), raw=True)
+    sys.stdout.write(text)
+    if not getattr(args, "follow", False):
+        return 0
+    # -f: keep printing what is appended until the pod has finished (polling the API)
+    seen = len(text)
+    try:
+        while True:
+            time.sleep(0.5)
+            text = c.req("GET", _path("pods", ns, args.pod, "log"), raw=True)
+            if len(text) > seen:
+                sys.stdout.write(text[seen:])
+                sys.stdout.flush()
+                seen = len(text)
+            phase = (c.req("GET", _path("pods", ns, args.pod)).get("status") or {}).get("phase", "")
+            if phase in ("Succeeded", "Failed"):
+                text = c.req("GET", _path("pods", ns, args.pod, "log"), raw=True)
+                sys.stdout.write(text[seen:])
+                return 0
+    except KeyboardInterrupt:
+        return 0
 
 
 def cmd_etcd(args) -> int:
@@ -474,7 +537,16 @@ def main(argv=None) -> int:
     p.add_argument("resource")
     p.add_argument("name", nargs="?")
     p.add_argument("-o", "--output", default="", choices=["", "wide", "yaml", "json"])
+    p.add_argument("-w", "--watch", action="store_true", help="keep printing when something changes")
+    p.add_argument("--watch-interval", type=float, default=0.5, help=argparse.SUPPRESS)
+    p.add_argument("--watch-timeout", type=float, default=0.0, help="stop watching after this many seconds (0: never)")
     p.set_defaults(fn=cmd_get)
+    p = client_parser("wait", "wait until a PaddleJob reaches a phase")
+    p.add_argument("resource", choices=["pdj", "paddlejob", "paddlejobs"])
+    p.add_argument("name")
+    p.add_argument("--for", dest="for_phase", default="Completed,Failed", help="comma list of phases (default Completed,Failed)")
+    p.add_argument("--timeout", type=float, default=300.0)
+    p.set_defaults(fn=cmd_wait)
     p = client_parser("describe", "show a PaddleJob with its pods and events")
     p.add_argument("resource", choices=["pdj", "paddlejob", "paddlejobs"])
     p.add_argument("name")
@@ -492,6 +564,7 @@ def main(argv=None) -> int:
     p.set_defaults(fn=cmd_scale)
     p = client_parser("logs", "print a rank's log")
     p.add_argument("pod")
+    p.add_argument("-f", "--follow", action="store_true", help="keep printing until the rank has finished")
     p.set_defaults(fn=cmd_logs)
     p = client_parser("events", "list events")
     p.set_defaults(fn=lambda a: cmd_get(argparse.Namespace(server=a.server, namespace=a.namespace, resource="events",

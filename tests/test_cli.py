@@ -187,3 +187,21 @@ def test_manager_restart_keeps_jobs_with_state_dir(tmp_path):
         assert "env-dump-worker-0" not in _pdj("get", "pods", server=url).stdout
     finally:
         _stop(p)
+
+
+def test_wait_watch_and_follow(manager):
+    """`pdj wait`, `pdj get -w` and `pdj logs -f` against a live manager."""
+    url, _ = manager
+    _pdj("apply", "-f", "examples/env_dump.yaml", server=url)
+    w = subprocess.Popen(PDJ + ["get", "pdj", "-w", "--watch-interval", "0.1", "--watch-timeout", "20", "--server", url],
+                         stdout=subprocess.PIPE, text=True, env=ENV, cwd=ROOT)
+    r = _pdj("wait", "pdj", "env-dump", "--for", "Completed", "--timeout", "60", server=url)
+    assert "condition met: Completed" in r.stdout
+    bad = _pdj("wait", "pdj", "env-dump", "--for", "Failed", "--timeout", "0.5", server=url, check=False)
+    assert bad.returncode == 1 and "timed out" in bad.stderr
+    logs = _pdj("logs", "-f", "env-dump-worker-0", server=url)   # finished pod: prints everything and returns
+    assert "PADDLE_TRAINER_ID" in logs.stdout
+    time.sleep(0.5)
+    w.terminate()
+    out = w.communicate(timeout=10)[0]
+    assert out.count("NAME") >= 2 and "Completed" in out   # re-printed as the phase moved on
