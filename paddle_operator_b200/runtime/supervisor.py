@@ -22,7 +22,9 @@ every Pod in the object store becomes one local process:
                    OnFailure/Always -> restarted in place with back-off
                    (controllers/paddlejob_helper.go:366-374 chooses the policy);
   * volumes      - hostPath volumes map to their path, emptyDir to a scratch
-                   directory (medium Memory -> /dev/shm); each mountPath is
+                   directory (medium Memory -> /dev/shm), a persistentVolumeClaim
+                   to <work_root>/pvc/<namespace>/<claimName> shared by all pods
+                   that mount the claim; each mountPath is
                    exported as PDJ_MOUNT_<path> (deploy/elastic/resnet.yaml:
                    25-36: /checkpoint <- hostPath /tmp/checkpoint);
   * deletion     - a deleted Pod's process group is terminated.
@@ -351,6 +353,11 @@ class Supervisor:
                 mem = (v["emptyDir"] or {}).get("medium") == "Memory"
                 base = "/dev/shm/pdjob" if mem and os.path.isdir("/dev/shm") else os.path.join(r.workdir, "volumes")
                 path = os.path.join(base, r.namespace, r.name, v["name"]) if mem else os.path.join(base, v["name"])
+            elif "persistentVolumeClaim" in v:
+                # a claim is one directory shared by every pod (and job) of the namespace that mounts it - what a
+                # PV/PVC pair gives the reference's users for data sets and models (docs/user-guide.md:260-347)
+                claim = (v["persistentVolumeClaim"] or {}).get("claimName") or v.get("name", "claim")
+                path = os.path.join(self.work_root, "pvc", r.namespace, claim)
             else:
                 path = os.path.join(r.workdir, "volumes", v.get("name", "vol"))
             try:

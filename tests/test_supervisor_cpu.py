@@ -141,3 +141,26 @@ def test_every_example_manifest_loads_and_resolves():
                 continue
             c0 = res.template["spec"]["containers"][0]
             assert resolve_command(c0), (f, c0)
+
+
+def test_volumes_map_to_host_directories_and_claims_are_shared(cluster, tmp_path):
+    """hostPath -> its path, emptyDir -> a per-rank scratch directory, persistentVolumeClaim -> one directory
+    shared by every pod that mounts the claim (the reference's 'Data Storage' recipe, docs/user-guide.md:260-347)."""
+    host = tmp_path / "ckpt"
+    tmpl = {"spec": {"volumes": [{"name": "ck", "hostPath": {"path": str(host)}},
+                                 {"name": "scratch", "emptyDir": {}},
+                                 {"name": "data", "persistentVolumeClaim": {"claimName": "dataset"}}],
+                     "containers": [{"name": "m", "image": "x",
+                                     "command": ["python", "-m", "paddle_operator_b200.workloads.env_dump"],
+                                     "volumeMounts": [{"name": "ck", "mountPath": "/checkpoint"},
+                                                      {"name": "scratch", "mountPath": "/scratch"},
+                                                      {"name": "data", "mountPath": "/data"}]}]}}
+    cluster.apply({"apiVersion": "batch.paddlepaddle.org/v1", "kind": "PaddleJob", "metadata": {"name": "vols"},
+                   "spec": {"worker": {"replicas": 2, "template": tmpl}}})
+    assert cluster.wait("vols", timeout=60) == "Completed"
+    d = _dumps(cluster)
+    w0, w1 = d["vols-worker-0"], d["vols-worker-1"]
+    assert w0["PDJ_MOUNT__checkpoint"] == str(host) == w1["PDJ_MOUNT__checkpoint"] and host.is_dir()
+    assert w0["PDJ_MOUNT__scratch"] != w1["PDJ_MOUNT__scratch"]                       # emptyDir: private
+    assert w0["PDJ_MOUNT__data"] == w1["PDJ_MOUNT__data"]                             # claim: shared
+    assert w0["PDJ_MOUNT__data"].endswith(os.path.join("pvc", "default", "dataset")) and os.path.isdir(w0["PDJ_MOUNT__data"])
