@@ -145,6 +145,11 @@ def print_objects(res: str, items: list, output: str) -> None:
         rows = [[age(o.get("firstTimestamp")), o.get("type", ""), o.get("reason", ""),
                  f"{o['involvedObject']['kind'].lower()}/{o['involvedObject']['name']}", o.get("message", "")] for o in items]
         print(table(rows, ["LAST SEEN", "TYPE", "REASON", "OBJECT", "MESSAGE"]))
+    elif plural == "podgroups":
+        rows = [[o["metadata"]["name"], (o.get("status") or {}).get("phase", "Pending"),
+                 (o.get("spec") or {}).get("minMember", ""), (o.get("spec") or {}).get("queue", ""),
+                 age(o["metadata"].get("creationTimestamp"))] for o in items]
+        print(table(rows, ["NAME", "STATUS", "MINMEMBER", "QUEUE", "AGE"]))
     else:
         print(table([[o["metadata"]["name"], age(o["metadata"].get("creationTimestamp"))] for o in items], ["NAME", "AGE"]))
 
