@@ -651,3 +651,78 @@ def test_running_job_is_recreated_from_its_persisted_spec(tmp_path):
     c2.manager.run_until_idle()
     assert len(c2.store.list("Pod", "default")) == n_pods             # ... the reconciler brings them back
     c2.stop()
+
+
+@pytest.mark.parametrize("seed", range(12))
+def test_random_operation_sequences_keep_the_invariants(seed):
+    """Chaos test: random apply / scale / pod-exit / delete sequences against the fake kubelet.  After
+    every settle: refs == child pods, the per-kind counters add up to the pods present, pod names are
+    exactly <job>-<kind>-<idx> for idx < replicas (plus pods still being torn down), no child outlives its
+    job, and the derived phase is one the reference can produce."""
+    import random
+
+    rnd = random.Random(seed)
+    env = Env(batch=rnd.random() < 0.5, init_image=rnd.choice(["busybox", ""]))
+    jobs = {}
+    produced = {"", "Pending", "Starting", "Running", "Failed", "Completed"}
+
+    def check():
+        live = {o["metadata"]["name"] for o in env.store.list("PaddleJob")}
+        for kind in ("Pod", "Service", "ConfigMap"):
+            for o in env.store.list(kind):
+                owners = [r["name"] for r in o["metadata"].get("ownerReferences") or []]
+                assert owners and owners[0] in live, (kind, o["metadata"]["name"], owners)
+        for name in live:
+            job = env.job(name)
+            pods = [p for p in env.store.list("Pod") if p["metadata"]["ownerReferences"][0]["name"] == name]
+            assert job.status.phase in produced, job.status.phase
+            total_refs = 0
+            for kind in ("ps", "worker", "heter"):
+                st, sp = getattr(job.status, kind), getattr(job.spec, kind)
+                mine = [p for p in pods if p["metadata"]["labels"]["paddle-res-type"] == kind]
+                if sp is None:
+                    assert not mine
+                    continue
+                if st is None:
+                    continue
+                total_refs += len(st.refs)
+                assert st.pending + st.starting + st.running + st.failed + st.succeeded <= len(st.refs)
+                for p in mine:
+                    n = p["metadata"]["name"]
+                    assert n.startswith(f"{name}-{kind}-") and n.rsplit("-", 1)[1].isdigit()
+            assert total_refs == len(pods), (name, total_refs, [p["metadata"]["name"] for p in pods])
+
+    for step in range(40):
+        op = rnd.choice(["apply", "scale", "scale", "exit", "finish", "delete", "settle"])
+        names = list(jobs)
+        if op == "apply" and len(jobs) < 3:
+            name = f"j{seed}-{step}"
+            ps = rnd.choice([None, 1, 2])
+            env.apply(_job(name, ps=ps, worker=rnd.randint(1, 3), heter=rnd.choice([None, None, 1]),
+                           cleanPodPolicy=rnd.choice(["", "Never", "Always", "OnFailure", "OnCompletion"]),
+                           intranet=rnd.choice(["", "PodIP", "Service"])))
+            jobs[name] = True
+        elif op == "scale" and names:
+            name = rnd.choice(names)
+            obj = env.store.get("PaddleJob", "default", name)
+            kind = rnd.choice([k for k in ("ps", "worker", "heter") if obj["spec"].get(k)])
+            obj["spec"][kind]["replicas"] = rnd.randint(1, 4)
+            env.store.update(obj)
+        elif op == "exit" and names:
+            pods = env.store.list("Pod")
+            if pods:
+                p = rnd.choice(pods)
+                if (p.get("status") or {}).get("phase") == "Running":
+                    env.sup.finish("default", p["metadata"]["name"], succeeded=rnd.random() < 0.7)
+        elif op == "finish" and names:
+            env.sup.finish_all(succeeded=True)
+        elif op == "delete" and names:
+            name = rnd.choice(names)
+            env.store.delete("PaddleJob", "default", name)
+            del jobs[name]
+        env.settle()
+        check()
+    for name in list(jobs):
+        env.store.delete("PaddleJob", "default", name)
+    env.settle()
+    assert env.store.list("PaddleJob") == [] and env.store.list("Pod") == [] and env.store.list("ConfigMap") == []
