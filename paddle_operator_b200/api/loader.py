@@ -51,6 +51,17 @@ def _validate(doc: dict) -> None:
         tmpl = rs.get("template")
         if tmpl is not None and not isinstance(tmpl, dict):
             raise ValidationError(f"spec.{res}.template must be a mapping")
+        # requests / limits are the minimum / maximum replica count of the kind (api/v1/paddlejob_types.go:
+        # 155-161).  The reference never reads them; here an ELASTIC job may only be scaled inside that window -
+        # non-elastic jobs keep the reference's behaviour (stored, not enforced).
+        lo, hi = rs.get("requests"), rs.get("limits")
+        if lo is not None and hi is not None and lo > hi:
+            raise ValidationError(f"spec.{res}.requests ({lo}) is larger than spec.{res}.limits ({hi})")
+        if (spec or {}).get("elastic") is not None:
+            if lo is not None and rs["replicas"] < lo:
+                raise ValidationError(f"spec.{res}.replicas ({rs['replicas']}) is below spec.{res}.requests ({lo}) of this elastic job")
+            if hi is not None and rs["replicas"] > hi:
+                raise ValidationError(f"spec.{res}.replicas ({rs['replicas']}) is above spec.{res}.limits ({hi}) of this elastic job")
     for k in ("withGloo", "elastic"):
         v = (spec or {}).get(k)
         if v is not None and (not isinstance(v, int) or isinstance(v, bool)):

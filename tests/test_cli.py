@@ -205,3 +205,19 @@ def test_wait_watch_and_follow(manager):
     w.terminate()
     out = w.communicate(timeout=10)[0]
     assert out.count("NAME") >= 2 and "Completed" in out   # re-printed as the phase moved on
+
+
+def test_scale_outside_the_elastic_window_is_rejected(manager, tmp_path):
+    url, _ = manager
+    doc = {"apiVersion": "batch.paddlepaddle.org/v1", "kind": "PaddleJob", "metadata": {"name": "el"},
+           "spec": {"elastic": 1, "worker": {"replicas": 2, "requests": 1, "limits": 3, "template": {"spec": {"containers": [
+               {"name": "m", "image": "local/pdjob-b200:env-dump"}]}}}}}
+    f = tmp_path / "el.json"
+    f.write_text(json.dumps(doc))
+    _pdj("apply", "-f", str(f), server=url)
+    ok = _pdj("scale", "pdj", "el", "--replicas", "3", server=url)
+    assert "scaled" in ok.stdout
+    bad = _pdj("scale", "pdj", "el", "--replicas", "4", server=url, check=False)
+    assert bad.returncode != 0 and "422" in (bad.stderr + bad.stdout) and "limits" in (bad.stderr + bad.stdout)
+    spec = json.loads(_pdj("get", "pdj", "el", "-o", "json", server=url).stdout)["spec"]
+    assert spec["worker"]["replicas"] == 3

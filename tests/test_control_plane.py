@@ -726,3 +726,23 @@ def test_random_operation_sequences_keep_the_invariants(seed):
         env.store.delete("PaddleJob", "default", name)
     env.settle()
     assert env.store.list("PaddleJob") == [] and env.store.list("Pod") == [] and env.store.list("ConfigMap") == []
+
+
+def test_elastic_jobs_scale_only_inside_requests_limits():
+    """ResourceSpec.requests / limits (min / max replicas): stored and ignored for ordinary jobs like the reference,
+    enforced as the scaling window of elastic jobs."""
+    ok = _job("e", ps=None, worker=4, elastic=1)
+    ok["spec"]["worker"].update(requests=2, limits=8)
+    assert loader.paddlejob_from_doc(ok).spec.worker.limits == 8
+    for bad in (1, 9):
+        doc = _job("e", ps=None, worker=bad, elastic=1)
+        doc["spec"]["worker"].update(requests=2, limits=8)
+        with pytest.raises(loader.ValidationError):
+            loader.paddlejob_from_doc(doc)
+    plain = _job("p", ps=None, worker=9)
+    plain["spec"]["worker"].update(requests=2, limits=8)
+    assert loader.paddlejob_from_doc(plain).spec.worker.replicas == 9      # not elastic: as in the reference
+    inverted = _job("i", ps=None, worker=3)
+    inverted["spec"]["worker"].update(requests=5, limits=2)
+    with pytest.raises(loader.ValidationError):
+        loader.paddlejob_from_doc(inverted)
