@@ -144,6 +144,8 @@ def main() -> int:
             "prof_emb": "Sharded-embedding kernels and bias colsum (Wide&Deep step, batch 32768, 16.7 M rows)",
             "prof_conv": "tcgen05 convolution kernels (1x1 + BN statistics, dgrad + skip add, stem forward / wgrad) and "
                          "TMA-streamed BN reductions on ResNet-50 layer shapes, batch 256 (profiles/run_conv_kernels.py)",
+            "prof_wdhead": "Wide&Deep fused head: output layer + wide part + BCE loss (forward) and the masked gradient of the "
+                           "top layer (backward), batch 32768 (profiles/run_wd_step.py)",
             "prof_collectives": "Fused all-reduce / all-to-all kernel bodies, 8 ranks emulated on one GPU "
                                 "(cooperative launch; bandwidths here are HBM-local, NVLink numbers are in r1/sweep_n8.json)"}
     for n, t in reps.items():
