@@ -512,7 +512,7 @@ def cmd_client_demo(args) -> int:
     return 0
 
 
-def main(argv=None) -> int:
+def build_parser() -> argparse.ArgumentParser:
     ap = argparse.ArgumentParser(prog="pdj", description=__doc__.split("\n\n")[0])
     sub = ap.add_subparsers(dest="cmd", required=True)
 
@@ -582,7 +582,11 @@ def main(argv=None) -> int:
     p.add_argument("--listen", default="127.0.0.1:2379")
     p.set_defaults(fn=cmd_etcd)
 
-    args = ap.parse_args(argv)
+    return ap
+
+
+def main(argv=None) -> int:
+    args = build_parser().parse_args(argv)
     return args.fn(args)
 
 

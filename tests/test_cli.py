@@ -221,3 +221,29 @@ def test_scale_outside_the_elastic_window_is_rejected(manager, tmp_path):
     assert bad.returncode != 0 and "422" in (bad.stderr + bad.stdout) and "limits" in (bad.stderr + bad.stdout)
     spec = json.loads(_pdj("get", "pdj", "el", "-o", "json", server=url).stdout)["spec"]
     assert spec["worker"]["replicas"] == 3
+
+
+def test_installer_renders_units_from_values(tmp_path):
+    """deploy/install.py --dry-run: the Helm-values / kustomize role of the reference's deployment manifests."""
+    out = tmp_path / "units"
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "deploy", "install.py"), "--dry-run", "--out", str(out),
+                        "SCHEDULING=volcano", "GPUS=0,1", "NAMESPACE=team-a", "STATE_DIR=/srv/pdj"],
+                       capture_output=True, text=True, cwd=ROOT, timeout=60)
+    assert r.returncode == 0, r.stderr
+    unit = (out / "pdjob-manager.service").read_text()
+    for frag in ("--leader-elect", "--scheduling volcano", "--gpus 0,1", "--namespace team-a", "--state-dir /srv/pdj",
+                 "MemoryMax=300M", "paddle_operator_b200.cli manager"):
+        assert frag in unit, frag
+    assert "cli etcd --listen 127.0.0.1:2379" in (out / "pdjob-etcd.service").read_text()
+    # the manager accepts exactly the flags the unit passes
+    line = [l for l in unit.splitlines() if l.startswith("ExecStart=")][0]
+    flags = line.split(" manager ", 1)[1].split()
+    import shlex
+
+    from paddle_operator_b200 import cli
+
+    ns = cli.build_parser().parse_args(["manager", *shlex.split(" ".join(flags))])
+    assert ns.scheduling == "volcano" and ns.state_dir == "/srv/pdj" and ns.leader_elect
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "deploy", "install.py"), "--dry-run", "--uninstall", "--out",
+                        str(out)], capture_output=True, text=True, cwd=ROOT, timeout=60)
+    assert r.returncode == 0 and not list(out.iterdir())
