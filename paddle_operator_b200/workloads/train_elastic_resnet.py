@@ -97,6 +97,9 @@ def main() -> int:
         job = _DryJob(args.dry_step_time)
         comm = None
     else:
+        from . import require_gpu
+
+        require_gpu("train_elastic_resnet", "--cpu-dry-run")
         import torch
 
         from ..parallel.symm import Communicator

@@ -23,6 +23,9 @@ def main() -> int:
     ap.add_argument("--lr", type=float, default=0.1)
     ap.add_argument("--log-every", type=int, default=10)
     args = ap.parse_args()
+    from . import require_gpu
+
+    require_gpu("train_resnet")
     from ..parallel.symm import Communicator
     from .resnet import ResNetJob
 

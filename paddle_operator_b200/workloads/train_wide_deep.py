@@ -51,6 +51,9 @@ def main() -> int:
             time.sleep(0.1)
         return 1
     if not dry:
+        from . import require_gpu
+
+        require_gpu("train_wide_deep", "--cpu-dry-run")
         import torch
 
         from .wide_deep import WideDeepJob

@@ -164,3 +164,18 @@ def test_volumes_map_to_host_directories_and_claims_are_shared(cluster, tmp_path
     assert w0["PDJ_MOUNT__scratch"] != w1["PDJ_MOUNT__scratch"]                       # emptyDir: private
     assert w0["PDJ_MOUNT__data"] == w1["PDJ_MOUNT__data"]                             # claim: shared
     assert w0["PDJ_MOUNT__data"].endswith(os.path.join("pvc", "default", "dataset")) and os.path.isdir(w0["PDJ_MOUNT__data"])
+
+
+def test_gpu_workloads_fail_with_one_clear_line_without_a_gpu():
+    import subprocess
+    import sys
+
+    import torch
+
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    for mod, extra in (("train_resnet", ["--tiny"]), ("train_wide_deep", [])):
+        r = subprocess.run([sys.executable, "-m", f"paddle_operator_b200.workloads.{mod}", *extra], capture_output=True,
+                           text=True, cwd=ROOT, timeout=120, env=dict(os.environ, TRAINING_ROLE="TRAINER", PYTHONPATH=ROOT))
+        assert r.returncode == 3, (mod, r.returncode, r.stderr[-300:])
+        assert "no usable NVIDIA GPU" in r.stderr and "Traceback" not in r.stderr
