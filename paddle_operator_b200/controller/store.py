@@ -22,7 +22,7 @@ import copy
 import datetime as _dt
 import threading
 import uuid
-from typing import Callable, Iterable, Optional
+from typing import Callable, Optional
 
 
 class StoreError(Exception):

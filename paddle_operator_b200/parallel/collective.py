@@ -22,7 +22,7 @@ import torch
 
 from ..ops import optim as pdj_optim
 from ..utils import trace
-from .symm import AR_NVLS, AR_ONESHOT, AR_TWOSHOT, Communicator
+from .symm import AR_ONESHOT, AR_TWOSHOT, Communicator
 
 
 def _round_up(n: int, m: int) -> int:

@@ -13,7 +13,6 @@ over unix sockets under a per-job directory).
 """
 from __future__ import annotations
 
-import array
 import ctypes
 import os
 import socket

@@ -21,7 +21,7 @@ import threading
 from http.server import BaseHTTPRequestHandler, ThreadingHTTPServer
 from typing import Optional
 
-from .etcd_store import EtcdStore, Event, KeyValue
+from .etcd_store import EtcdStore, KeyValue
 
 CLUSTER_ID = "14841639068965178418"
 MEMBER_ID = "10276657743932975437"

@@ -19,7 +19,6 @@ import sys
 import tempfile
 import time
 
-import yaml
 
 from ..runtime.cluster import LocalCluster
 from ..runtime.etcd_client import EtcdClient

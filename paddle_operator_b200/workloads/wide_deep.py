@@ -21,9 +21,9 @@ from typing import Optional
 
 import torch
 
-from ..models.wide_deep import DENSE_FEATURES, SPARSE_SLOTS, WideDeepDense, bce_with_logits
+from ..models.wide_deep import DENSE_FEATURES, SPARSE_SLOTS, WideDeepDense
 from ..parallel.collective import CollectiveTrainer
-from ..parallel.ps import ADAGRAD, SGD, ShardedEmbedding
+from ..parallel.ps import ADAGRAD, ShardedEmbedding
 from ..parallel.symm import Communicator
 
 
