@@ -138,9 +138,9 @@ def print_objects(res: str, items: list, output: str) -> None:
                 status = "Init:0/1"
             row = [o["metadata"]["name"], f"{ready}/{total}", status, restarts, age(o["metadata"].get("creationTimestamp"))]
             if output == "wide":
-                row += [st.get("podIP", "<none>")]
+                row += [st.get("podIP", "<none>"), ",".join(str(g) for g in st.get("gpus") or []) or "<none>"]
             rows.append(row)
-        print(table(rows, ["NAME", "READY", "STATUS", "RESTARTS", "AGE"] + (["IP"] if output == "wide" else [])))
+        print(table(rows, ["NAME", "READY", "STATUS", "RESTARTS", "AGE"] + (["IP", "GPUS"] if output == "wide" else [])))
     elif plural == "events":
         rows = [[age(o.get("firstTimestamp")), o.get("type", ""), o.get("reason", ""),
                  f"{o['involvedObject']['kind'].lower()}/{o['involvedObject']['name']}", o.get("message", "")] for o in items]

@@ -268,9 +268,11 @@ class Supervisor:
                      for c in pod["spec"].get("initContainers") or []]
             r.gate_open = not any(c["name"] == H.COORD_CONTAINER_NAME for c in inits)
 
-            def fn(st, ip=r.ip, inits=inits):
+            def fn(st, ip=r.ip, inits=inits, gpus=list(r.gpus)):
                 st.update({"phase": "Pending", "podIP": ip, "hostIP": "127.0.0.1",
                            "conditions": [{"type": "PodScheduled", "status": "True"}]})
+                if gpus:
+                    st["gpus"] = gpus  # which GPUs of the box the rank was given (`pdj get pods -o wide`)
                 if inits:
                     st["initContainerStatuses"] = inits
 

@@ -179,3 +179,22 @@ def test_gpu_workloads_fail_with_one_clear_line_without_a_gpu():
                            text=True, cwd=ROOT, timeout=120, env=dict(os.environ, TRAINING_ROLE="TRAINER", PYTHONPATH=ROOT))
         assert r.returncode == 3, (mod, r.returncode, r.stderr[-300:])
         assert "no usable NVIDIA GPU" in r.stderr and "Traceback" not in r.stderr
+
+
+def test_assigned_gpus_are_visible_in_the_pod_status(cluster):
+    tmpl = {"spec": {"containers": [{"name": "m", "image": "local/pdjob-b200:env-dump",
+                                     "resources": {"limits": {"nvidia.com/gpu": 1}}}]}}
+    cluster.apply({"apiVersion": "batch.paddlepaddle.org/v1", "kind": "PaddleJob", "metadata": {"name": "g"},
+                   "spec": {"cleanPodPolicy": "Never", "worker": {"replicas": 2, "template": tmpl}}})
+    assert cluster.wait("g", timeout=60) == "Completed"
+    got = sorted(tuple(p["status"].get("gpus") or []) for p in cluster.pods("g"))
+    assert len(got) == 2 and all(len(g) == 1 for g in got) and got[0] != got[1]
+
+    from paddle_operator_b200.cli import print_objects
+    import io
+    import contextlib
+
+    buf = io.StringIO()
+    with contextlib.redirect_stdout(buf):
+        print_objects("pods", cluster.pods("g"), "wide")
+    assert "GPUS" in buf.getvalue().splitlines()[0]
