@@ -7,15 +7,28 @@ box.  BASELINE.json config 2; see BASELINE.md section 3.
   python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 \
       --master-port 29500 bench.py --gpus 8 --steps 20 --warmup 5
 
---impl product    (default) this repository's engine: fused BN/add/ReLU kernels,
-                  fused NVSwitch all-reduce overlapped with backward, fused SGD,
-                  whole step in a CUDA graph.
---impl ddp        the yardstick BASELINE.md names: the same network out of stock
-                  torch modules under torch DDP/NCCL (+cuDNN/cuBLAS), eager.
+--impl product    (default) this repository's engine: tcgen05 convolutions, fused
+                  BN/add/ReLU kernels, fused NVSwitch all-reduce overlapped with
+                  backward, fused SGD, whole step in a CUDA graph.
+                  With the default --arms all the same invocation then also runs,
+                  with the same steps / warm-up, and attaches to the one JSON line:
+                    baselines.ddp_eager   torch DDP/NCCL, stock modules, eager (the
+                                          yardstick BASELINE.md names; vs_baseline =
+                                          value / its value)
+                    baselines.ddp_graph   the same stock step captured in a CUDA graph
+                    workloads.wide_deep   the PS-mode Wide&Deep product, with its own
+                                          torch + NCCL all-to-all baselines (eager
+                                          without host syncs, and graph-captured)
+                    allreduce_check       (N >= 2) every all-reduce algorithm incl. NVLS
+                                          against dist.all_reduce on 64 MiB of random
+                                          bf16; a mismatch makes the run exit 3.
+                  --arms primary runs the product arm only.
+--impl ddp | ddp_graph   one baseline arm alone.
 --impl reference  the unmodified reference.  It is a Go Kubernetes operator with
                   no Python package and no GPU path, so this prints
                   {"impl": "reference", "unavailable": ...} and exits 0.
---workload wide_deep switches to the PS-mode Wide&Deep benchmark (samples/s).
+--workload wide_deep  the PS-mode Wide&Deep benchmark (samples/s) as the primary
+                  line (--impl product | nccl | nccl_graph).
 
 Rank 0 prints exactly one JSON line on stdout.
 """
@@ -28,6 +41,7 @@ import statistics
 import subprocess
 import sys
 import tempfile
+import threading
 import time
 
 REPO = os.path.dirname(os.path.abspath(__file__))
@@ -39,7 +53,12 @@ def parse_args():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
-    ap.add_argument("--impl", default="product", choices=["product", "ddp", "reference"])
+    ap.add_argument("--impl", default="product", choices=["product", "ddp", "ddp_graph", "nccl", "nccl_graph", "reference"])
+    ap.add_argument("--arms", default="all", choices=["all", "primary"],
+                    help="all: baselines, Wide&Deep and the all-reduce check ride along with the product arm")
+    ap.add_argument("--wd-batch", type=int, default=0, help="per-GPU Wide&Deep batch (default 32768)")
+    ap.add_argument("--budget-s", type=float, default=900.0,
+                    help="wall-clock guard: print what has been measured so far and exit if the run takes longer")
     ap.add_argument("--workload", default="resnet50", choices=["resnet50", "wide_deep"])
     ap.add_argument("--batch", type=int, default=0, help="per-GPU batch (default 256 images / 32768 samples)")
     ap.add_argument("--no-graph", action="store_true")
@@ -146,13 +165,99 @@ def main() -> int:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
 
-    if args.workload == "wide_deep":
-        from paddle_operator_b200.workloads import bench_wide_deep
+    from paddle_operator_b200.workloads import bench_resnet, bench_wide_deep
+    from paddle_operator_b200.workloads.bench_common import ratio
 
-        return bench_wide_deep.run(args, rank, world, dev, ClockSampler)
-    from paddle_operator_b200.workloads import bench_resnet
+    wd_primary = args.workload == "wide_deep"
+    if wd_primary and args.batch and not args.wd_batch:
+        args.wd_batch = args.batch
+    mod = bench_wide_deep if wd_primary else bench_resnet
+    impl = args.impl
+    if wd_primary and impl in ("ddp", "ddp_graph"):
+        impl = {"ddp": "nccl", "ddp_graph": "nccl_graph"}[impl]
+    if not wd_primary and impl in ("nccl", "nccl_graph"):
+        impl = {"nccl": "ddp", "nccl_graph": "ddp_graph"}[impl]
 
-    return bench_resnet.run(args, rank, world, dev, ClockSampler)
+    out: dict = {}
+    printed = threading.Event()
+
+    def emit(note=None) -> None:
+        if printed.is_set():
+            return
+        printed.set()
+        if note:
+            out["truncated"] = note
+        if rank == 0:
+            print(json.dumps(out), flush=True)
+
+    def guard() -> None:  # a hung baseline arm must not cost the primary measurement
+        emit(f"wall-clock budget of {args.budget_s:.0f} s exceeded; arms not listed were not measured")
+        os._exit(0)
+
+    timer = threading.Timer(args.budget_s, guard)
+    timer.daemon = True
+    timer.start()
+
+    rec = mod.measure(args, impl, rank, world, dev, ClockSampler)
+    out.update({
+        "metric": rec["metric"], "value": rec["value"], "unit": rec["unit"], "n_gpus": world, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": rec["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": rec.get("dtype", "bf16"),
+        "data": rec.get("data", "synthetic (random uint8 224x224 images, random labels; random-init weights)"),
+        "impl": rec["impl"], "config": rec["config"], "clocks": rec["clocks"],
+        "e2e": dict(rec["e2e"], unit=rec["unit"]), "gpu_launches": rec["gpu_launches"], "loss": rec["loss"],
+    })
+    rc = 0
+    if args.arms == "all" and impl == "product" and not wd_primary:
+        def arm(module, name):
+            """One ride-along arm; a failure is recorded, not fatal (it fails on every rank alike)."""
+            try:
+                r = module.measure(args, name, rank, world, dev, ClockSampler)
+                return {k: r[k] for k in ("value", "ms_per_step", "e2e", "clocks", "impl_name", "loss", "gpu_launches")
+                        if k in r} | ({"invalid": r["invalid"]} if "invalid" in r else {})
+            except Exception as e:  # noqa: BLE001
+                return {"unavailable": f"{type(e).__name__}: {e}"[:300]}
+
+        def versus(prod, base):
+            if "value" in base and "invalid" not in base:
+                base["ratio"] = ratio(prod["value"], base["value"])
+                base["e2e_ratio"] = ratio(prod["e2e"]["value"], base["e2e"]["value"])
+
+        if world > 1:
+            from paddle_operator_b200.workloads.bench_common import job_key
+            from paddle_operator_b200.workloads.comm_check import allreduce_check
+
+            chk = allreduce_check(dev, rank, world, key=job_key("archeck"))
+            out["allreduce_check"] = chk
+            if not chk["ok"]:
+                rc = 3
+        # the yardstick first, then the second workload, then the graph-captured baselines
+        base = {"ddp_eager": arm(bench_resnet, "ddp")}
+        versus(rec, base["ddp_eager"])
+        out["baselines"] = base
+        if "ratio" in base["ddp_eager"]:
+            out["vs_baseline"] = base["ddp_eager"]["ratio"]
+            out["vs_baseline_is"] = "value / baselines.ddp_eager.value, both measured in this invocation"
+        wd = arm(bench_wide_deep, "product")
+        wd.update({"metric": "wide_deep_train_samples_per_sec", "unit": "samples/s", "per_gpu_batch": args.wd_batch or 32768,
+                   "vs_baseline": None})
+        out["workloads"] = {"wide_deep": wd}
+        if "value" in wd:
+            wd["baselines"] = {"nccl_eager": arm(bench_wide_deep, "nccl")}
+            versus(wd, wd["baselines"]["nccl_eager"])
+            wd["vs_baseline"] = wd["baselines"]["nccl_eager"].get("ratio")
+        base["ddp_graph"] = arm(bench_resnet, "ddp_graph")
+        versus(rec, base["ddp_graph"])
+        if "value" in wd:
+            wd["baselines"]["nccl_graph"] = arm(bench_wide_deep, "nccl_graph")
+            versus(wd, wd["baselines"]["nccl_graph"])
+    timer.cancel()
+    emit()
+    if world > 1:
+        torch.cuda.synchronize(dev)
+        dist.barrier(device_ids=[dev.index])
+        dist.destroy_process_group()
+    return rc
 
 
 if __name__ == "__main__":

@@ -727,6 +727,19 @@ int knob_cvt() {
   return (v == 1 || v == 2 || v == 4 || v == 8 || v == 16 || v == 32) ? v : 4;
 }
 
+// Channel-vectors per block actually used for width C.  The "last block" tickets are one counter per
+// channel tile (blockIdx.y) and only 64 of them exist (the first 256 bytes of the workspace, and of the
+// built-in array of pdj_bn_fwd_noalloc), so narrow tiles chosen with PDJ_BN_CVT=1|2 are widened for
+// C > 512 / 1024 until the channel-tile count is at most 64.  Used for the grid AND for the kernels'
+// cvt_max argument, which must agree.
+constexpr int kMaxChannelTiles = 64;
+int eff_cvt(int C) {
+  const int c8 = C / 8;
+  int cvt = knob_cvt();
+  while (c8 / cvt > kMaxChannelTiles) cvt *= 2;
+  return c8 < cvt ? c8 : cvt;
+}
+
 // TMA-streamed reductions: on by default for C % 64 == 0 (PDJ_BN_TMA=0 restores the plain-load kernels).
 int knob_tma() { static int v = env_int("PDJ_BN_TMA", 1); return v; }
 constexpr int kStatsStages = 4, kBwdStages = 3;
@@ -767,7 +780,7 @@ void launch_stats(dim3 g, cudaStream_t st, A... a) {
 
 int grid_rows(int M, int C, int sm_count) {
   const int c8 = C / 8;
-  const int cvt = c8 < knob_cvt() ? c8 : knob_cvt();
+  const int cvt = eff_cvt(C);
   const int gy = c8 / cvt;
   const int rows_par = kThreads / cvt;
   int gx = (knob_blocks_per_sm() * sm_count + gy - 1) / gy;
@@ -857,10 +870,10 @@ int pdj_bn_fwd_gate(const void* x, const void* res, void* y, void* gate, int M, 
     bn_stats_tma_kernel<kStatsStages><<<g, kThreads, kStatsSmem, st>>>(mx, M, C, gamma, beta, eps, momentum, running_mean,
                                                                       running_var, mean_rstd, scale_shift, partial, counter);
   } else {
-    const int c8 = C / 8, cvt = c8 < knob_cvt() ? c8 : knob_cvt();
+    const int c8 = C / 8, cvt = eff_cvt(C);
     dim3 g(grid_rows(M, C, sm_count()), c8 / cvt);
     launch_stats(g, st, (const __nv_bfloat16*)x, M, C, gamma, beta, eps, momentum, running_mean, running_var, mean_rstd,
-                 scale_shift, partial, counter, knob_cvt());
+                 scale_shift, partial, counter, cvt);
   }
   PDJ_CUDA_CHECK(cudaGetLastError());
   return launch_apply(x, res, y, gate_out, M, C, scale_shift, relu, st);
@@ -901,13 +914,13 @@ int pdj_bn_bwd_gate(const void* dy, const void* y, const void* gate, const void*
   const uint8_t* gate_in = reinterpret_cast<const uint8_t*>(gate);
   float* partial = reinterpret_cast<float*>(reinterpret_cast<char*>(workspace) + 256);
   unsigned int* counter = reinterpret_cast<unsigned int*>(workspace);
-  const int c8 = C / 8, cvt = c8 < knob_cvt() ? c8 : knob_cvt();
+  const int c8 = C / 8, cvt = eff_cvt(C);
   dim3 g(grid_rows(M, C, sm_count()), c8 / cvt);
   const __nv_bfloat16* dyb = (const __nv_bfloat16*)dy;
   const __nv_bfloat16* yb = (const __nv_bfloat16*)y;
   const __nv_bfloat16* xb = (const __nv_bfloat16*)x;
   __nv_bfloat16* dgb = (__nv_bfloat16*)dgb_bf16;
-  const int cm = knob_cvt();
+  const int cm = cvt;
   if (tma_path(M, C) && (!relu || gate_in != nullptr)) {
     if (int r = ensure_tma_attrs()) return r;
     CUtensorMap md, mx;
@@ -1055,13 +1068,13 @@ extern "C" int pdj_bn_fwd_noalloc(const void* x, const void* res, void* y, int M
   // Tickets must start at zero whatever the previous user of the array did.
   PDJ_CUDA_CHECK(cudaMemsetAsync(counter, 0, kNoAllocCounterBytes, st));
 
-  const int cvt = c8 < knob_cvt() ? c8 : knob_cvt();
+  const int cvt = eff_cvt(C);  // at most 64 channel tiles: the ticket region is 64 counters
   int gx = grid_rows(M, C, sms);
   const int cap = (int)(kNoAllocPartialBytes / ((size_t)2 * C * sizeof(float)));  // row blocks that fit
   if (gx > cap) gx = cap;
   dim3 g(gx, c8 / cvt);
   launch_stats(g, st, (const __nv_bfloat16*)x, M, C, gamma, beta, eps, momentum, running_mean, running_var, mean_rstd,
-               scale_shift, partial, counter, knob_cvt());
+               scale_shift, partial, counter, cvt);
   PDJ_CUDA_CHECK(cudaGetLastError());
   const size_t n_vec = (size_t)M * c8;
   size_t fg = (n_vec + (size_t)kThreads * 4 - 1) / ((size_t)kThreads * 4);

@@ -1,31 +1,23 @@
-"""ResNet-50 img/s measurement used by bench.py (product and ddp arms).
+"""ResNet-50 img/s measurement used by bench.py.
 
-Timing rules followed: >= 3 warm-up steps, CUDA events on the launching stream
-bracketed by barrier + synchronize, max over ranks, clocks sampled during the
-timed region, working set (activations, several GB per step) far larger than
-the 126 MB L2 so no explicit flush is needed.
+Arms (`measure(..., impl=...)`):
+  product    this repository's engine (tcgen05 convolutions, fused BN kernels, fused NVSwitch
+             all-reduce overlapped with backward, fused SGD, the whole step in a CUDA graph);
+  ddp        the yardstick BASELINE.md names: the same network out of stock torch modules under
+             torch DDP/NCCL (+cuDNN/cuBLAS), fused torch SGD, eager;
+  ddp_graph  the same stock network with the whole step (forward, backward, NCCL all-reduce of the
+             gradients, SGD) captured in a CUDA graph - separates "launch overhead removed by graph
+             capture" from "faster kernels" in the product / baseline ratio.
+
+Timing rules: see bench_common.py.  The working set (activations, several GB per step) is far larger
+than the 126 MB L2, so no explicit flush is needed.
 """
 from __future__ import annotations
-
-import json
-import time
 
 import torch
 import torch.distributed as dist
 
-
-def _max_over_ranks(ms: float, world: int, dev) -> float:
-    if world == 1:
-        return ms
-    t = torch.tensor([ms], dtype=torch.float64, device=dev)
-    dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    return float(t.item())
-
-
-def _sync_all(world: int, dev) -> None:
-    if world > 1:
-        dist.barrier(device_ids=[dev.index])
-    torch.cuda.synchronize(dev)
+from .bench_common import job_key, measure_job, release
 
 
 def _host_batches(batch: int, image: int, n: int = 3):
@@ -38,24 +30,11 @@ def _host_batches(batch: int, image: int, n: int = 3):
     return out
 
 
-def _time_region(fn, steps: int, world: int, dev) -> float:
-    _sync_all(world, dev)
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(steps):
-        fn()
-    e1.record()
-    torch.cuda.synchronize(dev)
-    ms = e0.elapsed_time(e1)
-    _sync_all(world, dev)
-    return _max_over_ranks(ms, world, dev)
-
-
 def _build_product(args, world, dev):
     from ..parallel.symm import AR_NVLS, AR_TWOSHOT, Communicator
     from .resnet import ResNetJob
 
-    comm = Communicator.from_env(arena_bytes=256 << 20) if world > 1 else None
+    comm = Communicator.from_env(arena_bytes=256 << 20, key=job_key("resnet")) if world > 1 else None
     algo = {"auto": None, "twoshot": AR_TWOSHOT, "nvls": AR_NVLS}[args.algo]
     job = ResNetJob(batch=args.batch or 256, comm=comm, device=dev, use_graph=not args.no_graph,
                     bucket_bytes=int(args.bucket_mb * (1 << 20)), comm_blocks=args.comm_blocks, algo=algo)
@@ -64,16 +43,21 @@ def _build_product(args, world, dev):
 
 
 class _DdpJob:
-    """The yardstick: stock torch modules, DDP/NCCL, fused torch SGD, eager."""
+    """The yardstick: stock torch modules, NCCL gradient all-reduce, fused torch SGD.
 
-    def __init__(self, batch, world, dev):
+    graph=False: torch DistributedDataParallel, eager (the arm BASELINE.md names).
+    graph=True:  the whole step in one CUDA graph; gradients are all-reduced with one
+                 dist.all_reduce per dtype on a flattened buffer inside the captured step."""
+
+    def __init__(self, batch, world, dev, graph: bool = False):
         from ..models.resnet import resnet50, to_training_dtype
 
         torch.manual_seed(0)
-        self.dev, self.batch = dev, batch
+        self.dev, self.batch, self.world, self.graph_mode = dev, batch, world, graph
         model = to_training_dtype(resnet50(fused=False).to(dev), torch.bfloat16, bn_fp32=True).train()
+        self.net = model
         self.model = model
-        if world > 1:
+        if world > 1 and not graph:
             self.model = torch.nn.parallel.DistributedDataParallel(model, device_ids=[dev.index],
                                                                    gradient_as_bucket_view=True)
         self.opt = torch.optim.SGD(model.parameters(), lr=0.1, momentum=0.9, weight_decay=1e-4, fused=True)
@@ -84,20 +68,66 @@ class _DdpJob:
         self.std = torch.tensor([0.229, 0.224, 0.225], device=dev).view(1, 1, 1, 3)
         self.loss = torch.zeros((), device=dev)
         self._loss_host = torch.zeros(1).pin_memory()
+        self._graph = None
+        if graph:
+            self._capture()
 
-    def step_device(self):
-        self.opt.zero_grad(set_to_none=True)
+    def _allreduce_grads(self) -> None:
+        by_dtype: dict = {}
+        for p in self.net.parameters():
+            by_dtype.setdefault(p.grad.dtype, []).append(p.grad)
+        for grads in by_dtype.values():
+            flat = torch.cat([g.reshape(-1) for g in grads])
+            dist.all_reduce(flat)
+            flat.mul_(1.0 / self.world)
+            views, off = [], 0
+            for g in grads:
+                views.append(flat[off:off + g.numel()].view(g.shape))
+                off += g.numel()
+            torch._foreach_copy_(grads, views)
+
+    def _body(self) -> None:
         loss = torch.nn.functional.cross_entropy(self.model(self.x).float(), self.y)
         loss.backward()
+        if self.graph_mode and self.world > 1:
+            self._allreduce_grads()
         self.opt.step()
-        self.loss = loss.detach()
+        self.loss.copy_(loss.detach())
+
+    def _capture(self) -> None:
+        s = torch.cuda.Stream(self.dev)
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
+            for _ in range(3):
+                self.opt.zero_grad(set_to_none=True)
+                self._body()
+        torch.cuda.current_stream().wait_stream(s)
+        torch.cuda.synchronize(self.dev)
+        if self.world > 1:
+            dist.barrier(device_ids=[self.dev.index])
+            torch.cuda.synchronize(self.dev)
+        # grads are None at capture: backward allocates them from the graph's pool and every replay
+        # overwrites them (the documented whole-network capture recipe)
+        self.opt.zero_grad(set_to_none=True)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, capture_error_mode="thread_local"):
+            self._body()
+        self._graph = g
+        torch.cuda.synchronize(self.dev)
+
+    def step_device(self):
+        if self._graph is not None:
+            self._graph.replay()
+        else:
+            self.opt.zero_grad(set_to_none=True)
+            self._body()
         return self.loss
 
     def train_step(self, images_u8, labels):
         xs = images_u8.to(self.dev, non_blocking=True)
-        self.y = labels.to(self.dev, non_blocking=True)
+        self.y.copy_(labels.to(self.dev, non_blocking=True))
         x = ((xs.float() / 255.0 - self.mean) / self.std).to(torch.bfloat16)
-        self.x = x.permute(0, 3, 1, 2)
+        self.x.copy_(x.permute(0, 3, 1, 2))
         loss = self.step_device()
         self._loss_host.copy_(loss.reshape(1), non_blocking=True)
         return self._loss_host
@@ -107,61 +137,31 @@ class _DdpJob:
     launches_per_step = 0
 
 
-def run(args, rank: int, world: int, dev, ClockSampler) -> int:
+IMPL_NAMES = {
+    "product": "this repository (tcgen05 convolutions, fused BN, fused NVSwitch all-reduce, CUDA graph)",
+    "ddp": "torch DDP/NCCL eager (stock modules, cuDNN NHWC, fused SGD)",
+    "ddp_graph": "stock torch modules + NCCL gradient all-reduce + fused SGD, whole step in a CUDA graph",
+}
+
+
+def measure(args, impl: str, rank: int, world: int, dev, ClockSampler) -> dict:
+    """Runs one arm and returns its record (no printing, the process group stays up)."""
     batch = args.batch or 256
     comm = None
-    if args.impl == "product":
+    if impl == "product":
         job, comm = _build_product(args, world, dev)
     else:
-        job = _DdpJob(batch, world, dev)
+        job = _DdpJob(batch, world, dev, graph=(impl == "ddp_graph"))
     steps, warmup = args.steps, max(args.warmup, 3)
-
-    # ---- device-timed: inputs resident on the device -------------------------
-    for _ in range(warmup):
-        job.step_device()
-    sampler = ClockSampler() if rank == 0 else None
-    if sampler:
-        sampler.start()
-        time.sleep(0.05)
-    ms = _time_region(job.step_device, steps, world, dev)
-    clocks = sampler.stop() if sampler else None
-    loss_dev = float(job.loss.item()) if hasattr(job, "loss") else float(job.trainer.loss.item())
-
-    # ---- end to end: pinned host batch in, loss out, every step --------------
-    hb = _host_batches(batch, 224)
-    k = [0]
-    last = [None]
-
-    def e2e_step():
-        x, y = hb[k[0] % len(hb)]
-        k[0] += 1
-        last[0] = job.train_step(x, y)
-
-    for _ in range(3):
-        e2e_step()
-    ms_e2e = _time_region(e2e_step, steps, world, dev)
-    loss_e2e = float(last[0].item())
-
-    imgs = batch * world * steps
-    value = imgs / (ms / 1e3)
-    e2e_value = imgs / (ms_e2e / 1e3)
-    launches = job.launches_per_step * steps
-    out = {
+    rec = measure_job(job, _host_batches(batch, 224), steps, warmup, world, rank, dev, ClockSampler, batch * world)
+    rec.update({
         "metric": "resnet50_train_images_per_sec",
-        "value": round(value, 1),
         "unit": "img/s",
-        "n_gpus": world,
-        "steps": steps,
-        "warmup": warmup,
-        "ms_per_step": round(ms / steps, 3),
-        "higher_is_better": True,
-        "scaling": "weak",
-        "vs_baseline": None,
-        "dtype": "bf16",
-        "data": "synthetic (random uint8 224x224 images, random labels; random-init weights)",
-        "impl": args.impl,
+        "impl": impl,
+        "impl_name": IMPL_NAMES[impl],
         "config": {
-            "model": "ResNet-50 v1.5, NHWC, SGD momentum 0.9 wd 1e-4, fp32 master weights"
+            "model": "ResNet-50 v1.5, NHWC, SGD momentum 0.9 wd 1e-4"
+                     + (", fp32 master weights" if impl == "product" else "")
                      + (" (7x7 stem evaluated as the equivalent 4x4 conv over space-to-depth input)"
                         if getattr(job, "s2d", False) else ""),
             "global_batch": batch * world,
@@ -170,26 +170,14 @@ def run(args, rank: int, world: int, dev, ClockSampler) -> int:
             "image": "3x224x224",
             "parallelism": f"dp{world}",
             "l2": "no explicit flush: each step streams several GB of activations, far larger than the 126 MB L2",
-            "cuda_graph": bool(args.impl == "product" and not args.no_graph),
-            "allreduce": (args.algo if world > 1 else "none"),
+            "cuda_graph": bool((impl == "product" and not args.no_graph) or impl == "ddp_graph"),
+            "allreduce": (args.algo if (world > 1 and impl == "product") else ("nccl" if world > 1 else "none")),
             "nvls": bool(comm is not None and comm.has_multicast),
         },
-        "clocks": clocks,
-        "e2e": {
-            "value": round(e2e_value, 1),
-            "unit": "img/s",
-            "ms_per_step": round(ms_e2e / steps, 3),
-            "h2d_bytes_per_step": job.h2d_bytes_per_step,
-            "d2h_bytes_per_step": job.d2h_bytes_per_step,
-        },
-        "gpu_launches": launches,
-        "loss": {"device": loss_dev, "e2e": loss_e2e},
-    }
-    if rank == 0:
-        print(json.dumps(out), flush=True)
+    })
+    torch.cuda.synchronize(dev)
+    del job
     if comm is not None:
-        torch.cuda.synchronize(dev)
-    if world > 1:
-        dist.barrier(device_ids=[dev.index])
-        dist.destroy_process_group()
-    return 0
+        comm.close()
+    release(dev)
+    return rec

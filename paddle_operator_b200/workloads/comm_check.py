@@ -101,6 +101,48 @@ def check(comm: Communicator, dev, rank, world) -> list[str]:
     return fails
 
 
+def allreduce_check(dev, rank, world, nbytes: int = 64 << 20, key: str = "archeck") -> dict:
+    """One all-reduce per algorithm on `nbytes` of random bf16 against `dist.all_reduce` (fp32 sum of the
+    same bf16 inputs).  Returns {"twoshot": "ok"|"MISMATCH", "nvls": ..., "oneshot": ..., "max_abs_err": e,
+    "ok": bool}; identical on every rank (errors are max-reduced), so all ranks can act on it together.
+    bench.py runs it before the timed arms: a wrong NVLS sum must not hide behind a finite loss."""
+    comm = Communicator.from_env(arena_bytes=2 * nbytes + (32 << 20), key=key)
+    out = {"bytes": nbytes, "nvls_available": bool(comm.has_multicast)}
+    n = nbytes // 2
+    a, b = comm.alloc(nbytes), comm.alloc(nbytes)
+    x = comm.tensor(a, (n,), torch.bfloat16)
+    torch.manual_seed(4321 + rank)
+    v = torch.randn(n, device=dev).to(torch.bfloat16)
+    ref = v.float()
+    dist.all_reduce(ref)
+    ref /= world
+    worst = 0.0
+    cases = [("twoshot", AR_TWOSHOT, n, a)] + ([("nvls", AR_NVLS, n, a)] if comm.has_multicast else [])
+    cases.append(("oneshot", AR_ONESHOT, (256 << 10) // 2, b))  # the small-message algorithm, out of place
+    for name, algo, m, out_off in cases:
+        x.copy_(v)
+        comm.barrier()
+        comm.all_reduce_bf16(a, out_off, m, scale=1.0 / world, algo=algo, nblocks=24)
+        torch.cuda.synchronize(dev)
+        got = comm.tensor(out_off, (m,), torch.bfloat16).float()
+        err = torch.tensor([float((got - ref[:m]).abs().max().item())], dtype=torch.float64, device=dev)
+        dist.all_reduce(err, op=dist.ReduceOp.MAX)
+        e = float(err.item())
+        worst = max(worst, e)
+        # bf16 rounding of a mean of N(0,1) samples: half an ulp at |x| < 4 is 2^-7
+        out[name] = "ok" if e < 2e-2 else "MISMATCH"
+        comm.barrier()
+    if not comm.has_multicast:
+        out["nvls"] = "not available (no multicast object on this box / world size)"
+    torch.cuda.synchronize(dev)
+    flags = comm.error_flags()[0]
+    out["max_abs_err"] = worst
+    out["ok"] = all(out[nm] == "ok" for nm, *_ in cases) and flags == 0
+    dist.barrier(device_ids=[dev.index])
+    comm.close()
+    return out
+
+
 def sweep(comm: Communicator, dev, rank, world, max_bytes, blocks_list) -> list[dict]:
     rows = []
     comm.reset_allocations()

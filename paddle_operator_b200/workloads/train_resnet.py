@@ -48,8 +48,11 @@ def main() -> int:
         if step % args.log_every == 0 or step == args.steps:
             torch.cuda.current_stream().synchronize()
             dt = time.time() - t0
+            # fp64 sum of the fp32 master weights: ranks that hold bit-identical parameters print the same digits
+            wsum = float(job.trainer.flat.master.double().sum().item())
             print(json.dumps({"rank": rank, "world": world, "step": step, "loss": round(float(loss.item()), 4),
-                              "img_per_s": round(step * args.batch * world / dt, 1)}), flush=True)
+                              "img_per_s": round(step * args.batch * world / dt, 1),
+                              "param_checksum": repr(wsum)}), flush=True)
     torch.cuda.synchronize()
     if comm is not None:
         comm.barrier()

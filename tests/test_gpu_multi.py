@@ -43,6 +43,8 @@ def test_data_parallel_resnet_ranks_agree():
         except ValueError:
             pass
     last = {x["rank"]: x for x in rows if x.get("step") == 12}
-    assert len(last) >= 1, r.stdout[-1500:]
-    # every rank sees a different batch but holds identical weights after the fused all-reduce
+    assert len(last) == 2, r.stdout[-1500:]
     assert all(x["loss"] == x["loss"] for x in last.values())
+    # every rank sees a different batch but holds bit-identical weights after the fused all-reduce
+    sums = {x["param_checksum"] for x in last.values()}
+    assert len(sums) == 1, f"ranks disagree on the parameters: {last}"
