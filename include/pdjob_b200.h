@@ -141,6 +141,16 @@ int pdj_stem_s2d_fwd(const void* x, const void* w, void* out, float* partial, in
 int pdj_stem_s2d_wgrad_ws_bytes(void);
 int pdj_stem_s2d_wgrad(const void* x, const void* dy, void* dw, void* ws, int N, int Ho, int Wo, cudaStream_t st);
 
+/* Weight gradient of a 3x3 / pad 1 / stride 1 NHWC convolution on tcgen05 (csrc/wgrad_tcgen05.cu):
+ * dw[Cout][3][3][Cin] bf16 (the memory of a channels-last [Cout, Cin, 3, 3] weight) from x[N][H][W][Cin] and
+ * dy[N][H][W][Cout].  One shared-memory X tile with its halo serves all nine taps through row-shifted matrix
+ * descriptors; accumulators stay in tensor memory for the whole kernel (split-K over pixel blocks), a second
+ * kernel adds the per-CTA partials held in `ws` (pdj_conv3x3_wgrad_ws_bytes bytes) in a fixed order.
+ * Cin % 32 == 0, Cout % 64 == 0, W <= 254.  ResNet-50's bottleneck 3x3 convolutions (deploy/examples/resnet.yaml). */
+size_t pdj_conv3x3_wgrad_ws_bytes(int N, int H, int W, int Cin, int Cout);
+int pdj_conv3x3_wgrad(const void* x, const void* dy, void* dw, void* ws, int N, int H, int W, int Cin, int Cout,
+                      cudaStream_t st);
+
 /* ---- ResNet-50 step kernels (csrc/bn_act.cu, csrc/optim_misc.cu) -----------
  * The workload of deploy/examples/resnet.yaml:13-19. NHWC bf16 activations
  * viewed as [M, C]; fp32 statistics. */

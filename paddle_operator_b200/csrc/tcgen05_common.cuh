@@ -44,6 +44,45 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
       "r"(parity)
       : "memory");
 }
+// Long waits (an epilogue warp waiting for a whole tile or a whole kernel's worth of MMAs): one lane polls with a
+// back-off and the rest of the warp parks at __syncwarp.  128 threads spinning on try_wait are 128 shared-memory
+// polls every few cycles, taken out of the 128 B/clk the tensor pipe needs for its operands.
+__device__ __forceinline__ void mbar_wait_warp_sleepy(uint32_t bar, uint32_t parity, uint32_t ns) {
+  if ((threadIdx.x & 31) == 0) {
+    uint32_t done = 0;
+    while (true) {
+      asm volatile(
+          "{\n\t"
+          ".reg .pred p;\n\t"
+          "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+          "selp.u32 %0, 1, 0, p;\n\t"
+          "}"
+          : "=r"(done)
+          : "r"(bar), "r"(parity)
+          : "memory");
+      if (done) break;
+      __nanosleep(ns);
+    }
+  }
+  __syncwarp();
+}
+// True in exactly one lane of a fully active warp.  The MMA issuer runs its loops with the WHOLE warp and guards only
+// the tcgen05 instructions with this: control flow and descriptor arithmetic then stay warp-uniform, the compiler
+// keeps them in uniform registers, and a UTCHMMA issues without the R2UR "waterfall" that per-lane code needs
+// (measured: ~120 -> ~56 cycles per N = 96 instruction).
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t"
+      "}"
+      : "=r"(pred));
+  return pred != 0;
+}
+// A value the compiler can prove warp-uniform (lane 0's copy).
+__device__ __forceinline__ uint32_t warp_uniform(uint32_t v) { return __shfl_sync(0xffffffffu, v, 0); }
 __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint32_t bar) {
   asm volatile(
       "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(dst),
@@ -65,6 +104,35 @@ __device__ __forceinline__ void tma_store_3d(const CUtensorMap* map, uint32_t sr
   asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(map), "r"(src), "r"(c0),
                "r"(c1), "r"(c2)
                : "memory");
+}
+__device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* map, int c0, int c1, int c2, int c3, uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4, %5}], [%6];" ::"r"(dst),
+      "l"(map), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(bar)
+      : "memory");
+}
+// im2col-mode load over an NHWC tensor map (cuTensorMapEncodeIm2col): `pixels per column` output pixels starting at
+// the one whose top-left filter tap sits at input coordinates (w, h) of image n, 64 channels from c; (off_w, off_h)
+// select the filter tap.  Pixels are walked W -> H -> N inside the padded bounding box; padding reads as zero.
+__device__ __forceinline__ void tma_load_im2col_4d(uint32_t dst, const CUtensorMap* map, int c, int w, int h, int n,
+                                                   uint16_t off_w, uint16_t off_h, uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.im2col.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4, %5}], [%6], {%7, %8};" ::
+          "r"(dst), "l"(map), "r"(c), "r"(w), "r"(h), "r"(n), "r"(bar), "h"(off_w), "h"(off_h)
+      : "memory");
+}
+// General shared-memory matrix descriptor (sm_100 version 1): start address, leading / stride byte offsets and the
+// swizzle mode (2 = 128 B, 4 = 64 B, 6 = 32 B, 0 = none).  The base-offset field stays 0 even when `smem_addr` is not
+// aligned to the swizzle pattern: the hardware applies the XOR to absolute shared-memory address bits, so a tile
+// written by TMA can be read from any 16-byte-aligned row of it (profiles/r2/desc_shift_experiment.log).
+__device__ __forceinline__ uint64_t umma_desc_ex(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes, uint32_t layout) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)(layout & 7) << 61;
+  return d;
 }
 // Shared-memory matrix descriptor: K-major tile, 128-byte swizzle, rows 128 B apart,
 // 8-row groups 1024 B apart (SBO), descriptor version 1 (sm_100).
@@ -89,6 +157,30 @@ __device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t da, uint64_t 
 }
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+
+// Warp-wide forms: every lane of a converged warp executes the statement, one elected lane issues the instruction.
+// No C++ branch surrounds it, so the operands stay in uniform registers (a branch on elect_one() makes the region
+// divergent for the compiler and brings the per-lane R2UR loop back).
+__device__ __forceinline__ void umma_f16_elect(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p, q;\n\t"
+      "elect.sync _|q, 0xffffffff;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "@q tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "}" ::"r"(tmem_d),
+      "l"(da), "l"(db), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit_elect(uint32_t bar) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred q;\n\t"
+      "elect.sync _|q, 0xffffffff;\n\t"
+      "@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t"
+      "}" ::"r"(bar)
+      : "memory");
 }
 
 // Shared-memory ring + accumulator hand-off barriers of one CTA.
@@ -151,4 +243,12 @@ int pdj_tc_make_map(CUtensorMap* map, const void* ptr, int rows, int cols, int l
                     bool swizzle);
 int pdj_tc_make_map3(CUtensorMap* map, const void* ptr, uint64_t d0, uint64_t d1, uint64_t d2, uint64_t s1, uint64_t s2,
                      int b0, int b1);
+// 4-D tiled map over an NHWC bf16 tensor {C, W, H, N} (strides in bytes for W, H, N); swizzle: 0 none, 1 32 B,
+// 2 64 B, 3 128 B.  Out-of-range box elements (negative or past-the-end coordinates) read as zero.
+int pdj_tc_make_map4(CUtensorMap* map, const void* ptr, const uint64_t dims[4], const uint64_t strides[3], const uint32_t box[4],
+                     int swizzle);
+// im2col map over an NHWC bf16 tensor for a ksize x ksize window with symmetric padding `pad` and traversal stride
+// `stride`: `pixels` output pixels x `channels` (<= 64) channels per load, 128-byte swizzle.
+int pdj_tc_make_im2col4(CUtensorMap* map, const void* ptr, int C, int W, int H, int N, int ksize, int pad, int stride,
+                        int channels, int pixels);
 int pdj_tc_sm_count();

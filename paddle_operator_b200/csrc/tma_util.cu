@@ -106,9 +106,69 @@ int make_map3(CUtensorMap* map, const void* ptr, uint64_t d0, uint64_t d1, uint6
   return 0;
 }
 
+typedef CUresult (*EncodeIm2colFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                   const int*, const int*, cuuint32_t, cuuint32_t, const cuuint32_t*, CUtensorMapInterleave,
+                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeIm2colFn g_encode_im2col = nullptr;
+
+int resolve_encode_im2col() {
+  if (g_encode_im2col != nullptr) return 0;
+  void* p = nullptr;
+  cudaDriverEntryPointQueryResult q;
+  cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeIm2col", &p, cudaEnableDefault, &q);
+  if (e != cudaSuccess || p == nullptr || q != cudaDriverEntryPointSuccess) {
+    pdj_set_error("cuTensorMapEncodeIm2col is unavailable: %s", cudaGetErrorString(e));
+    return -1;
+  }
+  g_encode_im2col = reinterpret_cast<EncodeIm2colFn>(p);
+  return 0;
+}
+
 int g_sms = 0;
 
 }  // namespace
+
+int pdj_tc_make_map4(CUtensorMap* map, const void* ptr, const uint64_t dims[4], const uint64_t strides[3], const uint32_t box[4],
+                     int swizzle) {
+  if (int r = resolve_encode()) return r;
+  if (int r = ensure_current_context()) return r;
+  const cuuint64_t d[4] = {dims[0], dims[1], dims[2], dims[3]};
+  const cuuint64_t s[3] = {strides[0], strides[1], strides[2]};
+  const cuuint32_t b[4] = {box[0], box[1], box[2], box[3]};
+  const cuuint32_t estr[4] = {1, 1, 1, 1};
+  static const CUtensorMapSwizzle modes[4] = {CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_SWIZZLE_32B, CU_TENSOR_MAP_SWIZZLE_64B,
+                                              CU_TENSOR_MAP_SWIZZLE_128B};
+  CUresult r = g_encode(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(ptr), d, s, b, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                        modes[swizzle & 3], CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    pdj_set_error("cuTensorMapEncodeTiled (4-D) failed with CUresult %d (dims %llu x %llu x %llu x %llu, box %u x %u x %u x %u)", (int)r,
+                  (unsigned long long)d[0], (unsigned long long)d[1], (unsigned long long)d[2], (unsigned long long)d[3], b[0], b[1],
+                  b[2], b[3]);
+    return (int)r;
+  }
+  return 0;
+}
+
+int pdj_tc_make_im2col4(CUtensorMap* map, const void* ptr, int C, int W, int H, int N, int ksize, int pad, int stride, int channels,
+                        int pixels) {
+  if (int r = resolve_encode_im2col()) return r;
+  if (int r = ensure_current_context()) return r;
+  const cuuint64_t d[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
+  const cuuint64_t s[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
+  // bounding box of the positions the top-left filter tap may take: [-pad, dim + pad - ksize] in W and H
+  const int lower[2] = {-pad, -pad};
+  const int upper[2] = {pad - (ksize - 1), pad - (ksize - 1)};
+  const cuuint32_t estr[4] = {1, (cuuint32_t)stride, (cuuint32_t)stride, 1};
+  CUresult r = g_encode_im2col(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(ptr), d, s, lower, upper,
+                               (cuuint32_t)channels, (cuuint32_t)pixels, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                               CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    pdj_set_error("cuTensorMapEncodeIm2col failed with CUresult %d (C=%d W=%d H=%d N=%d k=%d pad=%d stride=%d)", (int)r, C, W, H, N,
+                  ksize, pad, stride);
+    return (int)r;
+  }
+  return 0;
+}
 
 int pdj_tc_make_map(CUtensorMap* map, const void* ptr, int rows, int cols, int ld_elems, int box_cols, int box_rows,
                     bool swizzle) {

@@ -16,7 +16,7 @@ import torch
 import torch.nn as nn
 
 from ..ops.bn import FusedBnAct
-from ..ops.conv import conv1x1_dual, conv1x1_stats, stem_s2d_conv
+from ..ops.conv import conv1x1_dual, conv1x1_stats, conv3x3, stem_s2d_conv
 from ..ops.pool import FusedMaxPool2d
 
 
@@ -87,7 +87,8 @@ class Bottleneck(nn.Module):
                 y, p, d, pd = conv1x1_dual(x, self.conv1.weight, self.downsample.weight, self.downsample.stride[0])
                 identity = self.bn_ds(d, partial=pd)
             y = self.bn1(y, partial=p)
-            y = self.bn2(self.conv2(y))
+            # 3x3: weight gradient on the tcgen05 kernel of csrc/wgrad_tcgen05.cu (stride-1 layers)
+            y = self.bn2(conv3x3(y, self.conv2.weight, self.conv2.stride[0]))
             y, p = conv1x1_stats(y, self.conv3.weight)
             return self.bn3(y, identity, partial=p)
         y = self.bn1(self.conv1(x))

@@ -287,3 +287,65 @@ def stem_s2d_conv(x: torch.Tensor, weight: torch.Tensor):
     if stem_s2d_eligible(x, weight):
         return _StemS2dFn.apply(x, weight)
     return F.conv2d(x, weight), None
+
+
+# ---- 3x3 / pad 1 / stride 1 convolution: weight gradient on tcgen05 -------------------------------------------
+def conv3x3_wgrad_eligible(x: torch.Tensor, weight: torch.Tensor, stride=1, padding=1) -> bool:
+    s = stride if isinstance(stride, int) else (stride[0] if stride[0] == stride[1] else -1)
+    p = padding if isinstance(padding, int) else (padding[0] if padding[0] == padding[1] else -1)
+    return (x.is_cuda and x.dtype == torch.bfloat16 and weight.dtype == torch.bfloat16 and x.dim() == 4
+            and weight.dim() == 4 and weight.shape[2] == 3 and weight.shape[3] == 3 and s == 1 and p == 1
+            and weight.shape[0] % 64 == 0 and weight.shape[1] % 32 == 0 and x.shape[3] <= 254
+            and x.is_contiguous(memory_format=torch.channels_last))
+
+
+def conv3x3_wgrad(x: torch.Tensor, dy: torch.Tensor, weight_shape) -> torch.Tensor:
+    """dW (channels-last [Cout, Cin, 3, 3] bf16) of y = conv2d(x, w, padding=1) from x and dy, both NHWC bf16
+    (csrc/wgrad_tcgen05.cu: one halo tile per pixel block serves all nine taps, accumulators resident in TMEM)."""
+    lib = _lib.load()
+    n, c, h, w = x.shape
+    o = weight_shape[0]
+    assert dy.shape == (n, o, h, w) and dy.is_contiguous(memory_format=torch.channels_last)
+    dw = torch.empty((o, 3, 3, c), dtype=torch.bfloat16, device=x.device).permute(0, 3, 1, 2)  # channels-last strides
+    nbytes = lib.pdj_conv3x3_wgrad_ws_bytes(n, h, w, c, o)
+    if nbytes == 0:
+        raise ValueError(f"conv3x3_wgrad: unsupported shape {tuple(x.shape)} -> {o}")
+    ws = torch.empty(nbytes, dtype=torch.uint8, device=x.device)
+    _lib.check(lib.pdj_conv3x3_wgrad(x.data_ptr(), dy.data_ptr(), dw.data_ptr(), ws.data_ptr(), n, h, w, c, o,
+                                     torch.cuda.current_stream().cuda_stream), "conv3x3_wgrad")
+    _launches[0] += 2  # the tcgen05 kernel and the reduction of its per-CTA partials
+    return dw
+
+
+class _Conv3x3Fn(torch.autograd.Function):
+    """y = conv2d(x, weight, padding=1); the weight gradient runs on the tcgen05 kernel."""
+
+    @staticmethod
+    def forward(ctx, x, weight):
+        ctx.save_for_backward(x, weight)
+        return F.conv2d(x, weight, padding=1)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, weight = ctx.saved_tensors
+        if not dy.is_contiguous(memory_format=torch.channels_last):
+            dy = dy.contiguous(memory_format=torch.channels_last)
+        dx = dw = None
+        if ctx.needs_input_grad[0]:
+            dx, _, _ = torch.ops.aten.convolution_backward(dy, x, weight, None, [1, 1], [1, 1], [1, 1], False, [0, 0], 1,
+                                                           [True, False, False])
+        if ctx.needs_input_grad[1]:
+            dw = conv3x3_wgrad(x, dy, weight.shape)
+        return dx, dw
+
+
+WGRAD3X3_MIN_HW = int(os.environ.get("PDJ_WGRAD3X3_MIN_HW", "10"))
+
+
+def conv3x3(x: torch.Tensor, weight: torch.Tensor, stride: int = 1) -> torch.Tensor:
+    """3x3 / pad 1 convolution; stride-1 layers take the hand-written weight gradient.  Images smaller than
+    WGRAD3X3_MIN_HW pixels on a side (the 7x7 stage) stay with the library: a 49-pixel image fills 64-row blocks
+    only to 77 % and 64 (o, c) tiles leave no room for an even split (measured 85 vs 42 us at batch 256)."""
+    if stride == 1 and conv3x3_wgrad_eligible(x, weight) and min(x.shape[2], x.shape[3]) >= WGRAD3X3_MIN_HW:
+        return _Conv3x3Fn.apply(x, weight)
+    return F.conv2d(x, weight, stride=stride, padding=1)
