@@ -32,6 +32,18 @@ def _validate(doc: dict) -> None:
     meta = doc.get("metadata") or {}
     if not meta.get("name"):
         raise ValidationError("metadata.name is required")
+    # the API server of the reference rejects these with 422 before the controller ever sees the job
+    from ..controller.store import Invalid, validate_name
+
+    try:
+        validate_name(meta["name"])
+        if len(meta["name"]) > 63 or "." in meta["name"]:
+            # pods, services and the `<job>-worker-0` host names derive from it: a single DNS label
+            validate_name(meta["name"], namespace=True)
+        if meta.get("namespace") is not None:
+            validate_name(meta["namespace"], "metadata.namespace", namespace=True)
+    except Invalid as e:
+        raise ValidationError(str(e)) from None
     spec = doc.get("spec")
     if spec is not None and not isinstance(spec, dict):
         raise ValidationError("spec must be a mapping")

@@ -20,6 +20,7 @@ from __future__ import annotations
 
 import copy
 import datetime as _dt
+import re
 import threading
 import uuid
 from typing import Callable, Optional
@@ -39,6 +40,27 @@ class AlreadyExists(StoreError):
 
 class Conflict(StoreError):
     pass
+
+
+class Invalid(StoreError):
+    """A name or namespace Kubernetes would reject (the API server answers 422)."""
+
+
+# Kubernetes validates object names as RFC 1123 DNS subdomains (labels of [a-z0-9-] joined by single dots, at most
+# 253 characters) and namespaces as single labels of at most 63.  The reference inherits that from the API server;
+# here it also keeps names usable as path components (no "/", no "..") - the supervisor builds work directories
+# and log paths from them.
+_LABEL = r"[a-z0-9]([-a-z0-9]*[a-z0-9])?"
+_NAME_RE = re.compile(rf"^{_LABEL}(\.{_LABEL})*$")
+_NS_RE = re.compile(rf"^{_LABEL}$")
+
+
+def validate_name(name, what: str = "metadata.name", namespace: bool = False) -> None:
+    limit = 63 if namespace else 253
+    if not isinstance(name, str) or not name or len(name) > limit or not (_NS_RE if namespace else _NAME_RE).match(name):
+        raise Invalid(f"{what}: {name!r} is not a valid RFC 1123 {'label' if namespace else 'subdomain'} "
+                      f"(lower-case alphanumerics and '-'{'' if namespace else ', labels joined by single dots'}, "
+                      f"at most {limit} characters)")
 
 
 def _now() -> str:
@@ -67,12 +89,27 @@ class ObjectStore:
         self._objs: dict[Key, dict] = {}
         self._rv = 0
         self._watchers: list[WatchFn] = []
+        # (owner kind, namespace, owner name) -> keys of the objects that carry an ownerReference to it: serves
+        # list(owner=...) - the `.metadata.controller` field index of the reference - and garbage collection
+        self._by_owner: dict[tuple, set] = {}
 
     # -- helpers ----------------------------------------------------------------
     @staticmethod
     def key_of(obj: dict) -> Key:
         m = obj.get("metadata") or {}
         return (obj.get("kind", ""), m.get("namespace") or "default", m.get("name", ""))
+
+    def _index(self, key: Key, obj: dict, add: bool) -> None:
+        for ref in obj["metadata"].get("ownerReferences") or []:
+            okey = (ref.get("kind", ""), key[1], ref.get("name", ""))
+            if add:
+                self._by_owner.setdefault(okey, set()).add(key)
+            else:
+                bucket = self._by_owner.get(okey)
+                if bucket is not None:
+                    bucket.discard(key)
+                    if not bucket:
+                        del self._by_owner[okey]
 
     def _next_rv(self) -> str:
         self._rv += 1
@@ -100,6 +137,8 @@ class ObjectStore:
         meta.setdefault("namespace", "default")
         if not meta.get("name"):
             raise StoreError("metadata.name is required")
+        validate_name(meta["name"])
+        validate_name(meta["namespace"], "metadata.namespace", namespace=True)
         key = self.key_of(obj)
         with self._lock:
             if key in self._objs:
@@ -116,6 +155,7 @@ class ObjectStore:
             meta["creationTimestamp"] = meta.get("creationTimestamp") or _now()
             meta.pop("deletionTimestamp", None)
             self._objs[key] = obj
+            self._index(key, obj, True)
             self._notify("ADDED", obj)
             return _clone(obj)
 
@@ -128,6 +168,8 @@ class ObjectStore:
         meta.setdefault("namespace", "default")
         if not meta.get("name"):
             raise StoreError("metadata.name is required")
+        validate_name(meta["name"])
+        validate_name(meta["namespace"], "metadata.namespace", namespace=True)
         key = self.key_of(obj)
         with self._lock:
             if key in self._objs:
@@ -137,6 +179,7 @@ class ObjectStore:
             meta["generation"] = int(meta.get("generation") or 1)
             meta["creationTimestamp"] = meta.get("creationTimestamp") or _now()
             self._objs[key] = obj
+            self._index(key, obj, True)
             self._notify("ADDED", obj)
             return _clone(obj)
 
@@ -160,7 +203,12 @@ class ObjectStore:
         a label selector.  Sorted by name for determinism."""
         out = []
         with self._lock:
-            for (k, ns, _), obj in self._objs.items():
+            if owner is not None and namespace is not None:
+                # the owner index: only the owner's dependents are looked at, not every object of the kind
+                cand = [(k, self._objs[k]) for k in self._by_owner.get((owner_kind, namespace, owner), ()) if k in self._objs]
+            else:
+                cand = self._objs.items()
+            for (k, ns, _), obj in cand:
                 if k != kind or (namespace is not None and ns != namespace):
                     continue  # (a key-tuple compare; cloning the matches is what costs)
                 if owner is not None:
@@ -203,7 +251,9 @@ class ObjectStore:
             if meta.get("deletionTimestamp") and not meta.get("finalizers"):
                 self._remove(key)
                 return _clone(new)
+            self._index(key, cur, False)
             self._objs[key] = new
+            self._index(key, new, True)
             self._notify("MODIFIED", new)
             return _clone(new)
 
@@ -250,13 +300,14 @@ class ObjectStore:
         obj = self._objs.pop(key, None)
         if obj is None:
             return
+        self._index(key, obj, False)
         self._notify("DELETED", obj)
-        # garbage-collect dependents (background propagation)
+        # garbage-collect dependents (background propagation); candidates come from the owner index
         uid = obj["metadata"].get("uid")
-        deps = [k for k, o in self._objs.items()
-                if k[1] == key[1] and any(r.get("uid") == uid or (not r.get("uid") and r.get("name") == key[2]
-                                                                     and r.get("kind") == key[0])
-                                          for r in o["metadata"].get("ownerReferences") or [])]
+        deps = [k for k in list(self._by_owner.get((key[0], key[1], key[2]), ()))
+                if k in self._objs and any(r.get("uid") == uid or (not r.get("uid") and r.get("name") == key[2]
+                                                                      and r.get("kind") == key[0])
+                                           for r in self._objs[k]["metadata"].get("ownerReferences") or [])]
         for k in deps:
             d = self._objs.get(k)
             if d is None:
@@ -279,25 +330,62 @@ class ObjectStore:
 class EventRecorder:
     """k8s Events on the job (controllers/paddlejob_controller.go:383-405,215):
     Normal/Warning, reason, message.  Stored as Event objects so `pdj events`
-    and the tests can read the audit trail."""
+    and the tests can read the audit trail.
 
-    def __init__(self, store: ObjectStore, component: str = "paddlejob-controller"):
+    Kept bounded the way the API server keeps them bounded: a repeat of the latest event of an object (same type,
+    reason and message) bumps its `count` / `lastTimestamp` instead of creating a new object, events older than
+    `ttl_seconds` (Kubernetes: 1 h) are dropped when the next one is recorded, at most `max_per_object` are kept
+    per involved object, and every event carries an ownerReference to its object so that deleting a job
+    garbage-collects its events."""
+
+    def __init__(self, store: ObjectStore, component: str = "paddlejob-controller", ttl_seconds: float = 3600.0,
+                 max_per_object: int = 256):
         self.store, self.component = store, component
+        self.ttl_seconds, self.max_per_object = ttl_seconds, max_per_object
         self._n = 0
         self._lock = threading.Lock()
+        # (kind, namespace, name) of the involved object -> [(event name, monotonic time)], oldest first
+        self._recent: dict[tuple, list] = {}
 
     def event(self, involved: dict, etype: str, reason: str, message: str) -> None:
-        with self._lock:
-            self._n += 1
-            n = self._n
+        import time as _time
+
         m = involved.get("metadata") or {}
+        ns, name, kind = m.get("namespace", "default"), m.get("name", ""), involved.get("kind", "")
+        okey = (kind, ns, name)
+        now = _time.monotonic()
+        with self._lock:
+            mine = self._recent.setdefault(okey, [])
+            # expire by age and by count
+            while mine and (now - mine[0][1] > self.ttl_seconds or len(mine) >= self.max_per_object):
+                old, _ = mine.pop(0)
+                try:
+                    self.store.delete("Event", ns, old)
+                except NotFound:
+                    pass
+            if mine:
+                last = self.store.try_get("Event", ns, mine[-1][0])
+                if last is None:
+                    mine.clear()  # collected together with a previous incarnation of the object
+                elif (last.get("type"), last.get("reason"), last.get("message")) == (etype, reason, message) and \
+                        last["involvedObject"].get("uid", "") == m.get("uid", ""):
+                    last["count"] = int(last.get("count", 1)) + 1
+                    last["lastTimestamp"] = _now()
+                    last["metadata"].pop("resourceVersion", None)
+                    self.store.update(last)
+                    mine[-1] = (mine[-1][0], now)
+                    return
+            self._n += 1
+            ev_name = f"{name or 'obj'}.{self._n:08x}"
+            mine.append((ev_name, now))
+        owner = ([{"apiVersion": involved.get("apiVersion", ""), "kind": kind, "name": name, "uid": m["uid"]}]
+                 if m.get("uid") else [])
         self.store.create({
             "apiVersion": "v1", "kind": "Event",
-            "metadata": {"name": f"{m.get('name', 'obj')}.{n:08x}", "namespace": m.get("namespace", "default")},
-            "involvedObject": {"kind": involved.get("kind", ""), "name": m.get("name", ""),
-                               "namespace": m.get("namespace", "default"), "uid": m.get("uid", "")},
+            "metadata": {"name": ev_name, "namespace": ns, "ownerReferences": owner},
+            "involvedObject": {"kind": kind, "name": name, "namespace": ns, "uid": m.get("uid", "")},
             "type": etype, "reason": reason, "message": message,
-            "source": {"component": self.component}, "firstTimestamp": _now(), "count": 1,
+            "source": {"component": self.component}, "firstTimestamp": _now(), "lastTimestamp": _now(), "count": 1,
         })
 
     def events_for(self, kind: str, namespace: str, name: str) -> list[dict]:

@@ -21,7 +21,7 @@ from typing import Optional
 
 from ..api import loader
 from ..api.types import GROUP, KIND
-from ..controller.store import AlreadyExists, Conflict, NotFound, ObjectStore
+from ..controller.store import AlreadyExists, Conflict, NotFound, ObjectStore, Invalid
 
 PLURALS = {"paddlejobs": KIND, "pdj": KIND, "pods": "Pod", "services": "Service", "configmaps": "ConfigMap",
            "events": "Event", "podgroups": "PodGroup"}
@@ -167,7 +167,7 @@ def make_handler(cluster, serve_api: bool, serve_health: bool, serve_metrics: bo
                     body.pop("status", None)
                 body["kind"] = kind
                 return self._send(201, store.create(body))
-            except loader.ValidationError as e:
+            except (loader.ValidationError, Invalid) as e:
                 return self._status(422, "Invalid", str(e))
             except AlreadyExists as e:
                 return self._status(409, "AlreadyExists", str(e))

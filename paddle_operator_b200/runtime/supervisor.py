@@ -254,7 +254,12 @@ class Supervisor:
                         "conditions": [{"type": "PodScheduled", "status": "False", "reason": "Unschedulable",
                                         "message": f"0/{len(self.gpu_pool)} GPUs free, need {need}"}]}))
                 return
-            workdir = os.path.join(self.work_root, ns, name)
+            workdir = self._contained(ns, name)
+            if workdir is None:  # never reached through the API (names are validated there); belt and braces
+                self.store.patch_status("Pod", ns, name, lambda st: st.update({
+                    "phase": "Failed", "reason": "InvalidName",
+                    "message": "namespace / name would place the work directory outside the work root"}))
+                return
             shutil.rmtree(workdir, ignore_errors=True)
             os.makedirs(workdir, exist_ok=True)
             r = _Rank(ns, name, pod["metadata"].get("uid", ""), workdir,
@@ -466,10 +471,23 @@ class Supervisor:
             self._wake.set()
             return True
 
+    def _contained(self, namespace: str, name: str) -> Optional[str]:
+        """<work_root>/<namespace>/<name>, or None when that path would leave the work root ('..', '/', symlinks)."""
+        root = os.path.realpath(self.work_root)
+        path = os.path.realpath(os.path.join(root, namespace, name))
+        if os.path.commonpath([root, path]) != root or path == root:
+            return None
+        return path
+
     def logs(self, namespace: str, name: str) -> str:
         with self._lock:
             r = self._ranks.get((namespace, name))
-        path = r.log_path if r else os.path.join(self.work_root, namespace, name, "log.txt")
+        path = r.log_path if r else None
+        if path is None:
+            wd = self._contained(namespace, name)
+            if wd is None:
+                return ""
+            path = os.path.join(wd, "log.txt")
         try:
             with open(path, "r", errors="replace") as f:
                 return f.read()

@@ -746,3 +746,56 @@ def test_elastic_jobs_scale_only_inside_requests_limits():
     inverted["spec"]["worker"].update(requests=5, limits=2)
     with pytest.raises(loader.ValidationError):
         loader.paddlejob_from_doc(inverted)
+
+
+# ---- names are validated the way the API server validates them --------------------------------------------
+@pytest.mark.parametrize("ns,name", [("..", "job"), ("default", "../evil"), ("default", "a/b"), ("default", "Job"),
+                                     ("default", "a..b"), ("default", "-x"), ("Default", "job"), ("default", "x" * 64)])
+def test_invalid_names_are_rejected_everywhere(ns, name):
+    from paddle_operator_b200.api import loader
+    from paddle_operator_b200.controller.store import Invalid, ObjectStore
+
+    doc = {"apiVersion": "batch.paddlepaddle.org/v1", "kind": "PaddleJob", "metadata": {"name": name, "namespace": ns},
+           "spec": {"worker": {"replicas": 1, "template": {"spec": {"containers": [{"name": "c", "image": "x"}]}}}}}
+    with pytest.raises(loader.ValidationError):
+        loader.paddlejob_from_doc(doc)
+    if len(name) <= 63 or ns != "default":
+        with pytest.raises(Invalid):
+            ObjectStore().create({"kind": "Pod", "metadata": {"name": name, "namespace": ns}})
+
+
+def test_supervisor_never_leaves_its_work_root(tmp_path):
+    from paddle_operator_b200.controller.store import ObjectStore
+    from paddle_operator_b200.runtime.supervisor import Supervisor
+
+    sup = Supervisor(ObjectStore(), work_root=str(tmp_path / "root"), gpus=[])
+    assert sup._contained("default", "job-worker-0") == str(tmp_path / "root" / "default" / "job-worker-0")
+    assert sup._contained("..", "x") is None and sup._contained("default", "../../etc") is None
+    outside = tmp_path / "secret"
+    outside.mkdir()
+    (outside / "log.txt").write_text("do not read me")
+    assert sup.logs("..", "secret") == ""
+
+
+def test_owner_index_and_event_policy():
+    from paddle_operator_b200.controller.store import EventRecorder, ObjectStore
+
+    st = ObjectStore()
+    job = st.create({"kind": "PaddleJob", "metadata": {"name": "j", "namespace": "default"}, "spec": {}})
+    ref = [{"kind": "PaddleJob", "name": "j", "uid": job["metadata"]["uid"], "controller": True}]
+    for i in range(5):
+        st.create({"kind": "Pod", "metadata": {"name": f"j-worker-{i}", "namespace": "default", "ownerReferences": ref}})
+    st.create({"kind": "Pod", "metadata": {"name": "stranger", "namespace": "default"}})
+    assert [p["metadata"]["name"] for p in st.list("Pod", "default", owner="j")] == [f"j-worker-{i}" for i in range(5)]
+    assert ("PaddleJob", "default", "j") in st._by_owner  # served from the index, not from a scan
+    rec = EventRecorder(st, max_per_object=4)
+    for _ in range(10):
+        rec.event(job, "Normal", "Created", "pod created")  # a repeat: one object, count 10
+    evs = rec.events_for("PaddleJob", "default", "j")
+    assert len(evs) == 1 and evs[0]["count"] == 10
+    for i in range(10):
+        rec.event(job, "Normal", "Scaled", f"to {i}")
+    assert len(rec.events_for("PaddleJob", "default", "j")) <= 4  # capped per object
+    st.delete("PaddleJob", "default", "j")
+    assert st.list("Event", "default") == [] and st.list("Pod", "default", owner="j") == []  # collected with the job
+    assert ("PaddleJob", "default", "j") not in st._by_owner
