@@ -74,7 +74,7 @@ conv1x1_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_c
   uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(smem_raw + (tmem_slot - raw));
   float* scratch_f = reinterpret_cast<float*>(smem_raw + (scratch - raw));
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = (int)warp_uniform(threadIdx.x >> 5), lane = threadIdx.x & 31;
   const int tiles_n = N / block_n;
   const int total = WIN ? M : ((M + BM - 1) / BM) * tiles_n;  // WIN: M counts output rows, one tile each
   const int win_upi = WIN ? (win_ho + WIN_CHUNK - 1) / WIN_CHUNK : 1;   // work units (row chunks) per image
@@ -108,7 +108,7 @@ conv1x1_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_c
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-  const uint32_t tmem_base = *tmem_slot_ptr;
+  const uint32_t tmem_base = warp_uniform(*tmem_slot_ptr);
   const Pipe pipe{a_smem, b_smem, b_stage_bytes, full0, empty0, tfull0, tempty0, stages};
 
   if (warp == 0) {
@@ -134,10 +134,11 @@ conv1x1_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_c
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    {  // the whole warp runs the issue loops; one elected lane issues (umma_*_elect)
       if (WIN) {
         const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(block_n >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
         const uint32_t S = (uint32_t)stages;
+        const uint64_t d0 = umma_desc(0);
         mbar_wait(abar0, 0);
         uint32_t ix = 0, i = 0;
         for (int u = blockIdx.x; u < win_units; u += gridDim.x) {
@@ -153,17 +154,16 @@ conv1x1_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_c
 #pragma unroll
             for (int kb = 0; kb < 4; ++kb) {
               const uint32_t slot = (ix + j + kb) % S;
+              const uint64_t da = d0 + (uint64_t)((a_smem + slot * A_STAGE_BYTES) >> 4);
+              const uint64_t db = d0 + (uint64_t)((b_smem + kb * b_stage_bytes) >> 4);
 #pragma unroll
-              for (int k = 0; k < BK / UK; ++k) {
-                const uint64_t da = umma_desc(a_smem + slot * A_STAGE_BYTES + k * UK * 2);
-                const uint64_t db = umma_desc(b_smem + kb * b_stage_bytes + k * UK * 2);
-                umma_f16(tmem_d, da, db, idesc, (uint32_t)((kb | k) != 0));
-              }
+              for (int k = 0; k < BK / UK; ++k)
+                umma_f16_elect(tmem_d, da + (uint64_t)(k * UK * 2 >> 4), db + (uint64_t)(k * UK * 2 >> 4), idesc, (uint32_t)((kb | k) != 0));
             }
-            umma_commit(empty0 + 8 * ((ix + j) % S));  // input row y0 + j has served its last output row
+            umma_commit_elect(empty0 + 8 * ((ix + j) % S));  // input row y0 + j has served its last output row
             if (j == rows - 1)
-              for (int r = 1; r <= 3; ++r) umma_commit(empty0 + 8 * ((ix + j + r) % S));
-            umma_commit(tfull0 + 8 * buf);
+              for (int r = 1; r <= 3; ++r) umma_commit_elect(empty0 + 8 * ((ix + j + r) % S));
+            umma_commit_elect(tfull0 + 8 * buf);
           }
           ix += rows + 3;
         }
@@ -384,7 +384,7 @@ stem_wgrad_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_x, const __gri
   const uint32_t xfull = bars, xempty = xfull + 8 * WG_RX, yfull = xempty + 8 * WG_RX, yempty = yfull + 8 * WG_RY;
   const uint32_t done = yempty + 8 * WG_RY, tmem_slot = done + 8;
   uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(smem_raw + (tmem_slot - raw));
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = (int)warp_uniform(threadIdx.x >> 5), lane = threadIdx.x & 31;
   const int upi = (Ho + WG_CHUNK - 1) / WG_CHUNK;  // units per image
   const int units = n_img * upi;
 
@@ -406,7 +406,7 @@ stem_wgrad_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_x, const __gri
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-  const uint32_t tmem_base = *tmem_slot_ptr;
+  const uint32_t tmem_base = warp_uniform(*tmem_slot_ptr);
 
   if (warp == 0) {
     if (lane == 0) {
@@ -430,10 +430,11 @@ stem_wgrad_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_x, const __gri
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    {  // the whole warp runs the issue loop; one elected lane issues
       // D = f32, A = B = bf16, both MN-major (bits 15, 16), N = 64, M = 64
       const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) | ((64u >> 3) << 17) | ((64u >> 4) << 24);
       const int ksteps = kp / 16;
+      const uint64_t d0 = umma_desc_mn(0);
       uint32_t ix = 0, iy = 0;
       for (int u = blockIdx.x; u < units; u += gridDim.x) {
         const int y0 = (u % upi) * WG_CHUNK;
@@ -444,23 +445,23 @@ stem_wgrad_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_x, const __gri
           const uint32_t sy = iy % WG_RY;
           mbar_wait(yfull + 8 * sy, (iy / WG_RY) & 1u);
           asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          const uint64_t da0 = d0 + (uint64_t)((dy_smem + sy * tile) >> 4);
 #pragma unroll
           for (int jy = 0; jy < 4; ++jy) {
             const uint32_t xs = (ix + j + jy) % WG_RX;
-            for (int k = 0; k < ksteps; ++k) {
-              const uint64_t da = umma_desc_mn(dy_smem + sy * tile + (uint32_t)k * 2048u);
-              const uint64_t db = umma_desc_mn(x_smem + xs * tile + (uint32_t)k * 2048u);
-              umma_f16(tmem_base + (uint32_t)jy * 64u, da, db, idesc, (uint32_t)((iy | (uint32_t)k) != 0u));
-            }
+            const uint64_t db0 = d0 + (uint64_t)((x_smem + xs * tile) >> 4);
+            for (int k = 0; k < ksteps; ++k)
+              umma_f16_elect(tmem_base + (uint32_t)jy * 64u, da0 + (uint64_t)(k * 128), db0 + (uint64_t)(k * 128), idesc,
+                             (uint32_t)((iy | (uint32_t)k) != 0u));
           }
-          umma_commit(yempty + 8 * sy);
-          umma_commit(xempty + 8 * ((ix + j) % WG_RX));       // input row y0 + j has served its last output row
+          umma_commit_elect(yempty + 8 * sy);
+          umma_commit_elect(xempty + 8 * ((ix + j) % WG_RX));       // input row y0 + j has served its last output row
           if (j == rows - 1)
-            for (int r = 1; r <= 3; ++r) umma_commit(xempty + 8 * ((ix + j + r) % WG_RX));  // bottom halo rows
+            for (int r = 1; r <= 3; ++r) umma_commit_elect(xempty + 8 * ((ix + j + r) % WG_RX));  // bottom halo rows
         }
         ix += rows + 3;
       }
-      umma_commit(done);
+      umma_commit_elect(done);
     }
   } else {
     // epilogue: M = 64 accumulators occupy lanes 0..15 of each 32-lane TMEM quarter: row 16 * q + lane

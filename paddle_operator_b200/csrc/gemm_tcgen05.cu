@@ -54,7 +54,7 @@ linear_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
   const uint32_t tfull0 = bars + 16 * MAX_STAGES, tempty0 = tfull0 + 16, tmem_slot = tempty0 + 16;
   uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(smem_raw + (tmem_slot - raw));
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = (int)warp_uniform(threadIdx.x >> 5), lane = threadIdx.x & 31;
   const int tiles_n = (N + block_n - 1) / block_n;
   const int total = ((M + BM - 1) / BM) * tiles_n;
   const int num_kb = (K + BK - 1) / BK;
@@ -84,13 +84,13 @@ linear_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-  const uint32_t tmem_base = *tmem_slot_ptr;
+  const uint32_t tmem_base = warp_uniform(*tmem_slot_ptr);
   const Pipe pipe{a_smem, b_smem, b_stage_bytes, full0, empty0, tfull0, tempty0, stages};
 
   if (warp == 0) {
     if (lane == 0) producer_loop(&tma_a, &tma_b, pipe, total, tiles_n, block_n, num_kb);
   } else if (warp == 1) {
-    if (lane == 0) mma_loop(pipe, tmem_base, total, block_n, num_kb);
+    mma_loop(pipe, tmem_base, total, block_n, num_kb);  // whole warp, one elected lane issues
   } else {
     // ===== epilogue: warps 2..9.  Warp w reads TMEM lane quarter (w % 4) - a hardware rule -
     // and the two warps of a quarter split the columns in halves. =====

@@ -208,10 +208,12 @@ __device__ __forceinline__ void producer_loop(const CUtensorMap* tma_a, const CU
   }
 }
 
-// MMA issuer (one thread): tile i accumulates into TMEM buffer i & 1.
+// MMA issuer: called by the WHOLE warp (converged); one elected lane issues.  Tile i accumulates into TMEM buffer
+// i & 1.  Descriptors are built once and advanced by adding to their address field, all in uniform registers.
 __device__ __forceinline__ void mma_loop(const Pipe& p, uint32_t tmem_base, int total, int block_n, int num_kb) {
   // instruction descriptor: D = f32, A = B = bf16, both K-major, N >> 3, M >> 4
   const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(block_n >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+  const uint64_t d0 = umma_desc(0);
   uint32_t it = 0, i = 0;
   for (int t = blockIdx.x; t < total; t += gridDim.x, ++i) {
     const uint32_t buf = i & 1u, aph = (i >> 1) & 1u;
@@ -222,15 +224,14 @@ __device__ __forceinline__ void mma_loop(const Pipe& p, uint32_t tmem_base, int 
       const uint32_t s = it % (uint32_t)p.stages, ph = (it / (uint32_t)p.stages) & 1u;
       mbar_wait(p.full0 + 8 * s, ph);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      const uint64_t da = d0 + (uint64_t)((p.a_smem + s * A_STAGE_BYTES) >> 4);
+      const uint64_t db = d0 + (uint64_t)((p.b_smem + s * p.b_stage_bytes) >> 4);
 #pragma unroll
-      for (int k = 0; k < BK / UK; ++k) {
-        const uint64_t da = umma_desc(p.a_smem + s * A_STAGE_BYTES + k * UK * 2);
-        const uint64_t db = umma_desc(p.b_smem + s * p.b_stage_bytes + k * UK * 2);
-        umma_f16(tmem_d, da, db, idesc, (uint32_t)((kb | k) != 0));
-      }
-      umma_commit(p.empty0 + 8 * s);  // slot is free once these MMAs have read it
+      for (int k = 0; k < BK / UK; ++k)
+        umma_f16_elect(tmem_d, da + (uint64_t)(k * UK * 2 >> 4), db + (uint64_t)(k * UK * 2 >> 4), idesc, (uint32_t)((kb | k) != 0));
+      umma_commit_elect(p.empty0 + 8 * s);  // slot is free once these MMAs have read it
     }
-    umma_commit(p.tfull0 + 8 * buf);  // accumulator complete
+    umma_commit_elect(p.tfull0 + 8 * buf);  // accumulator complete
   }
 }
 
