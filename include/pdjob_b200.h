@@ -127,6 +127,15 @@ int pdj_conv1x1_bf16(const void* a, const void* b, void* out, float* partial, in
  * first 1x1 convolution with the skip connection's gradient folded in. */
 int pdj_conv1x1_add_bf16(const void* a, const void* b, const void* addend, void* out, int M, int N, int K, int lda,
                          int ldb, int ldc, int ldo, cudaStream_t st);
+/* General NHWC convolution forward (square filter k <= 7, symmetric padding, stride) as an implicit GEMM on the same
+ * pipeline: out[N][P][Q][Cout] from x[N][H][W][Cin] and the channels-last weight w[Cout][k][k][Cin].  The A operand is
+ * read with im2col-mode TMA loads (128 consecutive output pixels x 64 channels per filter tap; the TMA unit walks
+ * rows and images and zero-fills the padding), so nothing is materialised.  `partial` as above with
+ * pdj_conv_im2col_partial_rows(...) rows.  The input gradient of a stride-1 convolution is the same call on dy with
+ * the flipped, transposed weight.  Cin % 64 == 0, Cout % 64 == 0.  ResNet-50's 3x3 and strided convolutions. */
+int pdj_conv_im2col_partial_rows(int N, int H, int W, int Cout, int ksize, int pad, int stride);
+int pdj_conv_im2col_fwd(const void* x, const void* w, void* out, float* partial, int N, int H, int W, int Cin, int Cout,
+                        int ksize, int pad, int stride, cudaStream_t st);
 /* ResNet stem on the same pipeline: the 7x7 / stride-2 convolution expressed as a 4x4 / stride-1
  * convolution (16 -> 64 channels) over the space-to-depth input x[N][Ho+3][Wo+3][16] (see
  * pdj_preprocess_u8_s2d); w[64][4][4][16] bf16, out[N][Ho][Wo][64] bf16, Wo <= 128.  The A operand is read

@@ -477,17 +477,27 @@ def cmd_crd(args) -> int:
     from .api import loader
     from .api.types import GROUP, KIND, SHORT_NAME, VERSION
 
-    crd = {"apiVersion": "apiextensions.k8s.io/v1", "kind": "CustomResourceDefinition",
-           "metadata": {"name": f"paddlejobs.{GROUP}"},
-           "spec": {"group": GROUP, "scope": "Namespaced",
-                    "names": {"kind": KIND, "listKind": KIND + "List", "plural": "paddlejobs", "singular": "paddlejob",
-                              "shortNames": [SHORT_NAME]},
-                    "versions": [{"name": VERSION, "served": True, "storage": True, "subresources": {"status": {}},
-                                  "additionalPrinterColumns": [
-                                      {"name": "Status", "type": "string", "jsonPath": ".status.phase"},
-                                      {"name": "Mode", "type": "string", "jsonPath": ".status.mode"},
-                                      {"name": "Age", "type": "date", "jsonPath": ".metadata.creationTimestamp"}],
-                                  "schema": {"openAPIV3Schema": loader.openapi_schema()}}]}}
+    columns = [("Status", "string", ".status.phase"), ("Mode", "string", ".status.mode"),
+               ("Age", "date", ".metadata.creationTimestamp")]
+    names = {"kind": KIND, "listKind": KIND + "List", "plural": "paddlejobs", "singular": "paddlejob",
+             "shortNames": [SHORT_NAME]}
+    if getattr(args, "version", "v1") == "v1beta1":
+        # the apiextensions.k8s.io/v1beta1 variant the reference ships for clusters older than 1.16
+        # (deploy/v1beta1/crd.yaml, config/crd/v1beta1/): columns, subresources and the schema sit at the top of
+        # the spec (`JSONPath`, `validation`), and the served version is a plain list entry
+        crd = {"apiVersion": "apiextensions.k8s.io/v1beta1", "kind": "CustomResourceDefinition",
+               "metadata": {"name": f"paddlejobs.{GROUP}"},
+               "spec": {"additionalPrinterColumns": [{"JSONPath": p, "name": n, "type": t} for n, t, p in columns],
+                        "group": GROUP, "names": names, "scope": "Namespaced", "subresources": {"status": {}},
+                        "validation": {"openAPIV3Schema": loader.openapi_schema()},
+                        "version": VERSION, "versions": [{"name": VERSION, "served": True, "storage": True}]}}
+    else:
+        crd = {"apiVersion": "apiextensions.k8s.io/v1", "kind": "CustomResourceDefinition",
+               "metadata": {"name": f"paddlejobs.{GROUP}"},
+               "spec": {"group": GROUP, "scope": "Namespaced", "names": names,
+                        "versions": [{"name": VERSION, "served": True, "storage": True, "subresources": {"status": {}},
+                                      "additionalPrinterColumns": [{"name": n, "type": t, "jsonPath": p} for n, t, p in columns],
+                                      "schema": {"openAPIV3Schema": loader.openapi_schema()}}]}}
     print(yaml.safe_dump(crd, sort_keys=False))
     return 0
 
@@ -577,6 +587,8 @@ def build_parser() -> argparse.ArgumentParser:
     p = client_parser("client-demo", "CRUD round trip through the API")
     p.set_defaults(fn=cmd_client_demo)
     p = sub.add_parser("crd", help="print the PaddleJob schema (the generated CRD's top level) as YAML")
+    p.add_argument("--version", default="v1", choices=["v1", "v1beta1"],
+                   help="apiextensions.k8s.io version of the CustomResourceDefinition document (reference: deploy/v1 and deploy/v1beta1)")
     p.set_defaults(fn=cmd_crd)
     p = sub.add_parser("etcd", help="run the etcd-compatible store")
     p.add_argument("--listen", default="127.0.0.1:2379")

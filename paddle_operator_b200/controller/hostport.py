@@ -108,3 +108,146 @@ def parse_annotation(value: str) -> list[int]:
             raise ValueError(f"port {p} out of range")
         out.append(p)
     return out
+
+
+class LegacyHostPortManager:
+    """The stand-alone legacy allocator as a running controller
+    (third_party/hostport-allocator/pkg/core/hostportmanager.go): it watches one object kind (the reference:
+    TrainingJob), and for every object that carries `hostport-manager/portnum: "N"`
+
+      * with no `hostport-manager/hostport` yet: puts it on a work queue; the sync handler allocates N single
+        ports and writes them back as the comma list `hostport-manager/hostport` (:255-324);
+      * with the list already present (an informer re-list after a restart): marks those ports as taken
+        (handleObject :345-385);
+      * on delete: releases the ports named by the annotation (:388-418).
+
+    Differences kept deliberate: allocation is all-or-nothing (the reference leaks the ports it had taken when
+    AllocateNext fails half-way), the write-back retries on a resourceVersion conflict, and an invalid
+    annotation is reported as a Warning event instead of being logged and forgotten."""
+
+    def __init__(self, store, kind: str = "TrainingJob", start: int = 35000, end: int = 65000, recorder=None):
+        import queue
+
+        self.store, self.kind, self.recorder = store, kind, recorder
+        self.alloc = HostPortAllocator(start, end, block=1)
+        self._q: "queue.Queue" = queue.Queue()
+        self._stop = threading.Event()
+        self._thread: threading.Thread | None = None
+        self._cancel = None
+
+    # -- informer side ----------------------------------------------------------------------------
+    def _on_event(self, typ: str, obj: dict) -> None:
+        if obj.get("kind") != self.kind:
+            return
+        if typ == "DELETED":
+            self._release(obj)
+        else:
+            self._handle(obj)
+
+    @staticmethod
+    def _anno(obj: dict) -> dict:
+        return (obj.get("metadata") or {}).get("annotations") or {}
+
+    def _portnum(self, obj: dict) -> int:
+        raw = self._anno(obj).get(LEGACY_PORTNUM_ANNOTATION)
+        if raw is None:
+            return 0
+        try:
+            n = int(raw)
+        except (TypeError, ValueError):
+            n = -1
+        if n < 0:
+            self._warn(obj, "InvalidAnnotation", f"{LEGACY_PORTNUM_ANNOTATION} {raw!r} is not valid")
+            return 0
+        return n
+
+    def _handle(self, obj: dict) -> None:
+        need = self._portnum(obj)
+        if need == 0:
+            return
+        have = self._anno(obj).get(LEGACY_HOSTPORT_ANNOTATION)
+        if have is None:
+            m = obj["metadata"]
+            self._q.put((m.get("namespace", "default"), m["name"]))
+            return
+        try:
+            for p in parse_annotation(have):
+                self.alloc.mark(p)
+        except ValueError as e:
+            self._warn(obj, "InvalidAnnotation", f"{LEGACY_HOSTPORT_ANNOTATION}: {e}")
+
+    def _release(self, obj: dict) -> None:
+        try:
+            for p in parse_annotation(self._anno(obj).get(LEGACY_HOSTPORT_ANNOTATION, "")):
+                self.alloc.release(p)
+        except ValueError:
+            pass
+
+    def _warn(self, obj: dict, reason: str, msg: str) -> None:
+        if self.recorder is not None:
+            self.recorder.event(obj, "Warning", reason, msg)
+
+    # -- worker side (syncHandler) -------------------------------------------------------------------
+    def sync(self, namespace: str, name: str) -> bool:
+        """One pass of the sync handler; True when the object now carries its ports (or needs none)."""
+        from .store import Conflict, NotFound
+
+        for _ in range(10):
+            try:
+                obj = self.store.get(self.kind, namespace, name)
+            except NotFound:
+                return True  # "no longer exists": stop processing
+            need = self._portnum(obj)
+            if need == 0 or self._anno(obj).get(LEGACY_HOSTPORT_ANNOTATION) is not None:
+                return True
+            try:
+                ports = self.alloc.allocate_many(need)
+            except RuntimeError as e:
+                self._warn(obj, "PortsExhausted", str(e))
+                return False
+            obj["metadata"].setdefault("annotations", {})[LEGACY_HOSTPORT_ANNOTATION] = format_annotation(ports)
+            try:
+                self.store.update(obj)
+                return True
+            except Conflict:
+                for p in ports:
+                    self.alloc.release(p)
+            except NotFound:
+                for p in ports:
+                    self.alloc.release(p)
+                return True
+        return False
+
+    def _run(self) -> None:
+        import queue
+
+        while not self._stop.is_set():
+            try:
+                ns, name = self._q.get(timeout=0.1)
+            except queue.Empty:
+                continue
+            self.sync(ns, name)
+
+    def start(self) -> None:
+        """Lists what exists (ports already annotated are re-marked), then follows the watch."""
+        self._cancel = self.store.watch(self._on_event)
+        for obj in self.store.list(self.kind):
+            self._handle(obj)
+        self._thread = threading.Thread(target=self._run, name="hostport-manager", daemon=True)
+        self._thread.start()
+
+    def stop(self) -> None:
+        self._stop.set()
+        if self._cancel:
+            self._cancel()
+        if self._thread:
+            self._thread.join(2)
+
+    def drain(self, timeout: float = 5.0) -> None:
+        """Blocks until the work queue is empty (tests)."""
+        import time
+
+        end = time.time() + timeout
+        while time.time() < end and (not self._q.empty()):
+            time.sleep(0.01)
+        time.sleep(0.05)

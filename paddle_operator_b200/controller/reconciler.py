@@ -12,8 +12,10 @@ Deliberate differences from the reference:
     with a value and always writes);
   * per-pod counts are taken first and phase/mode/times derived from them in
     the same pass (the reference derives the phase from the previous counts);
-  * `batch=True` performs all creations/deletions of a step in one pass; the
-    default `batch=False` keeps one mutation per pass;
+  * `batch=True` performs all creations/deletions of a step in one pass, `batch=False` keeps one mutation per
+    pass as the reference does.  This class defaults to False (the reference's pacing, which the scenario tests
+    step through); `LocalCluster` - what `pdj manager` and every CLI path build - passes batch=True, so the
+    object a user gets batches (DESIGN.md section 3, row 3);
   * status.observedGeneration is set to metadata.generation (the reference
     zeroes it and then reads it for the volcano job-version annotation).
 """

@@ -50,14 +50,30 @@ constexpr int WIN_CHUNK = 28;  // WIN: output rows per work unit (3 halo input r
 // the 3-D TMA box {64 elements, 128 pixels, row n*Hi + y + jy} of a tensor map whose pixel stride is 16
 // elements - consecutive pixels' 64-element windows (4 taps x 16 channels) overlap in memory, so no
 // im2col buffer exists anywhere.  Pixels beyond Wo are zero-filled on load and clipped on store.
-template <int MODE, bool WIN>
+//
+// IM2COL (3x3 and strided convolutions): the A operand of k-block (tap, channel block) is one im2col-mode TMA load
+// (cuTensorMapEncodeIm2col) of 128 consecutive output pixels x 64 input channels of that filter tap - the TMA unit
+// walks the pixels across image rows and images and zero-fills the padding, so M tiles are dense whatever the image
+// size.  K runs over (ky, kx, c) exactly as the channels-last weight [Cout][kh][kw][Cin] is laid out.  The input
+// gradient of a stride-1 convolution is the same kernel on dY with the flipped, transposed weight.
+constexpr int SRC_ROWS = 0, SRC_WIN = 1, SRC_IM2COL = 2;
+struct ConvGeom {
+  int Q, PQ;        // output width, output pixels per image
+  int stride, pad;  // traversal stride and symmetric padding
+  int ksize;        // filter is ksize x ksize
+  int cblocks;      // Cin / 64
+};
+
+template <int MODE, int SRC>
 __global__ void __launch_bounds__(THREADS, 1)
 conv1x1_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                        const __grid_constant__ CUtensorMap tma_o, const __grid_constant__ CUtensorMap tma_c,
                        float* __restrict__ partial, int M, int N, int K, int block_n, int stages, int win_ho,
-                       int win_hi) {
+                       int win_hi, const ConvGeom geom) {
   constexpr bool STATS = MODE == MODE_STATS;
   constexpr bool ADD = MODE == MODE_ADD;
+  constexpr bool WIN = SRC == SRC_WIN;
+  constexpr bool IM2COL = SRC == SRC_IM2COL;
   static_assert(!(WIN && ADD), "the stem has no addend mode");
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
@@ -128,6 +144,27 @@ conv1x1_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_c
             mbar_expect_tx(full0 + 8 * s, A_STAGE_BYTES);
             tma_load_3d(a_smem + s * A_STAGE_BYTES, &tma_a, 0, 0, n * win_hi + y0 + r, full0 + 8 * s);
           }
+        }
+      } else if (IM2COL) {
+        const uint32_t stage_bytes = (uint32_t)A_STAGE_BYTES + b_stage_bytes;
+        uint32_t it = 0;
+        for (int t = blockIdx.x; t < total; t += gridDim.x) {
+          const int m0 = (t / tiles_n) * BM, n0 = (t % tiles_n) * block_n;
+          // first output pixel of the tile -> (image, row, column); the TMA coordinates name the input position of
+          // the top-left filter tap for that pixel
+          const int img = m0 / geom.PQ, rem = m0 % geom.PQ;
+          const int h0 = (rem / geom.Q) * geom.stride - geom.pad, w0 = (rem % geom.Q) * geom.stride - geom.pad;
+          int kb = 0;
+          for (int ky = 0; ky < geom.ksize; ++ky)
+            for (int kx = 0; kx < geom.ksize; ++kx)
+              for (int cb = 0; cb < geom.cblocks; ++cb, ++kb, ++it) {
+                const uint32_t s = it % (uint32_t)stages, ph = (it / (uint32_t)stages) & 1u;
+                mbar_wait(empty0 + 8 * s, ph ^ 1u);
+                mbar_expect_tx(full0 + 8 * s, stage_bytes);
+                tma_load_im2col_4d(a_smem + s * A_STAGE_BYTES, &tma_a, cb * BK, w0, h0, img, (uint16_t)kx, (uint16_t)ky,
+                                   full0 + 8 * s);
+                tma_load_2d(b_smem + s * b_stage_bytes, &tma_b, kb * BK, n0, full0 + 8 * s);
+              }
         }
       } else {
         producer_loop(&tma_a, &tma_b, pipe, total, tiles_n, block_n, num_kb);
@@ -520,12 +557,14 @@ int g_sms = 0;
 
 int ensure_init() {
   if (g_attr_set) return 0;
-  PDJ_CUDA_CHECK(cudaFuncSetAttribute(conv1x1_tcgen05_kernel<MODE_PLAIN, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
-  PDJ_CUDA_CHECK(cudaFuncSetAttribute(conv1x1_tcgen05_kernel<MODE_STATS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
-  PDJ_CUDA_CHECK(cudaFuncSetAttribute(conv1x1_tcgen05_kernel<MODE_ADD, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
-  PDJ_CUDA_CHECK(cudaFuncSetAttribute(conv1x1_tcgen05_kernel<MODE_PLAIN, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
-  PDJ_CUDA_CHECK(cudaFuncSetAttribute(conv1x1_tcgen05_kernel<MODE_STATS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+  PDJ_CUDA_CHECK(cudaFuncSetAttribute(conv1x1_tcgen05_kernel<MODE_PLAIN, SRC_ROWS>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+  PDJ_CUDA_CHECK(cudaFuncSetAttribute(conv1x1_tcgen05_kernel<MODE_STATS, SRC_ROWS>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+  PDJ_CUDA_CHECK(cudaFuncSetAttribute(conv1x1_tcgen05_kernel<MODE_ADD, SRC_ROWS>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+  PDJ_CUDA_CHECK(cudaFuncSetAttribute(conv1x1_tcgen05_kernel<MODE_PLAIN, SRC_WIN>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+  PDJ_CUDA_CHECK(cudaFuncSetAttribute(conv1x1_tcgen05_kernel<MODE_STATS, SRC_WIN>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
   PDJ_CUDA_CHECK(cudaFuncSetAttribute(stem_wgrad_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+  PDJ_CUDA_CHECK(cudaFuncSetAttribute(conv1x1_tcgen05_kernel<MODE_PLAIN, SRC_IM2COL>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+  PDJ_CUDA_CHECK(cudaFuncSetAttribute(conv1x1_tcgen05_kernel<MODE_STATS, SRC_IM2COL>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
   g_sms = pdj_tc_sm_count();
   g_attr_set = true;
   return 0;
@@ -603,11 +642,11 @@ static int launch_conv1x1(const void* a, const void* b, const void* addend, void
   const int smem = fixed + stages * stage_bytes;
   const int grid = conv_grid(M, N, bn, g_sms);
   if (addend != nullptr)
-    conv1x1_tcgen05_kernel<MODE_ADD, false><<<grid, THREADS, smem, st>>>(ma, mb, mo, mc, nullptr, M, N, K, bn, stages, 0, 0);
+    conv1x1_tcgen05_kernel<MODE_ADD, SRC_ROWS><<<grid, THREADS, smem, st>>>(ma, mb, mo, mc, nullptr, M, N, K, bn, stages, 0, 0, ConvGeom{});
   else if (partial != nullptr)
-    conv1x1_tcgen05_kernel<MODE_STATS, false><<<grid, THREADS, smem, st>>>(ma, mb, mo, mc, partial, M, N, K, bn, stages, 0, 0);
+    conv1x1_tcgen05_kernel<MODE_STATS, SRC_ROWS><<<grid, THREADS, smem, st>>>(ma, mb, mo, mc, partial, M, N, K, bn, stages, 0, 0, ConvGeom{});
   else
-    conv1x1_tcgen05_kernel<MODE_PLAIN, false><<<grid, THREADS, smem, st>>>(ma, mb, mo, mc, nullptr, M, N, K, bn, stages, 0, 0);
+    conv1x1_tcgen05_kernel<MODE_PLAIN, SRC_ROWS><<<grid, THREADS, smem, st>>>(ma, mb, mo, mc, nullptr, M, N, K, bn, stages, 0, 0, ConvGeom{});
   PDJ_CUDA_CHECK(cudaGetLastError());
   return 0;
 }
@@ -643,9 +682,9 @@ int pdj_stem_s2d_fwd(const void* x, const void* w, void* out, float* partial, in
   const int units = stem_units(N, Ho);
   const int grid = units < g_sms ? units : g_sms;
   if (partial != nullptr)
-    conv1x1_tcgen05_kernel<MODE_STATS, true><<<grid, THREADS, smem, st>>>(ma, mb, mo, mo, partial, rows, O, Kc, bn, stages, Ho, Hi);
+    conv1x1_tcgen05_kernel<MODE_STATS, SRC_WIN><<<grid, THREADS, smem, st>>>(ma, mb, mo, mo, partial, rows, O, Kc, bn, stages, Ho, Hi, ConvGeom{});
   else
-    conv1x1_tcgen05_kernel<MODE_PLAIN, true><<<grid, THREADS, smem, st>>>(ma, mb, mo, mo, nullptr, rows, O, Kc, bn, stages, Ho, Hi);
+    conv1x1_tcgen05_kernel<MODE_PLAIN, SRC_WIN><<<grid, THREADS, smem, st>>>(ma, mb, mo, mo, nullptr, rows, O, Kc, bn, stages, Ho, Hi, ConvGeom{});
   PDJ_CUDA_CHECK(cudaGetLastError());
   return 0;
 }
@@ -677,6 +716,47 @@ int pdj_stem_s2d_wgrad(const void* x, const void* dy, void* dw, void* ws, int N,
   stem_wgrad_tcgen05_kernel<<<grid, WG_THREADS, smem, st>>>(mx, my, (float*)ws, N, Ho, Hi, kp);
   PDJ_CUDA_CHECK(cudaGetLastError());
   stem_wgrad_reduce_kernel<<<64, 256, 0, st>>>((const float*)ws, grid, (__nv_bfloat16*)dw);
+  PDJ_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+int pdj_conv_im2col_partial_rows(int N, int H, int W, int Cout, int ksize, int pad, int stride) {
+  const int P = (H + 2 * pad - ksize) / stride + 1, Q = (W + 2 * pad - ksize) / stride + 1;
+  return pdj_conv1x1_partial_rows(N * P * Q, Cout);
+}
+
+// out[N][P][Q][Cout] = conv2d(x[N][H][W][Cin], w[Cout][k][k][Cin]) (NHWC bf16, square filter, symmetric padding,
+// P = (H + 2 pad - k) / stride + 1) as an implicit GEMM on the tcgen05 pipeline: the A operand comes from im2col-mode
+// TMA loads, nothing is materialised.  Optional BN partial sums as in pdj_conv1x1_bf16
+// (pdj_conv_im2col_partial_rows rows).  Cin % 64 == 0, Cout % 64 == 0.
+int pdj_conv_im2col_fwd(const void* x, const void* w, void* out, float* partial, int N, int H, int W, int Cin, int Cout,
+                        int ksize, int pad, int stride, cudaStream_t st) {
+  const int P = (H + 2 * pad - ksize) / stride + 1, Q = (W + 2 * pad - ksize) / stride + 1;
+  const long long Mll = (long long)N * P * Q;
+  if (N < 1 || P < 1 || Q < 1 || Cin % BK != 0 || Cout % BOX_N != 0 || ksize < 1 || ksize > 7 || stride < 1 || stride > 8 ||
+      pad < 0 || pad >= ksize || Mll >= (1ll << 31) || ((uintptr_t)x & 15) || ((uintptr_t)w & 15) || ((uintptr_t)out & 15)) {
+    pdj_set_error("pdj_conv_im2col_fwd: need Cin, Cout multiples of 64, 1 <= k <= 7, pad < k, 16-byte aligned tensors "
+                  "(N=%d H=%d W=%d Cin=%d Cout=%d k=%d pad=%d stride=%d)", N, H, W, Cin, Cout, ksize, pad, stride);
+    return -1;
+  }
+  if (int r = ensure_init()) return r;
+  const int M = (int)Mll, K = ksize * ksize * Cin;
+  const int bn = conv_block_n(M, Cout, sm_count_cached());
+  CUtensorMap ma, mb, mo;
+  if (int r = pdj_tc_make_im2col4(&ma, x, Cin, W, H, N, ksize, pad, stride, BK, BM)) return r;
+  if (int r = pdj_tc_make_map(&mb, w, Cout, K, K, BK, bn, true)) return r;
+  if (int r = pdj_tc_make_map(&mo, out, M, Cout, Cout, BOX_N, BM, true)) return r;
+  const int stage_bytes = A_STAGE_BYTES + bn * BK * 2;
+  const int fixed = 1024 + 256 + SW_STAGING_BYTES + SW_SCRATCH_BYTES;
+  int stages = (SMEM_LIMIT - fixed) / stage_bytes;
+  if (stages > MAX_STAGES) stages = MAX_STAGES;
+  const int smem = fixed + stages * stage_bytes;
+  const int grid = conv_grid(M, Cout, bn, g_sms);
+  const ConvGeom g{Q, P * Q, stride, pad, ksize, Cin / BK};
+  if (partial != nullptr)
+    conv1x1_tcgen05_kernel<MODE_STATS, SRC_IM2COL><<<grid, THREADS, smem, st>>>(ma, mb, mo, mo, partial, M, Cout, K, bn, stages, 0, 0, g);
+  else
+    conv1x1_tcgen05_kernel<MODE_PLAIN, SRC_IM2COL><<<grid, THREADS, smem, st>>>(ma, mb, mo, mo, nullptr, M, Cout, K, bn, stages, 0, 0, g);
   PDJ_CUDA_CHECK(cudaGetLastError());
   return 0;
 }

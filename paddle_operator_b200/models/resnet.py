@@ -87,8 +87,10 @@ class Bottleneck(nn.Module):
                 y, p, d, pd = conv1x1_dual(x, self.conv1.weight, self.downsample.weight, self.downsample.stride[0])
                 identity = self.bn_ds(d, partial=pd)
             y = self.bn1(y, partial=p)
-            # 3x3: weight gradient on the tcgen05 kernel of csrc/wgrad_tcgen05.cu (stride-1 layers)
-            y = self.bn2(conv3x3(y, self.conv2.weight, self.conv2.stride[0]))
+            # 3x3 on the tcgen05 kernels: im2col implicit GEMM forward (BN statistics fused) and input gradient,
+            # halo-tile weight gradient (csrc/conv_tcgen05.cu, csrc/wgrad_tcgen05.cu)
+            y, p = conv3x3(y, self.conv2.weight, self.conv2.stride[0])
+            y = self.bn2(y, partial=p)
             y, p = conv1x1_stats(y, self.conv3.weight)
             return self.bn3(y, identity, partial=p)
         y = self.bn1(self.conv1(x))

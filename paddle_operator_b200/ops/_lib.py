@@ -85,6 +85,8 @@ def _declare(lib: ctypes.CDLL) -> None:
         "pdj_stem_s2d_fwd": (c_int, [vp, vp, vp, vp, c_int, c_int, c_int, st]),
         "pdj_stem_s2d_wgrad_ws_bytes": (c_int, []),
         "pdj_stem_s2d_wgrad": (c_int, [vp, vp, vp, vp, c_int, c_int, c_int, st]),
+        "pdj_conv_im2col_partial_rows": (c_int, [c_int, c_int, c_int, c_int, c_int, c_int, c_int]),
+        "pdj_conv_im2col_fwd": (c_int, [vp, vp, vp, vp, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, st]),
         "pdj_conv3x3_wgrad_ws_bytes": (sz, [c_int, c_int, c_int, c_int, c_int]),
         "pdj_conv3x3_wgrad": (c_int, [vp, vp, vp, vp, c_int, c_int, c_int, c_int, c_int, st]),
         "pdj_bn_fwd_pre": (c_int, [vp, vp, vp, vp, c_int, c_int, vp, vp, c_float, c_float, vp, vp, vp, vp, c_int, vp, c_int, st]),

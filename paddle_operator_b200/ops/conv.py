@@ -317,35 +317,97 @@ def conv3x3_wgrad(x: torch.Tensor, dy: torch.Tensor, weight_shape) -> torch.Tens
     return dw
 
 
+def conv_im2col_eligible(x: torch.Tensor, weight: torch.Tensor) -> bool:
+    return (x.is_cuda and x.dtype == torch.bfloat16 and weight.dtype == torch.bfloat16 and x.dim() == 4
+            and weight.dim() == 4 and weight.shape[2] == weight.shape[3] and weight.shape[2] <= 7
+            and weight.shape[0] % 64 == 0 and weight.shape[1] % 64 == 0 and x.shape[1] == weight.shape[1]
+            and x.is_contiguous(memory_format=torch.channels_last)
+            and weight.is_contiguous(memory_format=torch.channels_last))
+
+
+def conv_im2col(x: torch.Tensor, weight: torch.Tensor, stride: int = 1, padding: int = 0, stats: bool = False):
+    """(y, partial) = conv2d(x, weight, stride, padding) as an implicit GEMM on the tcgen05 pipeline (im2col-mode TMA
+    loads for the A operand, csrc/conv_tcgen05.cu); `partial` are the BN partial sums of y when `stats`, else None."""
+    lib = _lib.load()
+    n, c, h, w = x.shape
+    o, k = weight.shape[0], weight.shape[2]
+    p_, q_ = (h + 2 * padding - k) // stride + 1, (w + 2 * padding - k) // stride + 1
+    y = torch.empty((n, p_, q_, o), dtype=torch.bfloat16, device=x.device).permute(0, 3, 1, 2)
+    partial = None
+    if stats:
+        rows = lib.pdj_conv_im2col_partial_rows(n, h, w, o, k, padding, stride)
+        partial = torch.empty((rows, 2, o), dtype=torch.float32, device=x.device)
+    _lib.check(lib.pdj_conv_im2col_fwd(x.data_ptr(), weight.data_ptr(), y.data_ptr(), _lib.ptr(partial), n, h, w, c, o, k,
+                                       padding, stride, torch.cuda.current_stream().cuda_stream), "conv_im2col_fwd")
+    _launches[0] += 1
+    return y, partial
+
+
+def conv3x3_fprop(x: torch.Tensor, weight: torch.Tensor, stride: int = 1, stats: bool = False):
+    y, partial = conv_im2col(x, weight, stride, 1, stats)
+    return (y, partial) if stats else y
+
+
+def flipped_transposed(weight: torch.Tensor) -> torch.Tensor:
+    """[O, I, k, k] -> the [I, O, k, k] weight whose stride-1 convolution over dY is the input gradient:
+    Wd[i, o, r, s] = W[o, i, k-1-r, k-1-s]; channels-last memory [I][k][k][O]."""
+    return weight.flip(2, 3).permute(1, 0, 2, 3).contiguous(memory_format=torch.channels_last)
+
+
+def conv3x3_dgrad(dy: torch.Tensor, weight: torch.Tensor) -> torch.Tensor:
+    """dX of y = conv2d(x, weight, padding=1) (stride 1): the same implicit GEMM over dY."""
+    return conv_im2col(dy, flipped_transposed(weight), 1, 1, False)[0]
+
+
+IM2COL_FPROP = os.environ.get("PDJ_CONV3X3_FPROP", "1") == "1"
+IM2COL_DGRAD = os.environ.get("PDJ_CONV3X3_DGRAD", "1") == "1"
+
+
 class _Conv3x3Fn(torch.autograd.Function):
-    """y = conv2d(x, weight, padding=1); the weight gradient runs on the tcgen05 kernel."""
+    """(y, partial) = conv2d(x, weight, stride, padding=1) with BN partial sums.  Forward and (stride 1) input gradient
+    on the im2col implicit GEMM, the (stride 1) weight gradient on the halo-tile kernel; what a kernel does not
+    take runs in the library."""
 
     @staticmethod
-    def forward(ctx, x, weight):
+    def forward(ctx, x, weight, stride):
         ctx.save_for_backward(x, weight)
-        return F.conv2d(x, weight, padding=1)
+        ctx.stride = stride
+        if IM2COL_FPROP and conv_im2col_eligible(x, weight):
+            y, partial = conv_im2col(x, weight, stride, 1, True)
+            ctx.mark_non_differentiable(partial)
+            return y, partial
+        return F.conv2d(x, weight, stride=stride, padding=1), None
 
     @staticmethod
-    def backward(ctx, dy):
+    def backward(ctx, dy, _dpartial):
         x, weight = ctx.saved_tensors
+        s = ctx.stride
         if not dy.is_contiguous(memory_format=torch.channels_last):
             dy = dy.contiguous(memory_format=torch.channels_last)
-        dx = dw = None
-        if ctx.needs_input_grad[0]:
-            dx, _, _ = torch.ops.aten.convolution_backward(dy, x, weight, None, [1, 1], [1, 1], [1, 1], False, [0, 0], 1,
-                                                           [True, False, False])
-        if ctx.needs_input_grad[1]:
-            dw = conv3x3_wgrad(x, dy, weight.shape)
-        return dx, dw
+        need_x, need_w = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
+        ours_x = need_x and s == 1 and IM2COL_DGRAD and weight.shape[0] % 64 == 0 and weight.shape[1] % 64 == 0
+        ours_w = (need_w and s == 1 and conv3x3_wgrad_eligible(x, weight)
+                  and min(x.shape[2], x.shape[3]) >= WGRAD3X3_MIN_HW)
+        dx = conv3x3_dgrad(dy, weight) if ours_x else None
+        dw = conv3x3_wgrad(x, dy, weight.shape) if ours_w else None
+        lib_x, lib_w = need_x and not ours_x, need_w and not ours_w
+        if lib_x or lib_w:
+            gx, gw, _ = torch.ops.aten.convolution_backward(dy, x, weight, None, [s, s], [1, 1], [1, 1], False, [0, 0], 1,
+                                                            [lib_x, lib_w, False])
+            dx = gx if lib_x else dx
+            dw = gw if lib_w else dw
+        return dx, dw, None
 
 
 WGRAD3X3_MIN_HW = int(os.environ.get("PDJ_WGRAD3X3_MIN_HW", "10"))
 
 
-def conv3x3(x: torch.Tensor, weight: torch.Tensor, stride: int = 1) -> torch.Tensor:
-    """3x3 / pad 1 convolution; stride-1 layers take the hand-written weight gradient.  Images smaller than
-    WGRAD3X3_MIN_HW pixels on a side (the 7x7 stage) stay with the library: a 49-pixel image fills 64-row blocks
-    only to 77 % and 64 (o, c) tiles leave no room for an even split (measured 85 vs 42 us at batch 256)."""
-    if stride == 1 and conv3x3_wgrad_eligible(x, weight) and min(x.shape[2], x.shape[3]) >= WGRAD3X3_MIN_HW:
-        return _Conv3x3Fn.apply(x, weight)
-    return F.conv2d(x, weight, stride=stride, padding=1)
+def conv3x3(x: torch.Tensor, weight: torch.Tensor, stride: int = 1):
+    """(y, partial) for a 3x3 / pad 1 convolution followed by BatchNorm; partial is None where the forward ran in the
+    library.  Images smaller than WGRAD3X3_MIN_HW pixels on a side (the 7x7 stage) keep the library weight gradient:
+    a 49-pixel image fills 64-row blocks only to 77 % and 64 (o, c) tiles leave no room for an even split (measured
+    85 vs 42 us at batch 256)."""
+    if (x.is_cuda and x.dtype == torch.bfloat16 and weight.dtype == torch.bfloat16 and weight.shape[2] == 3
+            and x.is_contiguous(memory_format=torch.channels_last)):
+        return _Conv3x3Fn.apply(x, weight, int(stride))
+    return F.conv2d(x, weight, stride=stride, padding=1), None

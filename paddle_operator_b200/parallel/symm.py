@@ -56,8 +56,27 @@ class FdExchange:
 
     def __init__(self, key: str, rank: int, nranks: int, timeout: float = 120.0):
         self.rank, self.nranks, self.timeout = rank, nranks, timeout
-        self.dir = os.path.join(tempfile.gettempdir(), f"pdj-{key}")
-        os.makedirs(self.dir, exist_ok=True)
+        # The directory carries the GPU-memory file descriptors of the job: it must belong to this user and be
+        # closed to everybody else.  Under the supervisor it sits next to the hosts file (PDJ_HOSTS_FILE, inside the
+        # manager's work root); otherwise under the temp dir, where a pre-created directory or a symlink planted by
+        # another local user is refused instead of followed.
+        hosts = os.environ.get("PDJ_HOSTS_FILE")
+        root = os.path.join(os.path.dirname(hosts), "fdx") if hosts else tempfile.gettempdir()
+        if hosts:
+            os.makedirs(root, mode=0o700, exist_ok=True)
+        safe = "".join(ch if (ch.isalnum() or ch in "-_.") else "_" for ch in key)
+        self.dir = os.path.join(root, f"pdj-{safe}")
+        try:
+            os.mkdir(self.dir, 0o700)
+        except FileExistsError:
+            pass
+        st = os.lstat(self.dir)
+        import stat as _stat
+
+        if _stat.S_ISLNK(st.st_mode) or not _stat.S_ISDIR(st.st_mode) or st.st_uid != os.geteuid():
+            raise PermissionError(f"{self.dir} is not a directory owned by uid {os.geteuid()}; refusing to exchange fds there")
+        if st.st_mode & 0o077:
+            os.chmod(self.dir, 0o700)
         self._round = 0
 
     def _path(self, rnd: int, rank: int) -> str:
@@ -91,7 +110,10 @@ class FdExchange:
                         src, has_fd, blen = struct.unpack("<iii", msg[:12])
                         body = msg[12:]
                         while len(body) < blen:
-                            body += conn.recv(blen - len(body))
+                            more = conn.recv(blen - len(body))
+                            if not more:
+                                raise ConnectionError(f"rank {src} closed the fd exchange after {len(body)} of {blen} bytes")
+                            body += more
                         out[src] = (fds[0] if has_fd and fds else None, bytes(body))
                         conn.sendall(b"k")
             except Exception as e:  # pragma: no cover - surfaced below

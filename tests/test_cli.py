@@ -247,3 +247,22 @@ def test_installer_renders_units_from_values(tmp_path):
     r = subprocess.run([sys.executable, os.path.join(ROOT, "deploy", "install.py"), "--dry-run", "--uninstall", "--out",
                         str(out)], capture_output=True, text=True, cwd=ROOT, timeout=60)
     assert r.returncode == 0 and not list(out.iterdir())
+
+
+def test_crd_v1beta1_variant_has_the_reference_shape(capsys):
+    """deploy/v1beta1/crd.yaml of the reference: printer columns (JSONPath), subresources and `validation` at the
+    top of the spec, `version: v1` next to the versions list."""
+    import yaml
+
+    from paddle_operator_b200 import cli
+
+    assert cli.main(["crd", "--version", "v1beta1"]) == 0
+    doc = yaml.safe_load(capsys.readouterr().out)
+    assert doc["apiVersion"] == "apiextensions.k8s.io/v1beta1"
+    spec = doc["spec"]
+    assert [c["JSONPath"] for c in spec["additionalPrinterColumns"]] == [".status.phase", ".status.mode", ".metadata.creationTimestamp"]
+    assert spec["version"] == "v1" and spec["versions"] == [{"name": "v1", "served": True, "storage": True}]
+    assert spec["subresources"] == {"status": {}} and "replicas" in str(spec["validation"]["openAPIV3Schema"])
+    assert cli.main(["crd"]) == 0
+    v1 = yaml.safe_load(capsys.readouterr().out)
+    assert v1["spec"]["versions"][0]["schema"]["openAPIV3Schema"] == spec["validation"]["openAPIV3Schema"]

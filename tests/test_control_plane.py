@@ -799,3 +799,32 @@ def test_owner_index_and_event_policy():
     st.delete("PaddleJob", "default", "j")
     assert st.list("Event", "default") == [] and st.list("Pod", "default", owner="j") == []  # collected with the job
     assert ("PaddleJob", "default", "j") not in st._by_owner
+
+
+def test_legacy_hostport_manager_runs_as_a_controller():
+    """third_party/hostport-allocator: watch -> queue -> allocate N ports -> annotate; re-mark on restart; release on delete."""
+    from paddle_operator_b200.controller.hostport import (LEGACY_HOSTPORT_ANNOTATION, LEGACY_PORTNUM_ANNOTATION,
+                                                          LegacyHostPortManager, parse_annotation)
+    from paddle_operator_b200.controller.store import ObjectStore
+
+    st = ObjectStore()
+    st.create({"kind": "TrainingJob", "metadata": {"name": "old", "annotations": {LEGACY_PORTNUM_ANNOTATION: "2",
+                                                                                   LEGACY_HOSTPORT_ANNOTATION: "35001,35002"}}})
+    mgr = LegacyHostPortManager(st, start=35000, end=35010)
+    mgr.start()
+    try:
+        assert mgr.alloc.is_allocated(35001) and mgr.alloc.is_allocated(35002)  # re-marked from the annotation
+        st.create({"kind": "TrainingJob", "metadata": {"name": "a", "annotations": {LEGACY_PORTNUM_ANNOTATION: "3"}}})
+        st.create({"kind": "TrainingJob", "metadata": {"name": "plain"}})  # no portnum: ignored
+        mgr.drain()
+        ports = parse_annotation(st.get("TrainingJob", "default", "a")["metadata"]["annotations"][LEGACY_HOSTPORT_ANNOTATION])
+        assert len(ports) == 3 and len(set(ports)) == 3 and not {35001, 35002} & set(ports)
+        assert LEGACY_HOSTPORT_ANNOTATION not in (st.get("TrainingJob", "default", "plain")["metadata"].get("annotations") or {})
+        st.delete("TrainingJob", "default", "a")
+        assert not any(mgr.alloc.is_allocated(p) for p in ports)  # released by the delete handler
+        st.create({"kind": "TrainingJob", "metadata": {"name": "big", "annotations": {LEGACY_PORTNUM_ANNOTATION: "50"}}})
+        mgr.drain()
+        assert LEGACY_HOSTPORT_ANNOTATION not in st.get("TrainingJob", "default", "big")["metadata"]["annotations"]
+        assert not mgr.alloc.is_allocated(35005)  # all-or-nothing: nothing leaked by the failed request
+    finally:
+        mgr.stop()

@@ -27,8 +27,56 @@ def test_conv3x3_wgrad_matches_fp32(hw, cin, cout, batch):
     torch.testing.assert_close(dw.float(), ref, atol=1e-2 * scale + 1e-3, rtol=2e-2)
 
 
+@pytest.mark.parametrize("hw,cin,cout,stride", [(56, 64, 64, 1), (28, 128, 128, 1), (14, 256, 256, 1), (7, 512, 512, 1),
+                                                (56, 128, 128, 2), (28, 256, 256, 2), (14, 512, 512, 2), (17, 64, 192, 1),
+                                                (15, 128, 64, 2)])
+def test_conv3x3_fprop_and_stats_match_fp32(hw, cin, cout, stride):
+    from paddle_operator_b200.ops.conv import conv_im2col
+
+    torch.manual_seed(hw + cin)
+    cl = torch.channels_last
+    x = torch.randn(5, cin, hw, hw, device="cuda").to(torch.bfloat16).contiguous(memory_format=cl)
+    w = (torch.randn(cout, cin, 3, 3, device="cuda") * 0.05).to(torch.bfloat16).contiguous(memory_format=cl)
+    y, partial = conv_im2col(x, w, stride, 1, stats=True)
+    ref = torch.nn.functional.conv2d(x.float(), w.float(), stride=stride, padding=1)
+    assert y.shape == ref.shape and y.is_contiguous(memory_format=cl)
+    torch.testing.assert_close(y.float(), ref, atol=3e-2, rtol=2e-2)
+    s = partial.sum(0)  # [2, C]: sum and sum of squares of the bf16-rounded output
+    yf = y.float()
+    torch.testing.assert_close(s[0], yf.sum((0, 2, 3)), atol=1e-2 * yf.abs().sum((0, 2, 3)).max().item() / 100 + 1e-2, rtol=1e-3)
+    torch.testing.assert_close(s[1], (yf * yf).sum((0, 2, 3)), atol=1e-2, rtol=1e-3)
+
+
+def test_strided_1x1_through_im2col():
+    """The projection shortcut of a down-sampling block: 1x1, stride 2."""
+    from paddle_operator_b200.ops.conv import conv_im2col
+
+    torch.manual_seed(9)
+    cl = torch.channels_last
+    x = torch.randn(4, 256, 28, 28, device="cuda").to(torch.bfloat16).contiguous(memory_format=cl)
+    w = (torch.randn(512, 256, 1, 1, device="cuda") * 0.05).to(torch.bfloat16).contiguous(memory_format=cl)
+    y, _ = conv_im2col(x, w, 2, 0)
+    torch.testing.assert_close(y.float(), torch.nn.functional.conv2d(x.float(), w.float(), stride=2), atol=3e-2, rtol=2e-2)
+
+
+@pytest.mark.parametrize("hw,cin,cout", [(56, 64, 64), (28, 128, 128), (14, 256, 256), (7, 512, 512), (11, 64, 128)])
+def test_conv3x3_dgrad_matches_fp32(hw, cin, cout):
+    from paddle_operator_b200.ops.conv import conv3x3_dgrad
+
+    torch.manual_seed(hw)
+    cl = torch.channels_last
+    dy = torch.randn(3, cout, hw, hw, device="cuda").to(torch.bfloat16).contiguous(memory_format=cl)
+    w = (torch.randn(cout, cin, 3, 3, device="cuda") * 0.05).to(torch.bfloat16).contiguous(memory_format=cl)
+    dx = conv3x3_dgrad(dy, w)
+    ref = torch.nn.grad.conv2d_input((3, cin, hw, hw), w.float(), dy.float(), padding=1)
+    torch.testing.assert_close(dx.float(), ref, atol=5e-2, rtol=2e-2)
+
+
 def test_conv3x3_autograd_matches_library():
-    from paddle_operator_b200.ops.conv import conv3x3
+    from paddle_operator_b200.ops.conv import conv3x3 as _conv3x3
+
+    def conv3x3(x, w):
+        return _conv3x3(x, w)[0]
 
     torch.manual_seed(5)
     cl = torch.channels_last
