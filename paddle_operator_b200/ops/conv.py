@@ -359,8 +359,13 @@ def conv3x3_dgrad(dy: torch.Tensor, weight: torch.Tensor) -> torch.Tensor:
     return conv_im2col(dy, flipped_transposed(weight), 1, 1, False)[0]
 
 
-IM2COL_FPROP = os.environ.get("PDJ_CONV3X3_FPROP", "1") == "1"
-IM2COL_DGRAD = os.environ.get("PDJ_CONV3X3_DGRAD", "1") == "1"
+# Which 3x3 layers take the im2col kernels, by input channels.  Measured at batch 256 (profiles/conv3x3_bench.py, and
+# end to end in the training step, profiles/r2/conv3x3_ab.md): the 1-CTA 128 x N tile needs ~125 B/clk/SM from L2
+# and reaches 0.85 PFLOP/s where the library's 2-CTA tiles reach 1.15, and the statistics pass it saves reads from
+# L2 at these sizes, so the step is 0.14 - 0.55 ms FASTER with the library forward.  The kernels stay available
+# (tests, PDJ_CONV3X3_FPROP_MIN_C=128 / PDJ_CONV3X3_DGRAD_MIN_C=128) and off by default until they have 2-CTA tiles.
+IM2COL_FPROP_MIN_C = int(os.environ.get("PDJ_CONV3X3_FPROP_MIN_C", "100000"))
+IM2COL_DGRAD_MIN_C = int(os.environ.get("PDJ_CONV3X3_DGRAD_MIN_C", "100000"))
 
 
 class _Conv3x3Fn(torch.autograd.Function):
@@ -372,7 +377,7 @@ class _Conv3x3Fn(torch.autograd.Function):
     def forward(ctx, x, weight, stride):
         ctx.save_for_backward(x, weight)
         ctx.stride = stride
-        if IM2COL_FPROP and conv_im2col_eligible(x, weight):
+        if weight.shape[1] >= IM2COL_FPROP_MIN_C and conv_im2col_eligible(x, weight):
             y, partial = conv_im2col(x, weight, stride, 1, True)
             ctx.mark_non_differentiable(partial)
             return y, partial
@@ -385,7 +390,8 @@ class _Conv3x3Fn(torch.autograd.Function):
         if not dy.is_contiguous(memory_format=torch.channels_last):
             dy = dy.contiguous(memory_format=torch.channels_last)
         need_x, need_w = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
-        ours_x = need_x and s == 1 and IM2COL_DGRAD and weight.shape[0] % 64 == 0 and weight.shape[1] % 64 == 0
+        ours_x = (need_x and s == 1 and weight.shape[0] >= IM2COL_DGRAD_MIN_C and weight.shape[0] % 64 == 0
+                  and weight.shape[1] % 64 == 0)
         ours_w = (need_w and s == 1 and conv3x3_wgrad_eligible(x, weight)
                   and min(x.shape[2], x.shape[3]) >= WGRAD3X3_MIN_HW)
         dx = conv3x3_dgrad(dy, weight) if ours_x else None
