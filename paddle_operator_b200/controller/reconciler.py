@@ -152,7 +152,7 @@ class PaddleJobReconciler:
     def _uses_volcano(self, pdj: PaddleJob) -> bool:
         return self.scheduling == H.SCHEDULER_NAME_VOLCANO and not H.without_volcano(pdj)
 
-    def _new_pod(self, pdj: PaddleJob, res_type: str, idx: int) -> dict:
+    def new_pod(self, pdj: PaddleJob, res_type: str, idx: int) -> dict:
         """constructPod + the decorations of createPod (:234-275)."""
         pod = H.construct_pod(pdj, res_type, idx)
         if self.init_image != "":
@@ -290,7 +290,7 @@ class PaddleJobReconciler:
             for i in range(specs[res].replicas):
                 if H.gen_paddle_res_name(name, res, i) in existing:
                     continue
-                if self._create(obj, self._new_pod(pdj, res, i)):
+                if self._create(obj, self.new_pod(pdj, res, i)):
                     created = True
                     if not self.batch:
                         return Result()

@@ -40,6 +40,8 @@ class LocalCluster:
         self.reconciler = PaddleJobReconciler(self.store, self.recorder, scheduling=scheduling, init_image=init_image,
                                               host_port_range=(start, end), etcd=etcd, batch=batch,
                                               exec_in_pod=self.supervisor.exec_in_pod if self.supervisor else None)
+        if self.supervisor is not None:
+            self.supervisor.pod_factory = self.reconciler.new_pod  # warm standbys are the reconciler's own pods
         self.gang = None
         if scheduling == "volcano":
             cap = gang_capacity

@@ -122,10 +122,25 @@ class _Rank:
     grace: float = 30.0    # terminationGracePeriodSeconds
 
 
+@dataclass
+class _Standby:
+    """A rank of an elastic job started ahead of its pod (see Supervisor._sync_standbys)."""
+    namespace: str
+    name: str          # the name the pod will have: <job>-worker-<idx>
+    job_uid: str
+    workdir: str
+    ip: str
+    gpus: list
+    proc: subprocess.Popen
+    gate: str          # file whose appearance lets the parked process register and join
+    log_path: str
+    host_network: bool = False
+
+
 class Supervisor:
     def __init__(self, store: ObjectStore, work_root: str = "/tmp/pdjob", gpus: Optional[list] = None,
                  isolate_gpus: bool = True, poll: float = 0.05, extra_env: Optional[dict] = None,
-                 backoff: float = 0.5, backoff_max: float = 10.0):
+                 backoff: float = 0.5, backoff_max: float = 10.0, warm_standby: bool = True):
         self.store = store
         self.work_root = work_root
         os.makedirs(work_root, exist_ok=True)
@@ -135,7 +150,14 @@ class Supervisor:
         self.extra_env = dict(extra_env or {})
         self.backoff, self.backoff_max = backoff, backoff_max
         self._ranks: dict[tuple, _Rank] = {}
+        # warm standbys of elastic jobs, keyed like ranks; PDJ_WARM_STANDBY=0 turns the feature off
+        self.warm_standby = warm_standby and os.environ.get("PDJ_WARM_STANDBY", "1") != "0"
+        self._standbys: dict[tuple, _Standby] = {}
+        # builds the pod the reconciler would create for (job, kind, index) - the reconciler's own constructor, wired
+        # in by LocalCluster; without it there are no standbys (the env of a parked rank must match its pod's)
+        self.pod_factory = None
         self._gpu_owner: dict[int, tuple] = {}
+        self._gpu_starved = False
         self._ip_next = 1
         self._lock = threading.RLock()
         self._stop = threading.Event()
@@ -156,7 +178,7 @@ class Supervisor:
 
     # -- plumbing -------------------------------------------------------------
     def _on_event(self, typ: str, obj: dict) -> None:
-        if obj.get("kind") in ("Pod", "ConfigMap"):
+        if obj.get("kind") in ("Pod", "ConfigMap", "PaddleJob"):
             self._wake.set()
 
     def _alloc_ip(self, host_network: bool) -> str:
@@ -206,6 +228,7 @@ class Supervisor:
     # -- reconcile local processes with the store ------------------------------------
     def sync(self) -> None:
         with self._lock:
+            self._gpu_starved = False
             pods = {(p["metadata"]["namespace"], p["metadata"]["name"]): p for p in self.store.list("Pod")}
             for key in list(self._ranks):
                 r = self._ranks[key]
@@ -237,6 +260,148 @@ class Supervisor:
                     self._sync_pod(key, pod)
                 except NotFound:
                     continue
+            if self.warm_standby or self._standbys:
+                self._sync_standbys(pods)
+
+    # -- warm standby ranks of elastic jobs --------------------------------------------------------------
+    def _sync_standbys(self, pods: dict) -> None:
+        """For every running elastic job, keeps the ranks it may still grow into (worker indices replicas ..
+        limits - 1) started and parked while GPUs are free.  A parked process has the interpreter, the CUDA
+        context and the model up and waits on its gate file without registering as a member; when `scale` makes
+        the reconciler create that pod, _sync_pod adopts the process instead of booting one.  Measured on the
+        8 -> 4 -> 8 rescale of ResNet-50: 8.8 of the 10.4 s of a scale-up were four fresh processes booting.
+        Standbys never compete with real pods: one is evicted whenever a pod finds no free GPU."""
+        from ..api.types import PaddleJob, PaddleJobPhase
+
+        want: dict[tuple, tuple] = {}   # ranks to keep parked: indices replicas .. limits - 1
+        keep: dict[tuple, str] = {}     # ranks that may stay parked: every index below limits (job uid)
+        if self.warm_standby and self.pod_factory is not None:
+            for obj in self.store.list("PaddleJob"):
+                try:
+                    pdj = PaddleJob.from_dict(obj)
+                except (ValueError, KeyError, TypeError):
+                    continue
+                w = pdj.spec.worker
+                if (pdj.spec.elastic is None or w is None or not w.limits or obj["metadata"].get("deletionTimestamp")
+                        or pdj.status.phase != PaddleJobPhase.RUNNING.value):
+                    continue
+                for idx in range(int(w.limits)):
+                    key = (pdj.namespace, H.gen_paddle_res_name(pdj.name, "worker", idx))
+                    # between `scale` raising replicas and the reconciler creating the pod, the rank is neither
+                    # wanted as a standby nor a pod yet: it must survive that window to be adopted
+                    keep[key] = pdj.metadata.uid
+                    if idx >= int(w.replicas):
+                        want[key] = (pdj, idx)
+        for key in list(self._standbys):
+            sb = self._standbys[key]
+            dead = sb.proc.poll() is not None
+            if key in pods:
+                continue  # its pod exists: _sync_pod adopts it (or has done so)
+            if dead or keep.get(key) != sb.job_uid:
+                self._drop_standby(key)
+        for key, (pdj, idx) in want.items():
+            if key in pods or key in self._standbys or key in self._ranks or self._gpu_starved:
+                continue
+            try:
+                pod = self.pod_factory(pdj, "worker", idx)  # exactly the pod the reconciler will create
+            except ValueError:
+                continue
+            need = H.gpus_requested(pod["spec"])
+            if need > len([g for g in self.gpu_pool if g not in self._gpu_owner]):
+                continue
+            self._spawn_standby(key, pdj, pod, need)
+
+    def _spawn_standby(self, key: tuple, pdj, pod: dict, need: int) -> None:
+        ns, name = key
+        c0 = pod["spec"]["containers"][0]
+        cmd = resolve_command(c0)
+        workdir = self._contained(ns, name)
+        if cmd is None or workdir is None:
+            return
+        skey = ("standby",) + key
+        gpus = self._alloc_gpus(skey, need) if need else []
+        if gpus is None:
+            return
+        shutil.rmtree(workdir, ignore_errors=True)
+        os.makedirs(workdir, exist_ok=True)
+        host_net = bool(pod["spec"].get("hostNetwork"))
+        r = _Rank(ns, name, "", workdir, self._alloc_ip(host_net), gpus or [])
+        r.log_path = os.path.join(workdir, "log.txt")
+        env = self._build_env(r, pod)
+        if env is None:
+            self._free_gpus(skey)
+            return
+        gate = os.path.join(workdir, "standby-go")
+        env["PDJ_STANDBY_GATE"] = gate
+        with open(r.log_path, "ab") as logf:
+            logf.write(f"--- standby start: {shlex.join(cmd)}\n".encode())
+            logf.flush()
+            try:
+                proc = subprocess.Popen(cmd, cwd=c0.get("workingDir") or workdir, env=env, stdout=logf,
+                                        stderr=subprocess.STDOUT, start_new_session=True)
+            except OSError:
+                self._free_gpus(skey)
+                return
+        self._standbys[key] = _Standby(ns, name, pdj.metadata.uid, workdir, r.ip, list(gpus or []), proc, gate, r.log_path, host_net)
+
+    def _drop_standby(self, key: tuple) -> None:
+        sb = self._standbys.pop(key, None)
+        if sb is None:
+            return
+        if sb.proc.poll() is None:
+            try:
+                os.killpg(sb.proc.pid, signal.SIGKILL)  # it holds no state worth a graceful exit
+            except (ProcessLookupError, PermissionError):
+                pass
+            try:
+                sb.proc.wait(2)
+            except subprocess.TimeoutExpired:
+                pass
+        self._free_gpus(("standby",) + key)
+
+    def _adopt_standby(self, key: tuple, pod: dict) -> bool:
+        """The pod of a parked rank has been created: hand the process over and open its gate."""
+        sb = self._standbys.get(key)
+        if sb is None:
+            return False
+        owner = H.controller_of(pod) or {}
+        if sb.proc.poll() is not None or (owner.get("uid") and owner.get("uid") != sb.job_uid) or \
+                H.gpus_requested(pod["spec"]) != len(sb.gpus) or bool(pod["spec"].get("hostNetwork")) != sb.host_network:
+            self._drop_standby(key)
+            return False
+        del self._standbys[key]
+        ns, name = key
+        for g in sb.gpus:
+            self._gpu_owner[g] = key
+        r = _Rank(ns, name, pod["metadata"].get("uid", ""), sb.workdir, sb.ip, list(sb.gpus))
+        r.proc, r.log_path, r.started, r.gate_open = sb.proc, sb.log_path, True, True
+        r.grace = float(pod["spec"].get("terminationGracePeriodSeconds", 30))
+        self._ranks[key] = r
+        self._write_hosts()
+        open(sb.gate, "a").close()
+        c0 = pod["spec"]["containers"][0]
+        inits = [{"name": c["name"], "ready": True, "restartCount": 0,
+                  "state": {"terminated": {"exitCode": 0, "reason": "Completed", "finishedAt": H.now_rfc3339()}}}
+                 for c in pod["spec"].get("initContainers") or []]
+        cs = [{"name": c0.get("name", "main"), "ready": True, "restartCount": 0,
+               "state": {"running": {"startedAt": H.now_rfc3339()}}, "pid": sb.proc.pid}]
+
+        def fn(st, ip=sb.ip, gpus=list(sb.gpus)):
+            st.update({"phase": "Running", "podIP": ip, "hostIP": "127.0.0.1", "containerStatuses": cs,
+                       "conditions": [{"type": "PodScheduled", "status": "True"}],
+                       "startTime": st.get("startTime") or H.now_rfc3339(), "adoptedStandby": True})
+            if gpus:
+                st["gpus"] = gpus
+            if inits:
+                st["initContainerStatuses"] = inits
+
+        self.store.patch_status("Pod", ns, name, fn)
+        return True
+
+    def standbys(self) -> list:
+        """(namespace, pod name, GPUs) of the parked ranks (`pdj` debugging, tests)."""
+        with self._lock:
+            return [(sb.namespace, sb.name, list(sb.gpus)) for sb in self._standbys.values()]
 
     def _sync_pod(self, key: tuple, pod: dict) -> None:
         ns, name = key
@@ -245,8 +410,17 @@ class Supervisor:
         if r is None:
             if phase in ("Succeeded", "Failed"):
                 return
+            if key in self._standbys and self._adopt_standby(key, pod):
+                return
             need = H.gpus_requested(pod["spec"])
             gpus = self._alloc_gpus(key, need) if need else []
+            if gpus is None:
+                self._gpu_starved = True  # no standby is (re)started in a pass in which a pod went without a GPU
+            if gpus is None and self._standbys:
+                # a real pod always beats a parked one: free a standby's GPUs and try again on the next pass
+                # (the highest worker index first: a scale-up takes the lowest missing indices)
+                self._drop_standby(max(self._standbys, key=lambda k: (H.extract_name_index(k[1])[1], k)))
+                self._wake.set()
             if gpus is None:
                 if phase != "Pending" or not (pod.get("status") or {}).get("conditions"):
                     self.store.patch_status("Pod", ns, name, lambda st: st.update({
@@ -521,4 +695,7 @@ class Supervisor:
             with self._lock:
                 for r in self._ranks.values():
                     self._kill(r, grace=1.0)
+        with self._lock:
+            for key in list(self._standbys):
+                self._drop_standby(key)
         self._cancel()

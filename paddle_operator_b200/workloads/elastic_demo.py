@@ -63,8 +63,22 @@ def _wait_progress(etcd, prefix: str, world: int, min_step: int, timeout: float,
     raise TimeoutError(f"no progress at world {world} within {timeout}s: {json.dumps(_reports(etcd, prefix))[:600]}")
 
 
+def _wait_standbys(cluster, lo: int, hi: int, timeout: float) -> float:
+    """Waits until the parked ranks of worker indices lo .. hi-1 have finished booting (their log says so);
+    returns the seconds waited."""
+    t0 = time.time()
+    want = {f"{JOB}-worker-{i}" for i in range(lo, hi)}
+    while time.time() - t0 < timeout:
+        ready = {name for ns, name, _ in cluster.supervisor.standbys()
+                 if name in want and '"event": "standby"' in cluster.supervisor.logs(ns, name)}
+        if ready == want:
+            break
+        time.sleep(0.05)
+    return round(time.time() - t0, 3)
+
+
 def run(sizes: list, steps_per_phase: int, dry: bool, batch: int, tiny: bool, gpus, work_root: str, timeout: float,
-        fail_rank: int = -1) -> dict:
+        fail_rank: int = -1, standby: bool = True) -> dict:
     ckpt_dir = os.path.join(work_root, "checkpoint")
     os.makedirs(ckpt_dir, exist_ok=True)
     total_steps = steps_per_phase * len(sizes) * 50  # the harness ends the job itself
@@ -82,6 +96,8 @@ def run(sizes: list, steps_per_phase: int, dry: bool, batch: int, tiny: bool, gp
         etcd = EtcdClient(srv.endpoint)
         cluster = LocalCluster(etcd=etcd, gpus=gpus, work_root=os.path.join(work_root, "pods"),
                                extra_env={"PDJ_ELASTIC_TTL": "3"})
+        cluster.supervisor.warm_standby = standby
+        result["warm_standby"] = standby
         prefix = f"/paddle/default-{JOB}"
         with cluster:
             t_apply = time.time()
@@ -89,6 +105,11 @@ def run(sizes: list, steps_per_phase: int, dry: bool, batch: int, tiny: bool, gp
             gen_seen = -1
             cur_step = 0
             for i, n in enumerate(sizes):
+                if i > 0 and standby and n > sizes[i - 1]:
+                    # a scale-up request that arrives while the parked ranks are still booting would measure their
+                    # boot, not the rescale: give them time (an operator scales up minutes after a scale-down)
+                    result.setdefault("standby_wait_seconds", []).append(
+                        _wait_standbys(cluster, sizes[i - 1], min(n, 8), min(timeout, 60.0)))
                 t_req = time.time()
                 if i > 0:
                     cluster.scale(JOB, n)
@@ -105,6 +126,8 @@ def run(sizes: list, steps_per_phase: int, dry: bool, batch: int, tiny: bool, gp
                         "resume_step": forms[0]["step"] if forms else None,
                         "request_to_stop_seconds": round(min(s["t"] for s in stops) - t_req, 3) if stops else None,
                         "form_seconds_max": max(f["form_seconds"] for f in forms) if forms else None,
+                        # joiners that were parked warm standbys (supervisor) rather than fresh processes
+                        "adopted_standbys": sum(1 for p in cluster.pods(JOB) if (p.get("status") or {}).get("adoptedStandby")),
                     })
                 else:
                     result["startup_seconds"] = round(t_first - t_apply, 3)
@@ -194,6 +217,7 @@ def main() -> int:
     ap.add_argument("--out", default="")
     ap.add_argument("--fail-rank", type=int, default=-1, help="fault injection instead of a rescale: rank to kill")
     ap.add_argument("--fail-step", type=int, default=25)
+    ap.add_argument("--no-standby", action="store_true", help="scale-ups boot fresh processes (the round-1 behaviour)")
     args = ap.parse_args()
     sizes = [int(x) for x in args.sizes.split(",")]
     gpus = None if not args.cpu_dry_run else list(range(max(sizes)))
@@ -203,7 +227,8 @@ def main() -> int:
             res = run_failure(sizes[0], args.fail_rank, args.fail_step, args.batch, args.tiny, gpus, work, args.timeout,
                               dry=args.cpu_dry_run)
         else:
-            res = run(sizes, args.steps_per_phase, args.cpu_dry_run, args.batch, args.tiny, gpus, work, args.timeout)
+            res = run(sizes, args.steps_per_phase, args.cpu_dry_run, args.batch, args.tiny, gpus, work, args.timeout,
+                      standby=not args.no_standby)
     except Exception:
         # post-mortem: every rank's log
         import glob

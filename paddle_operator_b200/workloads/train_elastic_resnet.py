@@ -67,8 +67,71 @@ class _DryJob:
         self.state = sd["state"]
 
 
+class _Reporter:
+    """Progress breadcrumbs leave through a queue and a thread: an HTTP put to the store must not sit in the
+    training loop."""
+
+    def __init__(self, agent):
+        import queue
+        import threading
+
+        self.agent, self.q = agent, queue.Queue()
+        self.t = threading.Thread(target=self._run, name="elastic-reporter", daemon=True)
+        self.t.start()
+
+    def _run(self):
+        while True:
+            item = self.q.get()
+            if item is None:
+                return
+            self.agent.report(*item)
+
+    def put(self, key, value):
+        self.q.put((key, value))
+
+    def flush(self, timeout: float = 5.0):
+        end = time.time() + timeout
+        while not self.q.empty() and time.time() < end:
+            time.sleep(0.005)
+
+
+class _LaggedLoss:
+    """Keeps the host at most `lag` steps ahead of the device without a per-step synchronisation: step k's loss is
+    copied to a pinned slot behind an event, and the host waits for the event of step k - lag.  The value read is
+    therefore `lag` steps old - good enough for a progress report, and the GPU never idles waiting for the host."""
+
+    def __init__(self, lag: int):
+        import torch
+
+        self.lag = lag
+        self.host = torch.zeros(lag + 1, dtype=torch.float32).pin_memory()
+        self.events = [torch.cuda.Event() for _ in range(lag + 1)]
+        self.n = 0
+        self.last = float("nan")
+
+    def push(self, loss_dev) -> float:
+        i = self.n % (self.lag + 1)
+        self.host[i:i + 1].copy_(loss_dev.reshape(1), non_blocking=True)
+        self.events[i].record()
+        self.n += 1
+        if self.n > self.lag:
+            j = (self.n - 1 - self.lag) % (self.lag + 1)
+            self.events[j].synchronize()
+            self.last = float(self.host[j])
+        return self.last
+
+    def drain(self) -> float:
+        import torch
+
+        torch.cuda.synchronize()
+        if self.n:
+            self.last = float(self.host[(self.n - 1) % (self.lag + 1)])
+        return self.last
+
+
 def main() -> int:
     ap = argparse.ArgumentParser()
+    ap.add_argument("--run-ahead", type=int, default=4, help="steps the host may queue ahead of the device")
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--batch", type=int, default=256)
     ap.add_argument("--image", type=int, default=224)
@@ -124,9 +187,25 @@ def main() -> int:
         job.trainer.use_graph = True
         torch.cuda.synchronize()
         comm = None
-    agent.report("boot_seconds", round(time.time() - t_boot, 3))
+    boot_seconds = round(time.time() - t_boot, 3)
+    # Warm standby (runtime/supervisor.py): the supervisor starts the ranks an elastic job may still grow into
+    # (limits - replicas) ahead of time with PDJ_STANDBY_GATE set.  Such a process has paid for the interpreter, the
+    # CUDA context, the model and the warm-up step above; it parks here, unregistered, until its pod is created and
+    # the supervisor opens the gate - a scale-up then costs a re-form, not a process boot.
+    gate = env.get("PDJ_STANDBY_GATE")
+    if gate:
+        print(json.dumps({"event": "standby", "boot_seconds": boot_seconds}), flush=True)
+        t_park = time.time()
+        while not os.path.exists(gate):
+            if agent.leaving:
+                return 0
+            time.sleep(0.01)
+        print(json.dumps({"event": "activated", "parked_seconds": round(time.time() - t_park, 3)}), flush=True)
+    agent.report("boot_seconds", boot_seconds)
+    agent.report("standby", bool(gate))
 
     saver = ckpt.AsyncSaver()
+    reporter = _Reporter(agent)
     m = agent.join()
     step = 0
     while True:
@@ -148,7 +227,7 @@ def main() -> int:
                 comm.close()
                 comm = None
             if m.world > 1:
-                comm = Communicator.create(m.rank, m.world, dev, 256 << 20, key=f"{job_key}-g{m.generation}")
+                comm = Communicator.create(m.rank, m.world, dev, 384 << 20, key=f"{job_key}-g{m.generation}")
             job.trainer.reform(comm)
             job.comm, job.rank, job.world = comm, m.rank, m.world
             if m.fresh and is_root:
@@ -173,6 +252,10 @@ def main() -> int:
         # ---- train inside this generation ------------------------------------------
         stop_at = None
         t0, s0 = time.time(), step
+        lagged = None if dry else _LaggedLoss(max(1, args.run_ahead))
+        # the stop step is proposed `margin` steps ahead of the proposer's host step; hosts run at most --run-ahead
+        # steps ahead of their devices and their devices are in lock-step, so no host can already be past it
+        margin = 4 if dry else 2 * max(1, args.run_ahead) + 4
         while step < args.steps:
             if args.fail_at_step == step + 1 and args.fail_rank == trainer_id and \
                     int(env.get("PDJ_RESTART_COUNT", "0")) == 0:
@@ -180,16 +263,18 @@ def main() -> int:
             if dry:
                 loss = job.step()
             else:
-                loss = float(job.step_device().item())  # one sync per step keeps host and device in lock-step
+                loss = lagged.push(job.step_device())  # no per-step sync: the host trails by --run-ahead steps
             step += 1
             if step % args.report_every == 0:
-                rate = (step - s0) * args.batch * m.world / max(1e-9, time.time() - t0)
-                agent.report("progress", {"gen": m.generation, "step": step, "world": m.world, "loss": loss,
+                # `done` = steps whose device work is known to be complete (the host may have queued more)
+                done = step if dry else max(s0, step - lagged.lag)
+                rate = (done - s0) * args.batch * m.world / max(1e-9, time.time() - t0)
+                reporter.put("progress", {"gen": m.generation, "step": step, "world": m.world, "loss": loss,
                                           "img_per_s": round(rate, 1), "t": time.time()})
             if m.rank == 0 and args.ckpt_every > 0 and step % args.ckpt_every == 0:
                 saver.save_dp(root_dir, step, m.world, {"trainer": job.state_dict() if dry else job.trainer.state_dict(),
                                                         "step": step})
-            stop_at = agent.should_stop(m, step)
+            stop_at = agent.should_stop(m, step, margin)
             if stop_at is not None:
                 if step > stop_at:
                     raise RuntimeError(f"rank passed the agreed stop step ({step} > {stop_at})")
@@ -201,11 +286,10 @@ def main() -> int:
             break
         # ---- re-form ----------------------------------------------------------------------
         t_stop = time.time()
-        agent.report(f"stopped/{m.generation}", {"step": step, "t": t_stop})
         if not dry:
-            import torch
-
-            torch.cuda.synchronize()
+            lagged.drain()
+        reporter.flush()
+        agent.report(f"stopped/{m.generation}", {"step": step, "t": t_stop})
         nm = agent.next_generation(m, step)
         if nm is None:
             print(json.dumps({"event": "leave", "gen": m.generation, "rank": m.rank, "step": step}), flush=True)
@@ -215,6 +299,9 @@ def main() -> int:
         m = nm
 
     # normal completion
+    if not dry and lagged is not None:
+        lagged.drain()
+    reporter.flush()
     saver.wait()
     if m.rank == 0:
         ckpt.save_dp(root_dir, step, m.world, {"trainer": job.state_dict() if dry else job.trainer.state_dict(),

@@ -20,6 +20,8 @@ def test_rescale_4_2_4_keeps_the_step():
     for p in res["phases"]:
         assert abs(p["loss"] - p["step"]) < 1e-6 or p["loss"] <= p["step"], p
     assert res["events"] == ["Scaled: scaled replicas to 2", "Scaled: scaled replicas to 4"]
+    # the scale-up adopted the two parked ranks the supervisor had started after the scale-down
+    assert res["rescales"][1]["adopted_standbys"] == 2, res["rescales"]
     assert res["job_phase"] in ("Running", "Starting", "Pending")
 
 

@@ -198,3 +198,42 @@ def test_assigned_gpus_are_visible_in_the_pod_status(cluster):
     with contextlib.redirect_stdout(buf):
         print_objects("pods", cluster.pods("g"), "wide")
     assert "GPUS" in buf.getvalue().splitlines()[0]
+
+
+def test_warm_standbys_hold_free_gpus_and_yield_to_real_pods(cluster):
+    """Elastic jobs get their possible extra ranks (replicas .. limits - 1) parked on free GPUs; a pod of another
+    job that finds no GPU evicts one; deleting the job removes the rest."""
+    sleeper = {"name": "m", "image": "x", "command": ["python", "-c", "import time; time.sleep(120)"],
+               "resources": {"limits": {"nvidia.com/gpu": 1}}}
+    cluster.apply({"apiVersion": "batch.paddlepaddle.org/v1", "kind": "PaddleJob", "metadata": {"name": "el"},
+                   "spec": {"elastic": 1, "worker": {"replicas": 1, "requests": 1, "limits": 4,
+                                                     "template": {"spec": {"containers": [sleeper]}}}}})
+    sup = cluster.supervisor
+    deadline = time.time() + 30
+    while time.time() < deadline and len(sup.standbys()) < 3:
+        time.sleep(0.05)
+    parked = sorted(sup.standbys())
+    assert [n for _, n, _ in parked] == ["el-worker-1", "el-worker-2", "el-worker-3"]
+    used = {g for _, _, gs in parked for g in gs} | {g for p in cluster.pods("el") for g in p["status"].get("gpus", [])}
+    assert used == {0, 1, 2, 3}  # every GPU of the box is either a rank's or a parked rank's
+    # another job needs a GPU: a standby gives way
+    cluster.apply({"apiVersion": "batch.paddlepaddle.org/v1", "kind": "PaddleJob", "metadata": {"name": "other"},
+                   "spec": {"worker": {"replicas": 1, "template": {"spec": {"containers": [sleeper]}}}}})
+    deadline = time.time() + 30
+    while time.time() < deadline and not any(p["status"].get("phase") == "Running" for p in cluster.pods("other")):
+        time.sleep(0.05)
+    assert any(p["status"].get("phase") == "Running" for p in cluster.pods("other"))
+    assert len(sup.standbys()) == 2
+    # scale-up adopts a parked rank instead of starting a process
+    cluster.scale("el", 2)
+    deadline = time.time() + 30
+    while time.time() < deadline and not any(p["status"].get("adoptedStandby") for p in cluster.pods("el")):
+        time.sleep(0.05)
+    adopted = [p for p in cluster.pods("el") if p["status"].get("adoptedStandby")]
+    assert len(adopted) == 1 and adopted[0]["status"]["phase"] == "Running"
+    cluster.delete("el")
+    cluster.wait_deleted("el", timeout=60)
+    deadline = time.time() + 10
+    while time.time() < deadline and sup.standbys():
+        time.sleep(0.05)
+    assert sup.standbys() == []
