@@ -108,6 +108,15 @@ class _LaggedLoss:
         self.events = [torch.cuda.Event() for _ in range(lag + 1)]
         self.n = 0
         self.last = float("nan")
+        self.done = 0            # steps of this generation known to have finished on the device
+        self.t_first = None      # host time at which the first of them was seen finished
+        self.t_last = None
+
+    def rate(self) -> float:
+        """Steps per second between the first and the latest step seen finished (no start-up, no queue depth)."""
+        if self.done < 2 or self.t_last is None or self.t_last <= self.t_first:
+            return 0.0
+        return (self.done - 1) / (self.t_last - self.t_first)
 
     def push(self, loss_dev) -> float:
         i = self.n % (self.lag + 1)
@@ -118,6 +127,10 @@ class _LaggedLoss:
             j = (self.n - 1 - self.lag) % (self.lag + 1)
             self.events[j].synchronize()
             self.last = float(self.host[j])
+            self.done += 1
+            self.t_last = time.time()
+            if self.t_first is None:
+                self.t_first = self.t_last
         return self.last
 
     def drain(self) -> float:
@@ -267,8 +280,10 @@ def main() -> int:
             step += 1
             if step % args.report_every == 0:
                 # `done` = steps whose device work is known to be complete (the host may have queued more)
-                done = step if dry else max(s0, step - lagged.lag)
-                rate = (done - s0) * args.batch * m.world / max(1e-9, time.time() - t0)
+                if dry:
+                    rate = (step - s0) * args.batch * m.world / max(1e-9, time.time() - t0)
+                else:
+                    rate = lagged.rate() * args.batch * m.world
                 reporter.put("progress", {"gen": m.generation, "step": step, "world": m.world, "loss": loss,
                                           "img_per_s": round(rate, 1), "t": time.time()})
             if m.rank == 0 and args.ckpt_every > 0 and step % args.ckpt_every == 0:
