@@ -66,6 +66,16 @@ int pdj_multicast_destroy(struct PdjMulticast* m);
 int pdj_barrier(const struct PdjComm* c, int emulate, cudaStream_t st);
 int pdj_allreduce_bf16(const struct PdjComm* c, size_t in_off, size_t out_off, size_t n_elems, float scale,
                        int algo, int out_f32, int nblocks, int emulate, cudaStream_t st);
+/* Gradient reduce-scatter + SGD-momentum + parameter broadcast in one kernel (K1b).  The four flat buffers - bf16
+ * gradients and parameters, fp32 masters and momentum - live in the arena at the given byte offsets; the call covers
+ * the elements [first_elem, first_elem + n_elems).  Each rank reduces its 1/N slice of every peer's gradients (P2P
+ * loads, or the switch's multimem.ld_reduce with PDJ_AR_NVLS), updates its master / momentum slice
+ * (hyper = {lr, momentum, weight_decay, grad_scale} in device memory; weight decay on elements < wd_split) and
+ * stores the new master and bf16 parameter into every rank's copy.  After it every rank holds identical
+ * parameters and masters; only the owner's momentum slice is current. */
+int pdj_allreduce_sgd(const struct PdjComm* c, size_t grad_off, size_t param_off, size_t master_off, size_t mom_off,
+                      size_t first_elem, size_t n_elems, size_t wd_split, const float* hyper, float scale, int algo,
+                      int nblocks, int emulate, cudaStream_t st);
 int pdj_alltoall(const struct PdjComm* c, size_t in_off, size_t out_off, size_t chunk_bytes, int nblocks,
                  int emulate, cudaStream_t st);
 int pdj_broadcast(const struct PdjComm* c, int root, size_t off, size_t bytes, int nblocks, int emulate,

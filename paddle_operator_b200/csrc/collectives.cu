@@ -169,6 +169,99 @@ allreduce_nvls_kernel(PdjComm c, size_t in_off, size_t out_off, size_t n_vec, fl
 }
 
 // ---------------------------------------------------------------------------
+// K1b: gradient reduce-scatter + SGD-momentum + parameter broadcast in ONE kernel per bucket.
+// The flat buffers (bf16 gradients and parameters, fp32 masters and momentum) all live in the arena at the same
+// offsets on every rank.  Rank r owns the r-th slice of the bucket: it pulls that slice of every peer's gradient
+// (or lets the switch add them: multimem.ld_reduce), applies
+//     g = sum * scale * hyper[3] + wd * w;  v = mu * v + g;  w -= lr * v
+// to its fp32 master and momentum, and pushes the new fp32 master and bf16 parameter into every rank's copy (peer
+// stores or multimem.st).  Reduced gradients never travel back and no rank runs an optimizer pass over the whole
+// model: each element is updated once, by its owner, and every rank ends up with bit-identical parameters.  Only the
+// owner's momentum slice is current (see CollectiveTrainer.sync_state for checkpoints and re-forms).
+// hyper = {lr, momentum, weight_decay, grad_scale} in device memory, as for pdj_sgd_momentum.
+template <int NR, bool NVLS>
+__global__ void __launch_bounds__(512)
+allreduce_sgd_kernel(PdjComm c, size_t grad_off, size_t param_off, size_t master_off, size_t mom_off, size_t vec0,
+                     size_t n_vec, size_t wd_split_vec, const float* __restrict__ hyper, float scale) {
+  const int rank = c.rank + blockIdx.y;
+  PdjSignalPad* me = pdj_pad(c, rank);
+  const uint32_t e = me->epoch[pdj_slot(c)];
+  pdj_block_barrier(c, rank, e + 1);  // every rank's gradients of this bucket are complete
+  const float lr = hyper[0], mu = hyper[1], wd = hyper[2], gs = hyper[3] * scale;
+  const size_t per = (n_vec + NR - 1) / NR;
+  const size_t beg = (size_t)rank * per;
+  const size_t end = beg + per < n_vec ? beg + per : n_vec;
+  char* mine = c.base[rank];
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (size_t i = beg + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < end; i += stride) {
+    const size_t g8 = vec0 + i;  // index of this group of 8 elements in the flat buffers
+    float g[8];
+    if (NVLS) {
+      uint4 u;
+      asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
+                   : "=r"(u.x), "=r"(u.y), "=r"(u.z), "=r"(u.w)
+                   : "l"(c.mc_base + grad_off + g8 * 16)
+                   : "memory");
+      const float2 a = pdj_bf2_to_f2(u.x), b = pdj_bf2_to_f2(u.y), cc = pdj_bf2_to_f2(u.z), d = pdj_bf2_to_f2(u.w);
+      g[0] = a.x; g[1] = a.y; g[2] = b.x; g[3] = b.y; g[4] = cc.x; g[5] = cc.y; g[6] = d.x; g[7] = d.y;
+    } else {
+      uint4 u[NR];
+#pragma unroll
+      for (int p = 0; p < NR; ++p) u[p] = pdj_ld16(c.base[(rank + p) % NR] + grad_off + g8 * 16);
+      // add in rank order: the sum does not depend on which rank owns the slice
+      Acc8<NR> acc;
+      acc.zero();
+#pragma unroll
+      for (int q = 0; q < NR; ++q) {
+#pragma unroll
+        for (int p = 0; p < NR; ++p)
+          if ((rank + p) % NR == q) acc.add(u[p]);
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) g[j] = acc.v[j];
+    }
+    float4* wp = reinterpret_cast<float4*>(mine + master_off + g8 * 32);
+    float4* mp = reinterpret_cast<float4*>(mine + mom_off + g8 * 32);
+    const float4 w0 = wp[0], w1 = wp[1], m0 = mp[0], m1 = mp[1];
+    float ww[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+    float mm[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
+    const float dec = g8 < wd_split_vec ? wd : 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float gj = fmaf(dec, ww[j], g[j] * gs);
+      mm[j] = fmaf(mu, mm[j], gj);
+      ww[j] = fmaf(-lr, mm[j], ww[j]);
+    }
+    mp[0] = make_float4(mm[0], mm[1], mm[2], mm[3]);
+    mp[1] = make_float4(mm[4], mm[5], mm[6], mm[7]);
+    uint4 lo, hi, pb;
+    lo.x = __float_as_uint(ww[0]); lo.y = __float_as_uint(ww[1]); lo.z = __float_as_uint(ww[2]); lo.w = __float_as_uint(ww[3]);
+    hi.x = __float_as_uint(ww[4]); hi.y = __float_as_uint(ww[5]); hi.z = __float_as_uint(ww[6]); hi.w = __float_as_uint(ww[7]);
+    pb.x = pdj_f2_to_bf2(ww[0], ww[1]); pb.y = pdj_f2_to_bf2(ww[2], ww[3]);
+    pb.z = pdj_f2_to_bf2(ww[4], ww[5]); pb.w = pdj_f2_to_bf2(ww[6], ww[7]);
+    if (NVLS) {
+      char* mc = c.mc_base;
+      asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc + master_off + g8 * 32), "r"(lo.x),
+                   "r"(lo.y), "r"(lo.z), "r"(lo.w) : "memory");
+      asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc + master_off + g8 * 32 + 16), "r"(hi.x),
+                   "r"(hi.y), "r"(hi.z), "r"(hi.w) : "memory");
+      asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc + param_off + g8 * 16), "r"(pb.x),
+                   "r"(pb.y), "r"(pb.z), "r"(pb.w) : "memory");
+    } else {
+#pragma unroll
+      for (int p = 0; p < NR; ++p) {
+        char* dst = c.base[(rank + p) % NR];
+        pdj_st16(dst + master_off + g8 * 32, lo);
+        pdj_st16(dst + master_off + g8 * 32 + 16, hi);
+        pdj_st16(dst + param_off + g8 * 16, pb);
+      }
+    }
+  }
+  pdj_block_barrier(c, rank, e + 2);  // every owner's pushes into my parameters have landed
+  if (threadIdx.x == 0) me->epoch[pdj_slot(c)] = e + 2;
+}
+
+// ---------------------------------------------------------------------------
 // K5 all-to-all: rank r's input is NR chunks of chunk_vec vectors; chunk p is
 // pushed to peer p's output slot r.
 __global__ void __launch_bounds__(512)
@@ -272,6 +365,35 @@ int pdj_allreduce_bf16(const PdjComm* c, size_t in_off, size_t out_off, size_t n
 #undef TWO
   }
   pdj_set_error("pdj_allreduce_bf16: unsupported nranks %d", nr);
+  return -1;
+}
+
+int pdj_allreduce_sgd(const PdjComm* c, size_t grad_off, size_t param_off, size_t master_off, size_t mom_off,
+                      size_t first_elem, size_t n_elems, size_t wd_split, const float* hyper, float scale, int algo,
+                      int nblocks, int emulate, cudaStream_t st) {
+  if (n_elems % 8 != 0 || first_elem % 8 != 0 || wd_split % 8 != 0 || grad_off % 16 != 0 || param_off % 16 != 0 ||
+      master_off % 16 != 0 || mom_off % 16 != 0 || hyper == nullptr) {
+    pdj_set_error("pdj_allreduce_sgd: element counts must be multiples of 8, offsets 16-byte aligned, hyper non-NULL");
+    return -1;
+  }
+  const size_t vec0 = first_elem / 8, n_vec = n_elems / 8, wdv = wd_split / 8;
+  const int nr = c->nranks;
+  if (algo == PDJ_AR_NVLS) {
+    if (c->mc_base == nullptr || emulate) {
+      pdj_set_error("pdj_allreduce_sgd: NVLS needs a multicast mapping and real ranks");
+      return -1;
+    }
+#define NV(NR) \
+  case NR: return launch_comm(allreduce_sgd_kernel<NR, true>, nblocks, 512, 0, nr, st, *c, grad_off, param_off, master_off, mom_off, vec0, n_vec, wdv, hyper, scale)
+    switch (nr) { NV(2); NV(3); NV(4); NV(5); NV(6); NV(7); NV(8); }
+#undef NV
+  } else {
+#define P2P(NR) \
+  case NR: return launch_comm(allreduce_sgd_kernel<NR, false>, nblocks, 512, emulate, nr, st, *c, grad_off, param_off, master_off, mom_off, vec0, n_vec, wdv, hyper, scale)
+    switch (nr) { P2P(1); P2P(2); P2P(3); P2P(4); P2P(5); P2P(6); P2P(7); P2P(8); }
+#undef P2P
+  }
+  pdj_set_error("pdj_allreduce_sgd: unsupported nranks %d", nr);
   return -1;
 }
 

@@ -70,6 +70,7 @@ def _declare(lib: ctypes.CDLL) -> None:
         "pdj_multicast_destroy": (c_int, [vp]),
         "pdj_barrier": (c_int, [POINTER(PdjComm), c_int, st]),
         "pdj_allreduce_bf16": (c_int, [POINTER(PdjComm), sz, sz, sz, c_float, c_int, c_int, c_int, c_int, st]),
+        "pdj_allreduce_sgd": (c_int, [POINTER(PdjComm), sz, sz, sz, sz, sz, sz, sz, vp, c_float, c_int, c_int, c_int, st]),
         "pdj_alltoall": (c_int, [POINTER(PdjComm), sz, sz, sz, c_int, c_int, st]),
         "pdj_broadcast": (c_int, [POINTER(PdjComm), c_int, sz, sz, c_int, c_int, st]),
         "pdj_emb_lookup": (c_int, [POINTER(PdjComm), POINTER(PdjEmbTable), sz, sz, sz, c_int, c_int, c_int, c_int, c_int, st]),

@@ -22,7 +22,7 @@ import torch
 
 from ..ops import optim as pdj_optim
 from ..utils import trace
-from .symm import AR_ONESHOT, AR_TWOSHOT, Communicator
+from .symm import Communicator
 
 
 def _round_up(n: int, m: int) -> int:
@@ -59,16 +59,8 @@ class FlatParams:
         self.numel = _round_up(cur, 8 * 8)  # whole 16-byte vectors per rank for up to 8 ranks
         self.comm = comm
         self.device = device
-        self.param = torch.zeros(self.numel, dtype=torch.bfloat16, device=device)
-        self.master = torch.zeros(self.numel, dtype=torch.float32, device=device)
-        self.momentum = torch.zeros(self.numel, dtype=torch.float32, device=device)
-        if comm is not None:
-            self.grad_off = comm.alloc(self.numel * 2)
-            self.grad = comm.tensor(self.grad_off, (self.numel,), torch.bfloat16)
-        else:
-            self.grad_off = 0
-            self.grad = torch.zeros(self.numel, dtype=torch.bfloat16, device=device)
-        self.grad.zero_()
+        self._order, self._offs = order, offs
+        self._allocate(comm)
         self.buckets: list[_Bucket] = []
         self.views: dict[int, tuple[torch.Tensor, torch.Tensor, torch.Tensor]] = {}
         cap = max(bucket_bytes // 2, 8)
@@ -95,6 +87,45 @@ class FlatParams:
         # masters were filled from the (bf16 or fp32) init values; make param == bf16(master)
         self.param.copy_(self.master.to(torch.bfloat16))
         self.bucket_of = {id(p): b for b in self.buckets for p in b.params}
+
+    def _allocate(self, comm: Optional[Communicator]) -> None:
+        """The four flat buffers.  With a communicator they ALL live in the symmetric arena, at offsets that are the
+        same on every rank: the fused bucket kernel (csrc/collectives.cu, K1b) reads peers' gradients and writes
+        peers' parameters and masters directly."""
+        n = self.numel
+        if comm is not None:
+            self.param_off, self.grad_off = comm.alloc(n * 2), comm.alloc(n * 2)
+            self.master_off, self.mom_off = comm.alloc(n * 4), comm.alloc(n * 4)
+            self.param = comm.tensor(self.param_off, (n,), torch.bfloat16)
+            self.grad = comm.tensor(self.grad_off, (n,), torch.bfloat16)
+            self.master = comm.tensor(self.master_off, (n,), torch.float32)
+            self.momentum = comm.tensor(self.mom_off, (n,), torch.float32)
+            for t in (self.param, self.grad, self.master, self.momentum):
+                t.zero_()
+        else:
+            self.param_off = self.grad_off = self.master_off = self.mom_off = 0
+            self.param = torch.zeros(n, dtype=torch.bfloat16, device=self.device)
+            self.grad = torch.zeros(n, dtype=torch.bfloat16, device=self.device)
+            self.master = torch.zeros(n, dtype=torch.float32, device=self.device)
+            self.momentum = torch.zeros(n, dtype=torch.float32, device=self.device)
+
+    def rehome(self, comm: Optional[Communicator]) -> None:
+        """Moves the buffers into `comm`'s arena (or into private memory for comm = None), keeping their contents,
+        and re-points the parameters and the per-parameter views.  The old communicator must still be open."""
+        old = (self.param, self.master, self.momentum)
+        self.comm = comm
+        self._allocate(comm)
+        with torch.no_grad():
+            self.param.copy_(old[0])
+            self.master.copy_(old[1])
+            self.momentum.copy_(old[2])
+        for b in self.buckets:
+            b.gviews = []
+        for p, off in zip(self._order, self._offs):
+            pv, gv = self._view(self.param, off, p), self._view(self.grad, off, p)
+            p.data = pv
+            self.views[id(p)] = (pv, gv, self.master[off:off + p.numel()])
+            self.bucket_of[id(p)].gviews.append(gv)
 
     @staticmethod
     def _view(flat: torch.Tensor, off: int, p: torch.Tensor) -> torch.Tensor:
@@ -138,6 +169,7 @@ class CollectiveTrainer:
         self.extra_kernels_per_step = extra_kernels_per_step  # the job's own kernels outside modules (loss, embedding)
         self._count = 0
         self.comm_stream = torch.cuda.Stream(self.device) if self.comm is not None else None
+        self.on_rehome: list = []  # callbacks of the job that re-attach views of the flat buffers after a re-form
         self._attach_masters()
         self._install_hooks()
 
@@ -177,13 +209,13 @@ class CollectiveTrainer:
         ev.record(main)
         self.comm_stream.wait_event(ev)
         n = b.end - b.start
-        off = self.flat.grad_off + b.start * 2
-        algo = self.algo if self.algo is not None else self.comm.pick_algo(n * 2)
-        if algo == AR_ONESHOT:
-            algo = AR_TWOSHOT  # in-place
-        with trace.span("bucket_allreduce", bytes=n * 2, algo=int(algo)):
-            self.comm.all_reduce_bf16(off, off, n, scale=1.0 / self.world, algo=algo, nblocks=self.comm_blocks,
-                                      stream=self.comm_stream)
+        f = self.flat
+        # one kernel per bucket: reduce-scatter + SGD-momentum on the owner's slice + broadcast of the new master and
+        # parameter (K1b).  Reduced gradients never come back and nobody runs an optimizer pass over the whole model.
+        with trace.span("bucket_allreduce_sgd", bytes=n * 2):
+            self.comm.allreduce_sgd(f.grad_off, f.param_off, f.master_off, f.mom_off, b.start, n, f.numel,
+                                    self.hyper.data_ptr(), 1.0 / self.world, algo=self.algo, nblocks=self.comm_blocks,
+                                    stream=self.comm_stream)
         self._count += 1
         done = torch.cuda.Event()
         done.record(self.comm_stream)
@@ -205,9 +237,11 @@ class CollectiveTrainer:
                 raise RuntimeError("a parameter received no gradient; every parameter must take part in the step")
             if b.event is not None:
                 main.wait_event(b.event)
-        pdj_optim.sgd_momentum_(self.flat.master, self.flat.momentum, self.flat.grad, self.flat.param, self.hyper,
-                                self.flat.numel)
-        self._count += 1
+        if self.comm is None:
+            pdj_optim.sgd_momentum_(self.flat.master, self.flat.momentum, self.flat.grad, self.flat.param, self.hyper,
+                                    self.flat.numel)
+            self._count += 1
+        # (with a communicator the update already happened, bucket by bucket, inside the fused collective)
         self._count += _conv.launch_count() - conv0  # tcgen05 convolution kernels launched by the model this step
         self.loss.copy_(loss.detach().float())
 
@@ -263,32 +297,19 @@ class CollectiveTrainer:
 
     # -- elastic re-form -----------------------------------------------------------
     def reform(self, comm: Optional[Communicator]) -> None:
-        """Switches to a new communicator (new world size) without touching the
-        parameters, masters, momentum or BN statistics, which stay where they are
-        in HBM.  Only the gradient buffer moves (it lives in the arena) and the
-        step graph is captured again for the new pointers."""
+        """Switches to a new communicator (new world size).  The flat buffers live in the arena, so they are copied
+        device-to-device into the new one (the OLD communicator must still be open: create the new one, call this,
+        then close the old one); BN statistics stay where they are.  The step graph is captured again for the new
+        pointers.  Call sync_state() on every rank of the old group first: momentum is only current on its owner."""
         torch.cuda.synchronize(self.device)
         self.graph = None
         self.comm = comm if (comm is not None and comm.nranks > 1) else None
         self.world = comm.nranks if comm is not None else 1
         self.comm_stream = torch.cuda.Stream(self.device) if self.comm is not None else None
-        flat = self.flat
-        flat.comm = self.comm
-        if self.comm is not None:
-            flat.grad_off = self.comm.alloc(flat.numel * 2)
-            flat.grad = self.comm.tensor(flat.grad_off, (flat.numel,), torch.bfloat16)
-        else:
-            flat.grad_off = 0
-            flat.grad = torch.zeros(flat.numel, dtype=torch.bfloat16, device=self.device)
-        flat.grad.zero_()
-        for b in flat.buckets:
-            b.gviews = []
-            for p in b.params:
-                pv, _, mv = flat.views[id(p)]
-                off = (pv.data_ptr() - flat.param.data_ptr()) // 2
-                gv = flat._view(flat.grad, off, p)
-                flat.views[id(p)] = (pv, gv, mv)
-                b.gviews.append(gv)
+        self.flat.rehome(self.comm)
+        self._attach_masters()
+        for fn in self.on_rehome:
+            fn()
         if self.use_graph:
             self.capture(warmup=0)
 
@@ -296,14 +317,20 @@ class CollectiveTrainer:
         """K6: every rank ends up with the root's masters, momentum, hyper-parameters and
         model buffers, moved GPU-to-GPU through the arena (no disk, no host).
 
-        The tensors are packed back to back into one staging window of the arena - as large as the arena still
-        allows (up to the whole state), 16-byte aligned segments - so the ~110 tensors of a ResNet-50 (two 100 MB
-        flat buffers and a hundred BatchNorm statistics) travel in one or two broadcast launches instead of one
-        launch and one barrier per 32 MiB piece or per small tensor."""
+        The two 100 MB flat buffers already live in the arena and are pulled from the root in place (one launch
+        each).  The small tensors (hyper-parameters and a hundred BatchNorm statistics for a ResNet-50) are packed
+        back to back, in 16-byte aligned segments, into one staging window of the arena and travel in one launch
+        instead of one launch and one barrier each.  Call sync_state() on the old group first: the root must hold
+        every rank's momentum slice."""
         if self.comm is None:
             return
         comm = self.comm
-        tensors = [self.flat.master, self.flat.momentum, self.hyper] + [b for _, b in self.model.named_buffers()]
+        # masters and momentum sit in the arena at the same offset on every rank: pulled from the root in place
+        nbytes = self.flat.numel * 4
+        comm.broadcast(root, self.flat.master_off, nbytes)
+        comm.broadcast(root, self.flat.mom_off, nbytes)
+        # the rest (hyper-parameters, BatchNorm statistics: ~100 small tensors) is packed into one staging window
+        tensors = [self.hyper] + [b for _, b in self.model.named_buffers()]
         flats = []
         for t in tensors:
             f = t.detach().reshape(-1) if t.is_contiguous() else t.detach().contiguous().reshape(-1)
@@ -349,6 +376,22 @@ class CollectiveTrainer:
         with torch.no_grad():
             self.flat.param.copy_(self.flat.master.to(torch.bfloat16))
         torch.cuda.synchronize(self.device)
+
+    def sync_state(self) -> None:
+        """Collective (every rank, same point of the step sequence): makes the momentum buffer complete on every
+        rank.  Inside the fused bucket kernel each element's momentum is kept by the rank that owns its slice
+        only; before a checkpoint, a re-form or a state broadcast the owners' slices are pulled together
+        (K6 per slice).  Masters and parameters are always complete everywhere."""
+        if self.comm is None:
+            return
+        comm, f, nr = self.comm, self.flat, self.world
+        for b in f.buckets:
+            n_vec = (b.end - b.start) // 8
+            per = (n_vec + nr - 1) // nr
+            for r in range(nr):
+                beg, end = r * per, min((r + 1) * per, n_vec)
+                if end > beg:
+                    comm.broadcast(r, f.mom_off + (b.start + beg * 8) * 4, (end - beg) * 32, nblocks=16)
 
     # -- state (checkpoint / elastic re-shard) -------------------------------------
     def state_dict(self) -> dict:

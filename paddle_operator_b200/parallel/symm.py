@@ -356,6 +356,17 @@ class Communicator:
                                           int(out_f32), nblocks, int(self.emulate), self._stream(stream)),
               "allreduce_bf16")
 
+    def allreduce_sgd(self, grad_off: int, param_off: int, master_off: int, mom_off: int, first_elem: int, n_elems: int,
+                      wd_split: int, hyper_ptr: int, scale: float, algo: Optional[int] = None, nblocks: int = 32,
+                      stream=None) -> None:
+        """K1b: reduce-scatter of the gradients + SGD-momentum on the owner's slice + broadcast of the new master and
+        bf16 parameter, one kernel (csrc/collectives.cu::allreduce_sgd_kernel)."""
+        if algo is None or algo == AR_ONESHOT:
+            algo = AR_NVLS if (self.has_multicast and not self.emulate and self.nranks >= 4) else AR_TWOSHOT
+        check(self.lib.pdj_allreduce_sgd(ctypes.byref(self._comm), grad_off, param_off, master_off, mom_off, first_elem,
+                                         n_elems, wd_split, ctypes.c_void_p(hyper_ptr), scale, algo, nblocks,
+                                         int(self.emulate), self._stream(stream)), "allreduce_sgd")
+
     def all_to_all(self, in_off: int, out_off: int, chunk_bytes: int, nblocks: int = 32, stream=None) -> None:
         check(self.lib.pdj_alltoall(ctypes.byref(self._comm), in_off, out_off, chunk_bytes, nblocks,
                                     int(self.emulate), self._stream(stream)), "alltoall")

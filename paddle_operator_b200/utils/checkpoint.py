@@ -48,39 +48,74 @@ def save_dp(root: str, step: int, world: int, state: dict, rank: int = 0) -> Non
 
 
 class AsyncSaver:
-    """Checkpoints without stalling the training loop: tensors are snapshotted to host memory
-    on the caller's thread (one device-to-host copy), the file is written by a background thread.
-    At most one save is in flight; a save requested while another runs is skipped (the next
-    interval will catch up), which keeps "overwrite the previous save" semantics."""
+    """Checkpoints without stalling the training loop.  The caller's thread only enqueues a device-side
+    snapshot of the tensors on its current stream (a copy at HBM speed) and an event; a background thread waits
+    for the event, brings the snapshot to the host on its own stream and writes the file.  The training stream
+    never waits for a device-to-host copy.  At most one save is in flight; a save requested while another runs is
+    skipped (the next interval will catch up), which keeps "overwrite the previous save" semantics."""
 
     def __init__(self):
         import threading
 
         self._thread = None
         self._lock = threading.Lock()
+        self._stream = None
 
     @staticmethod
-    def _to_host(obj):
+    def _map(obj, fn):
         import torch
 
         if torch.is_tensor(obj):
-            return obj.detach().to("cpu", copy=True)
+            return fn(obj)
         if isinstance(obj, dict):
-            return {k: AsyncSaver._to_host(v) for k, v in obj.items()}
+            return {k: AsyncSaver._map(v, fn) for k, v in obj.items()}
         if isinstance(obj, (list, tuple)):
-            return type(obj)(AsyncSaver._to_host(v) for v in obj)
+            return type(obj)(AsyncSaver._map(v, fn) for v in obj)
         return obj
+
+    @staticmethod
+    def _to_host(obj):
+        return AsyncSaver._map(obj, lambda t: t.detach().to("cpu", copy=True))
+
+    def _finish(self, root, step, world, snap, event, device) -> None:
+        import torch
+
+        if event is not None:
+            torch.cuda.set_device(device)
+            if self._stream is None:
+                self._stream = torch.cuda.Stream(device)
+            with torch.cuda.stream(self._stream):
+                self._stream.wait_event(event)
+                host = self._map(snap, lambda t: t.to("cpu", non_blocking=False) if t.is_cuda else t)
+            snap = host
+        save_dp(root, step, world, snap, 0)
 
     def save_dp(self, root: str, step: int, world: int, state: dict, rank: int = 0) -> bool:
         import threading
+
+        import torch
 
         if rank != 0:
             return False
         with self._lock:
             if self._thread is not None and self._thread.is_alive():
                 return False
-            snap = self._to_host(state)
-            self._thread = threading.Thread(target=save_dp, args=(root, step, world, snap, 0), daemon=True)
+            event, device = None, None
+            cuda = [False]
+
+            def snap_one(t):
+                if t.is_cuda:
+                    cuda[0] = True
+                    return t.detach().clone()  # device-side snapshot, stream-ordered after the step that produced it
+                return t.detach().clone()
+
+            snap = self._map(state, snap_one)
+            if cuda[0]:
+                device = torch.cuda.current_device()
+                event = torch.cuda.Event()
+                event.record()
+            self._thread = threading.Thread(target=self._finish, args=(root, step, world, snap, event, device),
+                                            daemon=True)
             self._thread.start()
             return True
 

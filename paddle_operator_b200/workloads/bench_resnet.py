@@ -34,7 +34,7 @@ def _build_product(args, world, dev):
     from ..parallel.symm import AR_NVLS, AR_TWOSHOT, Communicator
     from .resnet import ResNetJob
 
-    comm = Communicator.from_env(arena_bytes=256 << 20, key=job_key("resnet")) if world > 1 else None
+    comm = Communicator.from_env(arena_bytes=384 << 20, key=job_key("resnet")) if world > 1 else None
     algo = {"auto": None, "twoshot": AR_TWOSHOT, "nvls": AR_NVLS}[args.algo]
     job = ResNetJob(batch=args.batch or 256, comm=comm, device=dev, use_graph=not args.no_graph,
                     bucket_bytes=int(args.bucket_mb * (1 << 20)), comm_blocks=args.comm_blocks, algo=algo)

@@ -76,7 +76,7 @@ class ResNetJob:
         self.step_count = 0
 
     @classmethod
-    def from_env(cls, arena_bytes: int = 256 << 20, **kw) -> "ResNetJob":
+    def from_env(cls, arena_bytes: int = 384 << 20, **kw) -> "ResNetJob":
         world = int(os.environ.get("WORLD_SIZE", os.environ.get("PADDLE_TRAINERS_NUM", "1")))
         comm = Communicator.from_env(arena_bytes) if world > 1 else None
         return cls(comm=comm, **kw)

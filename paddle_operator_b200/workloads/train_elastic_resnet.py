@@ -236,12 +236,14 @@ def main() -> int:
         else:
             import torch
 
-            if comm is not None:
-                comm.close()
-                comm = None
+            # the flat buffers live in the arena: open the new group first, move them over, then close the old one
+            old_comm = comm
+            comm = None
             if m.world > 1:
-                comm = Communicator.create(m.rank, m.world, dev, 384 << 20, key=f"{job_key}-g{m.generation}")
+                comm = Communicator.create(m.rank, m.world, dev, 448 << 20, key=f"{job_key}-g{m.generation}")
             job.trainer.reform(comm)
+            if old_comm is not None:
+                old_comm.close()
             job.comm, job.rank, job.world = comm, m.rank, m.world
             if m.fresh and is_root:
                 sd = ckpt.load_dp(root_dir, map_location=device)
@@ -286,6 +288,8 @@ def main() -> int:
                     rate = lagged.rate() * args.batch * m.world
                 reporter.put("progress", {"gen": m.generation, "step": step, "world": m.world, "loss": loss,
                                           "img_per_s": round(rate, 1), "t": time.time()})
+            if not dry and args.ckpt_every > 0 and step % args.ckpt_every == 0:
+                job.trainer.sync_state()  # collective: momentum is kept by slice owners between checkpoints
             if m.rank == 0 and args.ckpt_every > 0 and step % args.ckpt_every == 0:
                 saver.save_dp(root_dir, step, m.world, {"trainer": job.state_dict() if dry else job.trainer.state_dict(),
                                                         "step": step})
@@ -302,6 +306,7 @@ def main() -> int:
         # ---- re-form ----------------------------------------------------------------------
         t_stop = time.time()
         if not dry:
+            job.trainer.sync_state()  # every member of the old group holds the full momentum before it re-forms
             lagged.drain()
         reporter.flush()
         agent.report(f"stopped/{m.generation}", {"step": step, "t": t_stop})
@@ -318,6 +323,11 @@ def main() -> int:
         lagged.drain()
     reporter.flush()
     saver.wait()
+    if not dry:
+        job.trainer.sync_state()
+        import torch
+
+        torch.cuda.synchronize()
     if m.rank == 0:
         ckpt.save_dp(root_dir, step, m.world, {"trainer": job.state_dict() if dry else job.trainer.state_dict(),
                                                "step": step})

@@ -34,7 +34,7 @@ def main() -> int:
     world = int(env.get("WORLD_SIZE", env.get("PADDLE_TRAINERS_NUM", "1")))
     dev = int(env.get("LOCAL_RANK", env.get("PDJ_LOCAL_DEVICE", "0")))
     torch.cuda.set_device(dev)
-    comm = Communicator.from_env(256 << 20) if world > 1 else None
+    comm = Communicator.from_env(384 << 20) if world > 1 else None
     job = ResNetJob(batch=args.batch, image=args.image, comm=comm, device=torch.device("cuda", dev), lr=args.lr,
                     tiny=args.tiny, num_classes=16 if args.tiny else 1000)
     job.prepare()

@@ -81,6 +81,7 @@ class WideDeepJob:
                                          # embedding kernels + per hidden layer: forward GEMM, dX GEMM, bias colsum
                                          extra_kernels_per_step=(3 if async_sgd else 4) + 3 * len(dense.layers) + 2)  # + fused head / loss, its dz
         self._attach_bias_masters()
+        self.trainer.on_rehome.append(self._attach_bias_masters)
         self._copy_stream = torch.cuda.Stream(self.device)
         self._stage = [(torch.empty_like(self.ids), torch.empty_like(self.dense_x), torch.empty_like(self.labels))
                        for _ in range(2)]

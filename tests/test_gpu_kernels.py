@@ -181,6 +181,54 @@ def test_allreduce_twoshot_inplace(comms, nranks, n):
             assert torch.equal(g0, comm.tensor(off, (n,), torch.bfloat16, rank=r))
 
 
+@pytest.mark.parametrize("nranks", [2, 4, 8])
+def test_allreduce_sgd_fused_matches_reduce_then_sgd(comms, nranks):
+    """K1b: reduce-scatter + SGD-momentum + master / parameter broadcast in one kernel, on a sub-range (a bucket)
+    of the flat buffers, against all-reduce followed by the plain update; two steps in a row."""
+    comm = comms(nranks)
+    comm.reset_allocations()
+    n, first, cnt = 8 * 2000, 8 * 300, 8 * 1203  # bucket = [first, first + cnt)
+    g_off, p_off = comm.alloc(n * 2), comm.alloc(n * 2)
+    m_off, v_off = comm.alloc(n * 4), comm.alloc(n * 4)
+    dev = comm.tensor(g_off, (1,), torch.bfloat16).device
+    hyper = torch.tensor([0.1, 0.9, 1e-2, 1.0], device=dev)
+    torch.manual_seed(1)
+    w0 = torch.randn(n, device=dev)
+    for r in range(nranks):
+        comm.tensor(m_off, (n,), torch.float32, rank=r).copy_(w0)
+        comm.tensor(v_off, (n,), torch.float32, rank=r).zero_()
+        comm.tensor(p_off, (n,), torch.bfloat16, rank=r).copy_(w0.to(torch.bfloat16))
+    w_ref, v_ref = w0.clone(), torch.zeros(n, device=dev)
+    wd_split = first + 8 * 600  # decay on the first part of the bucket only
+    for it in range(2):
+        grads = _fill(comm, g_off, n, seed=10 + it)
+        gsum = torch.stack([g.float() for g in grads]).sum(0) / nranks
+        sl = slice(first, first + cnt)
+        dec = torch.zeros(n, device=dev)
+        dec[:wd_split] = 1e-2
+        gj = dec[sl] * w_ref[sl] + gsum[sl]
+        v_ref[sl] = 0.9 * v_ref[sl] + gj
+        w_ref[sl] = w_ref[sl] - 0.1 * v_ref[sl]
+        comm.allreduce_sgd(g_off, p_off, m_off, v_off, first, cnt, wd_split, hyper.data_ptr(), 1.0 / nranks, nblocks=6)
+        torch.cuda.synchronize()
+        for r in range(nranks):
+            m = comm.tensor(m_off, (n,), torch.float32, rank=r)
+            torch.testing.assert_close(m, w_ref, atol=1e-5, rtol=1e-5)
+            assert torch.equal(comm.tensor(p_off, (n,), torch.bfloat16, rank=r), m.to(torch.bfloat16))
+        # masters and parameters are bit-identical on every rank; untouched elements stayed untouched
+        m0 = comm.tensor(m_off, (n,), torch.float32, rank=0)
+        for r in range(1, nranks):
+            assert torch.equal(m0, comm.tensor(m_off, (n,), torch.float32, rank=r))
+        assert torch.equal(m0[:first], w0[:first]) and torch.equal(m0[first + cnt:], w0[first + cnt:])
+        # momentum: every element's owner holds the reference value
+        per = (cnt // 8 + nranks - 1) // nranks * 8
+        for r in range(nranks):
+            a, b = first + r * per, min(first + (r + 1) * per, first + cnt)
+            if b > a:
+                torch.testing.assert_close(comm.tensor(v_off, (n,), torch.float32, rank=r)[a:b], v_ref[a:b], atol=1e-5, rtol=1e-5)
+    assert comm.error_flags() == [0] * comm.nranks
+
+
 @pytest.mark.parametrize("nranks", [2, 8])
 def test_allreduce_oneshot_and_f32(comms, nranks):
     from paddle_operator_b200.parallel.symm import AR_ONESHOT, AR_TWOSHOT
