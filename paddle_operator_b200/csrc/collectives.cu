@@ -274,9 +274,26 @@ alltoall_kernel(PdjComm c, size_t in_off, size_t out_off, size_t chunk_vec) {
   const char* in = c.base[rank] + in_off;
   const size_t stride = (size_t)gridDim.x * blockDim.x;
   const size_t total = chunk_vec * NR;
-  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
-    // Walk peers in a rotated order so that at any instant the N ranks target N
-    // different destinations.
+  // Four 16-byte vectors per thread per trip, all loads issued before the first store: the local loads overlap and
+  // four peer stores leave back to back (one vector per trip needed 148 blocks to cover the NVLink latency).
+  // Peers are walked in a rotated order so that at any instant the N ranks target N different destinations.
+  constexpr int U = 4;
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  for (; i + (U - 1) * stride < total; i += U * stride) {
+    uint4 v[U];
+    char* dst[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const size_t j = i + u * stride;
+      const size_t within = j % chunk_vec;
+      const int p = (int)((j / chunk_vec + rank) % NR);
+      v[u] = pdj_ld16(in + ((size_t)p * chunk_vec + within) * 16);
+      dst[u] = c.base[p] + out_off + ((size_t)rank * chunk_vec + within) * 16;
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) pdj_st16(dst[u], v[u]);
+  }
+  for (; i < total; i += stride) {
     const size_t within = i % chunk_vec;
     const int p = (int)((i / chunk_vec + rank) % NR);
     const uint4 v = pdj_ld16(in + ((size_t)p * chunk_vec + within) * 16);
@@ -298,8 +315,16 @@ broadcast_kernel(PdjComm c, int root, size_t off, size_t n_vec) {
     const char* src = c.base[root] + off;
     char* dst = c.base[rank] + off;
     const size_t stride = (size_t)gridDim.x * blockDim.x;
-    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_vec; i += stride)
-      pdj_st16(dst + i * 16, pdj_ld16(src + i * 16));
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    for (; i + 3 * stride < n_vec; i += 4 * stride) {  // four peer loads in flight per thread
+      const uint4 a = pdj_ld16(src + i * 16), b = pdj_ld16(src + (i + stride) * 16);
+      const uint4 cc = pdj_ld16(src + (i + 2 * stride) * 16), d = pdj_ld16(src + (i + 3 * stride) * 16);
+      pdj_st16(dst + i * 16, a);
+      pdj_st16(dst + (i + stride) * 16, b);
+      pdj_st16(dst + (i + 2 * stride) * 16, cc);
+      pdj_st16(dst + (i + 3 * stride) * 16, d);
+    }
+    for (; i < n_vec; i += stride) pdj_st16(dst + i * 16, pdj_ld16(src + i * 16));
   }
   pdj_block_barrier(c, rank, e + 2);
   if (threadIdx.x == 0) me->epoch[pdj_slot(c)] = e + 2;

@@ -333,25 +333,39 @@ class Communicator:
     def barrier(self, stream=None) -> None:
         check(self.lib.pdj_barrier(ctypes.byref(self._comm), int(self.emulate), self._stream(stream)), "barrier")
 
-    def pick_algo(self, nbytes: int) -> int:
+    def pick_algo(self, nbytes: int, in_place: bool = False) -> int:
+        """The all-reduce algorithm the product runs for a message of `nbytes`, from the sweeps in profiles/
+        (r1/sweep_n2.json, r1/sweep_n8.json, r2/): with a multicast object and >= 4 ranks the switch reduction wins
+        or ties at every size; peer-to-peer, the one-shot form only pays up to 64 KiB (and cannot run in place)."""
         if self.nranks == 1:
             return AR_TWOSHOT
-        if nbytes <= 256 << 10:
-            return AR_ONESHOT
-        # measured on B200 (profiles/): at 2 ranks the peer-to-peer two-shot beats the switch
-        # reduction at every size; NVLS pays off once there are more peers to pull from
         if self.has_multicast and not self.emulate and self.nranks >= 4:
             return AR_NVLS
+        if nbytes <= (64 << 10) and not in_place:
+            return AR_ONESHOT
         return AR_TWOSHOT
+
+    def pick_blocks(self, nbytes: int, algo: Optional[int] = None) -> int:
+        """Thread blocks for a collective of `nbytes` (same sweeps): launch-latency-bound messages want few blocks
+        (every block takes part in the device barrier), bandwidth-bound ones want the whole chip."""
+        if algo == AR_NVLS:
+            return 32
+        if nbytes <= (256 << 10):
+            return 16
+        if nbytes <= (1 << 20):
+            return 64
+        return 148
 
     def all_reduce_bf16(self, in_off: int, out_off: int, n_elems: int, scale: float = 1.0, algo: Optional[int] = None,
                         out_f32: bool = False, nblocks: int = 32, stream=None) -> None:
         if algo is None:
-            algo = self.pick_algo(n_elems * 2)
-            if algo == AR_ONESHOT and (in_off == out_off or out_f32):
+            algo = self.pick_algo(n_elems * 2, in_place=(in_off == out_off))
+            if algo == AR_ONESHOT and out_f32:
                 algo = AR_TWOSHOT
             if algo == AR_NVLS and out_f32:
                 algo = AR_TWOSHOT
+        if nblocks <= 0:
+            nblocks = self.pick_blocks(n_elems * 2, algo)
         check(self.lib.pdj_allreduce_bf16(ctypes.byref(self._comm), in_off, out_off, n_elems, scale, algo,
                                           int(out_f32), nblocks, int(self.emulate), self._stream(stream)),
               "allreduce_bf16")
@@ -367,7 +381,9 @@ class Communicator:
                                          n_elems, wd_split, ctypes.c_void_p(hyper_ptr), scale, algo, nblocks,
                                          int(self.emulate), self._stream(stream)), "allreduce_sgd")
 
-    def all_to_all(self, in_off: int, out_off: int, chunk_bytes: int, nblocks: int = 32, stream=None) -> None:
+    def all_to_all(self, in_off: int, out_off: int, chunk_bytes: int, nblocks: int = 0, stream=None) -> None:
+        if nblocks <= 0:
+            nblocks = self.pick_blocks(chunk_bytes * self.nranks)
         check(self.lib.pdj_alltoall(ctypes.byref(self._comm), in_off, out_off, chunk_bytes, nblocks,
                                     int(self.emulate), self._stream(stream)), "alltoall")
 

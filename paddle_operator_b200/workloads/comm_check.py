@@ -165,9 +165,14 @@ def sweep(comm: Communicator, dev, rank, world, max_bytes, blocks_list) -> list[
                 row[f"{ALGO_NAMES[algo]}_b{nb}_ms"] = t
                 if best is None or t < best[0]:
                     best = (t, ALGO_NAMES[algo], nb)
-        row.update({"ours_ms": best[0], "ours_algo": best[1], "ours_blocks": best[2],
-                    "ours_busbw_gbs": size / best[0] / 1e6 * 2 * (world - 1) / world,
-                    "speedup_vs_nccl": t_nccl / best[0]})
+        # what the PRODUCT runs for this size: pick_algo + pick_blocks, not the best cell of the table above
+        p_algo = comm.pick_algo(size, in_place=True)
+        p_blocks = comm.pick_blocks(size, p_algo)
+        t_prod = _time(lambda: comm.all_reduce_bf16(a, a, n, scale=1.0 / world, algo=p_algo, nblocks=p_blocks), iters, dev)
+        row.update({"product_ms": t_prod, "product_algo": ALGO_NAMES[p_algo], "product_blocks": p_blocks,
+                    "product_busbw_gbs": size / t_prod / 1e6 * 2 * (world - 1) / world,
+                    "product_speedup_vs_nccl": t_nccl / t_prod,
+                    "best_ms": best[0], "best_algo": best[1], "best_blocks": best[2]})
         rows.append(row)
         # all-to-all (size = total bytes sent per rank)
         if size >= 16 * world and size % (16 * world) == 0:
@@ -181,9 +186,10 @@ def sweep(comm: Communicator, dev, rank, world, max_bytes, blocks_list) -> list[
                 r2[f"b{nb}_ms"] = t
                 if best is None or t < best[0]:
                     best = (t, nb)
-            r2.update({"ours_ms": best[0], "ours_blocks": best[1],
-                       "ours_busbw_gbs": size / best[0] / 1e6 * (world - 1) / world,
-                       "speedup_vs_nccl": t_nccl / best[0]})
+            t_prod = _time(lambda: comm.all_to_all(a, b, chunk), iters, dev)  # default block count = pick_blocks
+            r2.update({"product_ms": t_prod, "product_blocks": comm.pick_blocks(size),
+                       "product_busbw_gbs": size / t_prod / 1e6 * (world - 1) / world,
+                       "product_speedup_vs_nccl": t_nccl / t_prod, "best_ms": best[0], "best_blocks": best[1]})
             rows.append(r2)
         size *= 4
     return rows
