@@ -107,6 +107,16 @@ struct PdjEmbTable {
 };
 int pdj_emb_lookup(const struct PdjComm* c, const struct PdjEmbTable* t, size_t ids_off, size_t out_deep_off,
                    size_t out_wide_off, int B, int S, int barrier, int nblocks, int emulate, cudaStream_t st);
+/* Same lookup, writing rows of `out_pitch` bf16 values (a multiple of 8, >= S * dim): the S * dim embedding values,
+ * then the sample's `dense_n` dense features (fp32 [B, dense_n] at arena offset dense_off, converted), then zeros -
+ * i.e. the padded input of the MLP tower in place, with no concatenation / conversion / fill kernels. */
+int pdj_emb_lookup2(const struct PdjComm* c, const struct PdjEmbTable* t, size_t ids_off, size_t out_deep_off,
+                    size_t out_wide_off, int B, int S, int barrier, int out_pitch, size_t dense_off, int dense_n,
+                    int nblocks, int emulate, cudaStream_t st);
+/* Same push, reading the deep gradient from rows of g_pitch bf16 values (the gradient of that padded input). */
+int pdj_emb_push2(const struct PdjComm* c, const struct PdjEmbTable* t, size_t ids_off, size_t gdeep_off,
+                  size_t gwide_off, int B, int S, int async_sgd, float lr, float grad_scale, int g_pitch, int nblocks,
+                  int emulate, cudaStream_t st);
 int pdj_emb_push(const struct PdjComm* c, const struct PdjEmbTable* t, size_t ids_off, size_t gdeep_off,
                  size_t gwide_off, int B, int S, int async_sgd, float lr, float grad_scale, int nblocks, int emulate,
                  cudaStream_t st);

@@ -59,10 +59,23 @@ __device__ __forceinline__ uint32_t atom_add_sys(uint32_t* p, uint32_t v) {
   return old;
 }
 
+// The columns of an output row past the S * D embedding values: the sample's dense features (fp32 -> bf16) and
+// zeros up to the row pitch.  With out_pitch = the padded input width of the MLP the lookup writes the tower's input
+// in place - no concatenation, no conversion kernel, no zero fill.
+__device__ __forceinline__ void emb_write_tail(const PdjComm& c, int rank, __nv_bfloat16* out_deep, int b, int used,
+                                               int out_pitch, size_t dense_off, int dense_n, int lane) {
+  if (out_pitch <= used) return;
+  const float* dense = dense_n > 0 ? reinterpret_cast<const float*>(c.base[rank] + dense_off) + (size_t)b * dense_n : nullptr;
+  for (int k = used + lane; k < out_pitch; k += 32) {
+    const int j = k - used;
+    out_deep[(size_t)b * out_pitch + k] = __float2bfloat16(j < dense_n ? dense[j] : 0.f);
+  }
+}
+
 // One warp per sample: S slots, D floats per row, D/4 lanes per row.
 __global__ void __launch_bounds__(1024)
 emb_lookup_kernel(PdjComm c, PdjEmbTable t, size_t ids_off, size_t out_deep_off, size_t out_wide_off, int B, int S,
-                  int do_barrier) {
+                  int do_barrier, int out_pitch, size_t dense_off, int dense_n) {
   const int rank = c.rank + blockIdx.y;
   const int NR = c.nranks;
   PdjSignalPad* me = pdj_pad(c, rank);
@@ -89,10 +102,11 @@ emb_lookup_kernel(PdjComm c, PdjEmbTable t, size_t ids_off, size_t out_deep_off,
         uint2 o;
         o.x = pdj_f2_to_bf2(v.x, v.y);
         o.y = pdj_f2_to_bf2(v.z, v.w);
-        *reinterpret_cast<uint2*>(out_deep + ((size_t)b * S + s) * D + part * 4) = o;
+        *reinterpret_cast<uint2*>(out_deep + (size_t)b * out_pitch + (size_t)s * D + part * 4) = o;
         if (part == 0 && t.has_wide) wide += ld_f1(c.base[owner] + t.wide_off + (size_t)row * 4);
       }
     }
+    emb_write_tail(c, rank, out_deep, b, S * D, out_pitch, dense_off, dense_n, lane);
     if (t.has_wide) {
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) wide += __shfl_xor_sync(0xffffffffu, wide, o);
@@ -112,7 +126,7 @@ __device__ __forceinline__ uint32_t emb_smem_u32(const void* p) { return (uint32
 
 __global__ void __launch_bounds__(1024)
 emb_lookup_tma_kernel(PdjComm c, PdjEmbTable t, size_t ids_off, size_t out_deep_off, size_t out_wide_off, int B, int S,
-                      int do_barrier) {
+                      int do_barrier, int out_pitch, size_t dense_off, int dense_n) {
   extern __shared__ __align__(128) uint8_t emb_sm[];
   __shared__ __align__(8) uint64_t bars[32][2];  // one pair per warp, up to 1024 threads
   const int rank = c.rank + blockIdx.y;
@@ -185,7 +199,7 @@ emb_lookup_tma_kernel(PdjComm c, PdjEmbTable t, size_t ids_off, size_t out_deep_
     }
     if (lane < S) {
       const uint32_t src = tile + ((uint32_t)buf * 32u + (uint32_t)lane) * row_bytes;
-      __nv_bfloat16* o = out_deep + ((size_t)b * S + lane) * D;
+      __nv_bfloat16* o = out_deep + (size_t)b * out_pitch + (size_t)lane * D;
       for (int k = 0; k < D; k += 8) {
         float4 v0, v1;
         asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v0.x), "=f"(v0.y), "=f"(v0.z), "=f"(v0.w) : "r"(src + k * 4));
@@ -202,6 +216,7 @@ emb_lookup_tma_kernel(PdjComm c, PdjEmbTable t, size_t ids_off, size_t out_deep_
       for (int o = 16; o > 0; o >>= 1) wide += __shfl_xor_sync(0xffffffffu, wide, o);
       if (lane == 0) out_wide[b] = wide;
     }
+    emb_write_tail(c, rank, out_deep, b, S * D, out_pitch, dense_off, dense_n, lane);
     __syncwarp();
     wv_cur = wv_next;
     buf ^= 1;
@@ -213,7 +228,7 @@ emb_lookup_tma_kernel(PdjComm c, PdjEmbTable t, size_t ids_off, size_t out_deep_
 // the row; mode 1 (async SGD): apply w -= lr * g on the owner directly.
 __global__ void __launch_bounds__(1024)
 emb_push_kernel(PdjComm c, PdjEmbTable t, size_t ids_off, size_t gdeep_off, size_t gwide_off, int B, int S, int mode,
-                float lr, float grad_scale) {
+                float lr, float grad_scale, int g_pitch) {
   const int rank = c.rank + blockIdx.y;
   const int NR = c.nranks;
   PdjSignalPad* me = pdj_pad(c, rank);
@@ -235,7 +250,7 @@ emb_push_kernel(PdjComm c, PdjEmbTable t, size_t ids_off, size_t gdeep_off, size
       const long long id = ids[(size_t)b * S + s];
       const int owner = (int)(id % NR);
       const long long row = id / NR;
-      const uint2 g = *reinterpret_cast<const uint2*>(gdeep + ((size_t)b * S + s) * D + part * 4);
+      const uint2 g = *reinterpret_cast<const uint2*>(gdeep + (size_t)b * g_pitch + (size_t)s * D + part * 4);
       const float2 g0 = pdj_bf2_to_f2(g.x), g1 = pdj_bf2_to_f2(g.y);
       char* ob = c.base[owner];
       const size_t deep_dst = (mode == 1 ? t.deep_off : t.gdeep_off) + ((size_t)row * D + part * 4) * 4;
@@ -377,7 +392,18 @@ extern "C" {
 
 int pdj_emb_lookup(const PdjComm* c, const PdjEmbTable* t, size_t ids_off, size_t out_deep_off, size_t out_wide_off,
                    int B, int S, int barrier, int nblocks, int emulate, cudaStream_t st) {
+  return pdj_emb_lookup2(c, t, ids_off, out_deep_off, out_wide_off, B, S, barrier, S * t->dim, 0, 0, nblocks, emulate, st);
+}
+
+int pdj_emb_lookup2(const PdjComm* c, const PdjEmbTable* t, size_t ids_off, size_t out_deep_off, size_t out_wide_off,
+                    int B, int S, int barrier, int out_pitch, size_t dense_off, int dense_n, int nblocks, int emulate,
+                    cudaStream_t st) {
   if (check_table(t)) return -1;
+  if (out_pitch < S * t->dim || out_pitch % 8 != 0 || dense_n < 0 || S * t->dim + dense_n > out_pitch || dense_off % 4 != 0) {
+    pdj_set_error("pdj_emb_lookup2: out_pitch (%d) must be a multiple of 8 and hold S * dim + dense_n = %d values", out_pitch,
+                  S * t->dim + dense_n);
+    return -1;
+  }
   static const bool no_tma = getenv("PDJ_EMB_NO_TMA") != nullptr;
   // Random 64-byte row gathers are latency-bound: what matters is rows in flight per SM.  With one block
   // per SM (the barrier-slot budget of a channel) that means many warps per block: 32 warps, two samples
@@ -395,20 +421,29 @@ int pdj_emb_lookup(const PdjComm* c, const PdjEmbTable* t, size_t ids_off, size_
       attr_set_for = smem;
     }
     return launch_emb(emb_lookup_tma_kernel, nblocks, threads, smem, emulate, c->nranks, st, *c, *t, ids_off, out_deep_off,
-                      out_wide_off, B, S, barrier);
+                      out_wide_off, B, S, barrier, out_pitch, dense_off, dense_n);
   }
   return launch_emb(emb_lookup_kernel, nblocks, threads, (size_t)0, emulate, c->nranks, st, *c, *t, ids_off, out_deep_off,
-                    out_wide_off, B, S, barrier);
+                    out_wide_off, B, S, barrier, out_pitch, dense_off, dense_n);
 }
 
 int pdj_emb_push(const PdjComm* c, const PdjEmbTable* t, size_t ids_off, size_t gdeep_off, size_t gwide_off, int B,
                  int S, int async_sgd, float lr, float grad_scale, int nblocks, int emulate, cudaStream_t st) {
+  return pdj_emb_push2(c, t, ids_off, gdeep_off, gwide_off, B, S, async_sgd, lr, grad_scale, S * t->dim, nblocks, emulate, st);
+}
+
+int pdj_emb_push2(const PdjComm* c, const PdjEmbTable* t, size_t ids_off, size_t gdeep_off, size_t gwide_off, int B,
+                  int S, int async_sgd, float lr, float grad_scale, int g_pitch, int nblocks, int emulate, cudaStream_t st) {
   if (check_table(t)) return -1;
+  if (g_pitch < S * t->dim || g_pitch % 4 != 0 || gdeep_off % 8 != 0) {
+    pdj_set_error("pdj_emb_push2: g_pitch (%d) must be a multiple of 4 and at least S * dim = %d", g_pitch, S * t->dim);
+    return -1;
+  }
   static const int knob_threads = getenv("PDJ_EMB_THREADS") ? atoi(getenv("PDJ_EMB_THREADS")) : 1024;
   int threads = emulate ? 256 : knob_threads;
   if (threads < 32 || threads > 1024 || threads % 32 != 0) threads = 256;
   return launch_emb(emb_push_kernel, nblocks, threads, (size_t)0, emulate, c->nranks, st, *c, *t, ids_off, gdeep_off, gwide_off,
-                    B, S, async_sgd ? 1 : 0, lr, grad_scale);
+                    B, S, async_sgd ? 1 : 0, lr, grad_scale, g_pitch);
 }
 
 int pdj_emb_apply(const PdjComm* c, const PdjEmbTable* t, int optimizer, float lr, float eps, int nblocks,

@@ -46,6 +46,8 @@ class WideDeepDense(nn.Module):
         return self.tower.layers
 
     def _tower_input(self, deep_emb: torch.Tensor, dense: torch.Tensor) -> torch.Tensor:
+        if deep_emb.shape[1] == self.in_dim and self.in_dim != self.raw_in - dense.shape[1]:
+            return deep_emb  # the lookup kernel already wrote [embeddings | dense | zero pad] (ShardedEmbedding.set_output_layout)
         parts = [deep_emb, dense.to(deep_emb.dtype)]
         if self.in_dim != self.raw_in:
             parts.append(torch.zeros((deep_emb.shape[0], self.in_dim - self.raw_in), dtype=deep_emb.dtype,

@@ -76,6 +76,10 @@ def _declare(lib: ctypes.CDLL) -> None:
         "pdj_emb_lookup": (c_int, [POINTER(PdjComm), POINTER(PdjEmbTable), sz, sz, sz, c_int, c_int, c_int, c_int, c_int, st]),
         "pdj_emb_push": (c_int, [POINTER(PdjComm), POINTER(PdjEmbTable), sz, sz, sz, c_int, c_int, c_int, c_float, c_float,
                                  c_int, c_int, st]),
+        "pdj_emb_lookup2": (c_int, [POINTER(PdjComm), POINTER(PdjEmbTable), sz, sz, sz, c_int, c_int, c_int, c_int, sz, c_int,
+                                    c_int, c_int, st]),
+        "pdj_emb_push2": (c_int, [POINTER(PdjComm), POINTER(PdjEmbTable), sz, sz, sz, c_int, c_int, c_int, c_float, c_float,
+                                  c_int, c_int, c_int, st]),
         "pdj_emb_apply": (c_int, [POINTER(PdjComm), POINTER(PdjEmbTable), c_int, c_float, c_float, c_int, c_int, st]),
         "pdj_linear_block_n": (c_int, [c_int]),
         "pdj_linear_bf16": (c_int, [vp, vp, vp, vp, vp, c_int, c_int, c_int, c_int, c_int, c_int, c_int, st]),

@@ -69,7 +69,9 @@ class ShardedEmbedding:
         self.t = t
         # per-step I/O buffers (also in the arena so the emulation can address every rank's)
         self.ids_off = a(max_batch * slots * 8)
-        self.out_deep_off = a(max_batch * slots * D * 2)
+        # rows of the lookup output may be wider than slots * dim (set_output_layout): room for 32 extra columns
+        self.out_pitch, self.dense_n, self.dense_off = slots * D, 0, 0
+        self.out_deep_off = a(max_batch * (slots * D + 32) * 2)
         self.out_wide_off = a(max_batch * 4)
         self.gdeep_in_off = a(max_batch * slots * D * 2)
         self.gwide_in_off = a(max_batch * 4)
@@ -112,23 +114,44 @@ class ShardedEmbedding:
     def ids_buffer(self, batch: int, rank: Optional[int] = None) -> torch.Tensor:
         return self.comm.tensor(self.ids_off, (batch, self.slots), torch.int64, rank)
 
+    def set_output_layout(self, pitch: int, dense_n: int = 0) -> None:
+        """Makes the lookup write rows of `pitch` bf16 values: the slots * dim embedding values, then `dense_n` dense
+        features taken (fp32 -> bf16) from `dense_buffer()`, then zeros - the padded input of the MLP tower in
+        place (csrc/embedding.cu::emb_write_tail).  Backward then reads gradients with the same pitch."""
+        used = self.slots * self.dim
+        if pitch % 8 != 0 or not used + dense_n <= pitch <= used + 32:
+            raise ValueError(f"pitch {pitch} must be a multiple of 8 in [{used + dense_n}, {used + 32}]")
+        self.out_pitch, self.dense_n = pitch, dense_n
+        if dense_n and not self.dense_off:
+            self.dense_off = self.comm.alloc(self.max_batch * dense_n * 4)
+
+    def dense_buffer(self, batch: int, rank: Optional[int] = None) -> torch.Tensor:
+        return self.comm.tensor(self.dense_off, (batch, self.dense_n), torch.float32, rank)
+
     def lookup_raw(self, batch: int, barrier: bool = True, stream=None) -> None:
         c = self.comm
-        check(self.lib.pdj_emb_lookup(ctypes.byref(self.cstruct), ctypes.byref(self.t), self.ids_off,
-                                      self.out_deep_off, self.out_wide_off, batch, self.slots, int(barrier),
-                                      self.nblocks, int(c.emulate), c._stream(stream)), "emb_lookup")
+        check(self.lib.pdj_emb_lookup2(ctypes.byref(self.cstruct), ctypes.byref(self.t), self.ids_off,
+                                       self.out_deep_off, self.out_wide_off, batch, self.slots, int(barrier),
+                                       self.out_pitch, self.dense_off, self.dense_n,
+                                       self.nblocks, int(c.emulate), c._stream(stream)), "emb_lookup")
 
-    def push_raw(self, batch: int, grad_scale: float = 1.0, stream=None) -> None:
+    def push_raw(self, batch: int, grad_scale: float = 1.0, stream=None, gdeep_off: Optional[int] = None,
+                 g_pitch: Optional[int] = None) -> None:
+        """`gdeep_off` / `g_pitch`: read the deep gradient from there instead of the staging buffer.  On a real rank
+        any device address works (pass address - arena base: the kernel adds the base back), which lets backward
+        hand the MLP's input gradient over without a copy."""
         c = self.comm
-        check(self.lib.pdj_emb_push(ctypes.byref(self.cstruct), ctypes.byref(self.t), self.ids_off, self.gdeep_in_off,
-                                    self.gwide_in_off, batch, self.slots, int(self.async_sgd), self.lr, grad_scale,
-                                    self.nblocks, int(c.emulate), c._stream(stream)), "emb_push")
+        check(self.lib.pdj_emb_push2(ctypes.byref(self.cstruct), ctypes.byref(self.t), self.ids_off,
+                                     self.gdeep_in_off if gdeep_off is None else gdeep_off,
+                                     self.gwide_in_off, batch, self.slots, int(self.async_sgd), self.lr, grad_scale,
+                                     self.slots * self.dim if g_pitch is None else g_pitch,
+                                     self.nblocks, int(c.emulate), c._stream(stream)), "emb_push")
         if not self.async_sgd:
             check(self.lib.pdj_emb_apply(ctypes.byref(self.cstruct), ctypes.byref(self.t), self.optimizer, self.lr,
                                          self.eps, 4 * 148, int(c.emulate), c._stream(stream)), "emb_apply")
 
     def out_deep(self, batch: int, rank: Optional[int] = None) -> torch.Tensor:
-        return self.comm.tensor(self.out_deep_off, (batch, self.slots * self.dim), torch.bfloat16, rank)
+        return self.comm.tensor(self.out_deep_off, (batch, self.out_pitch), torch.bfloat16, rank)
 
     def out_wide(self, batch: int, rank: Optional[int] = None) -> torch.Tensor:
         return self.comm.tensor(self.out_wide_off, (batch,), torch.float32, rank)
@@ -174,7 +197,14 @@ class _LookupFn(torch.autograd.Function):
     @staticmethod
     def backward(ctx, g_deep, g_wide):
         emb, b = ctx.emb, ctx.batch
-        emb.grad_deep_in(b).copy_(g_deep)
         emb.grad_wide_in(b).copy_(g_wide if g_wide is not None else torch.zeros(b, device=g_deep.device))
-        emb.push_raw(b, emb.grad_scale)
+        pitch = g_deep.stride(0)
+        if (not emb.comm.emulate and g_deep.dim() == 2 and g_deep.stride(1) == 1 and pitch % 4 == 0
+                and g_deep.data_ptr() % 8 == 0 and pitch >= emb.slots * emb.dim):
+            # no staging copy: the push kernel reads the gradient tensor where autograd left it
+            off = (g_deep.data_ptr() - emb.comm._bases[emb.comm.rank]) % (1 << 64)
+            emb.push_raw(b, emb.grad_scale, gdeep_off=off, g_pitch=pitch)
+        else:
+            emb.grad_deep_in(b).copy_(g_deep[:, :emb.slots * emb.dim])
+            emb.push_raw(b, emb.grad_scale)
         return None, None, None

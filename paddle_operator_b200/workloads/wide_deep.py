@@ -72,7 +72,11 @@ class WideDeepJob:
         dense = WideDeepDense(emb_dim, fused=True).to(self.device).to(torch.bfloat16)
         self.model = _Net(dense, self.emb).train()
         self.ids = torch.zeros((batch, SPARSE_SLOTS), dtype=torch.int64, device=self.device)
-        self.dense_x = torch.zeros((batch, DENSE_FEATURES), dtype=torch.float32, device=self.device)
+        # the lookup kernel writes the tower's padded input [26 x 16 embeddings | 13 dense | 3 zeros] in place: the
+        # dense features live in the arena where it reads them (no concatenation / conversion / fill kernels)
+        self.emb.set_output_layout(dense.in_dim, DENSE_FEATURES)
+        self.dense_x = self.emb.dense_buffer(batch)
+        self.dense_x.zero_()
         self.labels = torch.zeros((batch,), dtype=torch.float32, device=self.device)
         self.trainer = CollectiveTrainer(self.model, _loss_fn, (self.ids, self.dense_x, self.labels),
                                          comm=comm if world > 1 else None, lr=lr, momentum=0.9, weight_decay=0.0,

@@ -118,3 +118,52 @@ def test_autograd_lookup_and_fused_update_single_rank():
         assert losses[-1] < 0.5 * losses[0], losses
     finally:
         comm.close()
+
+
+@pytest.mark.parametrize("nranks", [1, 2])
+@pytest.mark.parametrize("tma", ["1", "0"])
+def test_lookup_writes_padded_tower_input_in_place(nranks, tma, monkeypatch):
+    """set_output_layout: rows of 432 = 26 x 16 embedding values | 13 dense features (fp32 -> bf16) | 3 zeros."""
+    from paddle_operator_b200.parallel.ps import embedding_reference
+
+    if tma == "0":
+        monkeypatch.setenv("PDJ_EMB_NO_TMA", "1")  # read once per process: only effective if this runs first; harmless otherwise
+    comm, emb = _mk(nranks, dim=16, slots=26)
+    try:
+        emb.set_output_layout(432, 13)
+        deep_t, wide_t = emb.full_tables()
+        torch.manual_seed(3)
+        ids = [torch.randint(0, emb.num_rows, (96, 26), device="cuda") for _ in range(nranks)]
+        dense = [torch.randn(96, 13, device="cuda") for _ in range(nranks)]
+        for r in range(nranks):
+            emb.ids_buffer(96, r).copy_(ids[r])
+            emb.dense_buffer(96, r).copy_(dense[r])
+            emb.out_deep(96, r).fill_(7.0)  # stale contents must be overwritten, pad included
+        emb.lookup_raw(96)
+        torch.cuda.synchronize()
+        for r in range(nranks):
+            d_ref, w_ref = embedding_reference(deep_t, wide_t, ids[r])
+            got = emb.out_deep(96, r).float()
+            assert got.shape == (96, 432)
+            torch.testing.assert_close(got[:, :416].view(96, 26, 16), d_ref.to(torch.bfloat16).float(), atol=0, rtol=0)
+            torch.testing.assert_close(got[:, 416:429], dense[r].to(torch.bfloat16).float(), atol=0, rtol=0)
+            assert float(got[:, 429:].abs().max()) == 0.0
+            torch.testing.assert_close(emb.out_wide(96, r), w_ref, atol=1e-5, rtol=1e-5)
+        # push with a pitched gradient (the gradient of that padded input) equals push of its first 416 columns
+        g = [(torch.randn(96, 432, device="cuda") * 0.1).to(torch.bfloat16) for _ in range(nranks)]
+        stage = emb.comm.alloc(96 * 432 * 2)
+        for r in range(nranks):
+            emb.comm.tensor(stage, (96, 432), torch.bfloat16, r).copy_(g[r])
+            emb.grad_wide_in(96, r).zero_()
+        before = emb.full_tables()[0].clone()
+        emb.push_raw(96, 1.0, gdeep_off=stage, g_pitch=432)
+        torch.cuda.synchronize()
+        after = emb.full_tables()[0]
+        ref = before.clone()
+        G = torch.zeros_like(ref)
+        for r in range(nranks):
+            G.index_add_(0, ids[r].reshape(-1), g[r][:, :416].float().reshape(-1, 16))
+        touched = G.abs().sum(1) > 0
+        assert bool((after[~touched] == before[~touched]).all()) and bool((after[touched] != before[touched]).any())
+    finally:
+        comm.close()
