@@ -84,8 +84,9 @@ int pdj_broadcast(const struct PdjComm* c, int root, size_t off, size_t bytes, i
 /* ---- PS mode: GPU-sharded embedding tables (csrc/embedding.cu) -------------
  * The PSERVER / TRAINER roles of the reference (api/v1/paddlejob_types.go:44-48,
  * PADDLE_PSERVERS_IP_PORT_LIST at controllers/paddlejob_helper.go:258-260;
- * pull / push semantics in docs/design-arch.md:49-74).  Row `id` lives on rank
- * id % nranks at local row id / nranks.  All offsets are arena offsets.
+ * pull / push semantics in docs/design-arch.md:49-74).  The table is cut into P shards (list_cap, the job's
+ * spec.ps.replicas; 0 = one per rank): row `id` belongs to shard id % P, which lives on rank (id % P) % nranks in
+ * slot (id % P) / nranks, at row id / P of the slot.  All offsets are arena offsets.
  *   lookup: out_deep[b, s, :] = bf16(table[id[b,s]]), out_wide[b] = sum_s wide[id[b,s]]
  *   push  : sync  - staging[id] += grad (peer red.add), row registered with its owner
  *           async - table[id]  -= lr * grad immediately (asynchronous SGD)
@@ -101,7 +102,7 @@ struct PdjEmbTable {
   size_t list_off;      /* unused (kept for ABI stability) */
   size_t count_off;     /* u32 [2]: touched rows this step, last step */
   long long rows_per_shard;
-  unsigned int list_cap;
+  unsigned int list_cap; /* number of table shards P (the job's pserver count); 0 = one per rank */
   int dim;              /* power of two, 4..128 */
   int has_wide;
 };

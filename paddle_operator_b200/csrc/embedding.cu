@@ -59,6 +59,16 @@ __device__ __forceinline__ uint32_t atom_add_sys(uint32_t* p, uint32_t v) {
   return old;
 }
 
+// Where row `id` lives.  The table is cut into P = t.list_cap shards (0 = one per rank): the PSERVER count of the
+// job (spec.ps.replicas, controllers/paddlejob_helper.go:225-235,258-260).  Shard j = id % P sits on GPU j % NR in
+// slot j / NR of that GPU's table, at row id / P of the slot; a slot is t.rows_per_shard rows.
+__device__ __forceinline__ void emb_locate(const PdjEmbTable& t, int NR, long long id, int* owner, long long* row) {
+  const int P = t.list_cap ? (int)t.list_cap : NR;
+  const int shard = (int)(id % P);
+  *owner = shard % NR;
+  *row = (long long)(shard / NR) * t.rows_per_shard + id / P;
+}
+
 // The columns of an output row past the S * D embedding values: the sample's dense features (fp32 -> bf16) and
 // zeros up to the row pitch.  With out_pitch = the padded input width of the MLP the lookup writes the tower's input
 // in place - no concatenation, no conversion kernel, no zero fill.
@@ -96,8 +106,9 @@ emb_lookup_kernel(PdjComm c, PdjEmbTable t, size_t ids_off, size_t out_deep_off,
       const int s = s0 + sub;
       if (s < S) {
         const long long id = ids[(size_t)b * S + s];
-        const int owner = (int)(id % NR);
-        const long long row = id / NR;
+        int owner;
+        long long row;
+        emb_locate(t, NR, id, &owner, &row);
         const float4 v = ld_f4(c.base[owner] + t.deep_off + ((size_t)row * D + part * 4) * 4);
         uint2 o;
         o.x = pdj_f2_to_bf2(v.x, v.y);
@@ -160,8 +171,9 @@ emb_lookup_tma_kernel(PdjComm c, PdjEmbTable t, size_t ids_off, size_t out_deep_
     float wv = 0.f;
     if (lane < S) {
       const long long id = ids[(size_t)b * S + lane];
-      const int owner = (int)(id % NR);
-      const long long row = id / NR;
+      int owner;
+      long long row;
+      emb_locate(t, NR, id, &owner, &row);
       const char* src = c.base[owner] + t.deep_off + (size_t)row * row_bytes;
       const uint32_t dst = tile + ((uint32_t)buf * 32u + (uint32_t)lane) * row_bytes;
       asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
@@ -248,8 +260,9 @@ emb_push_kernel(PdjComm c, PdjEmbTable t, size_t ids_off, size_t gdeep_off, size
       const int s = s0 + sub;
       if (s >= S) continue;
       const long long id = ids[(size_t)b * S + s];
-      const int owner = (int)(id % NR);
-      const long long row = id / NR;
+      int owner;
+      long long row;
+      emb_locate(t, NR, id, &owner, &row);
       const uint2 g = *reinterpret_cast<const uint2*>(gdeep + (size_t)b * g_pitch + (size_t)s * D + part * 4);
       const float2 g0 = pdj_bf2_to_f2(g.x), g1 = pdj_bf2_to_f2(g.y);
       char* ob = c.base[owner];
@@ -286,7 +299,9 @@ emb_apply_kernel(PdjComm c, PdjEmbTable t, int opt, float lr, float eps) {
   const int lpr = D >> 2, rpw = 32 / lpr;
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   const int sub = lane / lpr, part = lane % lpr;
-  const long long nwin = (t.rows_per_shard + 127) / 128;
+  // every slot this GPU holds: ceil(P / NR) of them (the last may be unused on some ranks; its flags stay clear)
+  const int P_ = t.list_cap ? (int)t.list_cap : c.nranks;
+  const long long nwin = ((long long)((P_ + c.nranks - 1) / c.nranks) * t.rows_per_shard + 127) / 128;
   const long long gw = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const long long nw = ((long long)gridDim.x * blockDim.x) >> 5;
   uint32_t* flags32 = reinterpret_cast<uint32_t*>(base + t.flag_off);

@@ -13,9 +13,10 @@ Reference parity: PS mode = `spec.ps` present (controllers/paddlejob_helper.go:
 191-193); roles PSERVER/TRAINER (api/v1/paddlejob_types.go:44-48); what they do:
 docs/design-arch.md:7-9,49-74 ("trainers ... pull parameters ... push gradients;
 pservers update parameters", sync vs async SGD).  Mapping used here: shard j of
-the table lives on GPU j (one shard per trainer rank); `ps.replicas` PSERVER
-ranks still exist as processes for ordering/status, but the "server" is memory
-plus the owner-side half of the kernels.
+the table lives on GPU j mod ngpus, with P = `ps.replicas` shards (`num_shards`;
+PADDLE_PSERVERS_IP_PORT_LIST names them); the PSERVER ranks still exist as processes for
+ordering/status, but the "server" is memory plus the owner-side half of the kernels, and
+checkpoints are one `ps-<j>.pt` per shard.
 """
 from __future__ import annotations
 
@@ -41,11 +42,18 @@ def embedding_reference(table_deep, table_wide, ids):
 class ShardedEmbedding:
     def __init__(self, comm: Communicator, num_rows: int, dim: int, max_batch: int, slots: int,
                  has_wide: bool = True, optimizer: int = ADAGRAD, lr: float = 0.05, eps: float = 1e-6,
-                 async_sgd: bool = False, init_scale: float = 0.01, seed: int = 0, nblocks: int = 0):
+                 async_sgd: bool = False, init_scale: float = 0.01, seed: int = 0, nblocks: int = 0,
+                 num_shards: Optional[int] = None):
+        """`num_shards` = P, the PSERVER count of the job (spec.ps.replicas; the reference sizes its server side
+        from it, controllers/paddlejob_helper.go:225-235,258-260).  Shard j = id % P lives on GPU j % nranks; a GPU
+        holds ceil(P / nranks) shard slots.  Default: one shard per rank."""
         self.comm, self.dim, self.slots, self.max_batch = comm, dim, slots, max_batch
         self.nranks = comm.nranks
-        self.rows_per_shard = (num_rows + self.nranks - 1) // self.nranks
-        self.num_rows = self.rows_per_shard * self.nranks
+        self.num_shards = int(num_shards) if num_shards else self.nranks
+        self.slots_per_rank = (self.num_shards + self.nranks - 1) // self.nranks
+        self.shard_rows = (num_rows + self.num_shards - 1) // self.num_shards   # rows of one shard
+        self.rows_per_shard = self.shard_rows * self.slots_per_rank             # rows one GPU holds
+        self.num_rows = self.shard_rows * self.num_shards
         self.has_wide, self.optimizer, self.lr, self.eps, self.async_sgd = has_wide, optimizer, lr, eps, async_sgd
         self.nblocks = nblocks or 128
         self.cstruct = comm.channel_struct(1)  # never shares barrier slots with the dense all-reduce
@@ -65,7 +73,7 @@ class ShardedEmbedding:
         cap = 0
         t.list_off = 0
         t.count_off = a(256)
-        t.rows_per_shard, t.list_cap, t.dim, t.has_wide = R, cap, D, int(has_wide)
+        t.rows_per_shard, t.list_cap, t.dim, t.has_wide = self.shard_rows, self.num_shards, D, int(has_wide)
         self.t = t
         # per-step I/O buffers (also in the arena so the emulation can address every rank's)
         self.ids_off = a(max_batch * slots * 8)
@@ -100,14 +108,20 @@ class ShardedEmbedding:
                            (self.t.count_off, 64)):
                 self.comm.tensor(off, (n,), torch.float32, r).zero_()
 
+    def shards_of(self, rank: int) -> list:
+        """The shard indices GPU `rank` holds, in slot order."""
+        return [j for j in range(rank, self.num_shards, self.nranks)]
+
     def full_tables(self):
         """Gathers the whole table on this device (tests / checkpoints); needs the emulation
         or peer mappings, both of which let any rank read any shard."""
         deep = torch.empty(self.num_rows, self.dim, device=f"cuda:{self.comm.device}")
         wide = torch.empty(self.num_rows, device=f"cuda:{self.comm.device}")
+        P, R = self.num_shards, self.shard_rows
         for r in range(self.nranks):
-            deep[r::self.nranks] = self.shard(r)
-            wide[r::self.nranks] = self.shard_wide(r)
+            for k, j in enumerate(self.shards_of(r)):
+                deep[j::P] = self.shard(r)[k * R:(k + 1) * R]
+                wide[j::P] = self.shard_wide(r)[k * R:(k + 1) * R]
         return deep, wide
 
     # -- raw kernel launches (rank-local unless emulated) -----------------------------
@@ -171,18 +185,50 @@ class ShardedEmbedding:
         The sparse optimizer step runs inside backward."""
         return _LookupFn.apply(self, ids, torch.zeros((), device=ids.device, requires_grad=True))
 
+    def _acc(self):
+        R = self.rows_per_shard
+        return (self.comm.tensor(self.t.acc_deep_off, (R, self.dim), torch.float32),
+                self.comm.tensor(self.t.acc_wide_off, (R,), torch.float32))
+
+    def shard_state_dicts(self) -> dict:
+        """{shard index j: state} for the shards THIS rank holds - one `ps-<j>.pt` each (utils/checkpoint.py), named
+        by pserver index as the reference's server side would be, whatever the number of trainers."""
+        r, R = self.comm.rank, self.shard_rows
+        acc_d, acc_w = self._acc()
+        out = {}
+        for k, j in enumerate(self.shards_of(r)):
+            sl = slice(k * R, (k + 1) * R)
+            out[j] = {"deep": self.shard(r)[sl].clone(), "wide": self.shard_wide(r)[sl].clone(),
+                      "acc_deep": acc_d[sl].clone(), "acc_wide": acc_w[sl].clone(), "shard": j,
+                      "nshards": self.num_shards}
+        return out
+
+    def load_shard_state_dict(self, sd: dict) -> None:
+        j = int(sd["shard"])
+        if int(sd.get("nshards", self.num_shards)) != self.num_shards or j % self.nranks != self.comm.rank:
+            raise ValueError(f"shard {j} of {sd.get('nshards')} does not belong on rank {self.comm.rank} "
+                             f"of a {self.num_shards}-shard table")
+        k, R = j // self.nranks, self.shard_rows
+        sl = slice(k * R, (k + 1) * R)
+        acc_d, acc_w = self._acc()
+        self.shard()[sl].copy_(sd["deep"])
+        self.shard_wide()[sl].copy_(sd["wide"])
+        acc_d[sl].copy_(sd["acc_deep"])
+        acc_w[sl].copy_(sd["acc_wide"])
+
     def state_dict(self) -> dict:
+        """Everything this rank holds in one dict (one shard per rank: the round-1 format)."""
         r = self.comm.rank
-        return {"deep": self.shard(r).clone(), "wide": self.shard_wide(r).clone(),
-                "acc_deep": self.comm.tensor(self.t.acc_deep_off, (self.rows_per_shard, self.dim), torch.float32).clone(),
-                "acc_wide": self.comm.tensor(self.t.acc_wide_off, (self.rows_per_shard,), torch.float32).clone(),
-                "shard": r, "nshards": self.nranks}
+        acc_d, acc_w = self._acc()
+        return {"deep": self.shard(r).clone(), "wide": self.shard_wide(r).clone(), "acc_deep": acc_d.clone(),
+                "acc_wide": acc_w.clone(), "shard": r, "nshards": self.num_shards}
 
     def load_state_dict(self, sd: dict) -> None:
+        acc_d, acc_w = self._acc()
         self.shard().copy_(sd["deep"])
         self.shard_wide().copy_(sd["wide"])
-        self.comm.tensor(self.t.acc_deep_off, (self.rows_per_shard, self.dim), torch.float32).copy_(sd["acc_deep"])
-        self.comm.tensor(self.t.acc_wide_off, (self.rows_per_shard,), torch.float32).copy_(sd["acc_wide"])
+        acc_d.copy_(sd["acc_deep"])
+        acc_w.copy_(sd["acc_wide"])
 
 
 class _LookupFn(torch.autograd.Function):

@@ -35,6 +35,7 @@ def main() -> int:
     ap.add_argument("--emb-dim", type=int, default=16)
     ap.add_argument("--async-sgd", action="store_true")
     ap.add_argument("--log-every", type=int, default=10)
+    ap.add_argument("--ckpt-every", type=int, default=0, help="also checkpoint every N steps (always at the end)")
     ap.add_argument("--cpu-dry-run", action="store_true", help="no GPU: only exercise the role plumbing")
     args = ap.parse_args()
     env = os.environ
@@ -61,15 +62,28 @@ def main() -> int:
         torch.cuda.set_device(int(env.get("LOCAL_RANK", env.get("PDJ_LOCAL_DEVICE", "0"))))
         job = WideDeepJob.from_env(batch=args.batch, rows=args.rows, emb_dim=args.emb_dim, async_sgd=args.async_sgd)
         job.prepare()
+        from ..utils import checkpoint as ckpt
+
+        root = ckpt.checkpoint_root()
+        # checkpoints only where the job asked for a place to put them: a volume mounted at /checkpoint (the
+        # reference's examples mount one) or PDJ_CHECKPOINT_DIR
+        do_ckpt = root != "/tmp/checkpoint" or bool(env.get("PDJ_CHECKPOINT_DIR")) or args.ckpt_every > 0
+        start = (job.load_checkpoint(root) or 0) if do_ckpt else 0
+        if start:
+            print(json.dumps({"rank": rank, "resumed_from_step": start, "shards": job.emb.shards_of(job.rank)}), flush=True)
         batches = [job.synthetic_batch(s) for s in range(4)]
         t0 = time.time()
-        for step in range(1, args.steps + 1):
+        for step in range(start + 1, args.steps + 1):
             loss = job.train_step(*batches[step % 4])
             if step % args.log_every == 0 or step == args.steps:
                 torch.cuda.current_stream().synchronize()
                 print(json.dumps({"rank": rank, "world": world, "step": step, "loss": round(float(loss.item()), 4),
                                   "samples_per_s": round(step * args.batch * world / (time.time() - t0), 1)}), flush=True)
+            if do_ckpt and args.ckpt_every > 0 and step % args.ckpt_every == 0 and step < args.steps:
+                job.save_checkpoint(root, step)
         torch.cuda.synchronize()
+        if do_ckpt:
+            job.save_checkpoint(root, args.steps)
         if world > 1:
             job.comm.barrier()
             torch.cuda.synchronize()

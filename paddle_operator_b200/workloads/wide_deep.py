@@ -52,7 +52,7 @@ class WideDeepJob:
     def __init__(self, batch: int = 32768, rows: int = 1 << 24, emb_dim: int = 16, comm: Optional[Communicator] = None,
                  device: Optional[torch.device] = None, lr: float = 0.05, sparse_lr: float = 0.05,
                  optimizer: int = ADAGRAD, async_sgd: bool = False, use_graph: bool = True, seed: int = 0,
-                 arena_bytes: Optional[int] = None, emb_blocks: int = 0):
+                 arena_bytes: Optional[int] = None, emb_blocks: int = 0, num_shards: Optional[int] = None):
         self.device = device or torch.device("cuda", torch.cuda.current_device())
         self.batch, self.rows, self.emb_dim = batch, rows, emb_dim
         world = comm.nranks if comm is not None else 1
@@ -66,7 +66,8 @@ class WideDeepJob:
         self.comm = comm
         self.rank, self.world = comm.rank, world
         self.emb = ShardedEmbedding(comm, rows, emb_dim, batch, SPARSE_SLOTS, has_wide=True, optimizer=optimizer,
-                                    lr=sparse_lr, async_sgd=async_sgd, seed=seed, nblocks=emb_blocks or 148)
+                                    lr=sparse_lr, async_sgd=async_sgd, seed=seed, nblocks=emb_blocks or 148,
+                                    num_shards=num_shards)
         self.emb.grad_scale = 1.0 / world
         torch.manual_seed(seed)
         dense = WideDeepDense(emb_dim, fused=True).to(self.device).to(torch.bfloat16)
@@ -117,8 +118,14 @@ class WideDeepJob:
         env = os.environ
         world = int(env.get("WORLD_SIZE", env.get("PADDLE_TRAINERS_NUM", "1")))
         comm = None
+        # P table shards = the job's pserver count (spec.ps.replicas reaches the ranks as PADDLE_PSERVERS_IP_PORT_LIST,
+        # controllers/paddlejob_helper.go:258-260); shard j lives on GPU j mod world
+        ps = [e for e in env.get("PADDLE_PSERVERS_IP_PORT_LIST", "").split(",") if e.strip()]
+        if ps and "num_shards" not in kw:
+            kw["num_shards"] = len(ps)
         if world > 1:
-            comm = Communicator.from_env(cls.arena_bytes_needed(rows, emb_dim, batch, world))
+            slots = -(-(kw.get("num_shards") or world) // world)  # shard slots per GPU
+            comm = Communicator.from_env(cls.arena_bytes_needed(rows, emb_dim, batch, world) * max(1, slots * world // (kw.get("num_shards") or world)))
         return cls(batch=batch, rows=rows, emb_dim=emb_dim, comm=comm, **kw)
 
     def synthetic_batch(self, seed: int = 0, device=None):
@@ -173,6 +180,43 @@ class WideDeepJob:
     def launches_per_step(self) -> int:
         # lookup + push + apply + count reset, plus the trainer's all-reduce / fused SGD launches
         return self.trainer.kernels_per_step
+
+    # -- checkpoints in the reference's layout: model.pt (dense part) + one ps-<j>.pt per table shard + step.json ---
+    def save_checkpoint(self, root: str, step: int) -> None:
+        """Every rank writes the shards it holds (named by pserver index j, not by trainer rank), rank 0 the dense
+        part; step.json marks the checkpoint complete once every rank has passed the barrier."""
+        from ..utils import checkpoint as ckpt
+
+        torch.cuda.synchronize(self.device)
+        if self.world > 1:
+            self.trainer.sync_state()
+            torch.cuda.synchronize(self.device)
+        for j, sd in self.emb.shard_state_dicts().items():
+            ckpt.save_ps_shard(root, j, sd)
+        if self.rank == 0:
+            ckpt.save_dp(root, step, self.world, {"trainer": self.trainer.state_dict(), "step": step,
+                                                  "nshards": self.emb.num_shards})
+        if self.world > 1:
+            self.comm.barrier()
+            torch.cuda.synchronize(self.device)
+        if self.rank == 0:
+            ckpt.commit(root, step, self.world)
+
+    def load_checkpoint(self, root: str) -> Optional[int]:
+        """Resumes from `root` when it holds a complete checkpoint with the same shard count; returns its step."""
+        from ..utils import checkpoint as ckpt
+
+        meta = ckpt.latest(root)
+        dp = ckpt.load_dp(root, map_location=self.device) if meta else None
+        if dp is None or int(dp.get("nshards", -1)) != self.emb.num_shards:
+            return None
+        for j in self.emb.shards_of(self.rank):
+            sd = ckpt.load_ps_shard(root, j, map_location=self.device)
+            if sd is None:
+                return None
+            self.emb.load_shard_state_dict(sd)
+        self.trainer.load_state_dict(dp["trainer"])
+        return int(dp["step"])
 
     def close(self) -> None:
         torch.cuda.synchronize(self.device)

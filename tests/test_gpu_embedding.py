@@ -167,3 +167,42 @@ def test_lookup_writes_padded_tower_input_in_place(nranks, tma, monkeypatch):
         assert bool((after[~touched] == before[~touched]).all()) and bool((after[touched] != before[touched]).any())
     finally:
         comm.close()
+
+
+@pytest.mark.parametrize("nranks,shards", [(2, 3), (4, 2), (2, 8), (1, 2)])
+def test_shard_count_follows_the_pserver_count(nranks, shards):
+    """P = spec.ps.replicas shards over W GPUs, P != W: shard j = id % P on GPU j % W.  Lookup and a sync SGD push
+    agree with the unsharded reference, and the per-shard checkpoints are named by shard, not by trainer."""
+    from paddle_operator_b200.parallel.ps import SGD, embedding_reference
+
+    comm, emb = _mk(nranks, rows=1000, num_shards=shards, optimizer=SGD, lr=0.5)
+    try:
+        assert emb.num_shards == shards and emb.num_rows % shards == 0
+        held = [emb.shards_of(r) for r in range(nranks)]
+        assert sorted(j for h in held for j in h) == list(range(shards))
+        deep_t, wide_t = emb.full_tables()
+        torch.manual_seed(2)
+        B, S, D = 96, emb.slots, emb.dim
+        ids = [torch.randint(0, emb.num_rows, (B, S), device="cuda") for _ in range(nranks)]
+        for r in range(nranks):
+            emb.ids_buffer(B, r).copy_(ids[r])
+        emb.lookup_raw(B)
+        torch.cuda.synchronize()
+        for r in range(nranks):
+            d_ref, w_ref = embedding_reference(deep_t, wide_t, ids[r])
+            torch.testing.assert_close(emb.out_deep(B, r).float().view(B, S, D), d_ref.to(torch.bfloat16).float(), atol=0, rtol=0)
+            torch.testing.assert_close(emb.out_wide(B, r), w_ref, atol=1e-5, rtol=1e-5)
+        gd = [(torch.randn(B, S * D, device="cuda") * 0.1).to(torch.bfloat16) for _ in range(nranks)]
+        for r in range(nranks):
+            emb.grad_deep_in(B, r).copy_(gd[r])
+            emb.grad_wide_in(B, r).zero_()
+        emb.push_raw(B, 1.0)
+        torch.cuda.synchronize()
+        G = torch.zeros_like(deep_t)
+        for r in range(nranks):
+            G.index_add_(0, ids[r].reshape(-1), gd[r].float().reshape(-1, D))
+        torch.testing.assert_close(emb.full_tables()[0], deep_t - 0.5 * G, atol=1e-4, rtol=1e-4)
+        sds = emb.shard_state_dicts()  # rank 0's shards
+        assert sorted(sds) == held[0] and all(sd["deep"].shape == (emb.shard_rows, D) for sd in sds.values())
+    finally:
+        comm.close()
