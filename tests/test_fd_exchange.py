@@ -42,3 +42,21 @@ def test_fd_exchange_three_processes():
         assert p.exitcode == 0
     for r in range(n):
         assert res[r] == sorted(f"hello from {o}" for o in range(n) if o != r)
+
+
+def test_native_runtime_host_side_under_sanitizers(tmp_path):
+    """ASAN+UBSAN and TSAN builds of csrc/comm_runtime.cu + tma_util.cu driven by eight threads
+    (tests/native/sanitize_host.cpp).  Without a GPU every entry point must fail cleanly; with one the threads
+    create / export / import / destroy arenas concurrently."""
+    import shutil
+    import subprocess
+
+    import pytest
+
+    if shutil.which("nvcc") is None:
+        pytest.skip("nvcc not available")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([os.path.join(root, "tests", "native", "build_sanitize.sh"), str(tmp_path)], capture_output=True,
+                       text=True, timeout=900)
+    assert r.returncode == 0 and "sanitize: ok" in r.stdout, (r.stdout + r.stderr)[-3000:]
+    assert "ERROR: AddressSanitizer" not in r.stderr and "WARNING: ThreadSanitizer" not in r.stderr
