@@ -82,7 +82,7 @@ def summarize_launches(path: str, title: str) -> None:
             a[3] += v
     tot = sum(a[1] for a in agg.values()) or 1.0
     name = os.path.splitext(os.path.basename(path))[0]
-    ours = ("bn_", "maxpool", "sgd_momentum", "softmax_xent", "preprocess", "emb_", "linear_tcgen05", "colsum", "wd_head", "conv1x1_tcgen05", "stem_wgrad",
+    ours = ("bn_", "maxpool", "sgd_momentum", "softmax_xent", "preprocess", "emb_", "linear_tcgen05", "colsum", "wd_head", "conv1x1_tcgen05", "stem_wgrad", "wgrad3x3", "wgrad_reduce", "allreduce_", "alltoall_", "broadcast_kernel", "barrier_kernel",
             "allreduce", "alltoall", "broadcast", "barrier_kernel")
     with open(os.path.join(OUT, name + ".launches.md"), "w") as f:
         f.write(f"# {title}\n\nEvery kernel of one training step, serialised under ncu (cold caches: compare shares, "
@@ -147,7 +147,14 @@ def main() -> int:
             "prof_wdhead": "Wide&Deep fused head: output layer + wide part + BCE loss (forward) and the masked gradient of the "
                            "top layer (backward), batch 32768 (profiles/run_wd_step.py)",
             "prof_collectives": "Fused all-reduce / all-to-all kernel bodies, 8 ranks emulated on one GPU "
-                                "(cooperative launch; bandwidths here are HBM-local, NVLink numbers are in r1/sweep_n8.json)"}
+                                "(cooperative launch; bandwidths here are HBM-local, NVLink numbers are in r1/sweep_n8.json)",
+            "prof_wgrad3x3": "tcgen05 3x3 weight-gradient kernel (halo tile + row-shifted descriptors) on the four ResNet-50 "
+                             "stages, batch 256 (profiles/run_wgrad3x3.py); round 2",
+            "prof_collectives2": "Round 2: fused collectives incl. K1b (reduce-scatter + SGD-momentum + master / parameter "
+                                 "broadcast, allreduce_sgd_kernel) and the unrolled all-to-all, 8 ranks emulated on one GPU "
+                                 "(HBM-local; ncu may not wrap a multi-rank run, NVLink numbers: r2/sweep_n*.json)",
+            "prof_wd2": "Round 2: Wide&Deep step kernels at full size (batch 32768, 16.7 M rows, one GPU): TMA-fed lookup "
+                        "writing the padded tower input, push, apply, tcgen05 tower layers (profiles/run_wd_step.py)"}
     for n, t in reps.items():
         p = os.path.join(SCRATCH, n + ".ncu-rep")
         if os.path.exists(p):
@@ -158,7 +165,11 @@ def main() -> int:
              "launches6": "ResNet-50 step launch list (batch 256, one B200)",
              "launches_wd2": "Wide&Deep step launch list (batch 32768, one B200) - 256-thread embedding blocks",
              "launches_wd3": "Wide&Deep step launch list (batch 32768, one B200) - before the fused head / loss kernel",
-             "launches_wd4": "Wide&Deep step launch list (batch 32768, one B200)"}
+             "launches_wd4": "Wide&Deep step launch list (batch 32768, one B200)",
+             "launches7": "ResNet-50 step launch list (batch 256, one B200) - round 2: tcgen05 3x3 weight gradients, "
+                          "warp-uniform MMA issue",
+             "launches_wd5": "Wide&Deep step launch list (batch 32768, one B200) - round 2: lookup writes the padded tower "
+                             "input in place, zero-copy gradient push"}
     for n, t in lists.items():
         p = os.path.join(SCRATCH, n + ".csv")
         if os.path.exists(p):
