@@ -181,6 +181,14 @@ size_t pdj_conv3x3_wgrad_ws_bytes(int N, int H, int W, int Cin, int Cout);
 int pdj_conv3x3_wgrad(const void* x, const void* dy, void* dw, void* ws, int N, int H, int W, int Cin, int Cout,
                       cudaStream_t st);
 
+/* Weight gradient of a linear layer / 1x1 convolution on the same MN-major tcgen05 pipeline:
+ * dw[No][Nc] (bf16, row-major) = dy[M][No]^T . x[M][Nc], row pitches ldy / ldx in elements (multiples of 8), No and Nc
+ * multiples of 8; split-K over 128-row blocks with a fixed-order reduce of the per-CTA partials in `ws`
+ * (pdj_wgrad_mn_ws_bytes bytes).  The MLP of deploy/examples/wide_and_deep.yaml and ResNet's 1x1 convolutions. */
+size_t pdj_wgrad_mn_ws_bytes(int M, int No, int Nc);
+int pdj_wgrad_mn(const void* x, const void* dy, void* dw, void* ws, int M, int No, int Nc, int ldx, int ldy,
+                 cudaStream_t st);
+
 /* ---- ResNet-50 step kernels (csrc/bn_act.cu, csrc/optim_misc.cu) -----------
  * The workload of deploy/examples/resnet.yaml:13-19. NHWC bf16 activations
  * viewed as [M, C]; fp32 statistics. */

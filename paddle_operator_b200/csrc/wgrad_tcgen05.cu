@@ -248,6 +248,135 @@ void launch_reduce(const float* partial, int nparts, size_t n, __nv_bfloat16* ou
     wgrad_reduce_kernel<1><<<(unsigned)((n / 4 + 255) / 256), 256, 0, st>>>(partial, nparts, n, out);
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// dW[o][c] = sum over rows r of dY[r][o] * X[r][c]: the weight gradient of a 1x1 convolution / a linear layer.  Both
+// operands are row-major [rows][channels], i.e. MN-major for the MMA with the reduction running over tile rows.  A CTA
+// owns [128 o] x [NC <= 256 c] fp32 accumulators for its whole life (one N = NC instruction per 16 rows: operand reads
+// 4 KiB + NC * 32 B per instruction stay under the tensor pipe's time from NC = 128 up), walks its share of the
+// 128-row blocks (split-K across CTAs) and writes a partial tile; wgrad_reduce_kernel adds them in a fixed order.
+// Out-of-range rows / channels of a box arrive as zeros, so no shape needs padding.
+struct WgMnCfg {
+  int M, No, Nc;            // rows (reduction), output channels (dY columns), input channels (X columns)
+  int nc_tile, groups_c;    // channels per CTA tile (multiple of 64, <= 256) = groups_c x 64
+  int tiles_c, tiles, S, stages, blocks;
+  uint32_t slot_bytes;
+};
+constexpr int WM_KB = 128;                     // rows per block
+constexpr int WM_GROUP_BYTES = WM_KB * 128;    // one 64-channel group of a block: 16 KiB
+
+__global__ void __launch_bounds__(WG_THREADS, 1)
+wgrad_mn_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constant__ CUtensorMap tma_dy,
+                        float* __restrict__ partial, const WgMnCfg c) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  const uint32_t base = (raw + 1023u) & ~1023u;
+  const uint32_t bars = base + (uint32_t)c.stages * c.slot_bytes;
+  const uint32_t full0 = bars, empty0 = bars + 8 * MAX_STAGES, done = empty0 + 8 * MAX_STAGES, tmem_slot = done + 8;
+  uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(smem_raw + (tmem_slot - raw));
+  const int warp = (int)warp_uniform(threadIdx.x >> 5), lane = threadIdx.x & 31;
+  const int tile = (int)blockIdx.x % c.tiles, split = (int)blockIdx.x / c.tiles;
+  const int o0 = (tile / c.tiles_c) * 128, c0 = (tile % c.tiles_c) * c.nc_tile;
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_x) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_dy) : "memory");
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      for (int s = 0; s < c.stages; ++s) {
+        mbar_init(full0 + 8 * s, 1);
+        mbar_init(empty0 + 8 * s, 1);
+      }
+      mbar_init(done, 1);
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(256) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem_base = warp_uniform(*tmem_slot_ptr);
+  const uint32_t x_off = 2u * WM_GROUP_BYTES;  // slot = [dY group 0][dY group 1][X group 0 .. groups_c - 1]
+
+  if (warp == 0) {
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (int b = split; b < c.blocks; b += c.S, ++it) {
+        const uint32_t s = it % (uint32_t)c.stages, ph = (it / (uint32_t)c.stages) & 1u;
+        const uint32_t slot = base + s * c.slot_bytes;
+        mbar_wait(empty0 + 8 * s, ph ^ 1u);
+        mbar_expect_tx(full0 + 8 * s, (uint32_t)(2 + c.groups_c) * WM_GROUP_BYTES);
+        for (int g = 0; g < 2; ++g) tma_load_2d(slot + g * WM_GROUP_BYTES, &tma_dy, o0 + 64 * g, b * WM_KB, full0 + 8 * s);
+        for (int g = 0; g < c.groups_c; ++g)
+          tma_load_2d(slot + x_off + g * WM_GROUP_BYTES, &tma_x, c0 + 64 * g, b * WM_KB, full0 + 8 * s);
+      }
+    }
+  } else if (warp == 1) {
+    const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(c.nc_tile >> 3) << 17) |
+                           ((128u >> 4) << 24);
+    const uint64_t d0 = umma_desc_ex(0, WM_GROUP_BYTES, 1024, 2);  // 64-channel groups one tile apart
+    uint32_t it = 0;
+    for (int b = split; b < c.blocks; b += c.S, ++it) {
+      const uint32_t s = it % (uint32_t)c.stages, ph = (it / (uint32_t)c.stages) & 1u;
+      const uint32_t slot = base + s * c.slot_bytes;
+      mbar_wait(full0 + 8 * s, ph);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      uint64_t da = d0 + (uint64_t)(slot >> 4), db = d0 + (uint64_t)((slot + x_off) >> 4);
+#pragma unroll
+      for (int ks = 0; ks < WM_KB / 16; ++ks) {
+        umma_f16_elect(tmem_base, da, db, idesc, (uint32_t)((it | (uint32_t)ks) != 0u));
+        da += 2048 >> 4;
+        db += 2048 >> 4;
+      }
+      umma_commit_elect(empty0 + 8 * s);
+    }
+    umma_commit_elect(done);
+  } else {
+    const int q = warp & 3;
+    mbar_wait_warp_sleepy(done, 0, 512);
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const bool has_work = split < c.blocks;
+    const int pitch = c.nc_tile + 4;  // floats
+    const uint32_t stg = base + (uint32_t)(warp - 2) * (32u * (256 + 4) * 4u);
+    for (int col = 0; col < c.nc_tile; col += 16) {
+      uint32_t r[16];
+      asm volatile(
+          "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+          : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+            "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+          : "r"(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)col)
+          : "memory");
+      asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+      for (int v = 0; v < 4; ++v)
+        asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(stg + (uint32_t)(lane * pitch + col + 4 * v) * 4u),
+                     "r"(has_work ? r[4 * v] : 0u), "r"(has_work ? r[4 * v + 1] : 0u), "r"(has_work ? r[4 * v + 2] : 0u),
+                     "r"(has_work ? r[4 * v + 3] : 0u)
+                     : "memory");
+    }
+    __syncwarp();
+    // one row per trip: the warp writes the row's valid columns as consecutive float4s
+    for (int rl = 0; rl < 32; ++rl) {
+      const int o = o0 + q * 32 + rl;
+      if (o >= c.No) break;
+      float* drow = partial + ((size_t)split * c.No + o) * c.Nc + c0;
+      for (int cc = lane * 4; cc < c.nc_tile && c0 + cc < c.Nc; cc += 128) {
+        float4 v;
+        asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];"
+                     : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                     : "r"(stg + (uint32_t)(rl * pitch + cc) * 4u));
+        *reinterpret_cast<float4*>(drow + cc) = v;
+      }
+    }
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 1) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(256) : "memory");
+  }
+}
+
 int round_up(int a, int b) { return (a + b - 1) / b * b; }
 
 // Chooses rows per block (R), stages and the split for one layer shape.  Returns 0 when the shape is not supported.
@@ -336,6 +465,61 @@ int pdj_conv3x3_wgrad(const void* x, const void* dy, void* dw, void* ws, int N, 
   PDJ_CUDA_CHECK(cudaGetLastError());
   const size_t n = (size_t)Cout * WG_TAPS * Cin;
   launch_reduce((const float*)ws, c.S, n, (__nv_bfloat16*)dw, st);
+  PDJ_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+static int make_mn_cfg(int M, int No, int Nc, WgMnCfg* out) {
+  if (M < 1 || No < 1 || Nc < 8 || Nc % 8 != 0 || No % 8 != 0) return 0;
+  WgMnCfg c{};
+  c.M = M; c.No = No; c.Nc = Nc;
+  const int parts = (Nc + 255) / 256;
+  c.nc_tile = round_up((Nc + parts - 1) / parts, 64);
+  c.groups_c = c.nc_tile / 64;
+  c.tiles_c = (Nc + c.nc_tile - 1) / c.nc_tile;
+  c.tiles = ((No + 127) / 128) * c.tiles_c;
+  c.blocks = (M + WM_KB - 1) / WM_KB;
+  c.slot_bytes = (uint32_t)(2 + c.groups_c) * WM_GROUP_BYTES;
+  c.stages = (SMEM_LIMIT - 1024 - 512) / (int)c.slot_bytes;
+  if (c.stages > MAX_STAGES) c.stages = MAX_STAGES;
+  if (c.stages < 2) return 0;
+  c.S = pdj_tc_sm_count() / c.tiles;
+  if (c.S < 1) c.S = 1;
+  if (c.S > c.blocks) c.S = c.blocks;
+  *out = c;
+  return 1;
+}
+
+size_t pdj_wgrad_mn_ws_bytes(int M, int No, int Nc) {
+  WgMnCfg c;
+  if (!make_mn_cfg(M, No, Nc, &c)) return 0;
+  return (size_t)c.S * No * Nc * sizeof(float);
+}
+
+// dw[No][Nc] (bf16, row-major) = dy[M][No]^T . x[M][Nc]: the weight gradient of a linear layer or of a 1x1
+// convolution over NHWC activations viewed as [pixels][channels].  Row pitches ldy / ldx in elements (multiples of
+// 8); No and Nc multiples of 8.  `ws`: pdj_wgrad_mn_ws_bytes(M, No, Nc) bytes.
+int pdj_wgrad_mn(const void* x, const void* dy, void* dw, void* ws, int M, int No, int Nc, int ldx, int ldy,
+                 cudaStream_t st) {
+  WgMnCfg c;
+  if (!make_mn_cfg(M, No, Nc, &c) || ws == nullptr || ldx % 8 != 0 || ldy % 8 != 0 || ldx < Nc || ldy < No ||
+      ((uintptr_t)x & 15) || ((uintptr_t)dy & 15) || ((uintptr_t)dw & 7)) {
+    pdj_set_error("pdj_wgrad_mn: need No, Nc multiples of 8, row pitches multiples of 8 elements, 16-byte aligned tensors "
+                  "and a workspace (M=%d No=%d Nc=%d ldx=%d ldy=%d)", M, No, Nc, ldx, ldy);
+    return -1;
+  }
+  static bool attr = false;
+  if (!attr) {
+    PDJ_CUDA_CHECK(cudaFuncSetAttribute(wgrad_mn_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+    attr = true;
+  }
+  CUtensorMap mx, my;
+  if (int r = pdj_tc_make_map(&mx, x, M, Nc, ldx, 64, WM_KB, true)) return r;
+  if (int r = pdj_tc_make_map(&my, dy, M, No, ldy, 64, WM_KB, true)) return r;
+  const int smem = 1024 + c.stages * (int)c.slot_bytes + 512;
+  wgrad_mn_tcgen05_kernel<<<c.tiles * c.S, WG_THREADS, smem, st>>>(mx, my, (float*)ws, c);
+  PDJ_CUDA_CHECK(cudaGetLastError());
+  launch_reduce((const float*)ws, c.S, (size_t)No * Nc, (__nv_bfloat16*)dw, st);
   PDJ_CUDA_CHECK(cudaGetLastError());
   return 0;
 }

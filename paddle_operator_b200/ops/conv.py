@@ -99,8 +99,11 @@ def _rows(t: torch.Tensor) -> torch.Tensor:
 
 
 def _wgrad_1x1(dy: torch.Tensor, x: torch.Tensor, weight: torch.Tensor) -> torch.Tensor:
-    """dW[Cout,Cin,1,1] = dY^T[Cout,M] @ X[M,Cin] (library GEMM)."""
-    return torch.mm(_rows(dy).t(), _rows(x)).view(weight.shape)
+    """dW[Cout,Cin,1,1] = dY^T[Cout,M] @ X[M,Cin] on the MN-major tcgen05 kernel (ops.gemm.wgrad_mn)."""
+    from .gemm import wgrad_mn
+
+    _launches[0] += 2
+    return wgrad_mn(_rows(dy), _rows(x)).view(weight.shape)
 
 
 class _Conv1x1StatsFn(torch.autograd.Function):

@@ -12,6 +12,8 @@ from __future__ import annotations
 
 from typing import Optional
 
+import os
+
 import torch
 
 from . import _lib
@@ -69,10 +71,32 @@ class _LinearActFn(torch.autograd.Function):
             # dX[M,K] = dZ[M,N] @ W[N,K]  ==  dZ . (W^T)[K,N]^T : the B operand is W^T, K-major over N
             dx = linear_bf16(dz, weight.t().contiguous())
         if ctx.needs_input_grad[1]:
-            dw = dz.t().mm(x)
+            dw = wgrad_mn(dz, x)
         if ctx.has_bias and ctx.needs_input_grad[2]:
             db = dz.float().sum(0).to(ctx.bias_dtype)
         return dx, dw, db, None, None
+
+
+def wgrad_mn(dy: torch.Tensor, x: torch.Tensor) -> torch.Tensor:
+    """dW[No, Nc] = dy[M, No]^T @ x[M, Nc] (bf16) on the MN-major tcgen05 kernel (csrc/wgrad_tcgen05.cu: both operands
+    read as they sit in memory, accumulators resident in tensor memory, split-K with a fixed-order reduce).  Falls
+    back to the library GEMM for shapes the kernel does not take."""
+    m, no = dy.shape
+    nc = x.shape[1]
+    ok = (dy.is_cuda and dy.dtype == torch.bfloat16 and x.dtype == torch.bfloat16 and x.shape[0] == m and no % 8 == 0
+          and nc % 8 == 0 and dy.stride(1) == 1 and x.stride(1) == 1 and dy.stride(0) % 8 == 0 and x.stride(0) % 8 == 0
+          and dy.data_ptr() % 16 == 0 and x.data_ptr() % 16 == 0 and os.environ.get("PDJ_WGRAD_MN", "1") == "1")
+    if not ok:
+        return dy.t().mm(x)
+    lib = _lib.load()
+    nbytes = lib.pdj_wgrad_mn_ws_bytes(m, no, nc)
+    if nbytes == 0:
+        return dy.t().mm(x)
+    dw = torch.empty((no, nc), dtype=torch.bfloat16, device=x.device)
+    ws = torch.empty(nbytes, dtype=torch.uint8, device=x.device)
+    _lib.check(lib.pdj_wgrad_mn(x.data_ptr(), dy.data_ptr(), dw.data_ptr(), ws.data_ptr(), m, no, nc, x.stride(0),
+                                dy.stride(0), torch.cuda.current_stream().cuda_stream), "wgrad_mn")
+    return dw
 
 
 def linear_act(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] = None, relu: bool = False,

@@ -5,7 +5,7 @@
 Forward: L launches of the tcgen05 kernel (bias + ReLU in the epilogue).
 Backward, per layer from the top:
     db_l = colsum(dz_l)                                 (csrc/optim_misc.cu)
-    dW_l = dz_l^T h_{l-1}                               (library GEMM)
+    dW_l = dz_l^T h_{l-1}                               MN-major tcgen05 kernel (csrc/wgrad_tcgen05.cu)
     dz_{l-1} = (dz_l W_l) * (h_{l-1} > 0)               tcgen05 kernel, ReLU derivative as epilogue mask
 so the only stand-alone mask pass is the one on the incoming gradient.
 
@@ -17,7 +17,7 @@ from __future__ import annotations
 import torch
 
 from . import _lib
-from .gemm import linear_bf16
+from .gemm import linear_bf16, wgrad_mn
 
 
 def colsum(x: torch.Tensor) -> torch.Tensor:
@@ -58,7 +58,7 @@ class _FusedMLPFn(torch.autograd.Function):
         dx = None
         for l in range(n, 0, -1):  # layer l maps hs[l-1] -> hs[l] with ws[l-1]
             dbs[l - 1] = colsum(dz).to(ctx.bias_dtypes[l - 1])
-            dws[l - 1] = dz.t().mm(hs[l - 1])
+            dws[l - 1] = wgrad_mn(dz, hs[l - 1])
             if l > 1:
                 dz = linear_bf16(dz, ws[l - 1].t().contiguous(), mask=hs[l - 1])
             elif ctx.needs_input_grad[0]:

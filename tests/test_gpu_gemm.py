@@ -238,3 +238,17 @@ def test_stem_s2d_conv_matches_conv2d(n, img):
     wb = w.float().requires_grad_(True)
     torch.nn.functional.conv2d(x.float(), wb).backward(g.float())
     torch.testing.assert_close(wa.grad.float(), wb.grad, atol=0.5, rtol=5e-2)
+
+
+@pytest.mark.parametrize("m,no,nc", [(32768, 400, 432), (32768, 400, 400), (1000, 64, 256), (50176, 256, 1024),
+                                     (12544, 2048, 512), (300, 8, 8), (4096, 1000, 2048), (802816 // 4, 256, 64)])
+def test_wgrad_mn_matches_fp32(m, no, nc):
+    from paddle_operator_b200.ops.gemm import wgrad_mn
+
+    torch.manual_seed(m + no)
+    dy = (torch.randn(m, no, device="cuda") * 0.1).to(torch.bfloat16)
+    x = torch.randn(m, nc + 8, device="cuda").to(torch.bfloat16)[:, :nc]  # a row pitch wider than the row
+    dw = wgrad_mn(dy, x)
+    ref = dy.float().t() @ x.float()
+    assert dw.shape == (no, nc) and dw.dtype == torch.bfloat16
+    torch.testing.assert_close(dw.float(), ref, atol=1e-2 * float(ref.abs().max()) + 1e-3, rtol=2e-2)
