@@ -349,7 +349,9 @@ class Communicator:
         """Thread blocks for a collective of `nbytes` (same sweeps): launch-latency-bound messages want few blocks
         (every block takes part in the device barrier), bandwidth-bound ones want the whole chip."""
         if algo == AR_NVLS:
-            return 32
+            # 8 ranks: 32 and 148 blocks tie at every size; 4 ranks: 148 wins from 32 MiB up (r2/sweep_n4.json:
+            # 613 vs 699 us at 256 MiB)
+            return 148 if nbytes >= (32 << 20) else 32
         if nbytes <= (256 << 10):
             return 16
         if nbytes <= (1 << 20):
