@@ -99,7 +99,7 @@ struct PdjEmbTable {
   size_t acc_deep_off;  /* Adagrad accumulators, same shapes */
   size_t acc_wide_off;
   size_t flag_off;      /* u8 [rows_per_shard rounded up to 128]: row touched this step */
-  size_t list_off;      /* unused (kept for ABI stability) */
+  size_t list_off;      /* 0: separate arrays; S > 0: one S-byte record per row holds all six parts (see csrc/embedding.cu) */
   size_t count_off;     /* u32 [2]: touched rows this step, last step */
   long long rows_per_shard;
   unsigned int list_cap; /* number of table shards P (the job's pserver count); 0 = one per rank */

@@ -59,6 +59,14 @@ __device__ __forceinline__ uint32_t atom_add_sys(uint32_t* p, uint32_t v) {
   return old;
 }
 
+// Byte distance between consecutive rows of the deep arrays / of the wide arrays.  t.list_off = 0: separate dense
+// arrays (dim * 4 and 4 bytes).  t.list_off = S > 0: ONE record of S bytes per row holds the row's weights, Adagrad
+// accumulators and gradient staging (deep and wide of each next to one another; the *_off fields point at the
+// parts of record 0), so a lookup touches one 128-byte line per row instead of two, and the apply pass reads and
+// writes whole aligned records (256 B for dim 16) instead of six scattered sectors.
+__device__ __forceinline__ size_t emb_sd(const PdjEmbTable& t) { return t.list_off ? t.list_off : (size_t)t.dim * 4; }
+__device__ __forceinline__ size_t emb_sw(const PdjEmbTable& t) { return t.list_off ? t.list_off : (size_t)4; }
+
 // Where row `id` lives.  The table is cut into P = t.list_cap shards (0 = one per rank): the PSERVER count of the
 // job (spec.ps.replicas, controllers/paddlejob_helper.go:225-235,258-260).  Shard j = id % P sits on GPU j % NR in
 // slot j / NR of that GPU's table, at row id / P of the slot; a slot is t.rows_per_shard rows.
@@ -109,12 +117,12 @@ emb_lookup_kernel(PdjComm c, PdjEmbTable t, size_t ids_off, size_t out_deep_off,
         int owner;
         long long row;
         emb_locate(t, NR, id, &owner, &row);
-        const float4 v = ld_f4(c.base[owner] + t.deep_off + ((size_t)row * D + part * 4) * 4);
+        const float4 v = ld_f4(c.base[owner] + t.deep_off + (size_t)row * emb_sd(t) + part * 16);
         uint2 o;
         o.x = pdj_f2_to_bf2(v.x, v.y);
         o.y = pdj_f2_to_bf2(v.z, v.w);
         *reinterpret_cast<uint2*>(out_deep + (size_t)b * out_pitch + (size_t)s * D + part * 4) = o;
-        if (part == 0 && t.has_wide) wide += ld_f1(c.base[owner] + t.wide_off + (size_t)row * 4);
+        if (part == 0 && t.has_wide) wide += ld_f1(c.base[owner] + t.wide_off + (size_t)row * emb_sw(t));
       }
     }
     emb_write_tail(c, rank, out_deep, b, S * D, out_pitch, dense_off, dense_n, lane);
@@ -174,12 +182,12 @@ emb_lookup_tma_kernel(PdjComm c, PdjEmbTable t, size_t ids_off, size_t out_deep_
       int owner;
       long long row;
       emb_locate(t, NR, id, &owner, &row);
-      const char* src = c.base[owner] + t.deep_off + (size_t)row * row_bytes;
+      const char* src = c.base[owner] + t.deep_off + (size_t)row * emb_sd(t);
       const uint32_t dst = tile + ((uint32_t)buf * 32u + (uint32_t)lane) * row_bytes;
       asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
                    "l"(src), "r"(row_bytes), "r"(bar)
                    : "memory");
-      if (t.has_wide) wv = ld_f1(c.base[owner] + t.wide_off + (size_t)row * 4);
+      if (t.has_wide) wv = ld_f1(c.base[owner] + t.wide_off + (size_t)row * emb_sw(t));
     }
     return wv;
   };
@@ -266,10 +274,10 @@ emb_push_kernel(PdjComm c, PdjEmbTable t, size_t ids_off, size_t gdeep_off, size
       const uint2 g = *reinterpret_cast<const uint2*>(gdeep + (size_t)b * g_pitch + (size_t)s * D + part * 4);
       const float2 g0 = pdj_bf2_to_f2(g.x), g1 = pdj_bf2_to_f2(g.y);
       char* ob = c.base[owner];
-      const size_t deep_dst = (mode == 1 ? t.deep_off : t.gdeep_off) + ((size_t)row * D + part * 4) * 4;
+      const size_t deep_dst = (mode == 1 ? t.deep_off : t.gdeep_off) + (size_t)row * emb_sd(t) + part * 16;
       red_add_f4(ob + deep_dst, g0.x * k, g0.y * k, g1.x * k, g1.y * k);
       if (part == 0) {
-        if (t.has_wide) red_add_f1(ob + (mode == 1 ? t.wide_off : t.gwide_off) + (size_t)row * 4, gw);
+        if (t.has_wide) red_add_f1(ob + (mode == 1 ? t.wide_off : t.gwide_off) + (size_t)row * emb_sw(t), gw);
         if (mode == 0) {
           // Mark the row as touched: an idempotent one-byte store.  (A first version claimed a slot in
           // a per-owner list with atom.exch + atom.add on ONE counter; 850 k returning atomics on a
@@ -330,7 +338,7 @@ emb_apply_kernel(PdjComm c, PdjEmbTable t, int opt, float lr, float eps) {
       const int idx = i0 + sub;
       if (idx >= total) continue;
       const uint32_t row = queue[wib][idx];
-      const size_t o = ((size_t)row * D + part * 4) * 4;
+      const size_t o = (size_t)row * emb_sd(t) + part * 16;
       float4* gp = reinterpret_cast<float4*>(base + t.gdeep_off + o);
       float4* wp = reinterpret_cast<float4*>(base + t.deep_off + o);
       const float4 g = *gp;
@@ -348,11 +356,11 @@ emb_apply_kernel(PdjComm c, PdjEmbTable t, int opt, float lr, float eps) {
       *wp = wv;
       *gp = make_float4(0.f, 0.f, 0.f, 0.f);
       if (part == 0 && t.has_wide) {
-        float* gwp = reinterpret_cast<float*>(base + t.gwide_off) + row;
-        float* wwp = reinterpret_cast<float*>(base + t.wide_off) + row;
+        float* gwp = reinterpret_cast<float*>(base + t.gwide_off + (size_t)row * emb_sw(t));
+        float* wwp = reinterpret_cast<float*>(base + t.wide_off + (size_t)row * emb_sw(t));
         const float gwv = *gwp;
         if (opt == 1) {
-          float* awp = reinterpret_cast<float*>(base + t.acc_wide_off) + row;
+          float* awp = reinterpret_cast<float*>(base + t.acc_wide_off + (size_t)row * emb_sw(t));
           const float a = *awp + gwv * gwv;
           *awp = a;
           *wwp -= lr * gwv * rsqrtf(a + eps);

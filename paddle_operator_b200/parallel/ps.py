@@ -21,6 +21,7 @@ checkpoints are one `ps-<j>.pt` per shard.
 from __future__ import annotations
 
 import ctypes
+import os
 from typing import Optional
 
 import torch
@@ -62,16 +63,26 @@ class ShardedEmbedding:
         R, D = self.rows_per_shard, dim
         a = comm.alloc
         t = PdjEmbTable()
-        t.deep_off = a(R * D * 4)
-        t.wide_off = a(R * 4)
-        t.gdeep_off = a(R * D * 4)
-        t.gwide_off = a(R * 4)
-        t.acc_deep_off = a(R * D * 4)
-        t.acc_wide_off = a(R * 4)
+        # One record per row (default): | w deep D | w wide, pad 4 | acc deep D | acc wide, pad 4 | g deep D | g wide, pad 4 |
+        # rounded up to 128 B, so a lookup touches one line and the optimizer pass one or two adjacent ones instead of
+        # six arrays.  PDJ_EMB_LAYOUT=arrays keeps six separate arrays (the A/B arm).
+        self.record_floats = 0
+        if os.environ.get("PDJ_EMB_LAYOUT", "record") == "record":
+            self.record_floats = ((3 * D + 12) * 4 + 127) // 128 * 32
+            base = a(R * self.record_floats * 4)
+            t.deep_off, t.wide_off = base, base + D * 4
+            t.acc_deep_off, t.acc_wide_off = base + (D + 4) * 4, base + (2 * D + 4) * 4
+            t.gdeep_off, t.gwide_off = base + (2 * D + 8) * 4, base + (3 * D + 8) * 4
+        else:
+            t.deep_off = a(R * D * 4)
+            t.wide_off = a(R * 4)
+            t.gdeep_off = a(R * D * 4)
+            t.gwide_off = a(R * 4)
+            t.acc_deep_off = a(R * D * 4)
+            t.acc_wide_off = a(R * 4)
         self._flag_bytes = (R + 127) // 128 * 128
         t.flag_off = a(self._flag_bytes)  # one byte per row: "touched this step"
-        cap = 0
-        t.list_off = 0
+        t.list_off = self.record_floats * 4  # record stride in bytes; 0 = separate arrays
         t.count_off = a(256)
         t.rows_per_shard, t.list_cap, t.dim, t.has_wide = self.shard_rows, self.num_shards, D, int(has_wide)
         self.t = t
@@ -89,23 +100,40 @@ class ShardedEmbedding:
     def _ranks(self):
         return range(self.nranks) if self.comm.emulate else [self.comm.rank]
 
+    def _part(self, off: int, width: int, rank: Optional[int] = None) -> torch.Tensor:
+        """[rows_per_shard, width] fp32 view of one part of the table (width 0: a vector).  Strided in the record
+        layout, so index / copy_ / clone it - do not .view() it."""
+        R, F = self.rows_per_shard, self.record_floats
+        if not F:
+            return self.comm.tensor(off, (R, width) if width else (R,), torch.float32, rank)
+        rec = self.comm.tensor(self.t.deep_off, (R, F), torch.float32, rank)
+        c = (off - self.t.deep_off) // 4
+        return rec[:, c:c + width] if width else rec[:, c]
+
     def shard(self, rank: Optional[int] = None) -> torch.Tensor:
-        return self.comm.tensor(self.t.deep_off, (self.rows_per_shard, self.dim), torch.float32, rank)
+        return self._part(self.t.deep_off, self.dim, rank)
 
     def shard_wide(self, rank: Optional[int] = None) -> torch.Tensor:
-        return self.comm.tensor(self.t.wide_off, (self.rows_per_shard,), torch.float32, rank)
+        return self._part(self.t.wide_off, 0, rank)
+
+    def staging(self, rank: Optional[int] = None):
+        """(deep, wide) gradient staging rows: the sums pushed this step, zero between steps."""
+        return self._part(self.t.gdeep_off, self.dim, rank), self._part(self.t.gwide_off, 0, rank)
 
     def _init(self, scale: float, seed: int) -> None:
+        dev = f"cuda:{self.comm.device}"
         for r in self._ranks():
-            g = torch.Generator(device=f"cuda:{self.comm.device}").manual_seed(seed * 1000 + r)
-            self.shard(r).copy_(torch.randn(self.rows_per_shard, self.dim, generator=g,
-                                            device=f"cuda:{self.comm.device}") * scale)
-            self.shard_wide(r).copy_(torch.randn(self.rows_per_shard, generator=g,
-                                                 device=f"cuda:{self.comm.device}") * scale)
-            for off, n in ((self.t.gdeep_off, self.rows_per_shard * self.dim), (self.t.gwide_off, self.rows_per_shard),
-                           (self.t.acc_deep_off, self.rows_per_shard * self.dim),
-                           (self.t.acc_wide_off, self.rows_per_shard), (self.t.flag_off, self._flag_bytes // 4),
-                           (self.t.count_off, 64)):
+            g = torch.Generator(device=dev).manual_seed(seed * 1000 + r)
+            deep = torch.randn(self.rows_per_shard, self.dim, generator=g, device=dev) * scale
+            wide = torch.randn(self.rows_per_shard, generator=g, device=dev) * scale
+            if self.record_floats:
+                self.comm.tensor(self.t.deep_off, (self.rows_per_shard * self.record_floats,), torch.float32, r).zero_()
+            else:
+                for part in (*self.staging(r), *self._acc(r)):
+                    part.zero_()
+            self.shard(r).copy_(deep)
+            self.shard_wide(r).copy_(wide)
+            for off, n in ((self.t.flag_off, self._flag_bytes // 4), (self.t.count_off, 64)):
                 self.comm.tensor(off, (n,), torch.float32, r).zero_()
 
     def shards_of(self, rank: int) -> list:
@@ -185,10 +213,8 @@ class ShardedEmbedding:
         The sparse optimizer step runs inside backward."""
         return _LookupFn.apply(self, ids, torch.zeros((), device=ids.device, requires_grad=True))
 
-    def _acc(self):
-        R = self.rows_per_shard
-        return (self.comm.tensor(self.t.acc_deep_off, (R, self.dim), torch.float32),
-                self.comm.tensor(self.t.acc_wide_off, (R,), torch.float32))
+    def _acc(self, rank: Optional[int] = None):
+        return self._part(self.t.acc_deep_off, self.dim, rank), self._part(self.t.acc_wide_off, 0, rank)
 
     def shard_state_dicts(self) -> dict:
         """{shard index j: state} for the shards THIS rank holds - one `ps-<j>.pt` each (utils/checkpoint.py), named
