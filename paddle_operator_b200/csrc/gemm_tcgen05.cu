@@ -110,14 +110,33 @@ linear_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
       asm volatile("bar.sync 1, %0;" ::"n"(32 * EPI_WARPS) : "memory");  // previous tile's bias / staging are free
       for (int j = et; j < block_n; j += 32 * EPI_WARPS) bias_s[j] = (bias != nullptr && n0 + j < N) ? __ldg(bias + n0 + j) : 0.f;
       asm volatile("bar.sync 1, %0;" ::"n"(32 * EPI_WARPS) : "memory");
+      const int row = m0 + q * 32 + lane;
+      if (mask != nullptr && row < M) {
+        const char* mrow = reinterpret_cast<const char*>(mask + (size_t)row * ldo + n0 + c_begin);
+        const int nb = ((n0 + c_end < N ? c_end : N - n0) - c_begin) * 2;
+        for (int b = 0; b < nb; b += 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(mrow + b));
+      }
       mbar_wait(tfull0 + 8 * buf, aph);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-      const int row = m0 + q * 32 + lane;
       const uint32_t taddr_row = tmem_base + buf * MAX_BN + ((uint32_t)(q * 32) << 16);
       for (int c0 = c_begin; c0 < c_end; c0 += 32) {
         // two 16-column loads in flight, one wait
         uint32_t r[32];
         const bool second = c0 + 16 < c_end;
+        // ReLU mask of this chunk: one lane = one row, 16-byte loads (a full 32-byte sector per 16 columns), issued
+        // ahead of the TMEM loads so that both latencies overlap
+        uint4 mvec[4] = {};
+        if (mask != nullptr && row < M) {
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            const int col = n0 + c0 + 16 * h;
+            if ((h == 0 || second) && col + 16 <= N && (((size_t)row * ldo + col) & 7) == 0) {
+              const uint4* mp = reinterpret_cast<const uint4*>(mask + (size_t)row * ldo + col);
+              mvec[2 * h] = __ldg(mp);
+              mvec[2 * h + 1] = __ldg(mp + 1);
+            }
+          }
+        }
         asm volatile(
             "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
             : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
@@ -146,9 +165,21 @@ linear_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
           }
           if (mask != nullptr && row < M) {
             const __nv_bfloat16* mk = mask + (size_t)row * ldo + col;
+            if (col + 16 <= N && (((size_t)row * ldo + col) & 7) == 0) {
+              const uint4 m0v = mvec[2 * h], m1v = mvec[2 * h + 1];
+              const uint32_t mw[8] = {m0v.x, m0v.y, m0v.z, m0v.w, m1v.x, m1v.y, m1v.z, m1v.w};
 #pragma unroll
-            for (int j = 0; j < 16; ++j)
-              if (col + j < N && !(__bfloat162float(mk[j]) > 0.f)) v[j] = 0.f;
+              for (int j = 0; j < 8; ++j) {
+                // bf16 > 0  <=>  bits in [0x0001, 0x7f80] (sign clear, not zero, not NaN)
+                const uint32_t lo = mw[j] & 0xffffu, hi = mw[j] >> 16;
+                if (lo - 1u >= 0x7f80u) v[2 * j] = 0.f;
+                if (hi - 1u >= 0x7f80u) v[2 * j + 1] = 0.f;
+              }
+            } else {
+#pragma unroll
+              for (int j = 0; j < 16; ++j)
+                if (col + j < N && !(__bfloat162float(mk[j]) > 0.f)) v[j] = 0.f;
+            }
           }
           uint4 p0, p1;
           p0.x = pdj_f2_to_bf2(v[0], v[1]); p0.y = pdj_f2_to_bf2(v[2], v[3]);

@@ -169,7 +169,11 @@ def main() -> int:
              "launches7": "ResNet-50 step launch list (batch 256, one B200) - round 2: tcgen05 3x3 weight gradients, "
                           "warp-uniform MMA issue",
              "launches_wd5": "Wide&Deep step launch list (batch 32768, one B200) - round 2: lookup writes the padded tower "
-                             "input in place, zero-copy gradient push"}
+                             "input in place, zero-copy gradient push",
+             "launches8": "ResNet-50 step launch list (batch 256, one B200) - round 2, final: 1x1 / linear weight gradients "
+                          "on the MN-major tcgen05 kernel",
+             "launches_wd6": "Wide&Deep step launch list (batch 32768, one B200) - round 2, final: MN-major tcgen05 weight "
+                             "gradient for the tower, one record per table row"}
     for n, t in lists.items():
         p = os.path.join(SCRATCH, n + ".csv")
         if os.path.exists(p):
