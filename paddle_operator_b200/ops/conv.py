@@ -37,6 +37,10 @@ def launch_count() -> int:
     return _launches[0]
 
 
+# backward of a 1x1 convolution WITHOUT a skip gradient on the own kernels (dgrad GEMM + MN-major wgrad) when the input
+# is at least this large; smaller layers stay in the library (A/B: profiles/r2/conv1x1_bwd_ab.md)
+OWN_BWD = os.environ.get("PDJ_CONV1X1_OWN_BWD", "1") == "1"
+OWN_BWD_MIN_BYTES = int(float(os.environ.get("PDJ_CONV1X1_OWN_BWD_MIN_MB", "0")) * (1 << 20))
 MIN_OUTPUT_BYTES = int(float(os.environ.get("PDJ_CONV1X1_MIN_MB", "150")) * (1 << 20))
 
 
@@ -134,9 +138,18 @@ class _Conv1x1StatsFn(torch.autograd.Function):
             dy = dy.contiguous(memory_format=torch.channels_last)
         o, c = weight.shape[0], weight.shape[1]
         fuse = (ctx.carry_skip and dskip is not None and ctx.needs_input_grad[0] and c % 64 == 0 and o % 8 == 0)
+        own = (not fuse and OWN_BWD and c % 64 == 0 and o % 8 == 0 and x.numel() * 2 >= OWN_BWD_MIN_BYTES
+               and x.is_contiguous(memory_format=torch.channels_last))
         if fuse:
             # weight gradient as a plain library GEMM dY^T @ X (a wgrad-only cuDNN call picks a far slower kernel)
             dx, dw = None, (_wgrad_1x1(dy, x, weight) if ctx.needs_input_grad[1] else None)
+        elif own:
+            # no skip gradient to fold in (conv3 of a bottleneck): the same two kernels without the addend
+            dw = _wgrad_1x1(dy, x, weight) if ctx.needs_input_grad[1] else None
+            dx = None
+            if ctx.needs_input_grad[0]:
+                dx = torch.empty_like(x, memory_format=torch.channels_last)
+                conv1x1_gemm(_rows(dy), weight.reshape(o, c).t().contiguous(), stats=False, out=_rows(dx))
         else:
             dx, dw, _ = torch.ops.aten.convolution_backward(
                 dy, x, weight, None, [1, 1], [0, 0], [1, 1], False, [0, 0], 1,

@@ -82,7 +82,7 @@ def summarize_launches(path: str, title: str) -> None:
             a[3] += v
     tot = sum(a[1] for a in agg.values()) or 1.0
     name = os.path.splitext(os.path.basename(path))[0]
-    ours = ("bn_", "maxpool", "sgd_momentum", "softmax_xent", "preprocess", "emb_", "linear_tcgen05", "colsum", "wd_head", "conv1x1_tcgen05", "stem_wgrad", "wgrad3x3", "wgrad_reduce", "allreduce_", "alltoall_", "broadcast_kernel", "barrier_kernel",
+    ours = ("bn_", "maxpool", "sgd_momentum", "softmax_xent", "preprocess", "emb_", "linear_tcgen05", "colsum", "wd_head", "conv1x1_tcgen05", "stem_wgrad", "wgrad3x3", "wgrad_reduce", "wgrad_mn", "conv_tcgen05", "s2d_", "pool_", "allreduce_", "alltoall_", "broadcast_kernel", "barrier_kernel",
             "allreduce", "alltoall", "broadcast", "barrier_kernel")
     with open(os.path.join(OUT, name + ".launches.md"), "w") as f:
         f.write(f"# {title}\n\nEvery kernel of one training step, serialised under ncu (cold caches: compare shares, "

@@ -172,6 +172,27 @@ def test_conv1x1_skip_gradient_is_folded_into_dgrad(n, hw, cin, cout):
     torch.testing.assert_close(wa.grad.float(), wb.grad, atol=0.25, rtol=5e-2)
 
 
+@pytest.mark.parametrize("n,hw,cin,cout", [(4, 14, 64, 256), (2, 28, 128, 512), (3, 7, 512, 2048), (2, 9, 192, 128)])
+def test_conv1x1_backward_without_skip_runs_on_own_kernels(n, hw, cin, cout):
+    """conv3 of a bottleneck (no skip gradient to fold in): dgrad GEMM + MN-major wgrad vs an fp32 reference."""
+    from paddle_operator_b200.ops import conv as conv_ops
+
+    assert conv_ops.OWN_BWD
+    torch.manual_seed(cin + cout)
+    x = torch.randn(n, cin, hw, hw, device="cuda", dtype=torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    w = (torch.randn(cout, cin, 1, 1, device="cuda", dtype=torch.bfloat16) * 0.1).contiguous(memory_format=torch.channels_last)
+    gy = torch.randn(n, cout, hw, hw, device="cuda", dtype=torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    xa, wa = x.clone().requires_grad_(True), w.clone().requires_grad_(True)
+    before = conv_ops.launch_count()
+    y, _ = conv_ops.conv1x1_stats(xa, wa)
+    y.backward(gy)
+    assert conv_ops.launch_count() - before >= 3  # wgrad (+reduce) and the dgrad GEMM ran here, not in the library
+    xb, wb = x.float().requires_grad_(True), w.float().requires_grad_(True)
+    torch.nn.functional.conv2d(xb, wb).backward(gy.float())
+    torch.testing.assert_close(xa.grad.float(), xb.grad, atol=6e-2, rtol=3e-2)
+    torch.testing.assert_close(wa.grad.float(), wb.grad, atol=0.25, rtol=5e-2)
+
+
 def test_conv1x1_gemm_add_in_place():
     from paddle_operator_b200.ops import conv as conv_ops
 
