@@ -207,6 +207,10 @@ int pdj_bn_fwd_gate(const void* x, const void* res, void* y, void* gate, int M, 
 int pdj_bn_bwd_gate(const void* dy, const void* y, const void* gate, const void* x, void* dx, void* dres, int M, int C,
                     const float* gamma, const float* mean_rstd, float* dgamma_dbeta, void* dgb_bf16, float* coef,
                     int relu, void* workspace, cudaStream_t st);
+/* pdj_bn_bwd_gate with the two bf16 gradients at separate addresses (dgamma_bf16 / dbeta_bf16, both or neither). */
+int pdj_bn_bwd_gate2(const void* dy, const void* y, const void* gate, const void* x, void* dx, void* dres, int M, int C,
+                     const float* gamma, const float* mean_rstd, float* dgamma_dbeta, void* dgamma_bf16,
+                     void* dbeta_bf16, float* coef, int relu, void* workspace, cudaStream_t st);
 /* Forward with the statistics pre-reduced to `nb` partial rows ([nb][2][C] fp32) by the kernel that
  * produced x (pdj_conv1x1_bf16): finalisation + apply only. */
 int pdj_bn_fwd_pre(const void* x, const void* res, void* y, void* gate, int M, int C, const float* gamma,
@@ -242,6 +246,15 @@ int pdj_preprocess_u8_s2d(const void* in, void* out, int N, int H, int W, const 
                           cudaStream_t st);
 /* out[c] = sum_r x[r, c] for row-major bf16 x with row pitch ld (the bias gradient of a linear layer). */
 int pdj_colsum_bf16(const void* x, float* out, int M, int N, int ld, cudaStream_t st);
+/* Deterministic weighted column sums in one launch: res[c] = sum_r w[r] x[r,c] (x bf16 [M,N], N % 8 == 0),
+ * res[N+j] = sum_r w[r] xe[r,j] (xe fp32 [M,Ne], optional), res[N+Ne] = sum_r w[r] when `ones`;
+ * w[r] = wgt[r] * gscale[0], either may be NULL (= 1).  Result columns [dst_start[k], +dst_n[k]) go to dst[k] as
+ * bf16 (dst_bf16[k] != 0) or fp32, k < ndst <= 4.  `ws`: pdj_colsum_w_ws_bytes() bytes, first 4 zero before the
+ * first use (left zero by every call).  Bias gradients; every parameter gradient of the Wide&Deep head. */
+int pdj_colsum_w_ws_bytes(int M, int N, int Ne, int ones);
+int pdj_colsum_w(const void* x, int ld, int M, int N, const float* wgt, const float* gscale, const float* xe, int lde,
+                 int Ne, int ones, void* ws, void* const* dst, const int* dst_start, const int* dst_n,
+                 const int* dst_bf16, int ndst, cudaStream_t st);
 /* Wide&Deep head in one pass (one warp per sample): z = h . w_out + b_out + wide_sum + dense . w_d + b_d,
  * loss[b] = BCE-with-logits(z, labels[b]), dlogit[b] = (sigmoid(z) - labels[b]) * grad_scale.  h bf16 [B,N]
  * (row pitch ld), w_out / w_d / biases bf16 (biases may be NULL), dense fp32 [B,Dd], wide_sum fp32 or NULL.

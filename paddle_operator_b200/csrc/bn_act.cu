@@ -285,7 +285,7 @@ __global__ void __launch_bounds__(kThreads)
 bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ y,
                      const __nv_bfloat16* __restrict__ x, int M, int C, const float* __restrict__ gamma,
                      const float* __restrict__ mean_rstd, float* __restrict__ dgamma_dbeta /*[2][C] fp32*/,
-                     __nv_bfloat16* __restrict__ dgb_bf16 /*[2][C] or null*/,
+                     __nv_bfloat16* __restrict__ dgb_bf16 /*dgamma [C] or null*/, __nv_bfloat16* __restrict__ db_bf16 /*dbeta [C]*/,
                      float* __restrict__ coef /*[3][C]*/, float* __restrict__ partial,
                      unsigned int* __restrict__ counter, int cvt_max, const uint8_t* __restrict__ gate) {
   const Tile t = make_tile(C, cvt_max);
@@ -393,7 +393,7 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
     dgamma_dbeta[C + ch] = sdz;
     if (dgb_bf16 != nullptr) {
       dgb_bf16[ch] = __float2bfloat16(sdzx);
-      dgb_bf16[C + ch] = __float2bfloat16(sdz);
+      db_bf16[ch] = __float2bfloat16(sdz);
     }
     const float r = mean_rstd[C + ch], m = mean_rstd[ch];
     const float A = gamma[ch] * r;
@@ -617,7 +617,8 @@ template <bool RELU, int STAGES>
 __global__ void __launch_bounds__(kThreads, 2)
 bn_bwd_reduce_tma_kernel(const __grid_constant__ CUtensorMap tma_dy, const __grid_constant__ CUtensorMap tma_x, int M, int C,
                          const float* __restrict__ gamma, const float* __restrict__ mean_rstd,
-                         float* __restrict__ dgamma_dbeta, __nv_bfloat16* __restrict__ dgb_bf16, float* __restrict__ coef,
+                         float* __restrict__ dgamma_dbeta, __nv_bfloat16* __restrict__ dgb_bf16, __nv_bfloat16* __restrict__ db_bf16,
+                         float* __restrict__ coef,
                          float* __restrict__ partial, unsigned int* __restrict__ counter, const uint8_t* __restrict__ gate) {
   extern __shared__ uint8_t bn_dyn_smem[];
   TmaRing<2, STAGES> ring;
@@ -701,7 +702,7 @@ bn_bwd_reduce_tma_kernel(const __grid_constant__ CUtensorMap tma_dy, const __gri
     dgamma_dbeta[C + ch] = sdz;
     if (dgb_bf16 != nullptr) {
       dgb_bf16[ch] = __float2bfloat16(sdzx);
-      dgb_bf16[C + ch] = __float2bfloat16(sdz);
+      db_bf16[ch] = __float2bfloat16(sdz);
     }
     const float r = mean_rstd[C + ch], m = mean_rstd[ch];
     const float A = gamma[ch] * r;
@@ -910,6 +911,14 @@ int pdj_bn_bwd(const void* dy, const void* y, const void* x, void* dx, void* dre
 int pdj_bn_bwd_gate(const void* dy, const void* y, const void* gate, const void* x, void* dx, void* dres, int M, int C,
                     const float* gamma, const float* mean_rstd, float* dgamma_dbeta, void* dgb_bf16, float* coef,
                     int relu, void* workspace, cudaStream_t st) {
+  return pdj_bn_bwd_gate2(dy, y, gate, x, dx, dres, M, C, gamma, mean_rstd, dgamma_dbeta, dgb_bf16,
+                          dgb_bf16 ? (void*)((__nv_bfloat16*)dgb_bf16 + C) : nullptr, coef, relu, workspace, st);
+}
+
+// The same with the two bf16 gradients at separate addresses (a trainer's flat gradient buffer).
+int pdj_bn_bwd_gate2(const void* dy, const void* y, const void* gate, const void* x, void* dx, void* dres, int M, int C,
+                     const float* gamma, const float* mean_rstd, float* dgamma_dbeta, void* dgb_bf16, void* dbeta_bf16,
+                     float* coef, int relu, void* workspace, cudaStream_t st) {
   if (check_shape(M, C)) return -1;
   const uint8_t* gate_in = reinterpret_cast<const uint8_t*>(gate);
   float* partial = reinterpret_cast<float*>(reinterpret_cast<char*>(workspace) + 256);
@@ -920,6 +929,7 @@ int pdj_bn_bwd_gate(const void* dy, const void* y, const void* gate, const void*
   const __nv_bfloat16* yb = (const __nv_bfloat16*)y;
   const __nv_bfloat16* xb = (const __nv_bfloat16*)x;
   __nv_bfloat16* dgb = (__nv_bfloat16*)dgb_bf16;
+  __nv_bfloat16* dbb = (__nv_bfloat16*)dbeta_bf16;
   const int cm = cvt;
   if (tma_path(M, C) && (!relu || gate_in != nullptr)) {
     if (int r = ensure_tma_attrs()) return r;
@@ -929,23 +939,23 @@ int pdj_bn_bwd_gate(const void* dy, const void* y, const void* gate, const void*
     dim3 gt(tma_grid_rows(M, C, sm_count()), C / TC);
     if (relu)
       bn_bwd_reduce_tma_kernel<true, kBwdStages><<<gt, kThreads, kBwdSmem, st>>>(md, mx, M, C, gamma, mean_rstd, dgamma_dbeta,
-                                                                                dgb, coef, partial, counter, gate_in);
+                                                                                dgb, dbb, coef, partial, counter, gate_in);
     else
       bn_bwd_reduce_tma_kernel<false, kBwdStages><<<gt, kThreads, kBwdSmem, st>>>(md, mx, M, C, gamma, mean_rstd, dgamma_dbeta,
-                                                                                 dgb, coef, partial, counter, gate_in);
+                                                                                 dgb, dbb, coef, partial, counter, gate_in);
   } else if (knob_bwd_unroll() == 2) {
     if (relu)
-      bn_bwd_reduce_kernel<true, 2><<<g, kThreads, 0, st>>>(dyb, yb, xb, M, C, gamma, mean_rstd, dgamma_dbeta, dgb, coef,
+      bn_bwd_reduce_kernel<true, 2><<<g, kThreads, 0, st>>>(dyb, yb, xb, M, C, gamma, mean_rstd, dgamma_dbeta, dgb, dbb, coef,
                                                             partial, counter, cm, gate_in);
     else
-      bn_bwd_reduce_kernel<false, 2><<<g, kThreads, 0, st>>>(dyb, yb, xb, M, C, gamma, mean_rstd, dgamma_dbeta, dgb,
+      bn_bwd_reduce_kernel<false, 2><<<g, kThreads, 0, st>>>(dyb, yb, xb, M, C, gamma, mean_rstd, dgamma_dbeta, dgb, dbb,
                                                              coef, partial, counter, cm, gate_in);
   } else {
     if (relu)
-      bn_bwd_reduce_kernel<true, 1><<<g, kThreads, 0, st>>>(dyb, yb, xb, M, C, gamma, mean_rstd, dgamma_dbeta, dgb, coef,
+      bn_bwd_reduce_kernel<true, 1><<<g, kThreads, 0, st>>>(dyb, yb, xb, M, C, gamma, mean_rstd, dgamma_dbeta, dgb, dbb, coef,
                                                             partial, counter, cm, gate_in);
     else
-      bn_bwd_reduce_kernel<false, 1><<<g, kThreads, 0, st>>>(dyb, yb, xb, M, C, gamma, mean_rstd, dgamma_dbeta, dgb,
+      bn_bwd_reduce_kernel<false, 1><<<g, kThreads, 0, st>>>(dyb, yb, xb, M, C, gamma, mean_rstd, dgamma_dbeta, dgb, dbb,
                                                              coef, partial, counter, cm, gate_in);
   }
   PDJ_CUDA_CHECK(cudaGetLastError());

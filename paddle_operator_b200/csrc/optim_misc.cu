@@ -186,6 +186,107 @@ colsum_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ out, int 
   }
 }
 
+// ---- Weighted column sums, deterministic, one launch ---------------------------------------------------
+//   res[c]          = sum_r w[r] * x[r, c]        c < N        (x bf16, N % 8 == 0)
+//   res[N + j]      = sum_r w[r] * xe[r, j]       j < Ne       (xe fp32, optional)
+//   res[N + Ne]     = sum_r w[r]                               (optional "ones" column)
+// with w[r] = wgt[r] * gscale[0] (either may be absent = 1).  Bias gradients of linear layers (w = 1) and every
+// parameter gradient of the Wide&Deep head (x = top activation, xe = dense features, w = dlogit).
+// Block b reduces a fixed row range: a thread owns 8 adjacent columns of every RG-th row, the row groups are
+// folded in shared memory in a fixed order, the block writes one row of `partial`; the block that draws the last
+// ticket adds the partial rows in block order, converts and scatters the result to up to four destinations
+// (a trainer's flat gradient buffer) and resets the ticket.  Same bits every run, no memset, no conversion pass.
+constexpr int kCsThreads = 512;
+constexpr int kCsMaxSlots = 128;  // 8-column slots: N / 8 + ceil((Ne + ones) / 8)
+struct CsSeg { void* p; int start, n, bf16; };
+struct CsOut { CsSeg seg[4]; };
+
+__global__ void __launch_bounds__(kCsThreads)
+colsum_w_kernel(const __nv_bfloat16* __restrict__ x, int ld, int M, int N, const float* __restrict__ wgt,
+                const float* __restrict__ gscale, const float* __restrict__ xe, int lde, int Ne, int ones,
+                float* __restrict__ partial, unsigned int* __restrict__ counter, CsOut out) {
+  extern __shared__ float cs_smem[];  // [RG][slots * 8]
+  const int nv = N >> 3, ne = Ne + ones, slots = nv + ((ne + 7) >> 3), ntot = N + ne;
+  const int RG = kCsThreads / slots;
+  const int slot = threadIdx.x % slots, rg = threadIdx.x / slots;
+  const int rows_per = (M + gridDim.x - 1) / gridDim.x;
+  const int r0 = blockIdx.x * rows_per, r1 = min(M, r0 + rows_per);
+  const float gs = gscale ? __ldg(gscale) : 1.f;
+  float acc[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+  if (rg < RG) {
+    if (slot < nv) {
+      const __nv_bfloat16* xp = x + (size_t)slot * 8;
+#pragma unroll 4
+      for (int r = r0 + rg; r < r1; r += RG) {
+        const uint4 v = __ldg(reinterpret_cast<const uint4*>(xp + (size_t)r * ld));
+        const float w = wgt ? __ldg(wgt + r) * gs : gs;
+        const float2 a = pdj_bf2_to_f2(v.x), b = pdj_bf2_to_f2(v.y), c = pdj_bf2_to_f2(v.z), d = pdj_bf2_to_f2(v.w);
+        acc[0] = fmaf(w, a.x, acc[0]); acc[1] = fmaf(w, a.y, acc[1]);
+        acc[2] = fmaf(w, b.x, acc[2]); acc[3] = fmaf(w, b.y, acc[3]);
+        acc[4] = fmaf(w, c.x, acc[4]); acc[5] = fmaf(w, c.y, acc[5]);
+        acc[6] = fmaf(w, d.x, acc[6]); acc[7] = fmaf(w, d.y, acc[7]);
+      }
+    } else {
+      const int e0 = (slot - nv) * 8;
+      for (int r = r0 + rg; r < r1; r += RG) {
+        const float w = wgt ? __ldg(wgt + r) * gs : gs;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const int e = e0 + j;
+          if (e < Ne) acc[j] = fmaf(w, __ldg(xe + (size_t)r * lde + e), acc[j]);
+          else if (e < ne) acc[j] += w;
+        }
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) cs_smem[(rg * slots + slot) * 8 + j] = acc[j];
+  }
+  __syncthreads();
+  const int pitch = (ntot + 3) & ~3;  // partial rows are whole float4s
+  float* prow = partial + (size_t)blockIdx.x * pitch;
+  for (int c = threadIdx.x; c < pitch; c += kCsThreads) {
+    float t = 0.f;
+    if (c < ntot)
+      for (int g = 0; g < RG; ++g) t += cs_smem[g * slots * 8 + c];
+    prow[c] = t;
+  }
+  __shared__ unsigned int ticket;
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) ticket = atomicAdd(counter, 1u);
+  __syncthreads();
+  if (ticket != gridDim.x - 1) return;
+  __threadfence();
+  // last block: P2 row groups x float4 columns in parallel (independent loads), then a fixed-order fold
+  const int nvec = pitch >> 2, P2 = kCsThreads / nvec;
+  const int v = threadIdx.x % nvec, g2 = threadIdx.x / nvec;
+  if (g2 < P2) {
+    float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 8
+    for (int b = g2; b < (int)gridDim.x; b += P2) {
+      const float4 q = __ldcg(reinterpret_cast<const float4*>(partial + (size_t)b * pitch) + v);
+      t.x += q.x; t.y += q.y; t.z += q.z; t.w += q.w;
+    }
+    reinterpret_cast<float4*>(cs_smem)[g2 * nvec + v] = t;
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < ntot; c += kCsThreads) {
+    float t = 0.f;
+    for (int g = 0; g < P2; ++g) t += cs_smem[g * pitch + c];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const CsSeg sg = out.seg[k];
+      if (sg.p != nullptr && c >= sg.start && c < sg.start + sg.n) {
+        if (sg.bf16) reinterpret_cast<__nv_bfloat16*>(sg.p)[c - sg.start] = __float2bfloat16(t);
+        else reinterpret_cast<float*>(sg.p)[c - sg.start] = t;
+      }
+    }
+  }
+  if (threadIdx.x == 0) *counter = 0u;
+}
+
 // ---- Wide&Deep head: output layer + wide part + binary cross-entropy in one pass -------------------
 // One warp per sample:
 //   z = h[b,:] . w_out + b_out + wide_sum[b] + dense[b,:] . w_d + b_d
@@ -298,6 +399,37 @@ int pdj_colsum_bf16(const void* x, float* out, int M, int N, int ld, cudaStream_
   if (M < 1 || N < 1) return 0;
   PDJ_CUDA_CHECK(cudaMemsetAsync(out, 0, (size_t)N * sizeof(float), st));
   colsum_kernel<<<(M + kColsumRows - 1) / kColsumRows, 256, 0, st>>>((const __nv_bfloat16*)x, out, M, N, ld);
+  PDJ_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+int pdj_colsum_w_ws_bytes(int M, int N, int Ne, int ones) {
+  (void)M;
+  return 256 + 148 * ((N + Ne + ones + 3) & ~3) * (int)sizeof(float);
+}
+
+// See colsum_w_kernel.  `ws`: pdj_colsum_w_ws_bytes bytes whose first 4 are zero before the first call (the kernel
+// leaves them zero); dst[k] receives result columns [dst_start[k], dst_start[k] + dst_n[k]) as bf16 or fp32.
+int pdj_colsum_w(const void* x, int ld, int M, int N, const float* wgt, const float* gscale, const float* xe, int lde,
+                 int Ne, int ones, void* ws, void* const* dst, const int* dst_start, const int* dst_n,
+                 const int* dst_bf16, int ndst, cudaStream_t st) {
+  const int ne = Ne + (ones ? 1 : 0), slots = N / 8 + (ne + 7) / 8;
+  if (M < 1 || N < 0 || N % 8 != 0 || ld % 8 != 0 || ((uintptr_t)x & 15) || slots < 1 || slots > kCsMaxSlots || ndst < 1 ||
+      ndst > 4 || (Ne > 0 && xe == nullptr)) {
+    pdj_set_error("pdj_colsum_w: need N %% 8 == 0, ld %% 8 == 0, 16-byte aligned x, at most %d column slots, 1..4 destinations "
+                  "(N=%d ld=%d Ne=%d ndst=%d)", kCsMaxSlots, N, ld, Ne, ndst);
+    return -1;
+  }
+  CsOut out{};
+  for (int k = 0; k < ndst; ++k) out.seg[k] = CsSeg{dst[k], dst_start[k], dst_n[k], dst_bf16[k]};
+  int grid = (M + 63) / 64;
+  if (grid > 148) grid = 148;
+  const int RG = kCsThreads / slots;
+  const size_t smem = (size_t)RG * slots * 8 * sizeof(float);
+  unsigned int* counter = reinterpret_cast<unsigned int*>(ws);
+  float* partial = reinterpret_cast<float*>(reinterpret_cast<char*>(ws) + 256);
+  colsum_w_kernel<<<grid, kCsThreads, smem, st>>>((const __nv_bfloat16*)x, ld, M, N, wgt, gscale, xe, lde, Ne, ones ? 1 : 0,
+                                                  partial, counter, out);
   PDJ_CUDA_CHECK(cudaGetLastError());
   return 0;
 }

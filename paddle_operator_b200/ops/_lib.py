@@ -104,12 +104,16 @@ def _declare(lib: ctypes.CDLL) -> None:
         "pdj_maxpool_bwd": (c_int, [vp, vp, vp, c_int, c_int, c_int, c_int, c_int, c_int, c_int, st]),
         "pdj_bn_fwd_gate": (c_int, [vp, vp, vp, vp, c_int, c_int, vp, vp, c_float, c_float, vp, vp, vp, vp, c_int, vp, st]),
         "pdj_bn_bwd_gate": (c_int, [vp, vp, vp, vp, vp, vp, c_int, c_int, vp, vp, vp, vp, vp, c_int, vp, st]),
+        "pdj_bn_bwd_gate2": (c_int, [vp, vp, vp, vp, vp, vp, c_int, c_int, vp, vp, vp, vp, vp, vp, c_int, vp, st]),
         "pdj_sgd_momentum": (c_int, [vp, vp, vp, vp, sz, sz, vp, st]),
         "pdj_preprocess_u8": (c_int, [vp, vp, sz, fp, fp, st]),
         "pdj_preprocess_u8_s2d": (c_int, [vp, vp, c_int, c_int, c_int, fp, fp, st]),
         "pdj_wd_head": (c_int, [vp, c_int, vp, vp, vp, vp, vp, vp, vp, vp, vp, c_int, c_int, c_int, c_float, st]),
         "pdj_wd_head_dz": (c_int, [vp, vp, vp, c_int, vp, c_int, c_int, c_int, st]),
         "pdj_colsum_bf16": (c_int, [vp, vp, c_int, c_int, c_int, st]),
+        "pdj_colsum_w_ws_bytes": (c_int, [c_int, c_int, c_int, c_int]),
+        "pdj_colsum_w": (c_int, [vp, c_int, c_int, c_int, vp, vp, vp, c_int, c_int, c_int, vp, POINTER(c_void_p),
+                                 POINTER(c_int), POINTER(c_int), POINTER(c_int), c_int, st]),
         "pdj_softmax_xent": (c_int, [vp, vp, vp, vp, c_int, c_int, c_float, st]),
     }
     for name, (res, args) in sig.items():

@@ -1,0 +1,38 @@
+"""Gradient sinks: kernels write parameter gradients where the trainer wants them.
+
+A trainer that keeps its gradients in one flat buffer (parallel/collective.py, FlatParams) tags every parameter
+with `_grad_sink`, a view of that buffer with the parameter's shape and strides.  An op whose backward produces a
+parameter gradient with one of this repository's kernels asks `sink_of(param)`; when there is one, the kernel
+writes straight into it and the op returns `adopt(sink)` - a fresh alias that autograd installs as `.grad` without
+a copy.  The trainer's hook sees `.grad` already sitting at the sink's address and skips its copy, so no gradient
+is written twice and no `_foreach_copy_` runs (PDJ_GRAD_SINK=0 restores the copy path; anything that does not
+use a sink - library backward passes, accumulated gradients of shared weights - still takes it).
+
+Reference parity: none (the reference has no compute code).
+"""
+from __future__ import annotations
+
+import os
+from typing import Optional
+
+import torch
+
+ENABLED = os.environ.get("PDJ_GRAD_SINK", "1") == "1"
+
+
+def sink_of(p: Optional[torch.Tensor], dtype=torch.bfloat16) -> Optional[torch.Tensor]:
+    if p is None or not ENABLED:
+        return None
+    s = getattr(p, "_grad_sink", None)
+    if s is None or s.dtype != dtype or s.shape != p.shape or not s.is_cuda:
+        return None
+    return s
+
+
+def adopt(sink: torch.Tensor) -> torch.Tensor:
+    """A new tensor object over the sink's memory: autograd may take it as the gradient without copying."""
+    return sink.detach()
+
+
+def is_sunk(grad: Optional[torch.Tensor], sink: torch.Tensor) -> bool:
+    return grad is not None and grad.data_ptr() == sink.data_ptr() and grad.dtype == sink.dtype

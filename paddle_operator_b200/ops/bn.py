@@ -15,6 +15,7 @@ from typing import Optional
 import torch
 
 from . import _lib
+from ._sink import adopt, sink_of
 
 _workspaces: dict[int, torch.Tensor] = {}
 
@@ -83,6 +84,7 @@ class _BnActFn(torch.autograd.Function):
         ctx.relu = relu
         ctx.has_res = residual is not None
         ctx.wdtype = weight.dtype
+        ctx.affine = (weight, bias)  # parameters: backward only looks at their gradient sinks
         return y
 
     @staticmethod
@@ -97,15 +99,21 @@ class _BnActFn(torch.autograd.Function):
         dres = torch.empty_like(x, memory_format=torch.channels_last) if (ctx.has_res and ctx.relu) else None
         dgb = torch.empty(2, c, dtype=torch.float32, device=x.device)
         dgb16 = torch.empty(2, c, dtype=torch.bfloat16, device=x.device) if ctx.wdtype == torch.bfloat16 else None
+        # bf16 gradients of gamma / beta go straight into the trainer's gradient buffer when it provides sinks
+        gsink, bsink = sink_of(ctx.affine[0]), sink_of(ctx.affine[1])
+        sunk = dgb16 is not None and gsink is not None and bsink is not None
+        dg16, db16 = (gsink, bsink) if sunk else ((dgb16[0], dgb16[1]) if dgb16 is not None else (None, None))
         coef = torch.empty(3, c, dtype=torch.float32, device=x.device)
         ws = _workspace(x.device)
         st = torch.cuda.current_stream().cuda_stream
-        _lib.check(lib.pdj_bn_bwd_gate(dy.data_ptr(), None, _lib.ptr(gate), x.data_ptr(), dx.data_ptr(), _lib.ptr(dres),
-                                       m, c, gamma.data_ptr(), stats.data_ptr(), dgb.data_ptr(), _lib.ptr(dgb16),
-                                       coef.data_ptr(), int(ctx.relu), ws.data_ptr(), st), "bn_bwd")
+        _lib.check(lib.pdj_bn_bwd_gate2(dy.data_ptr(), None, _lib.ptr(gate), x.data_ptr(), dx.data_ptr(), _lib.ptr(dres),
+                                        m, c, gamma.data_ptr(), stats.data_ptr(), dgb.data_ptr(), _lib.ptr(dg16),
+                                        _lib.ptr(db16), coef.data_ptr(), int(ctx.relu), ws.data_ptr(), st), "bn_bwd")
         if ctx.has_res and not ctx.relu:
             dres = dy  # no activation: the skip branch sees dy unchanged
-        if dgb16 is not None:
+        if sunk:
+            dgamma, dbeta = adopt(gsink), adopt(bsink)
+        elif dgb16 is not None:
             dgamma, dbeta = dgb16[0], dgb16[1]
         else:
             dgamma, dbeta = dgb[0].to(ctx.wdtype), dgb[1].to(ctx.wdtype)

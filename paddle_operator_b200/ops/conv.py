@@ -26,6 +26,7 @@ import torch
 import torch.nn.functional as F
 
 from . import _lib
+from ._sink import adopt, sink_of
 
 
 # The fusion pays where the output does not fit in L2 (126 MB): below that the separate statistics
@@ -107,6 +108,10 @@ def _wgrad_1x1(dy: torch.Tensor, x: torch.Tensor, weight: torch.Tensor) -> torch
     from .gemm import wgrad_mn
 
     _launches[0] += 2
+    sink = sink_of(weight)  # [Cout,Cin,1,1] channels-last: the same dense [Cout, Cin] matrix in memory
+    if sink is not None:
+        wgrad_mn(_rows(dy), _rows(x), out=sink)
+        return adopt(sink)
     return wgrad_mn(_rows(dy), _rows(x)).view(weight.shape)
 
 
@@ -315,14 +320,18 @@ def conv3x3_wgrad_eligible(x: torch.Tensor, weight: torch.Tensor, stride=1, padd
             and x.is_contiguous(memory_format=torch.channels_last))
 
 
-def conv3x3_wgrad(x: torch.Tensor, dy: torch.Tensor, weight_shape) -> torch.Tensor:
+def conv3x3_wgrad(x: torch.Tensor, dy: torch.Tensor, weight_shape, out: Optional[torch.Tensor] = None) -> torch.Tensor:
     """dW (channels-last [Cout, Cin, 3, 3] bf16) of y = conv2d(x, w, padding=1) from x and dy, both NHWC bf16
     (csrc/wgrad_tcgen05.cu: one halo tile per pixel block serves all nine taps, accumulators resident in TMEM)."""
     lib = _lib.load()
     n, c, h, w = x.shape
     o = weight_shape[0]
     assert dy.shape == (n, o, h, w) and dy.is_contiguous(memory_format=torch.channels_last)
-    dw = torch.empty((o, 3, 3, c), dtype=torch.bfloat16, device=x.device).permute(0, 3, 1, 2)  # channels-last strides
+    if out is not None:  # e.g. a gradient sink: [Cout, Cin, 3, 3] with channels-last strides
+        assert out.dtype == torch.bfloat16 and out.shape == (o, c, 3, 3) and out.stride() == (9 * c, 1, 3 * c, c)
+        dw = out
+    else:
+        dw = torch.empty((o, 3, 3, c), dtype=torch.bfloat16, device=x.device).permute(0, 3, 1, 2)  # channels-last strides
     nbytes = lib.pdj_conv3x3_wgrad_ws_bytes(n, h, w, c, o)
     if nbytes == 0:
         raise ValueError(f"conv3x3_wgrad: unsupported shape {tuple(x.shape)} -> {o}")
@@ -411,7 +420,11 @@ class _Conv3x3Fn(torch.autograd.Function):
         ours_w = (need_w and s == 1 and conv3x3_wgrad_eligible(x, weight)
                   and min(x.shape[2], x.shape[3]) >= WGRAD3X3_MIN_HW)
         dx = conv3x3_dgrad(dy, weight) if ours_x else None
-        dw = conv3x3_wgrad(x, dy, weight.shape) if ours_w else None
+        dw = None
+        if ours_w:
+            sink = sink_of(weight)
+            dw = conv3x3_wgrad(x, dy, weight.shape, out=sink)
+            dw = adopt(dw) if sink is not None else dw
         lib_x, lib_w = need_x and not ours_x, need_w and not ours_w
         if lib_x or lib_w:
             gx, gw, _ = torch.ops.aten.convolution_backward(dy, x, weight, None, [s, s], [1, 1], [1, 1], False, [0, 0], 1,

@@ -17,6 +17,7 @@ import os
 import torch
 
 from . import _lib
+from ._sink import adopt, sink_of
 
 
 def linear_bf16(a: torch.Tensor, b: torch.Tensor, bias: Optional[torch.Tensor] = None, relu: bool = False,
@@ -59,6 +60,7 @@ class _LinearActFn(torch.autograd.Function):
         ctx.relu = relu
         ctx.has_bias = bias is not None
         ctx.bias_dtype = bias.dtype if bias is not None else None
+        ctx.bias = bias  # the parameter itself: backward only looks at its gradient sink
         return y
 
     @staticmethod
@@ -71,28 +73,41 @@ class _LinearActFn(torch.autograd.Function):
             # dX[M,K] = dZ[M,N] @ W[N,K]  ==  dZ . (W^T)[K,N]^T : the B operand is W^T, K-major over N
             dx = linear_bf16(dz, weight.t().contiguous())
         if ctx.needs_input_grad[1]:
-            dw = wgrad_mn(dz, x)
+            sink = sink_of(weight)
+            dw = wgrad_mn(dz, x, out=sink)
+            dw = adopt(dw) if sink is not None else dw
         if ctx.has_bias and ctx.needs_input_grad[2]:
-            db = dz.float().sum(0).to(ctx.bias_dtype)
+            from .mlp import colsum
+
+            sink = sink_of(ctx.bias)
+            if dz.stride(1) == 1:
+                db = colsum(dz, out=sink, dtype=ctx.bias_dtype)
+                db = adopt(db) if sink is not None else db
+            else:
+                db = dz.float().sum(0).to(ctx.bias_dtype)
         return dx, dw, db, None, None
 
 
-def wgrad_mn(dy: torch.Tensor, x: torch.Tensor) -> torch.Tensor:
+def wgrad_mn(dy: torch.Tensor, x: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
     """dW[No, Nc] = dy[M, No]^T @ x[M, Nc] (bf16) on the MN-major tcgen05 kernel (csrc/wgrad_tcgen05.cu: both operands
     read as they sit in memory, accumulators resident in tensor memory, split-K with a fixed-order reduce).  Falls
-    back to the library GEMM for shapes the kernel does not take."""
+    back to the library GEMM for shapes the kernel does not take.  `out`: a bf16 tensor whose memory is a dense
+    [No, Nc] matrix (e.g. a gradient sink, ops/_sink.py); it is returned."""
     m, no = dy.shape
     nc = x.shape[1]
     ok = (dy.is_cuda and dy.dtype == torch.bfloat16 and x.dtype == torch.bfloat16 and x.shape[0] == m and no % 8 == 0
           and nc % 8 == 0 and dy.stride(1) == 1 and x.stride(1) == 1 and dy.stride(0) % 8 == 0 and x.stride(0) % 8 == 0
           and dy.data_ptr() % 16 == 0 and x.data_ptr() % 16 == 0 and os.environ.get("PDJ_WGRAD_MN", "1") == "1")
-    if not ok:
-        return dy.t().mm(x)
-    lib = _lib.load()
-    nbytes = lib.pdj_wgrad_mn_ws_bytes(m, no, nc)
+    lib = _lib.load() if ok else None
+    nbytes = lib.pdj_wgrad_mn_ws_bytes(m, no, nc) if ok else 0
     if nbytes == 0:
-        return dy.t().mm(x)
-    dw = torch.empty((no, nc), dtype=torch.bfloat16, device=x.device)
+        dw = dy.t().mm(x)
+        if out is None:
+            return dw
+        out.view(-1).copy_(dw.view(-1)) if out.is_contiguous() else out.copy_(dw.view(out.shape))
+        return out
+    dw = torch.empty((no, nc), dtype=torch.bfloat16, device=x.device) if out is None else out
+    assert dw.dtype == torch.bfloat16 and dw.numel() == no * nc and dw.data_ptr() % 16 == 0
     ws = torch.empty(nbytes, dtype=torch.uint8, device=x.device)
     _lib.check(lib.pdj_wgrad_mn(x.data_ptr(), dy.data_ptr(), dw.data_ptr(), ws.data_ptr(), m, no, nc, x.stride(0),
                                 dy.stride(0), torch.cuda.current_stream().cuda_stream), "wgrad_mn")

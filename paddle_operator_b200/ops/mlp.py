@@ -14,18 +14,69 @@ Wide&Deep workload, deploy/examples/wide_and_deep.yaml.
 """
 from __future__ import annotations
 
+import ctypes
+from typing import Optional
+
 import torch
 
 from . import _lib
+from ._sink import adopt, sink_of
 from .gemm import linear_bf16, wgrad_mn
 
 
-def colsum(x: torch.Tensor) -> torch.Tensor:
-    """fp32 column sums of a 2-D bf16 CUDA tensor (last dim contiguous)."""
+_CS_WS: dict = {}
+
+
+def _cs_workspace(device, nbytes: int) -> torch.Tensor:
+    """Persistent partial-sum rows + ticket counter of the column-sum kernel (zeroed once; the kernel leaves the
+    ticket at zero).  Created on the first eager call, i.e. before any graph capture."""
+    key = (device.type, device.index)
+    ws = _CS_WS.get(key)
+    if ws is None or ws.numel() < nbytes:
+        ws = torch.zeros(max(nbytes, 1 << 20), dtype=torch.uint8, device=device)
+        _CS_WS[key] = ws
+    return ws
+
+
+def colsum_w(x: torch.Tensor, dests, weights: Optional[torch.Tensor] = None, gscale: Optional[torch.Tensor] = None,
+             extra: Optional[torch.Tensor] = None, ones: bool = False) -> None:
+    """Deterministic weighted column sums in one launch (csrc/optim_misc.cu, colsum_w_kernel):
+    res = [ w^T x | w^T extra | sum(w) ],  w = weights * gscale (each optional, default 1).
+    `dests`: up to four (tensor, first result column) pairs; each contiguous bf16 / fp32 tensor receives
+    tensor.numel() result columns."""
+    lib = _lib.load()
+    m, n = x.shape
+    ne = 0 if extra is None else extra.shape[1]
+    assert x.is_cuda and x.dtype == torch.bfloat16 and x.stride(1) == 1 and 1 <= len(dests) <= 4
+    assert weights is None or (weights.dtype == torch.float32 and weights.is_contiguous() and weights.numel() == m)
+    assert extra is None or (extra.dtype == torch.float32 and extra.stride(1) == 1 and extra.shape[0] == m)
+    ws = _cs_workspace(x.device, lib.pdj_colsum_w_ws_bytes(m, n, ne, int(ones)))
+    k = len(dests)
+    for t, _ in dests:
+        assert t.is_contiguous() and t.dtype in (torch.bfloat16, torch.float32)
+    ptrs = (ctypes.c_void_p * k)(*[t.data_ptr() for t, _ in dests])
+    starts = (ctypes.c_int * k)(*[int(c0) for _, c0 in dests])
+    counts = (ctypes.c_int * k)(*[t.numel() for t, _ in dests])
+    bf = (ctypes.c_int * k)(*[int(t.dtype == torch.bfloat16) for t, _ in dests])
+    _lib.check(lib.pdj_colsum_w(x.data_ptr(), x.stride(0), m, n, _lib.ptr(weights), _lib.ptr(gscale), _lib.ptr(extra),
+                                0 if extra is None else extra.stride(0), ne, int(ones), ws.data_ptr(), ptrs, starts,
+                                counts, bf, k, torch.cuda.current_stream().cuda_stream), "colsum_w")
+
+
+def colsum(x: torch.Tensor, out: Optional[torch.Tensor] = None, dtype=torch.float32) -> torch.Tensor:
+    """Column sums of a 2-D bf16 CUDA tensor (last dim contiguous) into `out` (bf16 or fp32, default a new `dtype`
+    tensor)."""
     assert x.is_cuda and x.dtype == torch.bfloat16 and x.dim() == 2 and x.stride(1) == 1
-    out = torch.empty(x.shape[1], dtype=torch.float32, device=x.device)
-    _lib.check(_lib.load().pdj_colsum_bf16(x.data_ptr(), out.data_ptr(), x.shape[0], x.shape[1], x.stride(0),
+    if out is None:
+        out = torch.empty(x.shape[1], dtype=dtype, device=x.device)
+    if x.shape[1] % 8 == 0 and x.stride(0) % 8 == 0 and x.data_ptr() % 16 == 0 and x.shape[1] <= 1000:
+        colsum_w(x, [(out, 0)])
+        return out
+    tmp = out if out.dtype == torch.float32 else torch.empty(x.shape[1], dtype=torch.float32, device=x.device)
+    _lib.check(_lib.load().pdj_colsum_bf16(x.data_ptr(), tmp.data_ptr(), x.shape[0], x.shape[1], x.stride(0),
                                            torch.cuda.current_stream().cuda_stream), "colsum_bf16")
+    if tmp is not out:
+        out.copy_(tmp)
     return out
 
 
@@ -43,6 +94,7 @@ class _FusedMLPFn(torch.autograd.Function):
         ctx.n = n_layers
         ctx.top_grad_masked = top_grad_masked
         ctx.bias_dtypes = [b.dtype for b in bs]
+        ctx.biases = list(bs)  # parameters (not saved tensors): only their gradient sinks are looked at
         return hs[-1]
 
     @staticmethod
@@ -57,8 +109,14 @@ class _FusedMLPFn(torch.autograd.Function):
         dws, dbs = [None] * n, [None] * n
         dx = None
         for l in range(n, 0, -1):  # layer l maps hs[l-1] -> hs[l] with ws[l-1]
-            dbs[l - 1] = colsum(dz).to(ctx.bias_dtypes[l - 1])
-            dws[l - 1] = wgrad_mn(dz, hs[l - 1])
+            # both parameter gradients land in the trainer's flat gradient buffer when it provides sinks
+            bsink, wsink = sink_of(ctx.biases[l - 1]), sink_of(ws[l - 1])
+            if ctx.needs_input_grad[3 + n + l - 1]:
+                db = colsum(dz, out=bsink, dtype=ctx.bias_dtypes[l - 1])
+                dbs[l - 1] = adopt(db) if bsink is not None else db
+            if ctx.needs_input_grad[3 + l - 1]:
+                dw = wgrad_mn(dz, hs[l - 1], out=wsink)
+                dws[l - 1] = adopt(dw) if wsink is not None else dw
             if l > 1:
                 dz = linear_bf16(dz, ws[l - 1].t().contiguous(), mask=hs[l - 1])
             elif ctx.needs_input_grad[0]:

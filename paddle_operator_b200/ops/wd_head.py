@@ -6,7 +6,8 @@
 CUDA bf16: one kernel computes every sample's logit, loss and dlogit (csrc/optim_misc.cu::wd_head_kernel,
 one warp per sample); backward forms the gradient entering the top ReLU layer with the ReLU mask already
 applied (wd_head_dz_kernel) - `h` must therefore be the OUTPUT of a ReLU (ops.mlp.FusedMLP with
-top_grad_masked=True skips its own mask pass).  The weight gradients are two small library GEMVs.
+top_grad_masked=True skips its own mask pass).  All four parameter gradients come from one weighted column-sum
+kernel (colsum_w_kernel).
 Anything else (CPU, fp32) runs the same math in plain torch.
 
 Reference parity: none - the reference has no model code; the loss of the Wide&Deep workload of
@@ -18,6 +19,8 @@ import torch
 import torch.nn.functional as F
 
 from . import _lib
+from ._sink import adopt, sink_of
+from .mlp import colsum_w
 
 
 def head_bce_reference(h, w_out, b_out, wide_sum, dense, w_d, b_d, labels):
@@ -45,6 +48,7 @@ class _HeadBceFn(torch.autograd.Function):
                                    torch.cuda.current_stream().cuda_stream), "wd_head")
         ctx.save_for_backward(h, w_out, dense32, dlogit)
         ctx.has = (b_out is not None, b_d is not None)
+        ctx.params = (b_out, w_d, b_d)  # parameters: backward only looks at their gradient sinks
         ctx.dtypes = (w_out.dtype, w_d.dtype, wide_sum.dtype)
         return loss_b.mean()
 
@@ -57,12 +61,22 @@ class _HeadBceFn(torch.autograd.Function):
         dh = torch.empty_like(h)
         _lib.check(lib.pdj_wd_head_dz(dl.data_ptr(), w_out.data_ptr(), h.data_ptr(), h.stride(0), dh.data_ptr(), dh.stride(0),
                                       bsz, n, torch.cuda.current_stream().cuda_stream), "wd_head_dz")
-        dl16 = dl.to(h.dtype)
-        dw_out = torch.mv(h.t(), dl16).view(1, n).to(ctx.dtypes[0])
-        dw_d = torch.mv(dense32.t(), dl).view(1, -1).to(ctx.dtypes[1])
-        dsum = dl.sum()
-        db_out = dsum.to(ctx.dtypes[0]).view(1) if ctx.has[0] else None
-        db_d = dsum.to(ctx.dtypes[1]).view(1) if ctx.has[1] else None
+        # every parameter gradient of the head is a column sum weighted by dlogit: one deterministic kernel, written
+        # straight into the trainer's gradient buffer where it provides sinks (ops/_sink.py)
+        b_out, w_d, b_d = ctx.params
+        dd = dense32.shape[1]
+        outs, dests = [], []
+        for prm, shape, col, dt in ((w_out, (1, n), 0, ctx.dtypes[0]), (w_d, (1, dd), n, ctx.dtypes[1]),
+                                    (b_out, (1,), n + dd, ctx.dtypes[0]), (b_d, (1,), n + dd, ctx.dtypes[1])):
+            if prm is None:
+                outs.append(None)
+                continue
+            sink = sink_of(prm, dt)
+            t = sink if (sink is not None and sink.is_contiguous()) else torch.empty(shape, dtype=dt, device=h.device)
+            dests.append((t, col))
+            outs.append(adopt(t) if t is sink else t)
+        colsum_w(h, dests, weights=dl, extra=dense32, ones=True)
+        dw_out, dw_d, db_out, db_d = outs
         return dh, dw_out, db_out, dl.to(ctx.dtypes[2]), None, dw_d, db_d, None
 
 

@@ -21,6 +21,7 @@ from typing import Callable, Optional
 import torch
 
 from ..ops import optim as pdj_optim
+from ..ops._sink import is_sunk
 from ..utils import trace
 from .symm import Communicator
 
@@ -74,6 +75,7 @@ class FlatParams:
                 pv.copy_(p.data)
                 mv.copy_(p.data.reshape(-1) if p.dim() != 4 else p.data.permute(0, 2, 3, 1).reshape(-1))
             p.data = pv
+            p._grad_sink = gv  # kernels write this parameter's gradient here directly (ops/_sink.py)
             self.views[id(p)] = (pv, gv, mv)
             b.params.append(p)
             b.gviews.append(gv)
@@ -124,6 +126,7 @@ class FlatParams:
         for p, off in zip(self._order, self._offs):
             pv, gv = self._view(self.param, off, p), self._view(self.grad, off, p)
             p.data = pv
+            p._grad_sink = gv
             self.views[id(p)] = (pv, gv, self.master[off:off + p.numel()])
             self.bucket_of[id(p)].gviews.append(gv)
 
@@ -189,7 +192,9 @@ class CollectiveTrainer:
 
     def _make_hook(self, bucket: _Bucket):
         def hook(p: torch.Tensor):
-            bucket.grads.append((self.flat.views[id(p)][1], p.grad))
+            gv = self.flat.views[id(p)][1]
+            if not is_sunk(p.grad, gv):  # else the producing kernel already wrote it in place
+                bucket.grads.append((gv, p.grad))
             p.grad = None
             bucket.pending -= 1
             if bucket.pending == 0:
@@ -198,10 +203,11 @@ class CollectiveTrainer:
         return hook
 
     def _bucket_ready(self, b: _Bucket) -> None:
-        dst = [d for d, _ in b.grads]
-        src = [s for _, s in b.grads]
-        torch._foreach_copy_(dst, src)
-        b.grads.clear()
+        if b.grads:
+            dst = [d for d, _ in b.grads]
+            src = [s for _, s in b.grads]
+            torch._foreach_copy_(dst, src)
+            b.grads.clear()
         if self.comm is None:
             return
         main = torch.cuda.current_stream()
