@@ -196,7 +196,7 @@ colsum_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ out, int 
 // folded in shared memory in a fixed order, the block writes one row of `partial`; the block that draws the last
 // ticket adds the partial rows in block order, converts and scatters the result to up to four destinations
 // (a trainer's flat gradient buffer) and resets the ticket.  Same bits every run, no memset, no conversion pass.
-constexpr int kCsThreads = 512;
+constexpr int kCsThreads = 1024;
 constexpr int kCsMaxSlots = 128;  // 8-column slots: N / 8 + ceil((Ne + ones) / 8)
 struct CsSeg { void* p; int start, n, bf16; };
 struct CsOut { CsSeg seg[4]; };
@@ -218,16 +218,29 @@ colsum_w_kernel(const __nv_bfloat16* __restrict__ x, int ld, int M, int N, const
   if (rg < RG) {
     if (slot < nv) {
       const __nv_bfloat16* xp = x + (size_t)slot * 8;
-#pragma unroll 4
-      for (int r = r0 + rg; r < r1; r += RG) {
-        const uint4 v = __ldg(reinterpret_cast<const uint4*>(xp + (size_t)r * ld));
-        const float w = wgt ? __ldg(wgt + r) * gs : gs;
+      auto fold = [&](const uint4 v, const float w) {
         const float2 a = pdj_bf2_to_f2(v.x), b = pdj_bf2_to_f2(v.y), c = pdj_bf2_to_f2(v.z), d = pdj_bf2_to_f2(v.w);
         acc[0] = fmaf(w, a.x, acc[0]); acc[1] = fmaf(w, a.y, acc[1]);
         acc[2] = fmaf(w, b.x, acc[2]); acc[3] = fmaf(w, b.y, acc[3]);
         acc[4] = fmaf(w, c.x, acc[4]); acc[5] = fmaf(w, c.y, acc[5]);
         acc[6] = fmaf(w, d.x, acc[6]); acc[7] = fmaf(w, d.y, acc[7]);
+      };
+      int r = r0 + rg;
+      // eight rows per round: all sixteen loads are issued before the first use (one block per SM, so the
+      // memory-level parallelism has to come from inside the thread)
+      for (; r + 7 * RG < r1; r += 8 * RG) {
+        uint4 v[8];
+        float w[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          v[u] = __ldg(reinterpret_cast<const uint4*>(xp + (size_t)(r + u * RG) * ld));
+          w[u] = wgt ? __ldg(wgt + r + u * RG) : 1.f;
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) fold(v[u], w[u] * gs);
       }
+      for (; r < r1; r += RG)
+        fold(__ldg(reinterpret_cast<const uint4*>(xp + (size_t)r * ld)), (wgt ? __ldg(wgt + r) : 1.f) * gs);
     } else {
       const int e0 = (slot - nv) * 8;
       for (int r = r0 + rg; r < r1; r += RG) {

@@ -173,7 +173,10 @@ def main() -> int:
              "launches8": "ResNet-50 step launch list (batch 256, one B200) - round 2, final: 1x1 / linear weight gradients "
                           "on the MN-major tcgen05 kernel",
              "launches_wd6": "Wide&Deep step launch list (batch 32768, one B200) - round 2, final: MN-major tcgen05 weight "
-                             "gradient for the tower, one record per table row"}
+                             "gradient for the tower, one record per table row",
+             "launches_wd7": "Wide&Deep step launch list (batch 32768, one B200) - round 2, final: vectorised mask read in "
+                             "the masked dgrad, gradient sinks (no gradient copies), one weighted column-sum kernel for "
+                             "the bias and head gradients"}
     for n, t in lists.items():
         p = os.path.join(SCRATCH, n + ".csv")
         if os.path.exists(p):
