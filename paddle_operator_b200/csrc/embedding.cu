@@ -22,6 +22,7 @@
 // Everything is addressed by arena offsets so the same arguments are valid on
 // every rank; the single-GPU emulation runs all ranks in one cooperative launch.
 #include <stdlib.h>
+#include <string.h>
 
 #include "common.cuh"
 #include "../../include/pdjob_b200.h"
@@ -72,9 +73,27 @@ __device__ __forceinline__ size_t emb_sw(const PdjEmbTable& t) { return t.list_o
 // slot j / NR of that GPU's table, at row id / P of the slot; a slot is t.rows_per_shard rows.
 __device__ __forceinline__ void emb_locate(const PdjEmbTable& t, int NR, long long id, int* owner, long long* row) {
   const int P = t.list_cap ? (int)t.list_cap : NR;
+  if (((unsigned long long)id >> 32) == 0ull) {  // every table that fits a GPU: 32-bit division instead of the 64-bit routine
+    const uint32_t u = (uint32_t)id, q = u / (uint32_t)P, shard = u - q * (uint32_t)P;
+    const uint32_t slot = shard / (uint32_t)NR;
+    *owner = (int)(shard - slot * (uint32_t)NR);
+    *row = (long long)slot * t.rows_per_shard + q;
+    return;
+  }
   const int shard = (int)(id % P);
   *owner = shard % NR;
   *row = (long long)(shard / NR) * t.rows_per_shard + id / P;
+}
+
+__device__ __forceinline__ long long ld_id(const long long* p) {
+  long long v;
+  asm volatile("ld.global.nc.L1::no_allocate.b64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint2 ld_u2(const void* p) {
+  uint2 v;
+  asm volatile("ld.global.nc.L1::no_allocate.v2.b32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p) : "memory");
+  return v;
 }
 
 // The columns of an output row past the S * D embedding values: the sample's dense features (fp32 -> bf16) and
@@ -123,6 +142,84 @@ emb_lookup_kernel(PdjComm c, PdjEmbTable t, size_t ids_off, size_t out_deep_off,
         o.y = pdj_f2_to_bf2(v.z, v.w);
         *reinterpret_cast<uint2*>(out_deep + (size_t)b * out_pitch + (size_t)s * D + part * 4) = o;
         if (part == 0 && t.has_wide) wide += ld_f1(c.base[owner] + t.wide_off + (size_t)row * emb_sw(t));
+      }
+    }
+    emb_write_tail(c, rank, out_deep, b, S * D, out_pitch, dense_off, dense_n, lane);
+    if (t.has_wide) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) wide += __shfl_xor_sync(0xffffffffu, wide, o);
+      if (lane == 0) out_wide[b] = wide;
+    }
+  }
+  if (do_barrier && threadIdx.x == 0) me->epoch[pdj_slot(c)] = e + 1;
+}
+
+// Batched lookup (the default for up to eight passes per sample).  A random-row gather is bound by memory-level
+// parallelism, not bytes, so every lane keeps PASSES row loads (16 B each, D/4 lanes per row) in flight at once -
+// ids first, all addresses, all loads, then the conversions - and the ids of the warp's NEXT sample are requested
+// before the current rows are touched, which takes the id load off the critical path (one DRAM / NVLink round trip
+// per sample instead of 2 x passes).  The loop above issues one dependent load at a time.
+template <int PASSES>
+__global__ void __launch_bounds__(PASSES <= 2 ? 1024 : 768)
+emb_lookup_batched_kernel(PdjComm c, PdjEmbTable t, size_t ids_off, size_t out_deep_off, size_t out_wide_off, int B, int S,
+                          int do_barrier, int out_pitch, size_t dense_off, int dense_n) {
+  const int rank = c.rank + blockIdx.y;
+  const int NR = c.nranks;
+  PdjSignalPad* me = pdj_pad(c, rank);
+  const uint32_t e = me->epoch[pdj_slot(c)];
+  if (do_barrier) pdj_block_barrier(c, rank, e + 1);  // owners finished applying the previous step
+  const int D = t.dim;
+  const int lpr = D >> 2, rpw = 32 / lpr;
+  const int lane = threadIdx.x & 31;
+  const int sub = lane / lpr, part = lane % lpr;
+  const long long* ids = reinterpret_cast<const long long*>(c.base[rank] + ids_off);
+  __nv_bfloat16* out_deep = reinterpret_cast<__nv_bfloat16*>(c.base[rank] + out_deep_off);
+  float* out_wide = reinterpret_cast<float*>(c.base[rank] + out_wide_off);
+  const int warps = (gridDim.x * blockDim.x) >> 5;
+  const size_t sd = emb_sd(t), sw = emb_sw(t);
+  const bool wide_lane = part == 0 && t.has_wide;
+  long long idn[PASSES];
+  auto load_ids = [&](int bb) {
+#pragma unroll
+    for (int p = 0; p < PASSES; ++p) {
+      const int s_ = p * rpw + sub;
+      idn[p] = (bb < B && s_ < S) ? ld_id(ids + (size_t)bb * S + s_) : -1ll;
+    }
+  };
+  int b = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  load_ids(b);
+  for (; b < B; b += warps) {
+    int owner[PASSES];
+    long long row[PASSES];
+    bool ok[PASSES];
+#pragma unroll
+    for (int p = 0; p < PASSES; ++p) {
+      ok[p] = idn[p] >= 0;
+      owner[p] = 0;
+      row[p] = 0;
+      if (ok[p]) emb_locate(t, NR, idn[p], &owner[p], &row[p]);
+    }
+    load_ids(b + warps);
+    float4 v[PASSES];
+    float wv[PASSES];
+#pragma unroll
+    for (int p = 0; p < PASSES; ++p) {
+      wv[p] = 0.f;
+      if (ok[p]) {
+        const char* ob = c.base[owner[p]];
+        v[p] = ld_f4(ob + t.deep_off + (size_t)row[p] * sd + part * 16);
+        if (wide_lane) wv[p] = ld_f1(ob + t.wide_off + (size_t)row[p] * sw);
+      }
+    }
+    float wide = 0.f;
+#pragma unroll
+    for (int p = 0; p < PASSES; ++p) {
+      if (ok[p]) {
+        uint2 o;
+        o.x = pdj_f2_to_bf2(v[p].x, v[p].y);
+        o.y = pdj_f2_to_bf2(v[p].z, v[p].w);
+        *reinterpret_cast<uint2*>(out_deep + (size_t)b * out_pitch + (size_t)(p * rpw + sub) * D + part * 4) = o;
+        wide += wv[p];
       }
     }
     emb_write_tail(c, rank, out_deep, b, S * D, out_pitch, dense_off, dense_n, lane);
@@ -294,13 +391,84 @@ emb_push_kernel(PdjComm c, PdjEmbTable t, size_t ids_off, size_t gdeep_off, size
   if (threadIdx.x == 0) me->epoch[pdj_slot(c)] = e + 1;
 }
 
+// Batched push: the same memory-level-parallelism treatment as emb_lookup_batched_kernel.  The ids and gradient
+// pieces of the warp's next sample are requested before the current sample's reductions are issued, so the only
+// thing a warp ever waits for is the previous iteration's prefetch.
+template <int PASSES>
+__global__ void __launch_bounds__(PASSES <= 2 ? 1024 : 768)
+emb_push_batched_kernel(PdjComm c, PdjEmbTable t, size_t ids_off, size_t gdeep_off, size_t gwide_off, int B, int S, int mode,
+                        float lr, float grad_scale, int g_pitch) {
+  const int rank = c.rank + blockIdx.y;
+  const int NR = c.nranks;
+  PdjSignalPad* me = pdj_pad(c, rank);
+  const uint32_t e = me->epoch[pdj_slot(c)];
+  const int D = t.dim;
+  const int lpr = D >> 2, rpw = 32 / lpr;
+  const int lane = threadIdx.x & 31;
+  const int sub = lane / lpr, part = lane % lpr;
+  const long long* ids = reinterpret_cast<const long long*>(c.base[rank] + ids_off);
+  const __nv_bfloat16* gdeep = reinterpret_cast<const __nv_bfloat16*>(c.base[rank] + gdeep_off);
+  const float* gwide = reinterpret_cast<const float*>(c.base[rank] + gwide_off);
+  const int warps = (gridDim.x * blockDim.x) >> 5;
+  const float k = mode == 1 ? -lr * grad_scale : grad_scale;
+  const size_t sd = emb_sd(t), sw = emb_sw(t);
+  const size_t deep_base = mode == 1 ? t.deep_off : t.gdeep_off, wide_base = mode == 1 ? t.wide_off : t.gwide_off;
+  long long idn[PASSES];
+  uint2 gn[PASSES];
+  float gwn = 0.f;
+  auto load_next = [&](int bb) {
+#pragma unroll
+    for (int p = 0; p < PASSES; ++p) {
+      const int s_ = p * rpw + sub;
+      const bool valid = bb < B && s_ < S;
+      idn[p] = valid ? ld_id(ids + (size_t)bb * S + s_) : -1ll;
+      gn[p] = valid ? ld_u2(gdeep + (size_t)bb * g_pitch + (size_t)s_ * D + part * 4) : make_uint2(0u, 0u);
+    }
+    gwn = (bb < B && t.has_wide) ? __ldg(gwide + bb) : 0.f;
+  };
+  int b = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  load_next(b);
+  for (; b < B; b += warps) {
+    int owner[PASSES];
+    long long row[PASSES];
+    uint2 g[PASSES];
+    bool ok[PASSES];
+    const float gw = gwn * k;
+#pragma unroll
+    for (int p = 0; p < PASSES; ++p) {
+      ok[p] = idn[p] >= 0;
+      g[p] = gn[p];
+      owner[p] = 0;
+      row[p] = 0;
+      if (ok[p]) emb_locate(t, NR, idn[p], &owner[p], &row[p]);
+    }
+    load_next(b + warps);
+#pragma unroll
+    for (int p = 0; p < PASSES; ++p) {
+      if (!ok[p]) continue;
+      const float2 g0 = pdj_bf2_to_f2(g[p].x), g1 = pdj_bf2_to_f2(g[p].y);
+      char* ob = c.base[owner[p]];
+      red_add_f4(ob + deep_base + (size_t)row[p] * sd + part * 16, g0.x * k, g0.y * k, g1.x * k, g1.y * k);
+      if (part == 0) {
+        if (t.has_wide) red_add_f1(ob + wide_base + (size_t)row[p] * sw, gw);
+        if (mode == 0)  // mark the row as touched: an idempotent one-byte store (see emb_push_kernel)
+          asm volatile("st.relaxed.sys.global.u8 [%0], %1;" ::"l"(ob + t.flag_off + (size_t)row[p]), "r"(1u) : "memory");
+      }
+    }
+  }
+  pdj_block_barrier(c, rank, e + 1);
+  if (threadIdx.x == 0) me->epoch[pdj_slot(c)] = e + 1;
+}
+
 // Owner-side optimizer over the touched rows.  opt 0 = SGD, 1 = Adagrad.
-// Each warp scans windows of 128 byte-flags (one 32-bit load per lane), compacts the set
-// rows into a shared-memory queue with a warp prefix sum, clears the flags, and then
-// updates the queued rows with D/4 lanes per row (float4 each).
+// Each warp scans windows of 512 byte-flags (one 16-byte load per lane), compacts the set rows into a
+// shared-memory queue with a warp prefix sum, clears the flags, and then updates the queued rows with D/4 lanes
+// per row (float4 each), four rows per lane at a time: all of their loads (gradient, weight, accumulator, and the
+// wide scalars) are issued before the first is used, so a warp pays two memory round trips per 512 rows.
+constexpr int kApplyWin = 512, kApplyBatch = 4;
 __global__ void __launch_bounds__(256)
 emb_apply_kernel(PdjComm c, PdjEmbTable t, int opt, float lr, float eps) {
-  __shared__ uint32_t queue[8][128];
+  __shared__ uint32_t queue[8][kApplyWin];
   const int rank = c.rank + blockIdx.y;
   char* base = c.base[rank];
   const int D = t.dim;
@@ -309,15 +477,25 @@ emb_apply_kernel(PdjComm c, PdjEmbTable t, int opt, float lr, float eps) {
   const int sub = lane / lpr, part = lane % lpr;
   // every slot this GPU holds: ceil(P / NR) of them (the last may be unused on some ranks; its flags stay clear)
   const int P_ = t.list_cap ? (int)t.list_cap : c.nranks;
-  const long long nwin = ((long long)((P_ + c.nranks - 1) / c.nranks) * t.rows_per_shard + 127) / 128;
+  const long long nrows = (long long)((P_ + c.nranks - 1) / c.nranks) * t.rows_per_shard;
+  const long long flag_limit = (nrows + 127) / 128 * 128;  // bytes the flag map holds
+  const long long nwin = (nrows + kApplyWin - 1) / kApplyWin;
   const long long gw = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const long long nw = ((long long)gridDim.x * blockDim.x) >> 5;
-  uint32_t* flags32 = reinterpret_cast<uint32_t*>(base + t.flag_off);
+  char* flags = base + t.flag_off;
+  const size_t sd = emb_sd(t), sw = emb_sw(t);
+  const bool wide_lane = part == 0 && t.has_wide;
   uint32_t touched = 0;
   for (long long w = gw; w < nwin; w += nw) {
-    const uint32_t f = flags32[w * 32 + lane];
-    const uint32_t m = ((f & 0xffu) ? 1u : 0u) | ((f & 0xff00u) ? 2u : 0u) | ((f & 0xff0000u) ? 4u : 0u) |
-                       ((f & 0xff000000u) ? 8u : 0u);
+    const long long r0 = w * kApplyWin + lane * 16;
+    uint4 f = make_uint4(0u, 0u, 0u, 0u);
+    if (r0 < flag_limit) f = *reinterpret_cast<const uint4*>(flags + r0);
+    const uint32_t fw[4] = {f.x, f.y, f.z, f.w};
+    uint32_t m = 0;
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+      m |= (((fw[q] & 0xffu) ? 1u : 0u) | ((fw[q] & 0xff00u) ? 2u : 0u) | ((fw[q] & 0xff0000u) ? 4u : 0u) |
+            ((fw[q] & 0xff000000u) ? 8u : 0u)) << (4 * q);
     if (__ballot_sync(0xffffffffu, m != 0u) == 0u) continue;
     const int cnt = __popc(m);
     int pre = cnt;  // inclusive prefix sum over the warp
@@ -329,45 +507,64 @@ emb_apply_kernel(PdjComm c, PdjEmbTable t, int opt, float lr, float eps) {
     const int total = __shfl_sync(0xffffffffu, pre, 31);
     int pos = pre - cnt;
 #pragma unroll
-    for (int b = 0; b < 4; ++b)
-      if ((m >> b) & 1u) queue[wib][pos++] = (uint32_t)(w * 128 + lane * 4 + b);
-    if (m != 0u) flags32[w * 32 + lane] = 0u;
+    for (int b = 0; b < 16; ++b)
+      if ((m >> b) & 1u) queue[wib][pos++] = (uint32_t)(r0 + b);
+    if (m != 0u) *reinterpret_cast<uint4*>(flags + r0) = make_uint4(0u, 0u, 0u, 0u);
     __syncwarp();
     touched += (uint32_t)total;
-    for (int i0 = 0; i0 < total; i0 += rpw) {
-      const int idx = i0 + sub;
-      if (idx >= total) continue;
-      const uint32_t row = queue[wib][idx];
-      const size_t o = (size_t)row * emb_sd(t) + part * 16;
-      float4* gp = reinterpret_cast<float4*>(base + t.gdeep_off + o);
-      float4* wp = reinterpret_cast<float4*>(base + t.deep_off + o);
-      const float4 g = *gp;
-      float4 wv = *wp;
-      if (opt == 1) {
-        float4* ap = reinterpret_cast<float4*>(base + t.acc_deep_off + o);
-        float4 a = *ap;
-        a.x += g.x * g.x; a.y += g.y * g.y; a.z += g.z * g.z; a.w += g.w * g.w;
-        *ap = a;
-        wv.x -= lr * g.x * rsqrtf(a.x + eps); wv.y -= lr * g.y * rsqrtf(a.y + eps);
-        wv.z -= lr * g.z * rsqrtf(a.z + eps); wv.w -= lr * g.w * rsqrtf(a.w + eps);
-      } else {
-        wv.x -= lr * g.x; wv.y -= lr * g.y; wv.z -= lr * g.z; wv.w -= lr * g.w;
+    for (int i0 = 0; i0 < total; i0 += rpw * kApplyBatch) {
+      bool ok[kApplyBatch];
+      size_t ro[kApplyBatch];
+      float4 g[kApplyBatch], wv[kApplyBatch], a[kApplyBatch];
+      float gs[kApplyBatch], ws[kApplyBatch], as[kApplyBatch];
+#pragma unroll
+      for (int k = 0; k < kApplyBatch; ++k) {
+        const int idx = i0 + k * rpw + sub;
+        ok[k] = idx < total;
+        ro[k] = ok[k] ? (size_t)queue[wib][idx] : 0;
       }
-      *wp = wv;
-      *gp = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (part == 0 && t.has_wide) {
-        float* gwp = reinterpret_cast<float*>(base + t.gwide_off + (size_t)row * emb_sw(t));
-        float* wwp = reinterpret_cast<float*>(base + t.wide_off + (size_t)row * emb_sw(t));
-        const float gwv = *gwp;
-        if (opt == 1) {
-          float* awp = reinterpret_cast<float*>(base + t.acc_wide_off + (size_t)row * emb_sw(t));
-          const float a = *awp + gwv * gwv;
-          *awp = a;
-          *wwp -= lr * gwv * rsqrtf(a + eps);
-        } else {
-          *wwp -= lr * gwv;
+#pragma unroll
+      for (int k = 0; k < kApplyBatch; ++k) {
+        if (!ok[k]) continue;
+        const size_t o = ro[k] * sd + part * 16;
+        g[k] = *reinterpret_cast<const float4*>(base + t.gdeep_off + o);
+        wv[k] = *reinterpret_cast<const float4*>(base + t.deep_off + o);
+        if (opt == 1) a[k] = *reinterpret_cast<const float4*>(base + t.acc_deep_off + o);
+        if (wide_lane) {
+          gs[k] = *reinterpret_cast<const float*>(base + t.gwide_off + ro[k] * sw);
+          ws[k] = *reinterpret_cast<const float*>(base + t.wide_off + ro[k] * sw);
+          if (opt == 1) as[k] = *reinterpret_cast<const float*>(base + t.acc_wide_off + ro[k] * sw);
         }
-        *gwp = 0.f;
+      }
+#pragma unroll
+      for (int k = 0; k < kApplyBatch; ++k) {
+        if (!ok[k]) continue;
+        const size_t o = ro[k] * sd + part * 16;
+        float4 w4 = wv[k];
+        const float4 g4 = g[k];
+        if (opt == 1) {
+          float4 a4 = a[k];
+          a4.x += g4.x * g4.x; a4.y += g4.y * g4.y; a4.z += g4.z * g4.z; a4.w += g4.w * g4.w;
+          *reinterpret_cast<float4*>(base + t.acc_deep_off + o) = a4;
+          w4.x -= lr * g4.x * rsqrtf(a4.x + eps); w4.y -= lr * g4.y * rsqrtf(a4.y + eps);
+          w4.z -= lr * g4.z * rsqrtf(a4.z + eps); w4.w -= lr * g4.w * rsqrtf(a4.w + eps);
+        } else {
+          w4.x -= lr * g4.x; w4.y -= lr * g4.y; w4.z -= lr * g4.z; w4.w -= lr * g4.w;
+        }
+        *reinterpret_cast<float4*>(base + t.deep_off + o) = w4;
+        *reinterpret_cast<float4*>(base + t.gdeep_off + o) = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (wide_lane) {
+          float wn = ws[k];
+          if (opt == 1) {
+            const float an = as[k] + gs[k] * gs[k];
+            *reinterpret_cast<float*>(base + t.acc_wide_off + ro[k] * sw) = an;
+            wn -= lr * gs[k] * rsqrtf(an + eps);
+          } else {
+            wn -= lr * gs[k];
+          }
+          *reinterpret_cast<float*>(base + t.wide_off + ro[k] * sw) = wn;
+          *reinterpret_cast<float*>(base + t.gwide_off + ro[k] * sw) = 0.f;
+        }
       }
     }
     __syncwarp();
@@ -427,7 +624,17 @@ int pdj_emb_lookup2(const PdjComm* c, const PdjEmbTable* t, size_t ids_off, size
                   S * t->dim + dense_n);
     return -1;
   }
-  static const bool no_tma = getenv("PDJ_EMB_NO_TMA") != nullptr;
+  // PDJ_EMB_LOOKUP = batched (default) | tma | loop
+  const char* how = getenv("PDJ_EMB_LOOKUP");
+  const bool no_tma = how == nullptr || strcmp(how, "tma") != 0;
+  const int passes = (S + (32 / (t->dim >> 2)) - 1) / (32 / (t->dim >> 2));
+  if ((how == nullptr || strcmp(how, "batched") == 0) && passes <= 8) {
+    int bt = emulate ? 256 : (passes <= 2 ? 1024 : 768);
+#define PDJ_LK(P) launch_emb(emb_lookup_batched_kernel<P>, nblocks, bt, (size_t)0, emulate, c->nranks, st, *c, *t, ids_off, \
+                             out_deep_off, out_wide_off, B, S, barrier, out_pitch, dense_off, dense_n)
+    return passes <= 1 ? PDJ_LK(1) : passes <= 2 ? PDJ_LK(2) : passes <= 4 ? PDJ_LK(4) : PDJ_LK(8);
+#undef PDJ_LK
+  }
   // Random 64-byte row gathers are latency-bound: what matters is rows in flight per SM.  With one block
   // per SM (the barrier-slot budget of a channel) that means many warps per block: 32 warps, two samples
   // in flight each.  The single-GPU emulation keeps small blocks so that all ranks stay co-resident.
@@ -465,6 +672,15 @@ int pdj_emb_push2(const PdjComm* c, const PdjEmbTable* t, size_t ids_off, size_t
   static const int knob_threads = getenv("PDJ_EMB_THREADS") ? atoi(getenv("PDJ_EMB_THREADS")) : 1024;
   int threads = emulate ? 256 : knob_threads;
   if (threads < 32 || threads > 1024 || threads % 32 != 0) threads = 256;
+  const char* how = getenv("PDJ_EMB_PUSH");  // batched (default) | loop
+  const int passes = (S + (32 / (t->dim >> 2)) - 1) / (32 / (t->dim >> 2));
+  if ((how == nullptr || strcmp(how, "batched") == 0) && passes <= 8) {
+    int bt = emulate ? 256 : (passes <= 2 ? 1024 : 768);
+#define PDJ_PS(P) launch_emb(emb_push_batched_kernel<P>, nblocks, bt, (size_t)0, emulate, c->nranks, st, *c, *t, ids_off, \
+                             gdeep_off, gwide_off, B, S, async_sgd ? 1 : 0, lr, grad_scale, g_pitch)
+    return passes <= 1 ? PDJ_PS(1) : passes <= 2 ? PDJ_PS(2) : passes <= 4 ? PDJ_PS(4) : PDJ_PS(8);
+#undef PDJ_PS
+  }
   return launch_emb(emb_push_kernel, nblocks, threads, (size_t)0, emulate, c->nranks, st, *c, *t, ids_off, gdeep_off, gwide_off,
                     B, S, async_sgd ? 1 : 0, lr, grad_scale, g_pitch);
 }

@@ -80,7 +80,7 @@ class ShardedEmbedding:
             t.gwide_off = a(R * 4)
             t.acc_deep_off = a(R * D * 4)
             t.acc_wide_off = a(R * 4)
-        self._flag_bytes = (R + 127) // 128 * 128
+        self._flag_bytes = (R + 511) // 512 * 512  # the apply kernel scans 512-row windows, 16 flags per lane
         t.flag_off = a(self._flag_bytes)  # one byte per row: "touched this step"
         t.list_off = self.record_floats * 4  # record stride in bytes; 0 = separate arrays
         t.count_off = a(256)

@@ -154,7 +154,10 @@ def main() -> int:
                                  "broadcast, allreduce_sgd_kernel) and the unrolled all-to-all, 8 ranks emulated on one GPU "
                                  "(HBM-local; ncu may not wrap a multi-rank run, NVLink numbers: r2/sweep_n*.json)",
             "prof_wd2": "Round 2: Wide&Deep step kernels at full size (batch 32768, 16.7 M rows, one GPU): TMA-fed lookup "
-                        "writing the padded tower input, push, apply, tcgen05 tower layers (profiles/run_wd_step.py)"}
+                        "writing the padded tower input, push, apply, tcgen05 tower layers (profiles/run_wd_step.py)",
+            "prof_wd3": "Round 2, final: Wide&Deep step kernels at full size (batch 32768, 16.7 M rows, one GPU) with one "
+                        "record per table row, the vectorised mask read, the MN-major tower weight gradient and the "
+                        "weighted column-sum kernel (profiles/run_wd_step.py)"}
     for n, t in reps.items():
         p = os.path.join(SCRATCH, n + ".ncu-rep")
         if os.path.exists(p):

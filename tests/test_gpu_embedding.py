@@ -121,13 +121,13 @@ def test_autograd_lookup_and_fused_update_single_rank():
 
 
 @pytest.mark.parametrize("nranks", [1, 2])
-@pytest.mark.parametrize("tma", ["1", "0"])
-def test_lookup_writes_padded_tower_input_in_place(nranks, tma, monkeypatch):
+@pytest.mark.parametrize("how", ["batched", "tma", "loop"])
+def test_lookup_writes_padded_tower_input_in_place(nranks, how, monkeypatch):
     """set_output_layout: rows of 432 = 26 x 16 embedding values | 13 dense features (fp32 -> bf16) | 3 zeros."""
     from paddle_operator_b200.parallel.ps import embedding_reference
 
-    if tma == "0":
-        monkeypatch.setenv("PDJ_EMB_NO_TMA", "1")  # read once per process: only effective if this runs first; harmless otherwise
+    monkeypatch.setenv("PDJ_EMB_LOOKUP", how)  # the three lookup kernels (csrc/embedding.cu); batched is the default
+    monkeypatch.setenv("PDJ_EMB_PUSH", "loop" if how == "loop" else "batched")
     comm, emb = _mk(nranks, dim=16, slots=26)
     try:
         emb.set_output_layout(432, 13)
