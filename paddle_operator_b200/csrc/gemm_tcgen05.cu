@@ -35,7 +35,61 @@ namespace {
 // Persistent: one CTA per SM walks tiles t = blockIdx.x, blockIdx.x + gridDim.x, ... (column tile
 // fastest, so CTAs running at the same time share A rows in L2).  The accumulator is double
 // buffered in TMEM: the epilogue of tile i overlaps the MMAs of tile i + 1.
-template <bool TMA_STORE>
+//
+// PAIR2: the same pipeline on CTA pairs (cluster of two, tcgen05 cta_group::2).  A pair owns a 256-row tile: each CTA
+// loads its own 128 rows of A and HALF of the B tile (block_n / 2 rows), the leader's elected thread issues M = 256
+// MMAs that read both halves of B out of the two CTAs' shared memory and write 128 accumulator rows into each CTA's
+// tensor memory, and tcgen05.commit multicasts the ring-slot / accumulator barriers to both CTAs.  Every byte of B
+// is fetched from L2 once per 256 rows instead of once per 128: skinny layers (K, N ~ 400) are bound by exactly
+// that traffic (150 MB L2 -> SM per 32768 x 400 x 432 layer against a measured ~12 TB/s ceiling).
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ uint32_t mapa_rank(uint32_t addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// TMA load of a CTA pair: data into this CTA's shared memory, bytes counted on the LEADER's mbarrier.
+__device__ __forceinline__ void tma_load_2d_pair(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint32_t leader_bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(dst),
+      "l"(map), "r"(c0), "r"(c1), "r"(leader_bar)
+      : "memory");
+}
+__device__ __forceinline__ void umma_f16_pair_elect(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p, q;\n\t"
+      "elect.sync _|q, 0xffffffff;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "@q tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "}" ::"r"(tmem_d),
+      "l"(da), "l"(db), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// Arrives on the barrier at this shared-memory offset in BOTH CTAs of the pair once the MMAs issued so far are done.
+__device__ __forceinline__ void umma_commit_pair_elect(uint32_t bar) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred q;\n\t"
+      "elect.sync _|q, 0xffffffff;\n\t"
+      "@q tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;\n\t"
+      "}" ::"r"(bar),
+      "h"((uint16_t)3)
+      : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_bar) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_bar) : "memory");
+}
+
+template <bool TMA_STORE, bool PAIR2>
 __global__ void __launch_bounds__(THREADS, 1)
 linear_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                       const __grid_constant__ CUtensorMap tma_o, __nv_bfloat16* __restrict__ out,
@@ -44,7 +98,7 @@ linear_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
   const uint32_t base = (raw + 1023u) & ~1023u;  // SWIZZLE_128B wants 1024-byte alignment
-  const uint32_t b_stage_bytes = (uint32_t)block_n * BK * 2;
+  const uint32_t b_stage_bytes = (uint32_t)(PAIR2 ? block_n / 2 : block_n) * BK * 2;  // PAIR2: this CTA's half of the B tile
   const uint32_t a_smem = base;
   const uint32_t b_smem = a_smem + stages * A_STAGE_BYTES;
   const uint32_t stage_out = b_smem + stages * b_stage_bytes;                    // [128][block_n] bf16 staging
@@ -56,8 +110,12 @@ linear_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
 
   const int warp = (int)warp_uniform(threadIdx.x >> 5), lane = threadIdx.x & 31;
   const int tiles_n = (N + block_n - 1) / block_n;
-  const int total = ((M + BM - 1) / BM) * tiles_n;
+  constexpr int TILE_M = PAIR2 ? 2 * BM : BM;          // rows per work item (a CTA or a CTA pair)
+  const int total = ((M + TILE_M - 1) / TILE_M) * tiles_n;
   const int num_kb = (K + BK - 1) / BK;
+  const uint32_t crank = PAIR2 ? warp_uniform(cluster_ctarank()) : 0u;
+  const int unit = PAIR2 ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;     // which persistent worker this CTA belongs to
+  const int units = PAIR2 ? (int)(gridDim.x >> 1) : (int)gridDim.x;
 
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_a) : "memory");
@@ -72,25 +130,79 @@ linear_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
       }
       for (int b = 0; b < 2; ++b) {
         mbar_init(tfull0 + 8 * b, 1);
-        mbar_init(tempty0 + 8 * b, EPI_WARPS);  // one arrival per epilogue warp
+        mbar_init(tempty0 + 8 * b, PAIR2 ? 2 * EPI_WARPS : EPI_WARPS);  // one arrival per epilogue warp (of both CTAs)
       }
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncwarp();
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(TMEM_COLS)
-                 : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    if (PAIR2) {
+      asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(TMEM_COLS)
+                   : "memory");
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    } else {
+      asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(TMEM_COLS)
+                   : "memory");
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
+  if (PAIR2) cluster_sync_all();  // the peer's barriers exist before anything arrives on them
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const uint32_t tmem_base = warp_uniform(*tmem_slot_ptr);
   const Pipe pipe{a_smem, b_smem, b_stage_bytes, full0, empty0, tfull0, tempty0, stages};
 
   if (warp == 0) {
-    if (lane == 0) producer_loop(&tma_a, &tma_b, pipe, total, tiles_n, block_n, num_kb);
+    if (lane == 0) {
+      if (PAIR2) {
+        // both CTAs load; the bytes of both land on the leader's barrier, which the leader arms for the pair
+        const uint32_t per_cta = (uint32_t)A_STAGE_BYTES + b_stage_bytes;
+        uint32_t it = 0;
+        for (int t = unit; t < total; t += units) {
+          const int m0 = (t / tiles_n) * TILE_M + (int)crank * BM;
+          const int n0 = (t % tiles_n) * block_n + (int)crank * (block_n / 2);
+          for (int kb = 0; kb < num_kb; ++kb, ++it) {
+            const uint32_t s_ = it % (uint32_t)stages, ph = (it / (uint32_t)stages) & 1u;
+            mbar_wait(empty0 + 8 * s_, ph ^ 1u);
+            if (crank == 0) mbar_expect_tx(full0 + 8 * s_, 2u * per_cta);
+            const uint32_t lbar = mapa_rank(full0 + 8 * s_, 0);
+            tma_load_2d_pair(a_smem + s_ * A_STAGE_BYTES, &tma_a, kb * BK, m0, lbar);
+            tma_load_2d_pair(b_smem + s_ * b_stage_bytes, &tma_b, kb * BK, n0, lbar);
+          }
+        }
+      } else {
+        producer_loop(&tma_a, &tma_b, pipe, total, tiles_n, block_n, num_kb);
+      }
+    }
   } else if (warp == 1) {
-    mma_loop(pipe, tmem_base, total, block_n, num_kb);  // whole warp, one elected lane issues
+    if (PAIR2) {
+      if (crank == 0) {  // the leader issues for the pair (whole warp, one elected lane)
+        const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(block_n >> 3) << 17) | ((uint32_t)(TILE_M >> 4) << 24);
+        const uint64_t d0 = umma_desc(0);
+        uint32_t it = 0, i = 0;
+        for (int t = unit; t < total; t += units, ++i) {
+          const uint32_t buf = i & 1u, aph = (i >> 1) & 1u;
+          mbar_wait(tempty0 + 8 * buf, aph ^ 1u);  // both CTAs' epilogues have drained this accumulator
+          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          const uint32_t tmem_d = tmem_base + buf * MAX_BN;
+          for (int kb = 0; kb < num_kb; ++kb, ++it) {
+            const uint32_t s_ = it % (uint32_t)stages, ph = (it / (uint32_t)stages) & 1u;
+            mbar_wait(full0 + 8 * s_, ph);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint64_t da = d0 + (uint64_t)((a_smem + s_ * A_STAGE_BYTES) >> 4);
+            const uint64_t db = d0 + (uint64_t)((b_smem + s_ * b_stage_bytes) >> 4);
+#pragma unroll
+            for (int k = 0; k < BK / UK; ++k)
+              umma_f16_pair_elect(tmem_d, da + (uint64_t)(k * UK * 2 >> 4), db + (uint64_t)(k * UK * 2 >> 4), idesc,
+                                  (uint32_t)((kb | k) != 0));
+            umma_commit_pair_elect(empty0 + 8 * s_);
+          }
+          umma_commit_pair_elect(tfull0 + 8 * buf);
+        }
+      }
+    } else {
+      mma_loop(pipe, tmem_base, total, block_n, num_kb);  // whole warp, one elected lane issues
+    }
   } else {
     // ===== epilogue: warps 2..9.  Warp w reads TMEM lane quarter (w % 4) - a hardware rule -
     // and the two warps of a quarter split the columns in halves. =====
@@ -102,8 +214,8 @@ linear_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
     const int c_end = (c_begin + ncols_half < block_n) ? c_begin + ncols_half : block_n;
     float* bias_s = reinterpret_cast<float*>(smem_raw + (bias_smem - raw));
     uint32_t i = 0;
-    for (int t = blockIdx.x; t < total; t += gridDim.x, ++i) {
-      const int m0 = (t / tiles_n) * BM, n0 = (t % tiles_n) * block_n;
+    for (int t = unit; t < total; t += units, ++i) {
+      const int m0 = (t / tiles_n) * TILE_M + (int)crank * BM, n0 = (t % tiles_n) * block_n;
       const uint32_t buf = i & 1u, aph = (i >> 1) & 1u;
       // bias slice of this column tile -> shared memory (overlaps the wait for the accumulator)
       if (TMA_STORE && et == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
@@ -206,7 +318,10 @@ linear_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
       // this accumulator buffer may be overwritten by the MMA warp now
       asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
       __syncwarp();
-      if (lane == 0) mbar_arrive(tempty0 + 8 * buf);
+      if (lane == 0) {
+        if (PAIR2) mbar_arrive_cluster(mapa_rank(tempty0 + 8 * buf, 0));  // the leader's MMA warp waits for both CTAs
+        else mbar_arrive(tempty0 + 8 * buf);
+      }
       if (TMA_STORE) {
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy writes -> visible to the TMA engine
         asm volatile("bar.sync 1, %0;" ::"n"(32 * EPI_WARPS) : "memory");
@@ -220,8 +335,10 @@ linear_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
+  if (PAIR2) cluster_sync_all();  // neither CTA leaves (or frees tensor memory) while the pair's MMAs may still touch it
   if (warp == 1) {
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
+    if (PAIR2) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
+    else asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
   }
 }
 
@@ -229,8 +346,10 @@ bool g_attr_set = false;
 
 int ensure_init() {
   if (g_attr_set) return 0;
-  PDJ_CUDA_CHECK(cudaFuncSetAttribute(linear_tcgen05_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
-  PDJ_CUDA_CHECK(cudaFuncSetAttribute(linear_tcgen05_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+  PDJ_CUDA_CHECK(cudaFuncSetAttribute(linear_tcgen05_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+  PDJ_CUDA_CHECK(cudaFuncSetAttribute(linear_tcgen05_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+  PDJ_CUDA_CHECK(cudaFuncSetAttribute(linear_tcgen05_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+  PDJ_CUDA_CHECK(cudaFuncSetAttribute(linear_tcgen05_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
   g_attr_set = true;
   return 0;
 }
@@ -264,16 +383,23 @@ int pdj_linear_bf16(const void* a, const void* b, void* out, const float* bias, 
   static const bool force_tma = getenv("PDJ_GEMM_TMA_STORE") != nullptr;
   const bool tma_ok = (ldo % 8 == 0) && (((uintptr_t)out & 15) == 0);
   const bool tma_store = tma_ok && !force_direct && (force_tma || bn < MAX_BN);
+  // CTA pairs (tcgen05 cta_group::2): each byte of B leaves L2 once per 256 rows.  PDJ_LINEAR_PAIR=0/1 overrides.
+  const char* pair_env = getenv("PDJ_LINEAR_PAIR");
+  const int sms = pdj_tc_sm_count();
+  // Measured (profiles/r2/linear_pair.md): +10..15 % where the B stream matters (8192 x 4096 x 4096: 1.55 -> 1.72 PFLOP/s,
+  // above the library's 1.56), a loss on the skinny Wide&Deep layers, whose limit is the A stream and the epilogue.
+  const bool pair_auto = K >= 1024 && N >= 256 && M >= 4 * BM;
+  const bool pair = (pair_env ? atoi(pair_env) != 0 : pair_auto) && bn % 16 == 0 && M >= 2 * BM && sms >= 2;
   CUtensorMap ma, mb, mo;
   if (int r = pdj_tc_make_map(&ma, a, M, K, lda, BK, BM, true)) return r;
-  if (int r = pdj_tc_make_map(&mb, b, N, K, ldb, BK, bn, true)) return r;
+  if (int r = pdj_tc_make_map(&mb, b, N, K, ldb, BK, pair ? bn / 2 : bn, true)) return r;
   if (tma_store) {
     if (int r = pdj_tc_make_map(&mo, out, M, N, ldo, bn, BM, false)) return r;
   } else {
     mo = ma;
   }
   if (int r = ensure_init()) return r;
-  const int stage_bytes = A_STAGE_BYTES + bn * BK * 2;
+  const int stage_bytes = A_STAGE_BYTES + (pair ? bn / 2 : bn) * BK * 2;
   const int fixed = 1024 /*alignment*/ + 256 /*barriers*/ + MAX_BN * 4 /*bias slice*/ + (tma_store ? BM * bn * 2 : 0);
   int stages = (SMEM_LIMIT - fixed) / stage_bytes;
   if (stages > MAX_STAGES) stages = MAX_STAGES;
@@ -282,15 +408,39 @@ int pdj_linear_bf16(const void* a, const void* b, void* out, const float* bias, 
     return -1;
   }
   const int smem = fixed + stages * stage_bytes;
-  const int total = ((M + BM - 1) / BM) * ((N + bn - 1) / bn);
-  const int sms = pdj_tc_sm_count();
+  const int tile_m = pair ? 2 * BM : BM;
+  const int total = ((M + tile_m - 1) / tile_m) * ((N + bn - 1) / bn);
+  if (pair) {
+    int grid = 2 * total < sms ? 2 * total : (sms & ~1);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(THREADS);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    __nv_bfloat16* outp = (__nv_bfloat16*)out;
+    const __nv_bfloat16* maskp = (const __nv_bfloat16*)mask;
+    if (tma_store)
+      PDJ_CUDA_CHECK(cudaLaunchKernelEx(&cfg, linear_tcgen05_kernel<true, true>, ma, mb, mo, outp, bias, maskp, M, N, K, ldo, bn,
+                                        stages, relu));
+    else
+      PDJ_CUDA_CHECK(cudaLaunchKernelEx(&cfg, linear_tcgen05_kernel<false, true>, ma, mb, mo, outp, bias, maskp, M, N, K, ldo, bn,
+                                        stages, relu));
+    return 0;
+  }
   const int grid = total < sms ? total : sms;
   if (tma_store)
-    linear_tcgen05_kernel<true><<<grid, THREADS, smem, st>>>(ma, mb, mo, (__nv_bfloat16*)out, bias, (const __nv_bfloat16*)mask,
-                                                            M, N, K, ldo, bn, stages, relu);
+    linear_tcgen05_kernel<true, false><<<grid, THREADS, smem, st>>>(ma, mb, mo, (__nv_bfloat16*)out, bias,
+                                                                   (const __nv_bfloat16*)mask, M, N, K, ldo, bn, stages, relu);
   else
-    linear_tcgen05_kernel<false><<<grid, THREADS, smem, st>>>(ma, mb, mo, (__nv_bfloat16*)out, bias,
-                                                             (const __nv_bfloat16*)mask, M, N, K, ldo, bn, stages, relu);
+    linear_tcgen05_kernel<false, false><<<grid, THREADS, smem, st>>>(ma, mb, mo, (__nv_bfloat16*)out, bias,
+                                                                    (const __nv_bfloat16*)mask, M, N, K, ldo, bn, stages, relu);
   PDJ_CUDA_CHECK(cudaGetLastError());
   return 0;
 }

@@ -33,9 +33,13 @@ for (m, n, k) in [(32768, 400, 432), (32768, 400, 400), (32768, 1, 400), (8192, 
     ac = a.contiguous()
     bias = torch.randn(n, device=dev)
     bias16 = bias.to(torch.bfloat16)
+    os.environ["PDJ_LINEAR_PAIR"] = "0"
     t_ours = timeit(lambda: linear_bf16(a, w, bias, relu=True))
+    os.environ["PDJ_LINEAR_PAIR"] = "1"  # CTA pairs (tcgen05 cta_group::2); read by the library on every call
+    t_pair = timeit(lambda: linear_bf16(a, w, bias, relu=True))
+    os.environ.pop("PDJ_LINEAR_PAIR")
     t_torch = timeit(lambda: torch.relu(torch.nn.functional.linear(ac, wc, bias16)))
     t_mm = timeit(lambda: torch.mm(ac, wc.t()))
     fl = 2.0 * m * n * k
-    print(f"M={m} N={n} K={k}: ours(fused) {t_ours:8.1f} us {fl / t_ours / 1e6:7.1f} TFLOP/s | torch linear+relu {t_torch:8.1f} us "
+    print(f"M={m} N={n} K={k}: ours(fused) {t_ours:8.1f} us {fl / t_ours / 1e6:7.1f} TFLOP/s | CTA pairs {t_pair:8.1f} us {fl / t_pair / 1e6:7.1f} TFLOP/s | torch linear+relu {t_torch:8.1f} us "
           f"| cuBLAS mm only {t_mm:8.1f} us {fl / t_mm / 1e6:7.1f} TFLOP/s", flush=True)

@@ -155,6 +155,8 @@ def main() -> int:
                                  "(HBM-local; ncu may not wrap a multi-rank run, NVLink numbers: r2/sweep_n*.json)",
             "prof_wd2": "Round 2: Wide&Deep step kernels at full size (batch 32768, 16.7 M rows, one GPU): TMA-fed lookup "
                         "writing the padded tower input, push, apply, tcgen05 tower layers (profiles/run_wd_step.py)",
+            "prof_gemm2": "Fused linear 8192 x 4096 x 4096 (bias + ReLU): one CTA per tile, then CTA pairs (tcgen05 cta_group::2, "
+                          "M = 256 tiles), twice each (profiles/run_gemm_pair.py); round 2",
             "prof_wd3": "Round 2, final: Wide&Deep step kernels at full size (batch 32768, 16.7 M rows, one GPU) with one "
                         "record per table row, the vectorised mask read, the MN-major tower weight gradient and the "
                         "weighted column-sum kernel (profiles/run_wd_step.py)"}

@@ -13,6 +13,29 @@ def _conv_gemm_for_every_size(monkeypatch):
     monkeypatch.setattr(conv_ops, "MIN_OUTPUT_BYTES", 0)
 
 
+@pytest.mark.parametrize("m,n,k", [(256, 128, 64), (300, 400, 432), (1000, 1000, 2048), (4096, 512, 1024), (2048, 48, 4096),
+                                   (257, 16, 40)])
+def test_linear_cta_pair_mode_matches_fp32(m, n, k, monkeypatch):
+    """tcgen05 cta_group::2: a CTA pair owns a 256-row tile (ragged last pair, odd pair counts, masks, narrow N)."""
+    from paddle_operator_b200.ops.gemm import linear_bf16
+
+    monkeypatch.setenv("PDJ_LINEAR_PAIR", "1")  # read by the library on every call
+    torch.manual_seed(m * 3 + n + k)
+    k8 = (k + 7) // 8 * 8
+    a = (torch.randn(m, k8, device="cuda") * 0.5).to(torch.bfloat16)[:, :k]
+    b = (torch.randn(n, k8, device="cuda") * 0.5).to(torch.bfloat16)[:, :k]
+    bias = torch.randn(n, device="cuda")
+    n8 = (n + 7) // 8 * 8
+    gate = (torch.randn(m, n8, device="cuda") > 0).to(torch.bfloat16)[:, :n]
+    ref = a.float() @ b.float().t() + bias
+    tol = dict(atol=3e-2 * (k ** 0.5) * 0.25 + 2e-2, rtol=2e-2)
+    torch.testing.assert_close(linear_bf16(a, b, bias, relu=True).float(), torch.relu(ref), **tol)
+    if n % 8 == 0:
+        torch.testing.assert_close(linear_bf16(a, b, bias, mask=gate).float(), ref * gate.float(), **tol)
+    monkeypatch.setenv("PDJ_LINEAR_PAIR", "0")
+    torch.testing.assert_close(linear_bf16(a, b, bias, relu=True).float(), torch.relu(ref), **tol)
+
+
 @pytest.mark.parametrize("m,n,k", [(128, 128, 64), (256, 400, 400), (1000, 400, 432), (4096, 1, 400), (77, 24, 40),
                                    (32768, 400, 400), (513, 1000, 2048)])
 @pytest.mark.parametrize("relu,use_bias", [(False, False), (True, True)])
