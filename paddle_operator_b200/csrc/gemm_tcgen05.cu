@@ -94,20 +94,27 @@ __global__ void __launch_bounds__(THREADS, 1)
 linear_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                       const __grid_constant__ CUtensorMap tma_o, __nv_bfloat16* __restrict__ out,
                       const float* __restrict__ bias, const __nv_bfloat16* __restrict__ mask, int M, int N, int K,
-                      int ldo, int block_n, int stages, int relu) {
+                      int ldo, int block_n, int stages, int relu, int b_resident) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
   const uint32_t base = (raw + 1023u) & ~1023u;  // SWIZZLE_128B wants 1024-byte alignment
   const uint32_t b_stage_bytes = (uint32_t)(PAIR2 ? block_n / 2 : block_n) * BK * 2;  // PAIR2: this CTA's half of the B tile
   const uint32_t a_smem = base;
   const uint32_t b_smem = a_smem + stages * A_STAGE_BYTES;
-  const uint32_t stage_out = b_smem + stages * b_stage_bytes;                    // [128][block_n] bf16 staging
+  // PAIR2 with b_resident: this CTA's half of the whole B panel (every k-block of its column tile) stays in shared
+  // memory for the life of the kernel and only A streams through the ring - possible because a pair always works
+  // on the same column tile (the host checks that the persistent stride is a multiple of the column-tile count).
+  const int num_kb_ = (K + BK - 1) / BK;
+  const uint32_t stage_out = b_smem + (uint32_t)((PAIR2 && b_resident) ? num_kb_ : stages) * b_stage_bytes;  // [128][block_n] bf16 staging
   const uint32_t bias_smem = stage_out + (TMA_STORE ? (uint32_t)BM * block_n * 2 : 0u);      // fp32 [block_n]
   const uint32_t bars = bias_smem + MAX_BN * 4;
   const uint32_t full0 = bars, empty0 = bars + 8 * MAX_STAGES;
   const uint32_t tfull0 = bars + 16 * MAX_STAGES, tempty0 = tfull0 + 16, tmem_slot = tempty0 + 16;
+  const uint32_t bres = tmem_slot + 16;  // resident B panel has landed (PAIR2 + b_resident)
   uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(smem_raw + (tmem_slot - raw));
 
+  const int dbg = relu >> 8;  // diagnostic bits (PDJ_LINEAR_DBG): 1 = no TMA store, 2 = no staging writes, 4 = no drain
+  relu &= 0xff;
   const int warp = (int)warp_uniform(threadIdx.x >> 5), lane = threadIdx.x & 31;
   const int tiles_n = (N + block_n - 1) / block_n;
   constexpr int TILE_M = PAIR2 ? 2 * BM : BM;          // rows per work item (a CTA or a CTA pair)
@@ -132,6 +139,7 @@ linear_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
         mbar_init(tfull0 + 8 * b, 1);
         mbar_init(tempty0 + 8 * b, PAIR2 ? 2 * EPI_WARPS : EPI_WARPS);  // one arrival per epilogue warp (of both CTAs)
       }
+      mbar_init(bres, 1);
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncwarp();
@@ -156,7 +164,13 @@ linear_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
     if (lane == 0) {
       if (PAIR2) {
         // both CTAs load; the bytes of both land on the leader's barrier, which the leader arms for the pair
-        const uint32_t per_cta = (uint32_t)A_STAGE_BYTES + b_stage_bytes;
+        const uint32_t per_cta = (uint32_t)A_STAGE_BYTES + (b_resident ? 0u : b_stage_bytes);
+        if (b_resident && unit < total) {
+          if (crank == 0) mbar_expect_tx(bres, 2u * (uint32_t)num_kb * b_stage_bytes);
+          const uint32_t lb = mapa_rank(bres, 0);
+          const int nb0 = (unit % tiles_n) * block_n + (int)crank * (block_n / 2);
+          for (int kb = 0; kb < num_kb; ++kb) tma_load_2d_pair(b_smem + kb * b_stage_bytes, &tma_b, kb * BK, nb0, lb);
+        }
         uint32_t it = 0;
         for (int t = unit; t < total; t += units) {
           const int m0 = (t / tiles_n) * TILE_M + (int)crank * BM;
@@ -167,7 +181,7 @@ linear_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
             if (crank == 0) mbar_expect_tx(full0 + 8 * s_, 2u * per_cta);
             const uint32_t lbar = mapa_rank(full0 + 8 * s_, 0);
             tma_load_2d_pair(a_smem + s_ * A_STAGE_BYTES, &tma_a, kb * BK, m0, lbar);
-            tma_load_2d_pair(b_smem + s_ * b_stage_bytes, &tma_b, kb * BK, n0, lbar);
+            if (!b_resident) tma_load_2d_pair(b_smem + s_ * b_stage_bytes, &tma_b, kb * BK, n0, lbar);
           }
         }
       } else {
@@ -180,6 +194,7 @@ linear_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
         const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(block_n >> 3) << 17) | ((uint32_t)(TILE_M >> 4) << 24);
         const uint64_t d0 = umma_desc(0);
         uint32_t it = 0, i = 0;
+        if (b_resident && unit < total) mbar_wait(bres, 0);
         for (int t = unit; t < total; t += units, ++i) {
           const uint32_t buf = i & 1u, aph = (i >> 1) & 1u;
           mbar_wait(tempty0 + 8 * buf, aph ^ 1u);  // both CTAs' epilogues have drained this accumulator
@@ -190,7 +205,7 @@ linear_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
             mbar_wait(full0 + 8 * s_, ph);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const uint64_t da = d0 + (uint64_t)((a_smem + s_ * A_STAGE_BYTES) >> 4);
-            const uint64_t db = d0 + (uint64_t)((b_smem + s_ * b_stage_bytes) >> 4);
+            const uint64_t db = d0 + (uint64_t)((b_smem + (uint32_t)(b_resident ? kb : (int)s_) * b_stage_bytes) >> 4);
 #pragma unroll
             for (int k = 0; k < BK / UK; ++k)
               umma_f16_pair_elect(tmem_d, da + (uint64_t)(k * UK * 2 >> 4), db + (uint64_t)(k * UK * 2 >> 4), idesc,
@@ -214,14 +229,19 @@ linear_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
     const int c_end = (c_begin + ncols_half < block_n) ? c_begin + ncols_half : block_n;
     float* bias_s = reinterpret_cast<float*>(smem_raw + (bias_smem - raw));
     uint32_t i = 0;
+    int bias_n0 = -1;
     for (int t = unit; t < total; t += units, ++i) {
       const int m0 = (t / tiles_n) * TILE_M + (int)crank * BM, n0 = (t % tiles_n) * block_n;
       const uint32_t buf = i & 1u, aph = (i >> 1) & 1u;
-      // bias slice of this column tile -> shared memory (overlaps the wait for the accumulator)
+      // bias slice of this column tile -> shared memory; reloaded only when the column tile changes (never, when the
+      // persistent stride is a multiple of the column-tile count): a global load + a second barrier per tile otherwise
       if (TMA_STORE && et == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
       asm volatile("bar.sync 1, %0;" ::"n"(32 * EPI_WARPS) : "memory");  // previous tile's bias / staging are free
-      for (int j = et; j < block_n; j += 32 * EPI_WARPS) bias_s[j] = (bias != nullptr && n0 + j < N) ? __ldg(bias + n0 + j) : 0.f;
-      asm volatile("bar.sync 1, %0;" ::"n"(32 * EPI_WARPS) : "memory");
+      if (n0 != bias_n0) {
+        for (int j = et; j < block_n; j += 32 * EPI_WARPS) bias_s[j] = (bias != nullptr && n0 + j < N) ? __ldg(bias + n0 + j) : 0.f;
+        asm volatile("bar.sync 1, %0;" ::"n"(32 * EPI_WARPS) : "memory");
+        bias_n0 = n0;
+      }
       const int row = m0 + q * 32 + lane;
       if (mask != nullptr && row < M) {
         const char* mrow = reinterpret_cast<const char*>(mask + (size_t)row * ldo + n0 + c_begin);
@@ -231,7 +251,7 @@ linear_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
       mbar_wait(tfull0 + 8 * buf, aph);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       const uint32_t taddr_row = tmem_base + buf * MAX_BN + ((uint32_t)(q * 32) << 16);
-      for (int c0 = c_begin; c0 < c_end; c0 += 32) {
+      for (int c0 = c_begin; c0 < ((dbg & 4) ? c_begin : c_end); c0 += 32) {
         // two 16-column loads in flight, one wait
         uint32_t r[32];
         const bool second = c0 + 16 < c_end;
@@ -298,7 +318,8 @@ linear_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
           p0.z = pdj_f2_to_bf2(v[4], v[5]); p0.w = pdj_f2_to_bf2(v[6], v[7]);
           p1.x = pdj_f2_to_bf2(v[8], v[9]); p1.y = pdj_f2_to_bf2(v[10], v[11]);
           p1.z = pdj_f2_to_bf2(v[12], v[13]); p1.w = pdj_f2_to_bf2(v[14], v[15]);
-          if (TMA_STORE) {
+          if (TMA_STORE && (dbg & 2)) {
+          } else if (TMA_STORE) {
             const uint32_t dst = stage_out + (uint32_t)((q * 32 + lane) * block_n + cc) * 2;
             asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(dst), "r"(p0.x), "r"(p0.y), "r"(p0.z), "r"(p0.w) : "memory");
             asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(dst + 16), "r"(p1.x), "r"(p1.y), "r"(p1.z), "r"(p1.w) : "memory");
@@ -326,7 +347,7 @@ linear_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy writes -> visible to the TMA engine
         asm volatile("bar.sync 1, %0;" ::"n"(32 * EPI_WARPS) : "memory");
         if (et == 0) {
-          tma_store_2d(&tma_o, stage_out, n0, m0);  // rows / columns beyond M, N are clipped by the tensor map
+          if (!(dbg & 1)) tma_store_2d(&tma_o, stage_out, n0, m0);  // rows / columns beyond M, N are clipped by the tensor map
           asm volatile("cp.async.bulk.commit_group;" ::: "memory");
         }
       }
@@ -375,6 +396,7 @@ int pdj_linear_bf16(const void* a, const void* b, void* out, const float* bias, 
     return -1;
   }
   const int bn = pdj_linear_block_n(N);
+  if (const char* d = getenv("PDJ_LINEAR_DBG")) relu |= atoi(d) << 8;  // diagnostics only (profiles/r2/linear_pair.md)
   // TMA store needs a 16-byte aligned output pitch; otherwise the epilogue stores directly.
   // Measured on B200 (profiles/gemm_bench.py): staging + TMA store wins for narrow outputs (it frees
   // the epilogue warps early), direct 32-byte stores win once the tile is 256 wide, where the staging
@@ -399,19 +421,27 @@ int pdj_linear_bf16(const void* a, const void* b, void* out, const float* bias, 
     mo = ma;
   }
   if (int r = ensure_init()) return r;
-  const int stage_bytes = A_STAGE_BYTES + (pair ? bn / 2 : bn) * BK * 2;
+  const int tile_m = pair ? 2 * BM : BM;
+  const int tiles_n_h = (N + bn - 1) / bn;
+  const int total = ((M + tile_m - 1) / tile_m) * tiles_n_h;
   const int fixed = 1024 /*alignment*/ + 256 /*barriers*/ + MAX_BN * 4 /*bias slice*/ + (tma_store ? BM * bn * 2 : 0);
-  int stages = (SMEM_LIMIT - fixed) / stage_bytes;
+  // CTA pairs that always work on the same column tile keep their half of the whole B panel in shared memory
+  const int pair_grid = 2 * total < sms ? 2 * total : (sms & ~1);
+  const int num_kb_h = (K + BK - 1) / BK;
+  const int panel = num_kb_h * (bn / 2) * BK * 2;
+  const char* res_env = getenv("PDJ_LINEAR_BRES");
+  const bool resident = pair && (res_env ? atoi(res_env) != 0 : true) && (pair_grid / 2) % tiles_n_h == 0 &&
+                        fixed + panel + 3 * A_STAGE_BYTES <= SMEM_LIMIT;
+  const int stage_bytes = resident ? A_STAGE_BYTES : A_STAGE_BYTES + (pair ? bn / 2 : bn) * BK * 2;
+  int stages = (SMEM_LIMIT - fixed - (resident ? panel : 0)) / stage_bytes;
   if (stages > MAX_STAGES) stages = MAX_STAGES;
   if (stages < 2) {
     pdj_set_error("pdj_linear_bf16: tile does not fit in shared memory (block_n=%d)", bn);
     return -1;
   }
-  const int smem = fixed + stages * stage_bytes;
-  const int tile_m = pair ? 2 * BM : BM;
-  const int total = ((M + tile_m - 1) / tile_m) * ((N + bn - 1) / bn);
+  const int smem = fixed + (resident ? panel : 0) + stages * stage_bytes;
   if (pair) {
-    int grid = 2 * total < sms ? 2 * total : (sms & ~1);
+    const int grid = pair_grid;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(grid);
     cfg.blockDim = dim3(THREADS);
@@ -428,19 +458,19 @@ int pdj_linear_bf16(const void* a, const void* b, void* out, const float* bias, 
     const __nv_bfloat16* maskp = (const __nv_bfloat16*)mask;
     if (tma_store)
       PDJ_CUDA_CHECK(cudaLaunchKernelEx(&cfg, linear_tcgen05_kernel<true, true>, ma, mb, mo, outp, bias, maskp, M, N, K, ldo, bn,
-                                        stages, relu));
+                                        stages, relu, resident ? 1 : 0));
     else
       PDJ_CUDA_CHECK(cudaLaunchKernelEx(&cfg, linear_tcgen05_kernel<false, true>, ma, mb, mo, outp, bias, maskp, M, N, K, ldo, bn,
-                                        stages, relu));
+                                        stages, relu, resident ? 1 : 0));
     return 0;
   }
   const int grid = total < sms ? total : sms;
   if (tma_store)
     linear_tcgen05_kernel<true, false><<<grid, THREADS, smem, st>>>(ma, mb, mo, (__nv_bfloat16*)out, bias,
-                                                                   (const __nv_bfloat16*)mask, M, N, K, ldo, bn, stages, relu);
+                                                                   (const __nv_bfloat16*)mask, M, N, K, ldo, bn, stages, relu, 0);
   else
     linear_tcgen05_kernel<false, false><<<grid, THREADS, smem, st>>>(ma, mb, mo, (__nv_bfloat16*)out, bias,
-                                                                    (const __nv_bfloat16*)mask, M, N, K, ldo, bn, stages, relu);
+                                                                    (const __nv_bfloat16*)mask, M, N, K, ldo, bn, stages, relu, 0);
   PDJ_CUDA_CHECK(cudaGetLastError());
   return 0;
 }

@@ -225,22 +225,21 @@ colsum_w_kernel(const __nv_bfloat16* __restrict__ x, int ld, int M, int N, const
         acc[4] = fmaf(w, c.x, acc[4]); acc[5] = fmaf(w, c.y, acc[5]);
         acc[6] = fmaf(w, d.x, acc[6]); acc[7] = fmaf(w, d.y, acc[7]);
       };
-      int r = r0 + rg;
-      // eight rows per round: all sixteen loads are issued before the first use (one block per SM, so the
-      // memory-level parallelism has to come from inside the thread)
-      for (; r + 7 * RG < r1; r += 8 * RG) {
+      // eight rows per round, the last round predicated: all loads of a round are issued before the first use (one
+      // block per SM, so the memory-level parallelism has to come from inside the thread) and no serial tail remains
+      for (int r = r0 + rg; r < r1; r += 8 * RG) {
         uint4 v[8];
         float w[8];
 #pragma unroll
         for (int u = 0; u < 8; ++u) {
-          v[u] = __ldg(reinterpret_cast<const uint4*>(xp + (size_t)(r + u * RG) * ld));
-          w[u] = wgt ? __ldg(wgt + r + u * RG) : 1.f;
+          const int ru = r + u * RG;
+          const bool in = ru < r1;
+          v[u] = in ? __ldg(reinterpret_cast<const uint4*>(xp + (size_t)ru * ld)) : make_uint4(0u, 0u, 0u, 0u);
+          w[u] = in ? (wgt ? __ldg(wgt + ru) : 1.f) : 0.f;
         }
 #pragma unroll
         for (int u = 0; u < 8; ++u) fold(v[u], w[u] * gs);
       }
-      for (; r < r1; r += RG)
-        fold(__ldg(reinterpret_cast<const uint4*>(xp + (size_t)r * ld)), (wgt ? __ldg(wgt + r) : 1.f) * gs);
     } else {
       const int e0 = (slot - nv) * 8;
       for (int r = r0 + rg; r < r1; r += RG) {
