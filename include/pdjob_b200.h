@@ -133,6 +133,10 @@ int pdj_emb_apply(const struct PdjComm* c, const struct PdjEmbTable* t, int opti
 int pdj_linear_block_n(int N);
 int pdj_linear_bf16(const void* a, const void* b, void* out, const float* bias, const void* mask, int M, int N, int K,
                     int lda, int ldb, int ldo, int relu, cudaStream_t st);
+/* pdj_linear_bf16 with B given as b_kn[K][N] (row pitch ldb >= N): out = epilogue(a . b_kn), e.g. dX = dZ . W with the
+ * weight W[out][in] read as stored. */
+int pdj_linear_bf16_kn(const void* a, const void* b_kn, void* out, const float* bias, const void* mask, int M, int N, int K,
+                       int lda, int ldb, int ldo, int relu, cudaStream_t st);
 /* 1x1 convolution over NHWC activations as a GEMM on the same tcgen05 pipeline, with the
  * per-channel sum / sum of squares of the (bf16-rounded) output accumulated in the epilogue:
  *   out[M,N] = A[M,K] . B[N,K]^T,   partial[p][0][n] = sum_m out, partial[p][1][n] = sum_m out^2
@@ -148,6 +152,10 @@ int pdj_conv1x1_bf16(const void* a, const void* b, void* out, float* partial, in
  * first 1x1 convolution with the skip connection's gradient folded in. */
 int pdj_conv1x1_add_bf16(const void* a, const void* b, const void* addend, void* out, int M, int N, int K, int lda,
                          int ldb, int ldc, int ldo, cudaStream_t st);
+/* Both of the above with B given as b_kn[K][N] (row pitch ldb >= N elements, a multiple of 8): the weight of a 1x1
+ * convolution used transposed for its input gradient, read as stored (MN-major tcgen05 operand).  addend may be NULL. */
+int pdj_conv1x1_kn_bf16(const void* a, const void* b_kn, const void* addend, void* out, int M, int N, int K, int lda, int ldb,
+                        int ldc, int ldo, cudaStream_t st);
 /* General NHWC convolution forward (square filter k <= 7, symmetric padding, stride) as an implicit GEMM on the same
  * pipeline: out[N][P][Q][Cout] from x[N][H][W][Cin] and the channels-last weight w[Cout][k][k][Cin].  The A operand is
  * read with im2col-mode TMA loads (128 consecutive output pixels x 64 channels per filter tap; the TMA unit walks

@@ -62,6 +62,7 @@ struct ConvGeom {
   int stride, pad;  // traversal stride and symmetric padding
   int ksize;        // filter is ksize x ksize
   int cblocks;      // Cin / 64
+  int b_mn;         // SRC_ROWS only: B is given as [K][N] (a weight used transposed) - MN-major operand, no transposed copy
 };
 
 template <int MODE, int SRC>
@@ -78,7 +79,7 @@ conv1x1_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_c
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
   const uint32_t base = (raw + 1023u) & ~1023u;
-  const uint32_t b_stage_bytes = (uint32_t)block_n * BK * 2;
+  const uint32_t b_stage_bytes = b_stage_bytes_for(block_n, (SRC == SRC_ROWS) ? geom.b_mn : 0);
   const uint32_t a_smem = base;
   const uint32_t b_smem = a_smem + stages * A_STAGE_BYTES;
   const uint32_t staging = b_smem + (WIN ? 4u : (uint32_t)stages) * b_stage_bytes;  // 1024-aligned (WIN: all 4 weight k-blocks resident)
@@ -125,7 +126,7 @@ conv1x1_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_c
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const uint32_t tmem_base = warp_uniform(*tmem_slot_ptr);
-  const Pipe pipe{a_smem, b_smem, b_stage_bytes, full0, empty0, tfull0, tempty0, stages};
+  const Pipe pipe{a_smem, b_smem, b_stage_bytes, full0, empty0, tfull0, tempty0, stages, (SRC == SRC_ROWS) ? geom.b_mn : 0};
 
   if (warp == 0) {
     if (lane == 0) {
@@ -613,7 +614,7 @@ int pdj_conv1x1_partial_rows(int M, int N) {
 }
 
 static int launch_conv1x1(const void* a, const void* b, const void* addend, void* out, float* partial, int M, int N, int K,
-                          int lda, int ldb, int ldc, int ldo, cudaStream_t st) {
+                          int lda, int ldb, int ldc, int ldo, cudaStream_t st, int b_kn = 0) {
   const int bn = (M >= 1 && N >= BOX_N && N % BOX_N == 0) ? conv_block_n(M, N, sm_count_cached()) : 0;
   if (M < 1 || K < 1 || bn == 0 || lda % 8 != 0 || ldb % 8 != 0 || ldo % 8 != 0 || ((uintptr_t)a & 15) ||
       ((uintptr_t)b & 15) || ((uintptr_t)out & 15) || (addend != nullptr && (ldc % 8 != 0 || ((uintptr_t)addend & 15)))) {
@@ -624,16 +625,22 @@ static int launch_conv1x1(const void* a, const void* b, const void* addend, void
   if (int r = ensure_init()) return r;
   CUtensorMap ma, mb, mo, mc;
   if (int r = pdj_tc_make_map(&ma, a, M, K, lda, BK, BM, true)) return r;
-  if (int r = pdj_tc_make_map(&mb, b, N, K, ldb, BK, bn, true)) return r;
+  if (b_kn) {  // b is [K][N], N a multiple of 64: one 4-D box per stage
+    if (int r = pdj_tc_make_map_kn(&mb, b, K, N, ldb, BK, bn / 64)) return r;
+  } else if (int r = pdj_tc_make_map(&mb, b, N, K, ldb, BK, bn, true)) {
+    return r;
+  }
   if (int r = pdj_tc_make_map(&mo, out, M, N, ldo, BOX_N, BM, true)) return r;
   if (addend != nullptr) {
     if (int r = pdj_tc_make_map(&mc, addend, M, N, ldc, BOX_N, BM, true)) return r;
   } else {
     mc = mo;
   }
-  const int stage_bytes = A_STAGE_BYTES + bn * BK * 2;
+  const int stage_bytes = A_STAGE_BYTES + (int)b_stage_bytes_for(bn, b_kn);
   const int fixed = 1024 /*alignment*/ + 256 /*barriers*/ + SW_STAGING_BYTES + SW_SCRATCH_BYTES;
   int stages = (SMEM_LIMIT - fixed) / stage_bytes;
+  ConvGeom geom{};
+  geom.b_mn = b_kn ? 2 : 0;
   if (stages > MAX_STAGES) stages = MAX_STAGES;
   if (stages < 2) {
     pdj_set_error("pdj_conv1x1: tile does not fit in shared memory (block_n=%d)", bn);
@@ -642,11 +649,11 @@ static int launch_conv1x1(const void* a, const void* b, const void* addend, void
   const int smem = fixed + stages * stage_bytes;
   const int grid = conv_grid(M, N, bn, g_sms);
   if (addend != nullptr)
-    conv1x1_tcgen05_kernel<MODE_ADD, SRC_ROWS><<<grid, THREADS, smem, st>>>(ma, mb, mo, mc, nullptr, M, N, K, bn, stages, 0, 0, ConvGeom{});
+    conv1x1_tcgen05_kernel<MODE_ADD, SRC_ROWS><<<grid, THREADS, smem, st>>>(ma, mb, mo, mc, nullptr, M, N, K, bn, stages, 0, 0, geom);
   else if (partial != nullptr)
-    conv1x1_tcgen05_kernel<MODE_STATS, SRC_ROWS><<<grid, THREADS, smem, st>>>(ma, mb, mo, mc, partial, M, N, K, bn, stages, 0, 0, ConvGeom{});
+    conv1x1_tcgen05_kernel<MODE_STATS, SRC_ROWS><<<grid, THREADS, smem, st>>>(ma, mb, mo, mc, partial, M, N, K, bn, stages, 0, 0, geom);
   else
-    conv1x1_tcgen05_kernel<MODE_PLAIN, SRC_ROWS><<<grid, THREADS, smem, st>>>(ma, mb, mo, mc, nullptr, M, N, K, bn, stages, 0, 0, ConvGeom{});
+    conv1x1_tcgen05_kernel<MODE_PLAIN, SRC_ROWS><<<grid, THREADS, smem, st>>>(ma, mb, mo, mc, nullptr, M, N, K, bn, stages, 0, 0, geom);
   PDJ_CUDA_CHECK(cudaGetLastError());
   return 0;
 }
@@ -773,6 +780,13 @@ int pdj_conv1x1_add_bf16(const void* a, const void* b, const void* addend, void*
     return -1;
   }
   return launch_conv1x1(a, b, addend, out, nullptr, M, N, K, lda, ldb, ldc, ldo, st);
+}
+
+// The two GEMMs above with B given as b_kn[K][N] (row pitch ldb >= N): the input gradient dX = (dskip +) dY . W reads the
+// weight W[Cout][Cin] as it is stored - no transposed copy.  `addend` may be NULL (plain product).
+int pdj_conv1x1_kn_bf16(const void* a, const void* b_kn, const void* addend, void* out, int M, int N, int K, int lda, int ldb,
+                        int ldc, int ldo, cudaStream_t st) {
+  return launch_conv1x1(a, b_kn, addend, out, nullptr, M, N, K, lda, ldb, ldc, ldo, st, 1);
 }
 
 }  // extern "C"

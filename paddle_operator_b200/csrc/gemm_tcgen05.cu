@@ -94,11 +94,12 @@ __global__ void __launch_bounds__(THREADS, 1)
 linear_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                       const __grid_constant__ CUtensorMap tma_o, __nv_bfloat16* __restrict__ out,
                       const float* __restrict__ bias, const __nv_bfloat16* __restrict__ mask, int M, int N, int K,
-                      int ldo, int block_n, int stages, int relu, int b_resident) {
+                      int ldo, int block_n, int stages, int relu, int flags) {
+  const int b_resident = flags & 1, b_mn = (flags >> 1) & 3;  // b_mn: B given as [K][N] (single-CTA path only), see Pipe
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
   const uint32_t base = (raw + 1023u) & ~1023u;  // SWIZZLE_128B wants 1024-byte alignment
-  const uint32_t b_stage_bytes = (uint32_t)(PAIR2 ? block_n / 2 : block_n) * BK * 2;  // PAIR2: this CTA's half of the B tile
+  const uint32_t b_stage_bytes = PAIR2 ? (uint32_t)(block_n / 2) * BK * 2 : b_stage_bytes_for(block_n, b_mn);  // PAIR2: this CTA's half of the B tile
   const uint32_t a_smem = base;
   const uint32_t b_smem = a_smem + stages * A_STAGE_BYTES;
   // PAIR2 with b_resident: this CTA's half of the whole B panel (every k-block of its column tile) stays in shared
@@ -158,7 +159,7 @@ linear_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
   if (PAIR2) cluster_sync_all();  // the peer's barriers exist before anything arrives on them
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const uint32_t tmem_base = warp_uniform(*tmem_slot_ptr);
-  const Pipe pipe{a_smem, b_smem, b_stage_bytes, full0, empty0, tfull0, tempty0, stages};
+  const Pipe pipe{a_smem, b_smem, b_stage_bytes, full0, empty0, tfull0, tempty0, stages, b_mn};
 
   if (warp == 0) {
     if (lane == 0) {
@@ -388,8 +389,8 @@ int pdj_linear_block_n(int N) {
   return bn;
 }
 
-int pdj_linear_bf16(const void* a, const void* b, void* out, const float* bias, const void* mask, int M, int N, int K,
-                    int lda, int ldb, int ldo, int relu, cudaStream_t st) {
+static int launch_linear(const void* a, const void* b, void* out, const float* bias, const void* mask, int M, int N, int K,
+                         int lda, int ldb, int ldo, int relu, int b_kn, cudaStream_t st) {
   if (M < 1 || N < 1 || K < 1 || lda % 8 != 0 || ldb % 8 != 0 || ((uintptr_t)a & 15) || ((uintptr_t)b & 15)) {
     pdj_set_error("pdj_linear_bf16: need M,N,K >= 1, 16-byte aligned operands and row pitches that are multiples of 8 elements "
                   "(lda=%d ldb=%d)", lda, ldb);
@@ -411,10 +412,17 @@ int pdj_linear_bf16(const void* a, const void* b, void* out, const float* bias, 
   // Measured (profiles/r2/linear_pair.md): +10..15 % where the B stream matters (8192 x 4096 x 4096: 1.55 -> 1.72 PFLOP/s,
   // above the library's 1.56), a loss on the skinny Wide&Deep layers, whose limit is the A stream and the epilogue.
   const bool pair_auto = K >= 1024 && N >= 256 && M >= 4 * BM;
-  const bool pair = (pair_env ? atoi(pair_env) != 0 : pair_auto) && bn % 16 == 0 && M >= 2 * BM && sms >= 2;
+  const bool pair = (pair_env ? atoi(pair_env) != 0 : pair_auto) && bn % 16 == 0 && M >= 2 * BM && sms >= 2 && !b_kn;
   CUtensorMap ma, mb, mo;
   if (int r = pdj_tc_make_map(&ma, a, M, K, lda, BK, BM, true)) return r;
-  if (int r = pdj_tc_make_map(&mb, b, N, K, ldb, BK, pair ? bn / 2 : bn, true)) return r;
+  const int kn_mode = !b_kn ? 0 : ((N % 64 == 0 && bn % 64 == 0) ? 2 : 1);
+  if (kn_mode == 2) {  // b is [K][N]: every 64-column group of a stage in one 4-D box
+    if (int r = pdj_tc_make_map_kn(&mb, b, K, N, ldb, BK, bn / 64)) return r;
+  } else if (kn_mode == 1) {  // boxes of 64 columns x BK rows, one per group
+    if (int r = pdj_tc_make_map(&mb, b, K, N, ldb, 64, BK, true)) return r;
+  } else if (int r = pdj_tc_make_map(&mb, b, N, K, ldb, BK, pair ? bn / 2 : bn, true)) {
+    return r;
+  }
   if (tma_store) {
     if (int r = pdj_tc_make_map(&mo, out, M, N, ldo, bn, BM, false)) return r;
   } else {
@@ -432,7 +440,7 @@ int pdj_linear_bf16(const void* a, const void* b, void* out, const float* bias, 
   const char* res_env = getenv("PDJ_LINEAR_BRES");
   const bool resident = pair && (res_env ? atoi(res_env) != 0 : true) && (pair_grid / 2) % tiles_n_h == 0 &&
                         fixed + panel + 3 * A_STAGE_BYTES <= SMEM_LIMIT;
-  const int stage_bytes = resident ? A_STAGE_BYTES : A_STAGE_BYTES + (pair ? bn / 2 : bn) * BK * 2;
+  const int stage_bytes = resident ? A_STAGE_BYTES : A_STAGE_BYTES + (pair ? (bn / 2) * BK * 2 : (int)b_stage_bytes_for(bn, b_kn));
   int stages = (SMEM_LIMIT - fixed - (resident ? panel : 0)) / stage_bytes;
   if (stages > MAX_STAGES) stages = MAX_STAGES;
   if (stages < 2) {
@@ -467,12 +475,24 @@ int pdj_linear_bf16(const void* a, const void* b, void* out, const float* bias, 
   const int grid = total < sms ? total : sms;
   if (tma_store)
     linear_tcgen05_kernel<true, false><<<grid, THREADS, smem, st>>>(ma, mb, mo, (__nv_bfloat16*)out, bias,
-                                                                   (const __nv_bfloat16*)mask, M, N, K, ldo, bn, stages, relu, 0);
+                                                                   (const __nv_bfloat16*)mask, M, N, K, ldo, bn, stages, relu, kn_mode << 1);
   else
     linear_tcgen05_kernel<false, false><<<grid, THREADS, smem, st>>>(ma, mb, mo, (__nv_bfloat16*)out, bias,
-                                                                    (const __nv_bfloat16*)mask, M, N, K, ldo, bn, stages, relu, 0);
+                                                                    (const __nv_bfloat16*)mask, M, N, K, ldo, bn, stages, relu, kn_mode << 1);
   PDJ_CUDA_CHECK(cudaGetLastError());
   return 0;
+}
+
+int pdj_linear_bf16(const void* a, const void* b, void* out, const float* bias, const void* mask, int M, int N, int K,
+                    int lda, int ldb, int ldo, int relu, cudaStream_t st) {
+  return launch_linear(a, b, out, bias, mask, M, N, K, lda, ldb, ldo, relu, 0, st);
+}
+
+// The same with B given as b_kn[K][N] (row pitch ldb >= N elements): out = epilogue(a . b_kn).  A weight [out, in] used
+// for the input gradient dX = dZ . W is exactly that, so no transposed copy is made (MN-major B operand).
+int pdj_linear_bf16_kn(const void* a, const void* b_kn, void* out, const float* bias, const void* mask, int M, int N, int K,
+                       int lda, int ldb, int ldo, int relu, cudaStream_t st) {
+  return launch_linear(a, b_kn, out, bias, mask, M, N, K, lda, ldb, ldo, relu, 1, st);
 }
 
 }  // extern "C"

@@ -189,7 +189,13 @@ struct Pipe {
   uint32_t full0, empty0;      // per ring slot: TMA -> MMA, MMA -> TMA
   uint32_t tfull0, tempty0;    // per accumulator buffer: MMA -> epilogue, epilogue -> MMA
   int stages;
+  int b_mn;                    // B is given as [K][N] (N contiguous, e.g. a weight used transposed): MN-major operand;
+                               // 1: one 2-D box per 64-column group, 2: one 4-D box {64, BK, groups, 1} (N % 64 == 0)
 };
+constexpr int B_MN_GROUP_BYTES = BK * 128;  // MN-major B stage: 64-column groups of [BK k-rows][128 B], 8 KiB each
+__device__ __host__ __forceinline__ uint32_t b_stage_bytes_for(int block_n, int b_mn) {
+  return b_mn ? (uint32_t)((block_n + 63) / 64) * B_MN_GROUP_BYTES : (uint32_t)block_n * BK * 2;
+}
 
 // TMA producer (one thread): walks this CTA's tiles and keeps the ring full.
 __device__ __forceinline__ void producer_loop(const CUtensorMap* tma_a, const CUtensorMap* tma_b, const Pipe& p, int total,
@@ -203,7 +209,14 @@ __device__ __forceinline__ void producer_loop(const CUtensorMap* tma_a, const CU
       mbar_wait(p.empty0 + 8 * s, ph ^ 1u);
       mbar_expect_tx(p.full0 + 8 * s, stage_bytes);
       tma_load_2d(p.a_smem + s * A_STAGE_BYTES, tma_a, kb * BK, m0, p.full0 + 8 * s);
-      tma_load_2d(p.b_smem + s * p.b_stage_bytes, tma_b, kb * BK, n0, p.full0 + 8 * s);
+      if (p.b_mn == 2) {  // all 64-column groups of the stage in one request
+        tma_load_4d(p.b_smem + s * p.b_stage_bytes, tma_b, 0, kb * BK, n0 >> 6, 0, p.full0 + 8 * s);
+      } else if (p.b_mn) {  // [k rows][64 columns] boxes of the [K][N] matrix, one per 64-column group
+        for (int g = 0; g * 64 < block_n; ++g)
+          tma_load_2d(p.b_smem + s * p.b_stage_bytes + g * B_MN_GROUP_BYTES, tma_b, n0 + 64 * g, kb * BK, p.full0 + 8 * s);
+      } else {
+        tma_load_2d(p.b_smem + s * p.b_stage_bytes, tma_b, kb * BK, n0, p.full0 + 8 * s);
+      }
     }
   }
 }
@@ -212,8 +225,13 @@ __device__ __forceinline__ void producer_loop(const CUtensorMap* tma_a, const CU
 // i & 1.  Descriptors are built once and advanced by adding to their address field, all in uniform registers.
 __device__ __forceinline__ void mma_loop(const Pipe& p, uint32_t tmem_base, int total, int block_n, int num_kb) {
   // instruction descriptor: D = f32, A = B = bf16, both K-major, N >> 3, M >> 4
-  const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(block_n >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+  // (bit 16: B is MN-major - its 64-column groups sit B_MN_GROUP_BYTES apart, 8-row k groups 1024 B apart, and one
+  // K = 16 step is sixteen 128-byte rows)
+  const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | (p.b_mn ? (1u << 16) : 0u) | ((uint32_t)(block_n >> 3) << 17) |
+                         ((uint32_t)(BM >> 4) << 24);
   const uint64_t d0 = umma_desc(0);
+  const uint64_t d0b = p.b_mn ? umma_desc_ex(0, B_MN_GROUP_BYTES, 1024, 2) : d0;
+  const uint32_t kstep_b = p.b_mn ? (16u * 128u) >> 4 : (uint32_t)(UK * 2) >> 4;
   uint32_t it = 0, i = 0;
   for (int t = blockIdx.x; t < total; t += gridDim.x, ++i) {
     const uint32_t buf = i & 1u, aph = (i >> 1) & 1u;
@@ -225,10 +243,10 @@ __device__ __forceinline__ void mma_loop(const Pipe& p, uint32_t tmem_base, int 
       mbar_wait(p.full0 + 8 * s, ph);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       const uint64_t da = d0 + (uint64_t)((p.a_smem + s * A_STAGE_BYTES) >> 4);
-      const uint64_t db = d0 + (uint64_t)((p.b_smem + s * p.b_stage_bytes) >> 4);
+      const uint64_t db = d0b + (uint64_t)((p.b_smem + s * p.b_stage_bytes) >> 4);
 #pragma unroll
       for (int k = 0; k < BK / UK; ++k)
-        umma_f16_elect(tmem_d, da + (uint64_t)(k * UK * 2 >> 4), db + (uint64_t)(k * UK * 2 >> 4), idesc, (uint32_t)((kb | k) != 0));
+        umma_f16_elect(tmem_d, da + (uint64_t)(k * UK * 2 >> 4), db + (uint64_t)((uint32_t)k * kstep_b), idesc, (uint32_t)((kb | k) != 0));
       umma_commit_elect(p.empty0 + 8 * s);  // slot is free once these MMAs have read it
     }
     umma_commit_elect(p.tfull0 + 8 * buf);  // accumulator complete
@@ -244,6 +262,9 @@ int pdj_tc_make_map(CUtensorMap* map, const void* ptr, int rows, int cols, int l
                     bool swizzle);
 int pdj_tc_make_map3(CUtensorMap* map, const void* ptr, uint64_t d0, uint64_t d1, uint64_t d2, uint64_t s1, uint64_t s2,
                      int b0, int b1);
+// Map over a row-major bf16 matrix b[K][N] (N % 64 == 0) as {64, K, N / 64, 1}: one box {64, box_k, groups, 1} lands as
+// `groups` consecutive [box_k][64] tiles, 128-byte swizzled - an MN-major tcgen05 B stage in one request.
+int pdj_tc_make_map_kn(CUtensorMap* map, const void* ptr, int K, int N, int ld_elems, int box_k, int groups);
 // 4-D tiled map over an NHWC bf16 tensor {C, W, H, N} (strides in bytes for W, H, N); swizzle: 0 none, 1 32 B,
 // 2 64 B, 3 128 B.  Out-of-range box elements (negative or past-the-end coordinates) read as zero.
 int pdj_tc_make_map4(CUtensorMap* map, const void* ptr, const uint64_t dims[4], const uint64_t strides[3], const uint32_t box[4],

@@ -180,6 +180,13 @@ int pdj_tc_make_map3(CUtensorMap* map, const void* ptr, uint64_t d0, uint64_t d1
   return make_map3(map, ptr, d0, d1, d2, s1, s2, b0, b1);
 }
 
+int pdj_tc_make_map_kn(CUtensorMap* map, const void* ptr, int K, int N, int ld_elems, int box_k, int groups) {
+  const uint64_t dims[4] = {64, (uint64_t)K, (uint64_t)(N / 64), 1};
+  const uint64_t strides[3] = {(uint64_t)ld_elems * 2, 128, (uint64_t)ld_elems * 2 * (uint64_t)K};
+  const uint32_t box[4] = {64, (uint32_t)box_k, (uint32_t)groups, 1};
+  return pdj_tc_make_map4(map, ptr, dims, strides, box, 3);
+}
+
 int pdj_tc_sm_count() {
   if (g_sms == 0) {
     int dev = 0;

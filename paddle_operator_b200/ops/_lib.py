@@ -83,9 +83,11 @@ def _declare(lib: ctypes.CDLL) -> None:
         "pdj_emb_apply": (c_int, [POINTER(PdjComm), POINTER(PdjEmbTable), c_int, c_float, c_float, c_int, c_int, st]),
         "pdj_linear_block_n": (c_int, [c_int]),
         "pdj_linear_bf16": (c_int, [vp, vp, vp, vp, vp, c_int, c_int, c_int, c_int, c_int, c_int, c_int, st]),
+        "pdj_linear_bf16_kn": (c_int, [vp, vp, vp, vp, vp, c_int, c_int, c_int, c_int, c_int, c_int, c_int, st]),
         "pdj_conv1x1_partial_rows": (c_int, [c_int, c_int]),
         "pdj_conv1x1_bf16": (c_int, [vp, vp, vp, vp, c_int, c_int, c_int, c_int, c_int, c_int, st]),
         "pdj_conv1x1_add_bf16": (c_int, [vp, vp, vp, vp, c_int, c_int, c_int, c_int, c_int, c_int, c_int, st]),
+        "pdj_conv1x1_kn_bf16": (c_int, [vp, vp, vp, vp, c_int, c_int, c_int, c_int, c_int, c_int, c_int, st]),
         "pdj_stem_s2d_partial_rows": (c_int, [c_int, c_int]),
         "pdj_stem_s2d_fwd": (c_int, [vp, vp, vp, vp, c_int, c_int, c_int, st]),
         "pdj_stem_s2d_wgrad_ws_bytes": (c_int, []),

@@ -38,6 +38,11 @@ def launch_count() -> int:
     return _launches[0]
 
 
+# Input-gradient GEMMs can read the weight [Cout, Cin] as stored (MN-major B operand, ops/gemm.py) instead of a
+# transposed copy.  Measured on the ResNet-50 step this LOSES 0.35 ms (19.9 -> 20.3 ms: 17 small transposes saved, but
+# every dgrad GEMM of the K = 64..512 layers runs slower with the MN-major operand), so it is off here and on for
+# the Wide&Deep tower (0.548 -> 0.543 ms).  PDJ_CONV_KN=1 enables it.
+CONV_KN = os.environ.get("PDJ_CONV_KN", "0") == "1"
 # backward of a 1x1 convolution WITHOUT a skip gradient on the own kernels (dgrad GEMM + MN-major wgrad) when the input
 # is at least this large; smaller layers stay in the library (A/B: profiles/r2/conv1x1_bwd_ab.md)
 OWN_BWD = os.environ.get("PDJ_CONV1X1_OWN_BWD", "1") == "1"
@@ -79,18 +84,29 @@ def conv1x1_gemm(x2: torch.Tensor, w2: torch.Tensor, stats: bool = True,
     return out, partial
 
 
-def conv1x1_gemm_add(a2: torch.Tensor, b2: torch.Tensor, addend2: torch.Tensor,
-                     out: Optional[torch.Tensor] = None) -> torch.Tensor:
-    """out[M,N] = addend2[M,N] + a2[M,K] @ b2[N,K]^T on the kernel (out may be addend2 itself)."""
+def conv1x1_gemm_add(a2: torch.Tensor, b2: torch.Tensor, addend2: Optional[torch.Tensor],
+                     out: Optional[torch.Tensor] = None, b_kn: bool = False) -> torch.Tensor:
+    """out[M,N] = addend2[M,N] + a2[M,K] @ b2[N,K]^T on the kernel (out may be addend2 itself).  With `b_kn`, b2 is
+    [K,N] (a weight [Cout, Cin] used for its input gradient, read as stored) and addend2 may be None."""
+    if b_kn and not CONV_KN:
+        b2, b_kn = b2.t().contiguous(), False
     m, k = a2.shape
-    n = b2.shape[0]
-    assert a2.stride(1) == 1 and b2.stride(1) == 1 and b2.shape[1] == k and addend2.shape == (m, n)
-    assert addend2.stride(1) == 1
+    n = b2.shape[1] if b_kn else b2.shape[0]
+    assert a2.stride(1) == 1 and b2.stride(1) == 1 and (b2.shape[0] if b_kn else b2.shape[1]) == k
+    assert addend2 is None or (addend2.shape == (m, n) and addend2.stride(1) == 1)
     if out is None:
         out = torch.empty((m, n), dtype=torch.bfloat16, device=a2.device)
-    _lib.check(_lib.load().pdj_conv1x1_add_bf16(a2.data_ptr(), b2.data_ptr(), addend2.data_ptr(), out.data_ptr(), m, n, k,
-                                                a2.stride(0), b2.stride(0), addend2.stride(0), out.stride(0),
-                                                torch.cuda.current_stream().cuda_stream), "conv1x1_add_bf16")
+    lib = _lib.load()
+    if b_kn:
+        _lib.check(lib.pdj_conv1x1_kn_bf16(a2.data_ptr(), b2.data_ptr(), _lib.ptr(addend2), out.data_ptr(), m, n, k,
+                                           a2.stride(0), b2.stride(0), 0 if addend2 is None else addend2.stride(0),
+                                           out.stride(0), torch.cuda.current_stream().cuda_stream), "conv1x1_kn_bf16")
+    elif addend2 is None:
+        return conv1x1_gemm(a2, b2, stats=False, out=out)[0]
+    else:
+        _lib.check(lib.pdj_conv1x1_add_bf16(a2.data_ptr(), b2.data_ptr(), addend2.data_ptr(), out.data_ptr(), m, n, k,
+                                            a2.stride(0), b2.stride(0), addend2.stride(0), out.stride(0),
+                                            torch.cuda.current_stream().cuda_stream), "conv1x1_add_bf16")
     _launches[0] += 1
     return out
 
@@ -154,7 +170,7 @@ class _Conv1x1StatsFn(torch.autograd.Function):
             dx = None
             if ctx.needs_input_grad[0]:
                 dx = torch.empty_like(x, memory_format=torch.channels_last)
-                conv1x1_gemm(_rows(dy), weight.reshape(o, c).t().contiguous(), stats=False, out=_rows(dx))
+                conv1x1_gemm_add(_rows(dy), weight.reshape(o, c), None, out=_rows(dx), b_kn=True)
         else:
             dx, dw, _ = torch.ops.aten.convolution_backward(
                 dy, x, weight, None, [1, 1], [0, 0], [1, 1], False, [0, 0], 1,
@@ -162,10 +178,9 @@ class _Conv1x1StatsFn(torch.autograd.Function):
         if fuse:
             if not dskip.is_contiguous(memory_format=torch.channels_last):
                 dskip = dskip.contiguous(memory_format=torch.channels_last)
-            # dX[M,Cin] = dskip + dY[M,Cout] @ W[Cout,Cin]: the B operand is W^T, K-major over Cout
-            wt = weight.reshape(o, c).t().contiguous()
+            # dX[M,Cin] = dskip + dY[M,Cout] @ W[Cout,Cin]: the B operand is the weight as stored (MN-major), no W^T copy
             dx = torch.empty_like(x, memory_format=torch.channels_last)
-            conv1x1_gemm_add(_rows(dy), wt, _rows(dskip), out=_rows(dx))
+            conv1x1_gemm_add(_rows(dy), weight.reshape(o, c), _rows(dskip), out=_rows(dx), b_kn=True)
         elif ctx.carry_skip and dskip is not None and dx is not None:
             dx = dx + dskip
         elif ctx.carry_skip and dskip is not None:
@@ -228,8 +243,7 @@ class _Conv1x1DualFn(torch.autograd.Function):
         if need_x:
             o1, c = w1.shape[0], w1.shape[1]
             g = g if g.is_contiguous(memory_format=cl) else g.contiguous(memory_format=cl)
-            wt = w1.reshape(o1, c).t().contiguous()
-            conv1x1_gemm_add(_rows(dy1), wt, _rows(g), out=_rows(g))  # in place: g += dY1 @ W1
+            conv1x1_gemm_add(_rows(dy1), w1.reshape(o1, c), _rows(g), out=_rows(g), b_kn=True)  # in place: g += dY1 @ W1
             dx = g
         return dx, dw1, dwd, None, None, None
 

@@ -20,26 +20,35 @@ from . import _lib
 from ._sink import adopt, sink_of
 
 
+# B operands given as [K, N] (a weight used transposed) are read as stored through an MN-major tcgen05 descriptor;
+# PDJ_GEMM_KN=0 makes the callers materialise the transposed copy instead (the A/B arm).
+KN = os.environ.get("PDJ_GEMM_KN", "1") == "1"
+
+
 def linear_bf16(a: torch.Tensor, b: torch.Tensor, bias: Optional[torch.Tensor] = None, relu: bool = False,
-                mask: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
-    """out[M,N] = epilogue(a[M,K] @ b[N,K]^T).  a, b: bf16, last dim contiguous, row pitch a multiple of 8."""
+                mask: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None, b_kn: bool = False) -> torch.Tensor:
+    """out[M,N] = epilogue(a[M,K] @ b[N,K]^T), or with `b_kn` epilogue(a[M,K] @ b[K,N]) - e.g. dX = dZ @ W with the
+    weight W[out, in] as stored.  a, b: bf16, last dim contiguous, row pitch a multiple of 8."""
     assert a.is_cuda and a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16
-    assert a.dim() == 2 and b.dim() == 2 and a.shape[1] == b.shape[1]
+    assert a.dim() == 2 and b.dim() == 2 and a.shape[1] == (b.shape[0] if b_kn else b.shape[1])
+    if b_kn and not KN:
+        b, b_kn = b.t().contiguous(), False
     if a.stride(1) != 1 or a.stride(0) % 8 != 0 or a.data_ptr() % 16 != 0:
         a = _pad_rows(a)
     if b.stride(1) != 1 or b.stride(0) % 8 != 0 or b.data_ptr() % 16 != 0:
         b = _pad_rows(b)
     m, k = a.shape
-    n = b.shape[0]
+    n = b.shape[1] if b_kn else b.shape[0]
     if out is None:
         out = torch.empty((m, n), dtype=torch.bfloat16, device=a.device)
     if bias is not None and bias.dtype != torch.float32:
         bias = bias.float()
     if mask is not None:
         assert mask.shape == out.shape and mask.stride() == out.stride() and mask.dtype == torch.bfloat16
-    _lib.check(_lib.load().pdj_linear_bf16(a.data_ptr(), b.data_ptr(), out.data_ptr(), _lib.ptr(bias), _lib.ptr(mask),
-                                           m, n, k, a.stride(0), b.stride(0), out.stride(0), int(relu),
-                                           torch.cuda.current_stream().cuda_stream), "linear_bf16")
+    fn = _lib.load().pdj_linear_bf16_kn if b_kn else _lib.load().pdj_linear_bf16
+    _lib.check(fn(a.data_ptr(), b.data_ptr(), out.data_ptr(), _lib.ptr(bias), _lib.ptr(mask),
+                  m, n, k, a.stride(0), b.stride(0), out.stride(0), int(relu),
+                  torch.cuda.current_stream().cuda_stream), "linear_bf16")
     return out
 
 
@@ -71,7 +80,7 @@ class _LinearActFn(torch.autograd.Function):
         dx = dw = db = None
         if ctx.needs_input_grad[0]:
             # dX[M,K] = dZ[M,N] @ W[N,K]  ==  dZ . (W^T)[K,N]^T : the B operand is W^T, K-major over N
-            dx = linear_bf16(dz, weight.t().contiguous())
+            dx = linear_bf16(dz, weight, b_kn=True)
         if ctx.needs_input_grad[1]:
             sink = sink_of(weight)
             dw = wgrad_mn(dz, x, out=sink)

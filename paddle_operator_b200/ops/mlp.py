@@ -118,9 +118,9 @@ class _FusedMLPFn(torch.autograd.Function):
                 dw = wgrad_mn(dz, hs[l - 1], out=wsink)
                 dws[l - 1] = adopt(dw) if wsink is not None else dw
             if l > 1:
-                dz = linear_bf16(dz, ws[l - 1].t().contiguous(), mask=hs[l - 1])
+                dz = linear_bf16(dz, ws[l - 1], mask=hs[l - 1], b_kn=True)  # dZ W: the weight as stored, no transposed copy
             elif ctx.needs_input_grad[0]:
-                dx = linear_bf16(dz, ws[0].t().contiguous())
+                dx = linear_bf16(dz, ws[0], b_kn=True)
         return (dx, None, None, *dws, *dbs, *([None] * n))
 
 

@@ -13,6 +13,40 @@ def _conv_gemm_for_every_size(monkeypatch):
     monkeypatch.setattr(conv_ops, "MIN_OUTPUT_BYTES", 0)
 
 
+@pytest.mark.parametrize("m,n,k", [(128, 64, 64), (1000, 432, 400), (4096, 400, 400), (513, 216, 72), (300, 1000, 136)])
+def test_linear_with_weight_as_stored(m, n, k):
+    """b_kn: out = a @ b with b given as [K, N] (dX = dZ W) - the MN-major B operand, incl. the mask epilogue."""
+    from paddle_operator_b200.ops import gemm
+
+    assert gemm.KN
+    torch.manual_seed(m + n * 7 + k)
+    a = (torch.randn(m, k, device="cuda") * 0.5).to(torch.bfloat16)
+    b = (torch.randn(k, n, device="cuda") * 0.5).to(torch.bfloat16)
+    gate = (torch.randn(m, n, device="cuda") > 0).to(torch.bfloat16)
+    ref = a.float() @ b.float()
+    tol = dict(atol=3e-2 * (k ** 0.5) * 0.25 + 2e-2, rtol=2e-2)
+    torch.testing.assert_close(gemm.linear_bf16(a, b, b_kn=True).float(), ref, **tol)
+    torch.testing.assert_close(gemm.linear_bf16(a, b, mask=gate, b_kn=True).float(), ref * gate.float(), **tol)
+    # same bits as the K-major path on the transposed copy: the products and the accumulation order are identical
+    assert torch.equal(gemm.linear_bf16(a, b, b_kn=True), gemm.linear_bf16(a, b.t().contiguous()))
+
+
+@pytest.mark.parametrize("m,n,k", [(784, 64, 256), (1568, 256, 64), (3136, 512, 128), (200, 2048, 512)])
+def test_conv1x1_input_gradient_reads_the_weight_as_stored(m, n, k, monkeypatch):
+    from paddle_operator_b200.ops import conv as conv_ops
+
+    monkeypatch.setattr(conv_ops, "CONV_KN", True)  # off by default in the product (slower on the ResNet step)
+    torch.manual_seed(m + n + k)
+    dy = (torch.randn(m, k, device="cuda") * 0.5).to(torch.bfloat16)
+    w = (torch.randn(k, n, device="cuda") * 0.1).to(torch.bfloat16)  # [Cout, Cin]
+    skip = torch.randn(m, n, device="cuda").to(torch.bfloat16)
+    ref = dy.float() @ w.float()
+    torch.testing.assert_close(conv_ops.conv1x1_gemm_add(dy, w, None, b_kn=True).float(), ref, atol=6e-2, rtol=3e-2)
+    got = conv_ops.conv1x1_gemm_add(dy, w, skip, b_kn=True)
+    torch.testing.assert_close(got.float(), ref + skip.float(), atol=8e-2, rtol=3e-2)
+    assert torch.equal(got, conv_ops.conv1x1_gemm_add(dy, w.t().contiguous(), skip))
+
+
 @pytest.mark.parametrize("m,n,k", [(256, 128, 64), (300, 400, 432), (1000, 1000, 2048), (4096, 512, 1024), (2048, 48, 4096),
                                    (257, 16, 40)])
 def test_linear_cta_pair_mode_matches_fp32(m, n, k, monkeypatch):
