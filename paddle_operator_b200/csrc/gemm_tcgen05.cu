@@ -92,7 +92,8 @@ __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_bar) {
 template <bool TMA_STORE, bool PAIR2>
 __global__ void __launch_bounds__(THREADS, 1)
 linear_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
-                      const __grid_constant__ CUtensorMap tma_o, __nv_bfloat16* __restrict__ out,
+                      const __grid_constant__ CUtensorMap tma_o, const __grid_constant__ CUtensorMap tma_m,
+                      __nv_bfloat16* __restrict__ out,
                       const float* __restrict__ bias, const __nv_bfloat16* __restrict__ mask, int M, int N, int K,
                       int ldo, int block_n, int stages, int relu, int flags) {
   const int b_resident = flags & 1, b_mn = (flags >> 1) & 3;  // b_mn: B given as [K][N] (single-CTA path only), see Pipe
@@ -112,6 +113,7 @@ linear_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
   const uint32_t full0 = bars, empty0 = bars + 8 * MAX_STAGES;
   const uint32_t tfull0 = bars + 16 * MAX_STAGES, tempty0 = tfull0 + 16, tmem_slot = tempty0 + 16;
   const uint32_t bres = tmem_slot + 16;  // resident B panel has landed (PAIR2 + b_resident)
+  const uint32_t mbar_m = bres + 8;      // the tile's ReLU mask has landed in the staging tile (TMA_STORE + mask)
   uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(smem_raw + (tmem_slot - raw));
 
   const int dbg = relu >> 8;  // diagnostic bits (PDJ_LINEAR_DBG): 1 = no TMA store, 2 = no staging writes, 4 = no drain
@@ -141,6 +143,7 @@ linear_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
         mbar_init(tempty0 + 8 * b, PAIR2 ? 2 * EPI_WARPS : EPI_WARPS);  // one arrival per epilogue warp (of both CTAs)
       }
       mbar_init(bres, 1);
+      mbar_init(mbar_m, 1);
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncwarp();
@@ -236,7 +239,16 @@ linear_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
       const uint32_t buf = i & 1u, aph = (i >> 1) & 1u;
       // bias slice of this column tile -> shared memory; reloaded only when the column tile changes (never, when the
       // persistent stride is a multiple of the column-tile count): a global load + a second barrier per tile otherwise
-      if (TMA_STORE && et == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+      if (TMA_STORE && et == 0) {
+        asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+        if (mask != nullptr) {
+          // the ReLU mask of the tile goes INTO the staging tile by TMA (a lane-per-row global read costs one L1 tag
+          // cycle per lane and instruction: ~2 us per tile); each thread later reads its elements there and writes
+          // the masked result over them
+          mbar_expect_tx(mbar_m, (uint32_t)BM * block_n * 2);
+          tma_load_2d(stage_out, &tma_m, n0, m0, mbar_m);
+        }
+      }
       asm volatile("bar.sync 1, %0;" ::"n"(32 * EPI_WARPS) : "memory");  // previous tile's bias / staging are free
       if (n0 != bias_n0) {
         for (int j = et; j < block_n; j += 32 * EPI_WARPS) bias_s[j] = (bias != nullptr && n0 + j < N) ? __ldg(bias + n0 + j) : 0.f;
@@ -244,32 +256,39 @@ linear_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
         bias_n0 = n0;
       }
       const int row = m0 + q * 32 + lane;
-      if (mask != nullptr && row < M) {
+      if (!TMA_STORE && mask != nullptr && row < M) {
         const char* mrow = reinterpret_cast<const char*>(mask + (size_t)row * ldo + n0 + c_begin);
         const int nb = ((n0 + c_end < N ? c_end : N - n0) - c_begin) * 2;
         for (int b = 0; b < nb; b += 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(mrow + b));
       }
+      // ReLU mask, one chunk (32 columns) ahead: one lane = one row, 16-byte loads (a full 32-byte sector per 16
+      // columns).  The first chunk is requested before the accumulator is waited for, chunk i + 1 before chunk i is
+      // processed, so a load has a whole chunk's worth of work (or the accumulator wait) to arrive in.
+      uint4 mnext[4] = {};
+      auto load_mask = [&](int c0_) {
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          const int cc_ = c0_ + 16 * h, col = n0 + cc_;
+          if (!TMA_STORE && mask != nullptr && row < M && cc_ < c_end && col + 16 <= N && (((size_t)row * ldo + col) & 7) == 0) {
+            const uint4* mp = reinterpret_cast<const uint4*>(mask + (size_t)row * ldo + col);
+            mnext[2 * h] = __ldg(mp);
+            mnext[2 * h + 1] = __ldg(mp + 1);
+          }
+        }
+      };
+      load_mask(c_begin);
       mbar_wait(tfull0 + 8 * buf, aph);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       const uint32_t taddr_row = tmem_base + buf * MAX_BN + ((uint32_t)(q * 32) << 16);
+      if (TMA_STORE && mask != nullptr) mbar_wait(mbar_m, i & 1u);  // one mask tile per tile of this CTA
       for (int c0 = c_begin; c0 < ((dbg & 4) ? c_begin : c_end); c0 += 32) {
         // two 16-column loads in flight, one wait
         uint32_t r[32];
         const bool second = c0 + 16 < c_end;
-        // ReLU mask of this chunk: one lane = one row, 16-byte loads (a full 32-byte sector per 16 columns), issued
-        // ahead of the TMEM loads so that both latencies overlap
-        uint4 mvec[4] = {};
-        if (mask != nullptr && row < M) {
+        uint4 mvec[4];
 #pragma unroll
-          for (int h = 0; h < 2; ++h) {
-            const int col = n0 + c0 + 16 * h;
-            if ((h == 0 || second) && col + 16 <= N && (((size_t)row * ldo + col) & 7) == 0) {
-              const uint4* mp = reinterpret_cast<const uint4*>(mask + (size_t)row * ldo + col);
-              mvec[2 * h] = __ldg(mp);
-              mvec[2 * h + 1] = __ldg(mp + 1);
-            }
-          }
-        }
+        for (int j = 0; j < 4; ++j) mvec[j] = mnext[j];
+        load_mask(c0 + 32);
         asm volatile(
             "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
             : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
@@ -296,10 +315,15 @@ linear_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
             v[j] = __uint_as_float(r[16 * h + j]) + bias_s[cc + j];
             if (relu) v[j] = fmaxf(v[j], 0.f);
           }
-          if (mask != nullptr && row < M) {
+          if (mask != nullptr && (TMA_STORE || row < M)) {
             const __nv_bfloat16* mk = mask + (size_t)row * ldo + col;
-            if (col + 16 <= N && (((size_t)row * ldo + col) & 7) == 0) {
-              const uint4 m0v = mvec[2 * h], m1v = mvec[2 * h + 1];
+            if (TMA_STORE || (col + 16 <= N && (((size_t)row * ldo + col) & 7) == 0)) {
+              uint4 m0v = mvec[2 * h], m1v = mvec[2 * h + 1];
+              if (TMA_STORE) {  // rows / columns beyond M, N were zero-filled by the load: masked out, clipped on store
+                const uint32_t src = stage_out + (uint32_t)((q * 32 + lane) * block_n + cc) * 2;
+                asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(m0v.x), "=r"(m0v.y), "=r"(m0v.z), "=r"(m0v.w) : "r"(src));
+                asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(m1v.x), "=r"(m1v.y), "=r"(m1v.z), "=r"(m1v.w) : "r"(src + 16));
+              }
               const uint32_t mw[8] = {m0v.x, m0v.y, m0v.z, m0v.w, m1v.x, m1v.y, m1v.z, m1v.w};
 #pragma unroll
               for (int j = 0; j < 8; ++j) {
@@ -423,10 +447,19 @@ static int launch_linear(const void* a, const void* b, void* out, const float* b
   } else if (int r = pdj_tc_make_map(&mb, b, N, K, ldb, BK, pair ? bn / 2 : bn, true)) {
     return r;
   }
+  CUtensorMap mm;
   if (tma_store) {
     if (int r = pdj_tc_make_map(&mo, out, M, N, ldo, bn, BM, false)) return r;
   } else {
     mo = ma;
+  }
+  mm = mo;
+  if (tma_store && mask != nullptr) {  // same geometry as the output (checked by the caller), loaded into the staging tile
+    if (((uintptr_t)mask & 15) != 0) {
+      pdj_set_error("pdj_linear_bf16: the mask must be 16-byte aligned");
+      return -1;
+    }
+    if (int r = pdj_tc_make_map(&mm, mask, M, N, ldo, bn, BM, false)) return r;
   }
   if (int r = ensure_init()) return r;
   const int tile_m = pair ? 2 * BM : BM;
@@ -465,19 +498,19 @@ static int launch_linear(const void* a, const void* b, void* out, const float* b
     __nv_bfloat16* outp = (__nv_bfloat16*)out;
     const __nv_bfloat16* maskp = (const __nv_bfloat16*)mask;
     if (tma_store)
-      PDJ_CUDA_CHECK(cudaLaunchKernelEx(&cfg, linear_tcgen05_kernel<true, true>, ma, mb, mo, outp, bias, maskp, M, N, K, ldo, bn,
+      PDJ_CUDA_CHECK(cudaLaunchKernelEx(&cfg, linear_tcgen05_kernel<true, true>, ma, mb, mo, mm, outp, bias, maskp, M, N, K, ldo, bn,
                                         stages, relu, resident ? 1 : 0));
     else
-      PDJ_CUDA_CHECK(cudaLaunchKernelEx(&cfg, linear_tcgen05_kernel<false, true>, ma, mb, mo, outp, bias, maskp, M, N, K, ldo, bn,
+      PDJ_CUDA_CHECK(cudaLaunchKernelEx(&cfg, linear_tcgen05_kernel<false, true>, ma, mb, mo, mm, outp, bias, maskp, M, N, K, ldo, bn,
                                         stages, relu, resident ? 1 : 0));
     return 0;
   }
   const int grid = total < sms ? total : sms;
   if (tma_store)
-    linear_tcgen05_kernel<true, false><<<grid, THREADS, smem, st>>>(ma, mb, mo, (__nv_bfloat16*)out, bias,
+    linear_tcgen05_kernel<true, false><<<grid, THREADS, smem, st>>>(ma, mb, mo, mm, (__nv_bfloat16*)out, bias,
                                                                    (const __nv_bfloat16*)mask, M, N, K, ldo, bn, stages, relu, kn_mode << 1);
   else
-    linear_tcgen05_kernel<false, false><<<grid, THREADS, smem, st>>>(ma, mb, mo, (__nv_bfloat16*)out, bias,
+    linear_tcgen05_kernel<false, false><<<grid, THREADS, smem, st>>>(ma, mb, mo, mm, (__nv_bfloat16*)out, bias,
                                                                     (const __nv_bfloat16*)mask, M, N, K, ldo, bn, stages, relu, kn_mode << 1);
   PDJ_CUDA_CHECK(cudaGetLastError());
   return 0;
