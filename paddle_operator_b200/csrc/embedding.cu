@@ -675,7 +675,11 @@ int pdj_emb_push2(const PdjComm* c, const PdjEmbTable* t, size_t ids_off, size_t
   const char* how = getenv("PDJ_EMB_PUSH");  // batched (default) | loop
   const int passes = (S + (32 / (t->dim >> 2)) - 1) / (32 / (t->dim >> 2));
   if ((how == nullptr || strcmp(how, "batched") == 0) && passes <= 8) {
-    int bt = emulate ? 256 : (passes <= 2 ? 1024 : 768);
+    // 512 threads (41 k registers) leave room for a weight-gradient CTA of the tower on the same SM: the push runs
+    // next to those kernels (ops/_sink.py, side stream).  PDJ_EMB_PUSH_THREADS overrides.
+    const char* pt = getenv("PDJ_EMB_PUSH_THREADS");
+    int bt = emulate ? 256 : (pt ? atoi(pt) : 512);
+    if (bt < 32 || bt > (passes <= 2 ? 1024 : 768) || bt % 32 != 0) bt = 512;
 #define PDJ_PS(P) launch_emb(emb_push_batched_kernel<P>, nblocks, bt, (size_t)0, emulate, c->nranks, st, *c, *t, ids_off, \
                              gdeep_off, gwide_off, B, S, async_sgd ? 1 : 0, lr, grad_scale, g_pitch)
     return passes <= 1 ? PDJ_PS(1) : passes <= 2 ? PDJ_PS(2) : passes <= 4 ? PDJ_PS(4) : PDJ_PS(8);

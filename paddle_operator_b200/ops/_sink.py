@@ -36,3 +36,49 @@ def adopt(sink: torch.Tensor) -> torch.Tensor:
 
 def is_sunk(grad: Optional[torch.Tensor], sink: torch.Tensor) -> bool:
     return grad is not None and grad.data_ptr() == sink.data_ptr() and grad.dtype == sink.dtype
+
+
+# ---- weight gradients on a side stream -----------------------------------------------------------------------------
+# Inside a trainer step (CollectiveTrainer sets `overlap_scope`), an op may compute its PARAMETER gradients on a side
+# stream so that the main stream can go on with the input-gradient chain and whatever follows it (in the Wide&Deep
+# step: the embedding push / apply, NVLink- and DRAM-bound, while the tower's weight gradients use the tensor cores).
+# The op records an event after its side-stream work and registers it here; the trainer makes every consumer of
+# the gradients (bucket collective, optimizer, end of step) wait for the registered events, and keeps the tensors the
+# side stream reads alive until the step is over (no allocator reuse while they are in flight).
+WGRAD_OVERLAP = os.environ.get("PDJ_WGRAD_OVERLAP", "1") == "1"
+_scope = {"on": False, "events": [], "keep": [], "streams": {}}
+
+
+def overlap_enabled() -> bool:
+    return WGRAD_OVERLAP and _scope["on"]
+
+
+def side_stream(device) -> "torch.cuda.Stream":
+    key = (device.type, device.index)
+    st = _scope["streams"].get(key)
+    if st is None:
+        st = _scope["streams"][key] = torch.cuda.Stream(device)
+    return st
+
+
+def register_side_work(event, *tensors) -> None:
+    _scope["events"].append(event)
+    _scope["keep"].extend(tensors)
+
+
+def begin_step() -> None:
+    _scope["on"] = True
+    _scope["events"].clear()
+    _scope["keep"].clear()
+
+
+def wait_side_work(stream) -> None:
+    """Make `stream` wait for every side-stream gradient computation registered so far in this step."""
+    for e in _scope["events"]:
+        stream.wait_event(e)
+
+
+def end_step() -> None:
+    _scope["on"] = False
+    _scope["events"].clear()
+    _scope["keep"].clear()

@@ -20,6 +20,7 @@ from typing import Optional
 import torch
 
 from . import _lib
+from . import _sink
 from ._sink import adopt, sink_of
 from .gemm import linear_bf16, wgrad_mn
 
@@ -108,19 +109,40 @@ class _FusedMLPFn(torch.autograd.Function):
             dz = torch.where(hs[n] > 0, dy, torch.zeros((), dtype=dy.dtype, device=dy.device)).contiguous()
         dws, dbs = [None] * n, [None] * n
         dx = None
+        # input-gradient chain first: dz_{l-1} = (dz_l W_l) * (h_{l-1} > 0), the weight read as stored
+        dzs = [None] * (n + 1)
+        dzs[n] = dz
         for l in range(n, 0, -1):  # layer l maps hs[l-1] -> hs[l] with ws[l-1]
-            # both parameter gradients land in the trainer's flat gradient buffer when it provides sinks
-            bsink, wsink = sink_of(ctx.biases[l - 1]), sink_of(ws[l - 1])
-            if ctx.needs_input_grad[3 + n + l - 1]:
-                db = colsum(dz, out=bsink, dtype=ctx.bias_dtypes[l - 1])
-                dbs[l - 1] = adopt(db) if bsink is not None else db
-            if ctx.needs_input_grad[3 + l - 1]:
-                dw = wgrad_mn(dz, hs[l - 1], out=wsink)
-                dws[l - 1] = adopt(dw) if wsink is not None else dw
             if l > 1:
-                dz = linear_bf16(dz, ws[l - 1], mask=hs[l - 1], b_kn=True)  # dZ W: the weight as stored, no transposed copy
+                dzs[l - 1] = linear_bf16(dzs[l], ws[l - 1], mask=hs[l - 1], b_kn=True)
             elif ctx.needs_input_grad[0]:
-                dx = linear_bf16(dz, ws[0], b_kn=True)
+                dx = linear_bf16(dzs[1], ws[0], b_kn=True)
+
+        def param_grads():
+            for l in range(n, 0, -1):
+                # both parameter gradients land in the trainer's flat gradient buffer when it provides sinks
+                bsink, wsink = sink_of(ctx.biases[l - 1]), sink_of(ws[l - 1])
+                if ctx.needs_input_grad[3 + n + l - 1]:
+                    db = colsum(dzs[l], out=bsink, dtype=ctx.bias_dtypes[l - 1])
+                    dbs[l - 1] = adopt(db) if bsink is not None else db
+                if ctx.needs_input_grad[3 + l - 1]:
+                    dw = wgrad_mn(dzs[l], hs[l - 1], out=wsink)
+                    dws[l - 1] = adopt(dw) if wsink is not None else dw
+
+        if _sink.overlap_enabled():
+            # the parameter gradients run on a side stream while the main stream continues with whatever consumes dx
+            # (the embedding push / apply); the trainer waits for the event before it touches the gradients
+            main, side = torch.cuda.current_stream(), _sink.side_stream(dy.device)
+            fork = torch.cuda.Event()
+            fork.record(main)
+            side.wait_event(fork)
+            with torch.cuda.stream(side):
+                param_grads()
+                done = torch.cuda.Event()
+                done.record(side)
+            _sink.register_side_work(done, *dzs, *hs)
+        else:
+            param_grads()
         return (dx, None, None, *dws, *dbs, *([None] * n))
 
 

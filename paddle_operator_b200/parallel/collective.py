@@ -21,6 +21,7 @@ from typing import Callable, Optional
 import torch
 
 from ..ops import optim as pdj_optim
+from ..ops import _sink
 from ..ops._sink import is_sunk
 from ..utils import trace
 from .symm import Communicator
@@ -204,6 +205,7 @@ class CollectiveTrainer:
 
     def _bucket_ready(self, b: _Bucket) -> None:
         if b.grads:
+            _sink.wait_side_work(torch.cuda.current_stream()) if self.device.type == "cuda" else None
             dst = [d for d, _ in b.grads]
             src = [s for _, s in b.grads]
             torch._foreach_copy_(dst, src)
@@ -214,6 +216,7 @@ class CollectiveTrainer:
         ev = torch.cuda.Event()
         ev.record(main)
         self.comm_stream.wait_event(ev)
+        _sink.wait_side_work(self.comm_stream)  # parameter gradients computed on a side stream (ops/_sink.py)
         n = b.end - b.start
         f = self.flat
         # one kernel per bucket: reduce-scatter + SGD-momentum on the owner's slice + broadcast of the new master and
@@ -235,9 +238,14 @@ class CollectiveTrainer:
         for b in self.flat.buckets:
             b.pending = len(b.params)
             b.event = None
+        cuda = self.device.type == "cuda"
+        if cuda:
+            _sink.begin_step()
         loss = self.loss_fn(self.model, *self.inputs)
         loss.backward()
-        main = torch.cuda.current_stream() if self.device.type == "cuda" else None
+        main = torch.cuda.current_stream() if cuda else None
+        if cuda:
+            _sink.wait_side_work(main)  # the optimizer below / the next step read what the side stream wrote
         for b in self.flat.buckets:
             if b.pending != 0:
                 raise RuntimeError("a parameter received no gradient; every parameter must take part in the step")
@@ -250,6 +258,8 @@ class CollectiveTrainer:
         # (with a communicator the update already happened, bucket by bucket, inside the fused collective)
         self._count += _conv.launch_count() - conv0  # tcgen05 convolution kernels launched by the model this step
         self.loss.copy_(loss.detach().float())
+        if cuda:
+            _sink.end_step()
 
     def capture(self, warmup: int = 2) -> None:
         """Runs `warmup` eager steps on a side stream, then captures the step."""
