@@ -45,7 +45,8 @@ def is_sunk(grad: Optional[torch.Tensor], sink: torch.Tensor) -> bool:
 # The op records an event after its side-stream work and registers it here; the trainer makes every consumer of
 # the gradients (bucket collective, optimizer, end of step) wait for the registered events, and keeps the tensors the
 # side stream reads alive until the step is over (no allocator reuse while they are in flight).
-WGRAD_OVERLAP = os.environ.get("PDJ_WGRAD_OVERLAP", "1") == "1"
+WGRAD_OVERLAP = os.environ.get("PDJ_WGRAD_OVERLAP", "1") in ("1", "2")
+WGRAD_OVERLAP_FORCE = os.environ.get("PDJ_WGRAD_OVERLAP", "1") == "2"
 _scope = {"on": False, "events": [], "keep": [], "streams": {}}
 
 
@@ -66,8 +67,8 @@ def register_side_work(event, *tensors) -> None:
     _scope["keep"].extend(tensors)
 
 
-def begin_step() -> None:
-    _scope["on"] = True
+def begin_step(overlap: bool = True) -> None:
+    _scope["on"] = overlap
     _scope["events"].clear()
     _scope["keep"].clear()
 
