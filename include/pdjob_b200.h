@@ -105,6 +105,9 @@ struct PdjEmbTable {
   unsigned int list_cap; /* number of table shards P (the job's pserver count); 0 = one per rank */
   int dim;              /* power of two, 4..128 */
   int has_wide;
+  size_t shadow_off;    /* record layout only, 0 = none: bf16 copy of the deep weights at the head of the record, directly
+                           followed by the wide weight (wide_off = shadow_off + 2 * dim) - the 64 bytes a lookup reads.
+                           pdj_emb_apply keeps it equal to bf16(weights); asynchronous SGD cannot (use 0). */
 };
 int pdj_emb_lookup(const struct PdjComm* c, const struct PdjEmbTable* t, size_t ids_off, size_t out_deep_off,
                    size_t out_wide_off, int B, int S, int barrier, int nblocks, int emulate, cudaStream_t st);

@@ -232,6 +232,81 @@ emb_lookup_batched_kernel(PdjComm c, PdjEmbTable t, size_t ids_off, size_t out_d
   if (do_barrier && threadIdx.x == 0) me->epoch[pdj_slot(c)] = e + 1;
 }
 
+// Lookup through the bf16 read view at the head of each record (PdjEmbTable.shadow_off): one 64-byte request per
+// row - [bf16 deep, 2 * dim bytes][wide weight] - instead of a 64-byte and a 32-byte one, nothing to convert, and
+// a third fewer bytes over NVLink (the pull is packet-bound there: 330 - 380 GB/s effective at 2 - 4 GPUs).  Same
+// batching as emb_lookup_batched_kernel.  LPR lanes per row, 16 bytes each: lanes < dim / 8 carry the deep values,
+// lane dim / 8 carries the wide weight in its first word, the rest (if any) stay idle.
+template <int PASSES>
+__global__ void __launch_bounds__(PASSES <= 2 ? 1024 : 768)
+emb_lookup_shadow_kernel(PdjComm c, PdjEmbTable t, size_t ids_off, size_t out_deep_off, size_t out_wide_off, int B, int S,
+                         int do_barrier, int out_pitch, size_t dense_off, int dense_n, int lpr) {
+  const int rank = c.rank + blockIdx.y;
+  const int NR = c.nranks;
+  PdjSignalPad* me = pdj_pad(c, rank);
+  const uint32_t e = me->epoch[pdj_slot(c)];
+  if (do_barrier) pdj_block_barrier(c, rank, e + 1);  // owners finished applying the previous step
+  const int D = t.dim;
+  const int dchunks = D >> 3;  // 16-byte chunks of bf16 deep values per row
+  const int rpw = 32 / lpr;
+  const int lane = threadIdx.x & 31;
+  const int sub = lane / lpr, part = lane % lpr;
+  const long long* ids = reinterpret_cast<const long long*>(c.base[rank] + ids_off);
+  __nv_bfloat16* out_deep = reinterpret_cast<__nv_bfloat16*>(c.base[rank] + out_deep_off);
+  float* out_wide = reinterpret_cast<float*>(c.base[rank] + out_wide_off);
+  const int warps = (gridDim.x * blockDim.x) >> 5;
+  const size_t sd = emb_sd(t);
+  const bool active = part < dchunks || (part == dchunks && t.has_wide);
+  long long idn[PASSES];
+  auto load_ids = [&](int bb) {
+#pragma unroll
+    for (int p = 0; p < PASSES; ++p) {
+      const int s_ = p * rpw + sub;
+      idn[p] = (bb < B && s_ < S && active) ? ld_id(ids + (size_t)bb * S + s_) : -1ll;
+    }
+  };
+  int b = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  load_ids(b);
+  for (; b < B; b += warps) {
+    int owner[PASSES];
+    long long row[PASSES];
+    bool ok[PASSES];
+#pragma unroll
+    for (int p = 0; p < PASSES; ++p) {
+      ok[p] = idn[p] >= 0;
+      owner[p] = 0;
+      row[p] = 0;
+      if (ok[p]) emb_locate(t, NR, idn[p], &owner[p], &row[p]);
+    }
+    load_ids(b + warps);
+    uint4 v[PASSES];
+#pragma unroll
+    for (int p = 0; p < PASSES; ++p) {
+      v[p] = make_uint4(0u, 0u, 0u, 0u);
+      if (ok[p]) {
+        const float4 f = ld_f4(c.base[owner[p]] + t.shadow_off + (size_t)row[p] * sd + part * 16);
+        v[p] = make_uint4(__float_as_uint(f.x), __float_as_uint(f.y), __float_as_uint(f.z), __float_as_uint(f.w));
+      }
+    }
+    float wide = 0.f;
+#pragma unroll
+    for (int p = 0; p < PASSES; ++p) {
+      if (!ok[p]) continue;
+      if (part < dchunks)
+        *reinterpret_cast<uint4*>(out_deep + (size_t)b * out_pitch + (size_t)(p * rpw + sub) * D + part * 8) = v[p];
+      else
+        wide += __uint_as_float(v[p].x);
+    }
+    emb_write_tail(c, rank, out_deep, b, S * D, out_pitch, dense_off, dense_n, lane);
+    if (t.has_wide) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) wide += __shfl_xor_sync(0xffffffffu, wide, o);
+      if (lane == 0) out_wide[b] = wide;
+    }
+  }
+  if (do_barrier && threadIdx.x == 0) me->epoch[pdj_slot(c)] = e + 1;
+}
+
 // TMA-fed lookup.  One warp per sample, double buffered: lane s asks the TMA engine for row
 // id[b, s] with one bulk copy (cp.async.bulk, 16-byte granularity, completion counted on an
 // mbarrier) straight from the owner GPU's HBM into this warp's shared-memory tile, for sample
@@ -552,6 +627,9 @@ emb_apply_kernel(PdjComm c, PdjEmbTable t, int opt, float lr, float eps) {
           w4.x -= lr * g4.x; w4.y -= lr * g4.y; w4.z -= lr * g4.z; w4.w -= lr * g4.w;
         }
         *reinterpret_cast<float4*>(base + t.deep_off + o) = w4;
+        if (t.shadow_off)  // the bf16 view lookups read
+          *reinterpret_cast<uint2*>(base + t.shadow_off + ro[k] * sd + part * 8) =
+              make_uint2(pdj_f2_to_bf2(w4.x, w4.y), pdj_f2_to_bf2(w4.z, w4.w));
         *reinterpret_cast<float4*>(base + t.gdeep_off + o) = make_float4(0.f, 0.f, 0.f, 0.f);
         if (wide_lane) {
           float wn = ws[k];
@@ -627,6 +705,19 @@ int pdj_emb_lookup2(const PdjComm* c, const PdjEmbTable* t, size_t ids_off, size
   // PDJ_EMB_LOOKUP = batched (default) | tma | loop
   const char* how = getenv("PDJ_EMB_LOOKUP");
   const bool no_tma = how == nullptr || strcmp(how, "tma") != 0;
+  if ((how == nullptr || strcmp(how, "batched") == 0) && t->shadow_off != 0 && t->list_off != 0 && t->dim >= 8 && t->dim <= 64) {
+    // read view: dim / 8 chunks of bf16 values + one chunk holding the wide weight, rounded up to a power of two lanes
+    int lpr = 1;
+    while (lpr < (t->dim >> 3) + (t->has_wide ? 1 : 0)) lpr <<= 1;
+    const int sp = (S + 32 / lpr - 1) / (32 / lpr);
+    if (sp <= 8 && t->wide_off == t->shadow_off + (size_t)t->dim * 2) {
+      const int bt = emulate ? 256 : (sp <= 2 ? 1024 : 768);
+#define PDJ_LS(P) launch_emb(emb_lookup_shadow_kernel<P>, nblocks, bt, (size_t)0, emulate, c->nranks, st, *c, *t, ids_off, \
+                             out_deep_off, out_wide_off, B, S, barrier, out_pitch, dense_off, dense_n, lpr)
+      return sp <= 1 ? PDJ_LS(1) : sp <= 2 ? PDJ_LS(2) : sp <= 4 ? PDJ_LS(4) : PDJ_LS(8);
+#undef PDJ_LS
+    }
+  }
   const int passes = (S + (32 / (t->dim >> 2)) - 1) / (32 / (t->dim >> 2));
   if ((how == nullptr || strcmp(how, "batched") == 0) && passes <= 8) {
     int bt = emulate ? 256 : (passes <= 2 ? 1024 : 768);

@@ -36,7 +36,7 @@ class PdjEmbTable(ctypes.Structure):
         ("deep_off", c_size_t), ("wide_off", c_size_t), ("gdeep_off", c_size_t), ("gwide_off", c_size_t),
         ("acc_deep_off", c_size_t), ("acc_wide_off", c_size_t), ("flag_off", c_size_t), ("list_off", c_size_t),
         ("count_off", c_size_t), ("rows_per_shard", ctypes.c_longlong), ("list_cap", ctypes.c_uint),
-        ("dim", c_int), ("has_wide", c_int),
+        ("dim", c_int), ("has_wide", c_int), ("shadow_off", c_size_t),
     ]
 
 

@@ -63,16 +63,35 @@ class ShardedEmbedding:
         R, D = self.rows_per_shard, dim
         a = comm.alloc
         t = PdjEmbTable()
-        # One record per row (default): | w deep D | w wide, pad 4 | acc deep D | acc wide, pad 4 | g deep D | g wide, pad 4 |
-        # rounded up to 128 B, so a lookup touches one line and the optimizer pass one or two adjacent ones instead of
-        # six arrays.  PDJ_EMB_LAYOUT=arrays keeps six separate arrays (the A/B arm).
+        # One record per row (default), 128-byte aligned:
+        #   head (64 B for dim 16): | bf16 copy of the deep weights | w wide | acc wide | g wide | pad |   <- a lookup reads
+        #   body:                   | g deep | w deep fp32 | acc deep |                                     only the head
+        # so a lookup is ONE 64-byte request per row (it used to be a 64-byte and a 32-byte one, and twice the bytes
+        # over NVLink), and the optimizer pass reads and writes whole aligned records instead of six arrays.  The bf16
+        # view is maintained by the apply kernel; asynchronous SGD updates weights with remote reductions and cannot
+        # keep it, so it gets none.  PDJ_EMB_LAYOUT=arrays keeps six separate arrays, =record_fp32 the record
+        # without the bf16 view (the A/B arms).
         self.record_floats = 0
-        if os.environ.get("PDJ_EMB_LAYOUT", "record") == "record":
-            self.record_floats = ((3 * D + 12) * 4 + 127) // 128 * 32
-            base = a(R * self.record_floats * 4)
-            t.deep_off, t.wide_off = base, base + D * 4
-            t.acc_deep_off, t.acc_wide_off = base + (D + 4) * 4, base + (2 * D + 4) * 4
-            t.gdeep_off, t.gwide_off = base + (2 * D + 8) * 4, base + (3 * D + 8) * 4
+        self.has_shadow = False
+        layout = os.environ.get("PDJ_EMB_LAYOUT", "record")
+        t.shadow_off = 0
+        if layout in ("record", "record_fp32"):
+            self.has_shadow = layout == "record" and not async_sgd and 8 <= D <= 64
+            head = (2 * D + 12 + 63) // 64 * 64 if self.has_shadow else 0
+            if self.has_shadow:
+                self.record_floats = (head + 12 * D + 127) // 128 * 32
+                base = a(R * self.record_floats * 4)
+                t.shadow_off = base
+                t.wide_off, t.acc_wide_off, t.gwide_off = base + 2 * D, base + 2 * D + 4, base + 2 * D + 8
+                # g deep directly after the head: a push touches g wide (head) and g deep in the same 128-byte line
+                t.gdeep_off, t.deep_off, t.acc_deep_off = base + head, base + head + 4 * D, base + head + 8 * D
+            else:
+                self.record_floats = ((3 * D + 12) * 4 + 127) // 128 * 32
+                base = a(R * self.record_floats * 4)
+                t.deep_off, t.wide_off = base, base + D * 4
+                t.acc_deep_off, t.acc_wide_off = base + (D + 4) * 4, base + (2 * D + 4) * 4
+                t.gdeep_off, t.gwide_off = base + (2 * D + 8) * 4, base + (3 * D + 8) * 4
+            self._rec_base = base
         else:
             t.deep_off = a(R * D * 4)
             t.wide_off = a(R * 4)
@@ -106,9 +125,20 @@ class ShardedEmbedding:
         R, F = self.rows_per_shard, self.record_floats
         if not F:
             return self.comm.tensor(off, (R, width) if width else (R,), torch.float32, rank)
-        rec = self.comm.tensor(self.t.deep_off, (R, F), torch.float32, rank)
-        c = (off - self.t.deep_off) // 4
+        rec = self.comm.tensor(self._rec_base, (R, F), torch.float32, rank)
+        c = (off - self._rec_base) // 4
         return rec[:, c:c + width] if width else rec[:, c]
+
+    def _shadow(self, rank: Optional[int] = None) -> torch.Tensor:
+        """[rows_per_shard, dim] bf16 view of the read view at the head of the records."""
+        rec = self.comm.tensor(self._rec_base, (self.rows_per_shard, self.record_floats * 2), torch.bfloat16, rank)
+        return rec[:, :self.dim]
+
+    def refresh_shadow(self, rank: Optional[int] = None) -> None:
+        """Re-derives the bf16 read view from the fp32 weights.  Call after writing `shard()` directly (the apply
+        kernel, `_init` and the checkpoint loaders do it themselves)."""
+        if self.has_shadow:
+            self._shadow(rank).copy_(self.shard(rank))
 
     def shard(self, rank: Optional[int] = None) -> torch.Tensor:
         return self._part(self.t.deep_off, self.dim, rank)
@@ -127,12 +157,13 @@ class ShardedEmbedding:
             deep = torch.randn(self.rows_per_shard, self.dim, generator=g, device=dev) * scale
             wide = torch.randn(self.rows_per_shard, generator=g, device=dev) * scale
             if self.record_floats:
-                self.comm.tensor(self.t.deep_off, (self.rows_per_shard * self.record_floats,), torch.float32, r).zero_()
+                self.comm.tensor(self._rec_base, (self.rows_per_shard * self.record_floats,), torch.float32, r).zero_()
             else:
                 for part in (*self.staging(r), *self._acc(r)):
                     part.zero_()
             self.shard(r).copy_(deep)
             self.shard_wide(r).copy_(wide)
+            self.refresh_shadow(r)
             for off, n in ((self.t.flag_off, self._flag_bytes // 4), (self.t.count_off, 64)):
                 self.comm.tensor(off, (n,), torch.float32, r).zero_()
 
@@ -241,6 +272,7 @@ class ShardedEmbedding:
         self.shard_wide()[sl].copy_(sd["wide"])
         acc_d[sl].copy_(sd["acc_deep"])
         acc_w[sl].copy_(sd["acc_wide"])
+        self.refresh_shadow()
 
     def state_dict(self) -> dict:
         """Everything this rank holds in one dict (one shard per rank: the round-1 format)."""
@@ -255,6 +287,7 @@ class ShardedEmbedding:
         self.shard_wide().copy_(sd["wide"])
         acc_d.copy_(sd["acc_deep"])
         acc_w.copy_(sd["acc_wide"])
+        self.refresh_shadow()
 
 
 class _LookupFn(torch.autograd.Function):

@@ -109,7 +109,8 @@ class WideDeepJob:
     @staticmethod
     def arena_bytes_needed(rows: int, dim: int, batch: int, world: int) -> int:
         r = (rows + world - 1) // world
-        table = r * (((3 * dim + 12) * 4 + 127) // 128 * 128) + r  # one record per row + flag bytes
+        head = (2 * dim + 12 + 63) // 64 * 64
+        table = r * ((head + 12 * dim + 127) // 128 * 128) + r  # one record per row + flag bytes
         io = batch * SPARSE_SLOTS * (8 + dim * 2 * 2 + 4 * world) + batch * 8
         return int(table + io + (96 << 20))
 

@@ -206,3 +206,42 @@ def test_shard_count_follows_the_pserver_count(nranks, shards):
         assert sorted(sds) == held[0] and all(sd["deep"].shape == (emb.shard_rows, D) for sd in sds.values())
     finally:
         comm.close()
+
+
+@pytest.mark.parametrize("nranks", [1, 2])
+@pytest.mark.parametrize("dim", [8, 16, 32, 64])
+def test_lookup_reads_the_bf16_view_kept_by_apply(nranks, dim):
+    """Record layout with the bf16 read view: after push + apply a lookup returns bf16(updated fp32 weights), and
+    refresh_shadow() re-derives the view after a direct write to shard()."""
+    from paddle_operator_b200.parallel.ps import ADAGRAD, embedding_reference
+
+    comm, emb = _mk(nranks, rows=777, dim=dim, slots=7, optimizer=ADAGRAD, lr=0.3, eps=1e-6)
+    try:
+        assert emb.has_shadow and emb.t.shadow_off != 0
+        B, S, D = 96, emb.slots, dim
+        torch.manual_seed(dim)
+        for step in range(2):
+            ids = [torch.randint(0, emb.num_rows, (B, S), device="cuda") for _ in range(nranks)]
+            for r in range(nranks):
+                emb.ids_buffer(B, r).copy_(ids[r])
+                emb.grad_deep_in(B, r).copy_((torch.randn(B, S * D, device="cuda") * 0.5).to(torch.bfloat16))
+                emb.grad_wide_in(B, r).copy_(torch.randn(B, device="cuda"))
+            emb.push_raw(B)
+            emb.lookup_raw(B)
+            torch.cuda.synchronize()
+            deep_t, wide_t = emb.full_tables()
+            for r in range(nranks):
+                d_ref, w_ref = embedding_reference(deep_t, wide_t, ids[r])
+                got = emb.out_deep(B, r).float().view(B, S, D)
+                torch.testing.assert_close(got, d_ref.to(torch.bfloat16).float(), atol=0, rtol=0)
+                torch.testing.assert_close(emb.out_wide(B, r), w_ref, atol=1e-5, rtol=1e-5)
+        for r in range(nranks):
+            emb.shard(r).mul_(2.0)
+            emb.refresh_shadow(r)
+        emb.lookup_raw(B)
+        torch.cuda.synchronize()
+        deep_t, wide_t = emb.full_tables()
+        d_ref, _ = embedding_reference(deep_t, wide_t, ids[0])
+        torch.testing.assert_close(emb.out_deep(B, 0).float().view(B, S, D), d_ref.to(torch.bfloat16).float(), atol=0, rtol=0)
+    finally:
+        comm.close()
