@@ -179,6 +179,12 @@ def main() -> int:
                           "on the MN-major tcgen05 kernel",
              "launches_wd6": "Wide&Deep step launch list (batch 32768, one B200) - round 2, final: MN-major tcgen05 weight "
                              "gradient for the tower, one record per table row",
+             "launches9": "ResNet-50 step launch list (batch 256, one B200) - round 2, final: + own backward for 1x1 convolutions "
+                          "without a skip gradient, gradient sinks (no gradient copies)",
+             "launches_wd8": "Wide&Deep step launch list (batch 32768, one B200) - round 2, final: bf16 read view in the table "
+                             "records, batched lookup / push / apply, weights read as stored by the dgrad GEMMs, mask tile by "
+                             "TMA, gradient sinks, one column-sum kernel (side-stream weight gradients do not show: ncu "
+                             "serialises)",
              "launches_wd7": "Wide&Deep step launch list (batch 32768, one B200) - round 2, final: vectorised mask read in "
                              "the masked dgrad, gradient sinks (no gradient copies), one weighted column-sum kernel for "
                              "the bias and head gradients"}
