@@ -21,7 +21,8 @@ KEEP = re.compile(r"\b(UTC[A-Z]*MMA|UTCBAR|UTCCP|LDTM|STTM|UTMALDG|UTMASTG|UTMAP
                   r"RED[G]?|ATOM[GS]?|LDG\.E[^ ]*\.(SYS|STRONG)[^ ]*|STG\.E[^ ]*\.(SYS|STRONG)[^ ]*|LD\.E[^ ]*SYS|ST\.E[^ ]*SYS|"
                   r"ELECT|MEMBAR|FENCE|HMMA|CCTL|ERRBAR|NANOSLEEP)\b")
 WANT = ["allreduce_nvls", "allreduce_twoshot", "allreduce_oneshot", "allreduce_sgd", "alltoall", "broadcast_kernel",
-        "barrier_kernel", "emb_lookup_tma", "emb_lookup_kernel", "emb_push", "emb_apply", "wd_head", "linear_tcgen05",
+        "barrier_kernel", "emb_lookup_tma", "emb_lookup_kernel", "emb_lookup_batched", "emb_lookup_shadow", "emb_push", "emb_apply",
+        "wd_head", "colsum_w", "linear_tcgen05", "wgrad_mn",
         "conv1x1_tcgen05", "stem_wgrad", "wgrad3x3", "wgrad_reduce", "bn_stats_tma", "bn_bwd_reduce_tma"]
 
 
