@@ -10,6 +10,8 @@ Arms (`measure(..., impl=...)`):
 """
 from __future__ import annotations
 
+import os
+
 import torch
 import torch.distributed as dist
 
@@ -171,6 +173,7 @@ class NcclShardedJob:
         return self.loss
 
     def train_step(self, ids, dense, labels):
+        self._h2d_bytes = sum(t.numel() * t.element_size() for t in (ids, dense, labels))
         self.ids.copy_(ids, non_blocking=True)
         self.dense_x.copy_(dense, non_blocking=True)
         self.labels.copy_(labels, non_blocking=True)
@@ -182,7 +185,7 @@ class NcclShardedJob:
         """This rank's shard without the spare row (tests)."""
         return self.deep[:self.rps], self.wide[:self.rps]
 
-    h2d_bytes_per_step = property(lambda s: s.batch * (SPARSE_SLOTS * 8 + DENSE_FEATURES * 4 + 4))
+    h2d_bytes_per_step = property(lambda s: getattr(s, "_h2d_bytes", s.batch * (SPARSE_SLOTS * 8 + DENSE_FEATURES * 4 + 4)))
     d2h_bytes_per_step = 4
     launches_per_step = 0
 
@@ -214,7 +217,8 @@ def measure(args, impl: str, rank: int, world: int, dev, ClockSampler) -> dict:
         job = NcclShardedJob(batch, rows, dim, rank, world, dev, graph=(impl == "nccl_graph"))
         num_rows = job.num_rows
         g = torch.Generator().manual_seed(100 + rank)
-        hb = [(torch.randint(0, num_rows, (batch, SPARSE_SLOTS), generator=g).pin_memory(),
+        ids_dtype = torch.int32 if os.environ.get("PDJ_WD_IDS", "int32") == "int32" else torch.int64  # 16.7 M rows fit 32 bits
+        hb = [(torch.randint(0, num_rows, (batch, SPARSE_SLOTS), generator=g).to(ids_dtype).pin_memory(),
                torch.randn(batch, DENSE_FEATURES, generator=g).pin_memory(),
                (torch.rand(batch, generator=g) > 0.75).float().pin_memory()) for _ in range(3)]
     steps, warmup = args.steps, max(args.warmup, 3)
@@ -227,7 +231,8 @@ def measure(args, impl: str, rank: int, world: int, dev, ClockSampler) -> dict:
         "impl": impl,
         "impl_name": IMPL_NAMES[impl],
         "dtype": "bf16 (MLP) / fp32 (tables)",
-        "data": "synthetic (uniform random ids over the table, random dense features and labels; random-init weights)",
+        "data": "synthetic (uniform random ids over the table - int32 on the host, widened on the device; random dense features "
+                "and labels; random-init weights)",
         "config": {"model": "Wide&Deep: 26 sparse slots x dim 16 + 13 dense -> 400-400-400-1, Adagrad (sparse) + SGD momentum (dense)",
                    "table_rows": num_rows, "global_batch": batch * world, "per_gpu_batch": batch, "seq_len": None,
                    "parallelism": f"ps{world}+dp{world} (one table shard per GPU)",

@@ -136,6 +136,8 @@ class WideDeepJob:
         labels = (torch.rand((self.batch,), generator=g) > 0.75).float()
         if device is not None:
             return ids.to(device), dense.to(device), labels.to(device)
+        if self.emb.num_rows < (1 << 31) and os.environ.get("PDJ_WD_IDS", "int32") == "int32":
+            ids = ids.to(torch.int32)  # what a data loader hands over for a table this size: half the PCIe bytes
         return ids.pin_memory(), dense.pin_memory(), labels.pin_memory()
 
     def prepare(self) -> None:
@@ -149,9 +151,16 @@ class WideDeepJob:
         return self.trainer.step()
 
     def train_step(self, ids: torch.Tensor, dense: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
+        """One step on a pinned host batch: ids [B, 26] int64 or int32 (a table of fewer than 2^31 rows needs no
+        more; half the bytes over PCIe, widened on the device), dense [B, 13] fp32, labels [B] fp32.  The copy of
+        batch k + 1 runs on a side stream under step k; returns a pinned one-element tensor holding the loss."""
         s = self._slot
         self._slot ^= 1
         main = torch.cuda.current_stream()
+        if self._stage[s][0].dtype != ids.dtype:  # first int32 batch: staging buffers of the host dtype
+            torch.cuda.synchronize(self.device)
+            self._stage = [(torch.empty(self.ids.shape, dtype=ids.dtype, device=self.device), st[1], st[2])
+                           for st in self._stage]
         st = self._stage[s]
         with torch.cuda.stream(self._copy_stream):
             self._copy_stream.wait_event(self._consumed[s])
@@ -164,6 +173,7 @@ class WideDeepJob:
         self.dense_x.copy_(st[1])
         self.labels.copy_(st[2])
         self._consumed[s].record(main)
+        self._h2d_bytes = sum(t.numel() * t.element_size() for t in (ids, dense, labels))
         loss = self.step_device()
         i = self._loss_i
         self._loss_i = (i + 1) % self._loss_host.numel()
@@ -173,7 +183,8 @@ class WideDeepJob:
 
     @property
     def h2d_bytes_per_step(self) -> int:
-        return self.batch * (SPARSE_SLOTS * 8 + DENSE_FEATURES * 4 + 4)
+        # bytes of the last batch handed to train_step (int64 ids until one has been seen)
+        return getattr(self, "_h2d_bytes", self.batch * (SPARSE_SLOTS * 8 + DENSE_FEATURES * 4 + 4))
 
     d2h_bytes_per_step = 4
 

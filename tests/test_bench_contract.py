@@ -91,10 +91,9 @@ def test_nccl_baseline_step_runs_and_learns_on_cpu():
     from paddle_operator_b200.workloads.bench_wide_deep import NcclShardedJob
 
     job = NcclShardedJob(batch=256, rows=1000, dim=8, rank=0, world=1, dev=torch.device("cpu"))
-    first = float(job.step_device())
-    for _ in range(30):
-        last = float(job.step_device())
-    assert last < first and not bool(job.overflowed)
+    losses = [float(job.step_device()) for _ in range(40)]
+    # (each step draws a fresh random batch, so single losses jitter: compare averages)
+    assert sum(losses[-10:]) / 10 < sum(losses[:5]) / 5 and not bool(job.overflowed)
 
 
 _TWO_RANK_ROUTING = '''
