@@ -117,7 +117,7 @@ l0 = float(job.step_device())
 for _ in range(20):
     l1 = float(job.step_device())
 assert l1 < l0 and not bool(job.overflowed), (l0, l1)
-print("rank", r, "ok")
+sys.stdout.write("rank " + str(r) + " ok" + chr(10)); sys.stdout.flush()  # one write: the two ranks share a pipe
 '''
 
 
