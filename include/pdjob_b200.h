@@ -199,6 +199,11 @@ int pdj_conv3x3_wgrad(const void* x, const void* dy, void* dw, void* ws, int N, 
 size_t pdj_wgrad_mn_ws_bytes(int M, int No, int Nc);
 int pdj_wgrad_mn(const void* x, const void* dy, void* dw, void* ws, int M, int No, int Nc, int ldx, int ldy,
                  cudaStream_t st);
+/* pdj_wgrad_mn that also returns db[No] (bf16) = column sums of dy (the bias gradient), computed from the dY tiles the
+ * kernel streams anyway.  `ws`: pdj_wgrad_mn_db_ws_bytes(M, No, Nc) bytes. */
+size_t pdj_wgrad_mn_db_ws_bytes(int M, int No, int Nc);
+int pdj_wgrad_mn_db(const void* x, const void* dy, void* dw, void* db, void* ws, int M, int No, int Nc, int ldx, int ldy,
+                    cudaStream_t st);
 
 /* ---- ResNet-50 step kernels (csrc/bn_act.cu, csrc/optim_misc.cu) -----------
  * The workload of deploy/examples/resnet.yaml:13-19. NHWC bf16 activations

@@ -260,17 +260,22 @@ struct WgMnCfg {
   int nc_tile, groups_c;    // channels per CTA tile (multiple of 64, <= 256) = groups_c x 64
   int tiles_c, tiles, S, stages, blocks;
   uint32_t slot_bytes;
+  int with_db;              // also produce the column sums of dY (the bias gradient) with one extra N = 16 MMA per step
 };
 constexpr int WM_KB = 128;                     // rows per block
 constexpr int WM_GROUP_BYTES = WM_KB * 128;    // one 64-channel group of a block: 16 KiB
 
 __global__ void __launch_bounds__(WG_THREADS, 1)
 wgrad_mn_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constant__ CUtensorMap tma_dy,
-                        float* __restrict__ partial, const WgMnCfg c) {
+                        float* __restrict__ partial, float* __restrict__ db_partial, const WgMnCfg c) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
   const uint32_t base = (raw + 1023u) & ~1023u;
-  const uint32_t bars = base + (uint32_t)c.stages * c.slot_bytes;
+  // with_db: a [128 k][64] tile of bf16 ones.  D2[o][0..15] += dY^T . ones = the column sums of dY - the bias gradient of
+  // the layer - from the dY tile that is in shared memory anyway: no separate pass over dY (26 MB and ~14 us per layer
+  // of the Wide&Deep tower).  Only the CTAs of column tile 0 issue the extra N = 16 instruction.
+  const uint32_t ones = base + (uint32_t)c.stages * c.slot_bytes;
+  const uint32_t bars = ones + (c.with_db ? (uint32_t)WM_GROUP_BYTES : 0u);
   const uint32_t full0 = bars, empty0 = bars + 8 * MAX_STAGES, done = empty0 + 8 * MAX_STAGES, tmem_slot = done + 8;
   uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(smem_raw + (tmem_slot - raw));
   const int warp = (int)warp_uniform(threadIdx.x >> 5), lane = threadIdx.x & 31;
@@ -290,8 +295,14 @@ wgrad_mn_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncwarp();
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(256) : "memory");
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(512) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  const bool do_db = c.with_db && (tile % c.tiles_c) == 0;
+  if (do_db) {
+    for (uint32_t i = threadIdx.x; i < (uint32_t)WM_GROUP_BYTES / 16u; i += blockDim.x)
+      asm volatile("st.shared.v4.b32 [%0], {%1,%1,%1,%1};" ::"r"(ones + i * 16u), "r"(0x3f803f80u) : "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic writes -> visible to the tensor core's reads
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
@@ -316,6 +327,7 @@ wgrad_mn_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_
     const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(c.nc_tile >> 3) << 17) |
                            ((128u >> 4) << 24);
     const uint64_t d0 = umma_desc_ex(0, WM_GROUP_BYTES, 1024, 2);  // 64-channel groups one tile apart
+    const uint32_t idesc16 = (idesc & ~(0x3fu << 17)) | ((16u >> 3) << 17);
     uint32_t it = 0;
     for (int b = split; b < c.blocks; b += c.S, ++it) {
       const uint32_t s = it % (uint32_t)c.stages, ph = (it / (uint32_t)c.stages) & 1u;
@@ -323,8 +335,13 @@ wgrad_mn_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_
       mbar_wait(full0 + 8 * s, ph);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       uint64_t da = d0 + (uint64_t)(slot >> 4), db = d0 + (uint64_t)((slot + x_off) >> 4);
+      uint64_t d1 = d0 + (uint64_t)(ones >> 4);
 #pragma unroll
       for (int ks = 0; ks < WM_KB / 16; ++ks) {
+        if (do_db) {  // column sums of dY: accumulator columns 256..271
+          umma_f16_elect(tmem_base + 256u, da, d1, idesc16, (uint32_t)((it | (uint32_t)ks) != 0u));
+          d1 += 2048 >> 4;
+        }
         umma_f16_elect(tmem_base, da, db, idesc, (uint32_t)((it | (uint32_t)ks) != 0u));
         da += 2048 >> 4;
         db += 2048 >> 4;
@@ -355,6 +372,18 @@ wgrad_mn_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_
                      "r"(has_work ? r[4 * v + 3] : 0u)
                      : "memory");
     }
+    if (do_db) {
+      uint32_t r[16];
+      asm volatile(
+          "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+          : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+            "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+          : "r"(tmem_base + ((uint32_t)(q * 32) << 16) + 256u)
+          : "memory");
+      asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+      const int o = o0 + q * 32 + lane;
+      if (o < c.No) db_partial[(size_t)split * c.No + o] = has_work ? __uint_as_float(r[0]) : 0.f;
+    }
     __syncwarp();
     // one row per trip: the warp writes the row's valid columns as consecutive float4s
     for (int rl = 0; rl < 32; ++rl) {
@@ -373,7 +402,7 @@ wgrad_mn_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
   if (warp == 1) {
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(256) : "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512) : "memory");
   }
 }
 
@@ -469,10 +498,11 @@ int pdj_conv3x3_wgrad(const void* x, const void* dy, void* dw, void* ws, int N, 
   return 0;
 }
 
-static int make_mn_cfg(int M, int No, int Nc, WgMnCfg* out) {
+static int make_mn_cfg(int M, int No, int Nc, WgMnCfg* out, int with_db = 0) {
   if (M < 1 || No < 1 || Nc < 8 || Nc % 8 != 0 || No % 8 != 0) return 0;
   WgMnCfg c{};
   c.M = M; c.No = No; c.Nc = Nc;
+  c.with_db = with_db;
   const int parts = (Nc + 255) / 256;
   c.nc_tile = round_up((Nc + parts - 1) / parts, 64);
   c.groups_c = c.nc_tile / 64;
@@ -480,7 +510,7 @@ static int make_mn_cfg(int M, int No, int Nc, WgMnCfg* out) {
   c.tiles = ((No + 127) / 128) * c.tiles_c;
   c.blocks = (M + WM_KB - 1) / WM_KB;
   c.slot_bytes = (uint32_t)(2 + c.groups_c) * WM_GROUP_BYTES;
-  c.stages = (SMEM_LIMIT - 1024 - 512) / (int)c.slot_bytes;
+  c.stages = (SMEM_LIMIT - 1024 - 512 - (with_db ? WM_GROUP_BYTES : 0)) / (int)c.slot_bytes;
   if (c.stages > MAX_STAGES) c.stages = MAX_STAGES;
   if (c.stages < 2) return 0;
   c.S = pdj_tc_sm_count() / c.tiles;
@@ -499,11 +529,11 @@ size_t pdj_wgrad_mn_ws_bytes(int M, int No, int Nc) {
 // dw[No][Nc] (bf16, row-major) = dy[M][No]^T . x[M][Nc]: the weight gradient of a linear layer or of a 1x1
 // convolution over NHWC activations viewed as [pixels][channels].  Row pitches ldy / ldx in elements (multiples of
 // 8); No and Nc multiples of 8.  `ws`: pdj_wgrad_mn_ws_bytes(M, No, Nc) bytes.
-int pdj_wgrad_mn(const void* x, const void* dy, void* dw, void* ws, int M, int No, int Nc, int ldx, int ldy,
-                 cudaStream_t st) {
+static int launch_wgrad_mn(const void* x, const void* dy, void* dw, void* db, void* ws, int M, int No, int Nc, int ldx, int ldy,
+                           cudaStream_t st) {
   WgMnCfg c;
-  if (!make_mn_cfg(M, No, Nc, &c) || ws == nullptr || ldx % 8 != 0 || ldy % 8 != 0 || ldx < Nc || ldy < No ||
-      ((uintptr_t)x & 15) || ((uintptr_t)dy & 15) || ((uintptr_t)dw & 7)) {
+  if (!make_mn_cfg(M, No, Nc, &c, db != nullptr) || ws == nullptr || ldx % 8 != 0 || ldy % 8 != 0 || ldx < Nc || ldy < No ||
+      ((uintptr_t)x & 15) || ((uintptr_t)dy & 15) || ((uintptr_t)dw & 7) || ((uintptr_t)db & 7)) {
     pdj_set_error("pdj_wgrad_mn: need No, Nc multiples of 8, row pitches multiples of 8 elements, 16-byte aligned tensors "
                   "and a workspace (M=%d No=%d Nc=%d ldx=%d ldy=%d)", M, No, Nc, ldx, ldy);
     return -1;
@@ -516,12 +546,37 @@ int pdj_wgrad_mn(const void* x, const void* dy, void* dw, void* ws, int M, int N
   CUtensorMap mx, my;
   if (int r = pdj_tc_make_map(&mx, x, M, Nc, ldx, 64, WM_KB, true)) return r;
   if (int r = pdj_tc_make_map(&my, dy, M, No, ldy, 64, WM_KB, true)) return r;
-  const int smem = 1024 + c.stages * (int)c.slot_bytes + 512;
-  wgrad_mn_tcgen05_kernel<<<c.tiles * c.S, WG_THREADS, smem, st>>>(mx, my, (float*)ws, c);
+  const int smem = 1024 + c.stages * (int)c.slot_bytes + (c.with_db ? WM_GROUP_BYTES : 0) + 512;
+  float* dbp = db != nullptr ? (float*)ws + (size_t)c.S * No * Nc : nullptr;
+  wgrad_mn_tcgen05_kernel<<<c.tiles * c.S, WG_THREADS, smem, st>>>(mx, my, (float*)ws, dbp, c);
   PDJ_CUDA_CHECK(cudaGetLastError());
   launch_reduce((const float*)ws, c.S, (size_t)No * Nc, (__nv_bfloat16*)dw, st);
+  if (db != nullptr) launch_reduce(dbp, c.S, (size_t)No, (__nv_bfloat16*)db, st);
   PDJ_CUDA_CHECK(cudaGetLastError());
   return 0;
+}
+
+int pdj_wgrad_mn(const void* x, const void* dy, void* dw, void* ws, int M, int No, int Nc, int ldx, int ldy,
+                 cudaStream_t st) {
+  return launch_wgrad_mn(x, dy, dw, nullptr, ws, M, No, Nc, ldx, ldy, st);
+}
+
+// The same plus db[No] (bf16) = the column sums of dy - the bias gradient - from the dY tiles the kernel already has in
+// shared memory (one extra N = 16 tensor-core instruction per 16 rows against a tile of ones).
+// `ws`: pdj_wgrad_mn_db_ws_bytes(M, No, Nc) bytes.
+size_t pdj_wgrad_mn_db_ws_bytes(int M, int No, int Nc) {
+  WgMnCfg c;
+  if (!make_mn_cfg(M, No, Nc, &c, 1)) return 0;
+  return (size_t)c.S * No * Nc * sizeof(float) + (size_t)c.S * No * sizeof(float);
+}
+
+int pdj_wgrad_mn_db(const void* x, const void* dy, void* dw, void* db, void* ws, int M, int No, int Nc, int ldx, int ldy,
+                    cudaStream_t st) {
+  if (db == nullptr) {
+    pdj_set_error("pdj_wgrad_mn_db: db is NULL");
+    return -1;
+  }
+  return launch_wgrad_mn(x, dy, dw, db, ws, M, No, Nc, ldx, ldy, st);
 }
 
 }  // extern "C"

@@ -98,6 +98,8 @@ def _declare(lib: ctypes.CDLL) -> None:
         "pdj_conv3x3_wgrad": (c_int, [vp, vp, vp, vp, c_int, c_int, c_int, c_int, c_int, st]),
         "pdj_wgrad_mn_ws_bytes": (sz, [c_int, c_int, c_int]),
         "pdj_wgrad_mn": (c_int, [vp, vp, vp, vp, c_int, c_int, c_int, c_int, c_int, st]),
+        "pdj_wgrad_mn_db_ws_bytes": (sz, [c_int, c_int, c_int]),
+        "pdj_wgrad_mn_db": (c_int, [vp, vp, vp, vp, vp, c_int, c_int, c_int, c_int, c_int, st]),
         "pdj_bn_fwd_pre": (c_int, [vp, vp, vp, vp, c_int, c_int, vp, vp, c_float, c_float, vp, vp, vp, vp, c_int, vp, c_int, st]),
         "pdj_bn_workspace_bytes": (sz, []),
         "pdj_bn_fwd": (c_int, [vp, vp, vp, c_int, c_int, vp, vp, c_float, c_float, vp, vp, vp, vp, c_int, vp, st]),

@@ -81,11 +81,20 @@ class _LinearActFn(torch.autograd.Function):
         if ctx.needs_input_grad[0]:
             # dX[M,K] = dZ[M,N] @ W[N,K]  ==  dZ . (W^T)[K,N]^T : the B operand is W^T, K-major over N
             dx = linear_bf16(dz, weight, b_kn=True)
+        db_done = False
+        need_b = ctx.has_bias and ctx.needs_input_grad[2]
         if ctx.needs_input_grad[1]:
             sink = sink_of(weight)
-            dw = wgrad_mn(dz, x, out=sink)
+            dbt = None
+            if need_b and ctx.bias_dtype == torch.bfloat16 and dz.stride(1) == 1:  # bias gradient from the same kernel
+                bsink = sink_of(ctx.bias)
+                dbt = bsink if bsink is not None else torch.empty(dz.shape[1], dtype=torch.bfloat16, device=dz.device)
+            res = wgrad_mn(dz, x, out=sink, db_out=dbt)
+            dw, db_done = res if dbt is not None else (res, False)
             dw = adopt(dw) if sink is not None else dw
-        if ctx.has_bias and ctx.needs_input_grad[2]:
+            if db_done:
+                db = adopt(dbt) if dbt is sink_of(ctx.bias) else dbt
+        if need_b and not db_done:
             from .mlp import colsum
 
             sink = sink_of(ctx.bias)
@@ -97,30 +106,50 @@ class _LinearActFn(torch.autograd.Function):
         return dx, dw, db, None, None
 
 
-def wgrad_mn(dy: torch.Tensor, x: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+# the bias gradient (column sums of dy) comes out of the weight-gradient kernel itself; PDJ_WGRAD_DB=0 = separate pass
+WGRAD_DB = os.environ.get("PDJ_WGRAD_DB", "1") == "1"
+
+
+def wgrad_mn(dy: torch.Tensor, x: torch.Tensor, out: Optional[torch.Tensor] = None,
+             db_out: Optional[torch.Tensor] = None):
     """dW[No, Nc] = dy[M, No]^T @ x[M, Nc] (bf16) on the MN-major tcgen05 kernel (csrc/wgrad_tcgen05.cu: both operands
     read as they sit in memory, accumulators resident in tensor memory, split-K with a fixed-order reduce).  Falls
     back to the library GEMM for shapes the kernel does not take.  `out`: a bf16 tensor whose memory is a dense
-    [No, Nc] matrix (e.g. a gradient sink, ops/_sink.py); it is returned."""
+    [No, Nc] matrix (e.g. a gradient sink, ops/_sink.py); it is returned.
+    `db_out`: a contiguous bf16 [No] tensor that receives the column sums of dy (the bias gradient) from the same
+    kernel - one extra N = 16 tensor-core instruction per step against a tile of ones instead of a pass over dy.  With
+    `db_out` the result is (dW, filled) where `filled` tells whether the kernel produced it (False: the caller
+    computes the bias gradient itself)."""
     m, no = dy.shape
     nc = x.shape[1]
     ok = (dy.is_cuda and dy.dtype == torch.bfloat16 and x.dtype == torch.bfloat16 and x.shape[0] == m and no % 8 == 0
           and nc % 8 == 0 and dy.stride(1) == 1 and x.stride(1) == 1 and dy.stride(0) % 8 == 0 and x.stride(0) % 8 == 0
           and dy.data_ptr() % 16 == 0 and x.data_ptr() % 16 == 0 and os.environ.get("PDJ_WGRAD_MN", "1") == "1")
     lib = _lib.load() if ok else None
-    nbytes = lib.pdj_wgrad_mn_ws_bytes(m, no, nc) if ok else 0
+    with_db = (ok and db_out is not None and WGRAD_DB and db_out.dtype == torch.bfloat16 and db_out.is_contiguous()
+               and db_out.numel() == no and db_out.data_ptr() % 8 == 0)
+    if with_db:
+        nbytes = lib.pdj_wgrad_mn_db_ws_bytes(m, no, nc)
+        with_db = nbytes != 0
+    if not with_db:
+        nbytes = lib.pdj_wgrad_mn_ws_bytes(m, no, nc) if ok else 0
     if nbytes == 0:
         dw = dy.t().mm(x)
-        if out is None:
-            return dw
-        out.view(-1).copy_(dw.view(-1)) if out.is_contiguous() else out.copy_(dw.view(out.shape))
-        return out
+        if out is not None:
+            out.view(-1).copy_(dw.view(-1)) if out.is_contiguous() else out.copy_(dw.view(out.shape))
+            dw = out
+        return dw if db_out is None else (dw, False)
     dw = torch.empty((no, nc), dtype=torch.bfloat16, device=x.device) if out is None else out
     assert dw.dtype == torch.bfloat16 and dw.numel() == no * nc and dw.data_ptr() % 16 == 0
     ws = torch.empty(nbytes, dtype=torch.uint8, device=x.device)
-    _lib.check(lib.pdj_wgrad_mn(x.data_ptr(), dy.data_ptr(), dw.data_ptr(), ws.data_ptr(), m, no, nc, x.stride(0),
-                                dy.stride(0), torch.cuda.current_stream().cuda_stream), "wgrad_mn")
-    return dw
+    st = torch.cuda.current_stream().cuda_stream
+    if with_db:
+        _lib.check(lib.pdj_wgrad_mn_db(x.data_ptr(), dy.data_ptr(), dw.data_ptr(), db_out.data_ptr(), ws.data_ptr(), m, no, nc,
+                                       x.stride(0), dy.stride(0), st), "wgrad_mn_db")
+    else:
+        _lib.check(lib.pdj_wgrad_mn(x.data_ptr(), dy.data_ptr(), dw.data_ptr(), ws.data_ptr(), m, no, nc, x.stride(0),
+                                    dy.stride(0), st), "wgrad_mn")
+    return dw if db_out is None else (dw, with_db)
 
 
 def linear_act(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] = None, relu: bool = False,

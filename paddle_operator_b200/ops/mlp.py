@@ -122,12 +122,23 @@ class _FusedMLPFn(torch.autograd.Function):
             for l in range(n, 0, -1):
                 # both parameter gradients land in the trainer's flat gradient buffer when it provides sinks
                 bsink, wsink = sink_of(ctx.biases[l - 1]), sink_of(ws[l - 1])
-                if ctx.needs_input_grad[3 + n + l - 1]:
+                need_b, need_w = ctx.needs_input_grad[3 + n + l - 1], ctx.needs_input_grad[3 + l - 1]
+                db_done = False
+                if need_w:
+                    # a bf16 bias gradient comes out of the weight-gradient kernel (column sums of dz against a tile
+                    # of ones on the tensor cores) - no separate pass over dz
+                    db = None
+                    if need_b and ctx.bias_dtypes[l - 1] == torch.bfloat16:
+                        db = bsink if bsink is not None else torch.empty(dzs[l].shape[1], dtype=torch.bfloat16,
+                                                                         device=dzs[l].device)
+                    res = wgrad_mn(dzs[l], hs[l - 1], out=wsink, db_out=db)
+                    dw, db_done = res if db is not None else (res, False)
+                    dws[l - 1] = adopt(dw) if wsink is not None else dw
+                    if db_done:
+                        dbs[l - 1] = adopt(db) if bsink is not None else db
+                if need_b and not db_done:
                     db = colsum(dzs[l], out=bsink, dtype=ctx.bias_dtypes[l - 1])
                     dbs[l - 1] = adopt(db) if bsink is not None else db
-                if ctx.needs_input_grad[3 + l - 1]:
-                    dw = wgrad_mn(dzs[l], hs[l - 1], out=wsink)
-                    dws[l - 1] = adopt(dw) if wsink is not None else dw
 
         if _sink.overlap_enabled():
             # the parameter gradients run on a side stream while the main stream continues with whatever consumes dx

@@ -157,7 +157,10 @@ def main() -> int:
                         "writing the padded tower input, push, apply, tcgen05 tower layers (profiles/run_wd_step.py)",
             "prof_gemm2": "Fused linear 8192 x 4096 x 4096 (bias + ReLU): one CTA per tile, then CTA pairs (tcgen05 cta_group::2, "
                           "M = 256 tiles), twice each (profiles/run_gemm_pair.py); round 2",
-            "prof_wd3": "Round 2, final: Wide&Deep step kernels at full size (batch 32768, 16.7 M rows, one GPU) with one "
+            "prof_wd4": "Round 2, final: every hand-written kernel of the Wide&Deep step at full size (batch 32768, 16.7 M rows, one "
+                        "GPU): read-view lookup, batched push, 512-row-window apply, tower GEMMs (weights as stored, mask tile "
+                        "by TMA), MN-major weight gradients, weighted column sums, head (profiles/run_wd_step.py)",
+            "prof_wd3": "Round 2, second half: Wide&Deep step kernels at full size (batch 32768, 16.7 M rows, one GPU) with one "
                         "record per table row, the vectorised mask read, the MN-major tower weight gradient and the "
                         "weighted column-sum kernel (profiles/run_wd_step.py)"}
     for n, t in reps.items():

@@ -13,6 +13,23 @@ def _conv_gemm_for_every_size(monkeypatch):
     monkeypatch.setattr(conv_ops, "MIN_OUTPUT_BYTES", 0)
 
 
+@pytest.mark.parametrize("m,no,nc", [(32768, 400, 432), (1000, 400, 400), (4096, 128, 64), (777, 1000, 2048), (300, 64, 512)])
+def test_wgrad_mn_also_returns_the_bias_gradient(m, no, nc):
+    """db = column sums of dy from the weight-gradient kernel (extra N = 16 MMA against a tile of ones)."""
+    from paddle_operator_b200.ops.gemm import wgrad_mn
+
+    torch.manual_seed(m + no + nc)
+    dy = (torch.randn(m, no, device="cuda") * 0.5).to(torch.bfloat16)
+    x = (torch.randn(m, nc, device="cuda") * 0.5).to(torch.bfloat16)
+    db = torch.full((no,), 7.0, dtype=torch.bfloat16, device="cuda")
+    dw, filled = wgrad_mn(dy, x, db_out=db)
+    assert filled
+    ref_db = dy.float().sum(0)
+    torch.testing.assert_close(db.float(), ref_db, atol=0.02 * m ** 0.5 + 0.05, rtol=1e-2)
+    torch.testing.assert_close(dw.float(), dy.float().t() @ x.float(), atol=0.05 * m ** 0.5, rtol=2e-2)
+    assert torch.equal(dw, wgrad_mn(dy, x))  # the weight gradient itself is unchanged, bit for bit
+
+
 @pytest.mark.parametrize("m,n,k", [(128, 64, 64), (1000, 432, 400), (4096, 400, 400), (513, 216, 72), (300, 1000, 136)])
 def test_linear_with_weight_as_stored(m, n, k):
     """b_kn: out = a @ b with b given as [K, N] (dX = dZ W) - the MN-major B operand, incl. the mask epilogue."""
