@@ -209,14 +209,15 @@ class ShardedEmbedding:
                                        self.nblocks, int(c.emulate), c._stream(stream)), "emb_lookup")
 
     def push_raw(self, batch: int, grad_scale: float = 1.0, stream=None, gdeep_off: Optional[int] = None,
-                 g_pitch: Optional[int] = None) -> None:
+                 g_pitch: Optional[int] = None, gwide_off: Optional[int] = None) -> None:
         """`gdeep_off` / `g_pitch`: read the deep gradient from there instead of the staging buffer.  On a real rank
         any device address works (pass address - arena base: the kernel adds the base back), which lets backward
         hand the MLP's input gradient over without a copy."""
         c = self.comm
         check(self.lib.pdj_emb_push2(ctypes.byref(self.cstruct), ctypes.byref(self.t), self.ids_off,
                                      self.gdeep_in_off if gdeep_off is None else gdeep_off,
-                                     self.gwide_in_off, batch, self.slots, int(self.async_sgd), self.lr, grad_scale,
+                                     self.gwide_in_off if gwide_off is None else gwide_off, batch, self.slots,
+                                     int(self.async_sgd), self.lr, grad_scale,
                                      self.slots * self.dim if g_pitch is None else g_pitch,
                                      self.nblocks, int(c.emulate), c._stream(stream)), "emb_push")
         if not self.async_sgd:
@@ -294,7 +295,9 @@ class _LookupFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, emb: ShardedEmbedding, ids: torch.Tensor, _anchor: torch.Tensor):
         b = ids.shape[0]
-        emb.ids_buffer(b).copy_(ids)
+        buf = emb.ids_buffer(b)
+        if ids.data_ptr() != buf.data_ptr() or ids.dtype != buf.dtype:  # a caller may keep its ids in the arena buffer itself
+            buf.copy_(ids)
         emb.lookup_raw(b)
         ctx.emb, ctx.batch = emb, b
         return emb.out_deep(b), emb.out_wide(b)
@@ -302,14 +305,20 @@ class _LookupFn(torch.autograd.Function):
     @staticmethod
     def backward(ctx, g_deep, g_wide):
         emb, b = ctx.emb, ctx.batch
-        emb.grad_wide_in(b).copy_(g_wide if g_wide is not None else torch.zeros(b, device=g_deep.device))
+        base = emb.comm._bases[emb.comm.rank]
+        real = not emb.comm.emulate  # on a real rank any device address works: the kernel adds the arena base back
+        gwide_off = None
+        if real and g_wide is not None and g_wide.dtype == torch.float32 and g_wide.is_contiguous() and g_wide.data_ptr() % 4 == 0:
+            gwide_off = (g_wide.data_ptr() - base) % (1 << 64)  # no staging copy of the wide gradient either
+        else:
+            emb.grad_wide_in(b).copy_(g_wide if g_wide is not None else torch.zeros(b, device=g_deep.device))
         pitch = g_deep.stride(0)
-        if (not emb.comm.emulate and g_deep.dim() == 2 and g_deep.stride(1) == 1 and pitch % 4 == 0
+        if (real and g_deep.dim() == 2 and g_deep.stride(1) == 1 and pitch % 4 == 0
                 and g_deep.data_ptr() % 8 == 0 and pitch >= emb.slots * emb.dim):
             # no staging copy: the push kernel reads the gradient tensor where autograd left it
-            off = (g_deep.data_ptr() - emb.comm._bases[emb.comm.rank]) % (1 << 64)
-            emb.push_raw(b, emb.grad_scale, gdeep_off=off, g_pitch=pitch)
+            off = (g_deep.data_ptr() - base) % (1 << 64)
+            emb.push_raw(b, emb.grad_scale, gdeep_off=off, g_pitch=pitch, gwide_off=gwide_off)
         else:
             emb.grad_deep_in(b).copy_(g_deep[:, :emb.slots * emb.dim])
-            emb.push_raw(b, emb.grad_scale)
+            emb.push_raw(b, emb.grad_scale, gwide_off=gwide_off)
         return None, None, None

@@ -72,10 +72,13 @@ class WideDeepJob:
         torch.manual_seed(seed)
         dense = WideDeepDense(emb_dim, fused=True).to(self.device).to(torch.bfloat16)
         self.model = _Net(dense, self.emb).train()
-        self.ids = torch.zeros((batch, SPARSE_SLOTS), dtype=torch.int64, device=self.device)
+        # the step's ids live where the lookup kernel reads them (no per-step copy into the arena)
+        self.ids = None
         # the lookup kernel writes the tower's padded input [26 x 16 embeddings | 13 dense | 3 zeros] in place: the
         # dense features live in the arena where it reads them (no concatenation / conversion / fill kernels)
         self.emb.set_output_layout(dense.in_dim, DENSE_FEATURES)
+        self.ids = self.emb.ids_buffer(batch)
+        self.ids.zero_()
         self.dense_x = self.emb.dense_buffer(batch)
         self.dense_x.zero_()
         self.labels = torch.zeros((batch,), dtype=torch.float32, device=self.device)
