@@ -406,7 +406,182 @@ wgrad_mn_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// CTA-pair version (cluster of two, tcgen05 cta_group::2) of the MN-major weight gradient.  A pair owns [256 o] x
+// [nct c] accumulators: each CTA loads its own 128 output channels of dY and HALF of the X columns, the leader issues
+// M = 256 instructions that read both halves out of the two CTAs' shared memory, and each CTA ends up with its 128
+// output rows of every column in its tensor memory.  The single-CTA kernel reads X once per 128 output channels
+// and dY once per 256 columns; the pair reads X once per 256 output channels and dY once - half the L2 -> SM
+// traffic, which is what bounds the kernel (~95 B/clk/SM against a ~42 B/clk/SM ceiling on the Wide&Deep tower).
+// One instruction covers at most 256 columns = 128 of each CTA's half, so a wider tile takes two per K step; the
+// accumulator columns of instruction i are [256 i, 256 i + 2 w): CTA 0's w columns, then CTA 1's.
+struct WgPairCfg {
+  int M, No, Nc;
+  int nct, half, groups_h;   // tile columns (multiple of 16), columns per CTA, 64-column groups loaded per CTA
+  int tiles_c, tiles, S, stages, blocks;
+  uint32_t slot_bytes;
+  int with_db;
+};
+constexpr uint32_t WP_DBCOL = 496;  // accumulator columns of the bias gradient (with_db: nct <= 496)
+
+__device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t (&r)[8]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+               : "r"(taddr)
+               : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+__global__ void __launch_bounds__(WG_THREADS, 1)
+wgrad_mn_pair_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constant__ CUtensorMap tma_dy,
+                     float* __restrict__ partial, float* __restrict__ db_partial, const WgPairCfg c) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  const uint32_t base = (raw + 1023u) & ~1023u;
+  const uint32_t ones = base + (uint32_t)c.stages * c.slot_bytes;
+  const uint32_t bars = ones + (c.with_db ? (uint32_t)WM_GROUP_BYTES : 0u);
+  const uint32_t full0 = bars, empty0 = bars + 8 * MAX_STAGES, done = empty0 + 8 * MAX_STAGES, tmem_slot = done + 8;
+  uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(smem_raw + (tmem_slot - raw));
+  const int warp = (int)warp_uniform(threadIdx.x >> 5), lane = threadIdx.x & 31;
+  const uint32_t crank = warp_uniform(cluster_ctarank());
+  const int unit = (int)(blockIdx.x >> 1);
+  const int tile = unit % c.tiles, split = unit / c.tiles;
+  const int o0 = (tile / c.tiles_c) * 256 + (int)crank * 128;  // this CTA's output channels
+  const int c0 = (tile % c.tiles_c) * c.nct;                   // the pair's columns
+  const int ch0 = c0 + (int)crank * c.half;                    // the half this CTA loads
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_x) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tma_dy) : "memory");
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      for (int s = 0; s < c.stages; ++s) {
+        mbar_init(full0 + 8 * s, 1);
+        mbar_init(empty0 + 8 * s, 1);
+      }
+      mbar_init(done, 1);
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(512) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+  }
+  const bool do_db = c.with_db && (tile % c.tiles_c) == 0;
+  if (do_db) {  // both CTAs: the instruction reads 8 of the 16 ones-columns from each
+    for (uint32_t i = threadIdx.x; i < (uint32_t)WM_GROUP_BYTES / 16u; i += blockDim.x)
+      asm volatile("st.shared.v4.b32 [%0], {%1,%1,%1,%1};" ::"r"(ones + i * 16u), "r"(0x3f803f80u) : "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  cluster_sync_all();  // the peer's barriers and ones tile exist before anything touches them
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem_base = warp_uniform(*tmem_slot_ptr);
+  const uint32_t x_off = 2u * WM_GROUP_BYTES;  // slot = [dY group 0][dY group 1][X group 0 .. groups_h - 1]
+  const int n_inst = (c.half + 127) / 128;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (int b = split; b < c.blocks; b += c.S, ++it) {
+        const uint32_t s = it % (uint32_t)c.stages, ph = (it / (uint32_t)c.stages) & 1u;
+        const uint32_t slot = base + s * c.slot_bytes;
+        mbar_wait(empty0 + 8 * s, ph ^ 1u);
+        if (crank == 0) mbar_expect_tx(full0 + 8 * s, 2u * (uint32_t)(2 + c.groups_h) * WM_GROUP_BYTES);
+        const uint32_t lbar = mapa_rank(full0 + 8 * s, 0);
+        for (int g = 0; g < 2; ++g) tma_load_2d_pair(slot + g * WM_GROUP_BYTES, &tma_dy, o0 + 64 * g, b * WM_KB, lbar);
+        for (int g = 0; g < c.groups_h; ++g)
+          tma_load_2d_pair(slot + x_off + g * WM_GROUP_BYTES, &tma_x, ch0 + 64 * g, b * WM_KB, lbar);
+      }
+    }
+  } else if (warp == 1) {
+    if (crank == 0) {  // the leader issues for the pair (whole warp, one elected lane)
+      const uint32_t idesc0 = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) | ((256u >> 4) << 24);
+      const uint64_t d0 = umma_desc_ex(0, WM_GROUP_BYTES, 1024, 2);
+      uint32_t it = 0;
+      for (int b = split; b < c.blocks; b += c.S, ++it) {
+        const uint32_t s = it % (uint32_t)c.stages, ph = (it / (uint32_t)c.stages) & 1u;
+        const uint32_t slot = base + s * c.slot_bytes;
+        mbar_wait(full0 + 8 * s, ph);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        uint64_t da = d0 + (uint64_t)(slot >> 4), db = d0 + (uint64_t)((slot + x_off) >> 4);
+        uint64_t d1 = d0 + (uint64_t)(ones >> 4);
+#pragma unroll
+        for (int ks = 0; ks < WM_KB / 16; ++ks) {
+          const uint32_t acc = (uint32_t)((it | (uint32_t)ks) != 0u);
+          if (do_db) {
+            umma_f16_pair_elect(tmem_base + WP_DBCOL, da, d1, idesc0 | ((16u >> 3) << 17), acc);
+            d1 += 2048 >> 4;
+          }
+          for (int i = 0; i < n_inst; ++i) {
+            const uint32_t w = (uint32_t)((c.half - 128 * i) < 128 ? (c.half - 128 * i) : 128);
+            umma_f16_pair_elect(tmem_base + 256u * (uint32_t)i, da, db + (uint64_t)((uint32_t)i * (2u * WM_GROUP_BYTES >> 4)),
+                                idesc0 | (((2u * w) >> 3) << 17), acc);
+          }
+          da += 2048 >> 4;
+          db += 2048 >> 4;
+        }
+        umma_commit_pair_elect(empty0 + 8 * s);
+      }
+      umma_commit_pair_elect(done);
+    }
+  } else {
+    const int q = warp & 3;
+    mbar_wait_warp_sleepy(done, 0, 512);
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const bool has_work = split < c.blocks;
+    const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16);
+    const uint32_t stg = base + (uint32_t)(warp - 2) * (32u * (128 + 4) * 4u);
+    const int o_first = o0 + q * 32;
+    if (do_db) {
+      uint32_t r[8];
+      tmem_ld8(lane_base + WP_DBCOL, r);
+      const int o = o_first + lane;
+      if (o < c.No) db_partial[(size_t)split * c.No + o] = has_work ? __uint_as_float(r[0]) : 0.f;
+    }
+    for (int i = 0; i < n_inst; ++i) {
+      const int w = (c.half - 128 * i) < 128 ? (c.half - 128 * i) : 128;
+      const int pitch = w + 4;  // floats
+      for (int h = 0; h < 2; ++h) {
+        const uint32_t t0 = 256u * (uint32_t)i + (uint32_t)(h * w);   // accumulator columns of this segment
+        const int gc = c0 + h * c.half + 128 * i;                     // where they belong in dW
+        for (int col = 0; col < w; col += 8) {
+          uint32_t r[8];
+          tmem_ld8(lane_base + t0 + (uint32_t)col, r);
+#pragma unroll
+          for (int v = 0; v < 2; ++v)
+            asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(stg + (uint32_t)(lane * pitch + col + 4 * v) * 4u),
+                         "r"(has_work ? r[4 * v] : 0u), "r"(has_work ? r[4 * v + 1] : 0u), "r"(has_work ? r[4 * v + 2] : 0u),
+                         "r"(has_work ? r[4 * v + 3] : 0u)
+                         : "memory");
+        }
+        __syncwarp();
+        for (int rl = 0; rl < 32; ++rl) {
+          const int o = o_first + rl;
+          if (o >= c.No) break;
+          float* drow = partial + ((size_t)split * c.No + o) * c.Nc + gc;
+          for (int cc = lane * 4; cc < w && gc + cc < c.Nc; cc += 128) {
+            float4 v;
+            asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];"
+                         : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                         : "r"(stg + (uint32_t)(rl * pitch + cc) * 4u));
+            *reinterpret_cast<float4*>(drow + cc) = v;
+          }
+        }
+        __syncwarp();
+      }
+    }
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  cluster_sync_all();  // neither CTA leaves or frees tensor memory while the pair's instructions may still touch it
+  if (warp == 1) {
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512) : "memory");
+  }
+}
+
 int round_up(int a, int b) { return (a + b - 1) / b * b; }
+constexpr bool PAIR_WGRAD_DEFAULT = false;  // see profiles/r2/wgrad_pair.md
 
 // Chooses rows per block (R), stages and the split for one layer shape.  Returns 0 when the shape is not supported.
 int make_cfg(int N, int H, int W, int Cin, int Cout, Wg3Cfg* out) {
@@ -520,10 +695,42 @@ static int make_mn_cfg(int M, int No, int Nc, WgMnCfg* out, int with_db = 0) {
   return 1;
 }
 
+// CTA pairs pay when there are more than 128 output channels to share an X tile between (PDJ_WGRAD_PAIR=0/1 overrides).
+static int make_pair_cfg(int M, int No, int Nc, WgPairCfg* out, int with_db) {
+  const char* e = getenv("PDJ_WGRAD_PAIR");
+  const bool want = e ? atoi(e) != 0 : PAIR_WGRAD_DEFAULT;
+  if (!want || M < 1 || No <= 128 || Nc < 16 || Nc % 8 != 0 || No % 8 != 0) return 0;
+  WgPairCfg c{};
+  c.M = M; c.No = No; c.Nc = Nc;
+  c.with_db = with_db;
+  const int maxw = 496;
+  const int parts = (Nc + maxw - 1) / maxw;
+  c.nct = round_up((Nc + parts - 1) / parts, 16);
+  if (c.nct > maxw) return 0;
+  c.half = c.nct / 2;
+  c.groups_h = (c.half + 63) / 64;
+  c.tiles_c = (Nc + c.nct - 1) / c.nct;
+  c.tiles = ((No + 255) / 256) * c.tiles_c;
+  c.blocks = (M + WM_KB - 1) / WM_KB;
+  c.slot_bytes = (uint32_t)(2 + c.groups_h) * WM_GROUP_BYTES;
+  c.stages = (SMEM_LIMIT - 1024 - 512 - (with_db ? WM_GROUP_BYTES : 0)) / (int)c.slot_bytes;
+  if (c.stages > MAX_STAGES) c.stages = MAX_STAGES;
+  if (c.stages < 2) return 0;
+  const int units = pdj_tc_sm_count() / 2;
+  if (units < c.tiles) return 0;
+  c.S = units / c.tiles;
+  if (c.S > c.blocks) c.S = c.blocks;
+  *out = c;
+  return 1;
+}
+
 size_t pdj_wgrad_mn_ws_bytes(int M, int No, int Nc) {
   WgMnCfg c;
   if (!make_mn_cfg(M, No, Nc, &c)) return 0;
-  return (size_t)c.S * No * Nc * sizeof(float);
+  size_t n = (size_t)c.S * No * Nc * sizeof(float);
+  WgPairCfg p;
+  if (make_pair_cfg(M, No, Nc, &p, 0)) n = n > (size_t)p.S * No * Nc * sizeof(float) ? n : (size_t)p.S * No * Nc * sizeof(float);
+  return n;
 }
 
 // dw[No][Nc] (bf16, row-major) = dy[M][No]^T . x[M][Nc]: the weight gradient of a linear layer or of a 1x1
@@ -546,6 +753,33 @@ static int launch_wgrad_mn(const void* x, const void* dy, void* dw, void* db, vo
   CUtensorMap mx, my;
   if (int r = pdj_tc_make_map(&mx, x, M, Nc, ldx, 64, WM_KB, true)) return r;
   if (int r = pdj_tc_make_map(&my, dy, M, No, ldy, 64, WM_KB, true)) return r;
+  WgPairCfg pc;
+  if (make_pair_cfg(M, No, Nc, &pc, db != nullptr)) {
+    static bool pattr = false;
+    if (!pattr) {
+      PDJ_CUDA_CHECK(cudaFuncSetAttribute(wgrad_mn_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+      pattr = true;
+    }
+    const int psmem = 1024 + pc.stages * (int)pc.slot_bytes + (pc.with_db ? WM_GROUP_BYTES : 0) + 512;
+    float* pdb = db != nullptr ? (float*)ws + (size_t)pc.S * No * Nc : nullptr;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(2 * pc.tiles * pc.S);
+    cfg.blockDim = dim3(WG_THREADS);
+    cfg.dynamicSmemBytes = psmem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr1[1];
+    attr1[0].id = cudaLaunchAttributeClusterDimension;
+    attr1[0].val.clusterDim.x = 2;
+    attr1[0].val.clusterDim.y = 1;
+    attr1[0].val.clusterDim.z = 1;
+    cfg.attrs = attr1;
+    cfg.numAttrs = 1;
+    PDJ_CUDA_CHECK(cudaLaunchKernelEx(&cfg, wgrad_mn_pair_kernel, mx, my, (float*)ws, pdb, pc));
+    launch_reduce((const float*)ws, pc.S, (size_t)No * Nc, (__nv_bfloat16*)dw, st);
+    if (db != nullptr) launch_reduce(pdb, pc.S, (size_t)No, (__nv_bfloat16*)db, st);
+    PDJ_CUDA_CHECK(cudaGetLastError());
+    return 0;
+  }
   const int smem = 1024 + c.stages * (int)c.slot_bytes + (c.with_db ? WM_GROUP_BYTES : 0) + 512;
   float* dbp = db != nullptr ? (float*)ws + (size_t)c.S * No * Nc : nullptr;
   wgrad_mn_tcgen05_kernel<<<c.tiles * c.S, WG_THREADS, smem, st>>>(mx, my, (float*)ws, dbp, c);
@@ -567,7 +801,13 @@ int pdj_wgrad_mn(const void* x, const void* dy, void* dw, void* ws, int M, int N
 size_t pdj_wgrad_mn_db_ws_bytes(int M, int No, int Nc) {
   WgMnCfg c;
   if (!make_mn_cfg(M, No, Nc, &c, 1)) return 0;
-  return (size_t)c.S * No * Nc * sizeof(float) + (size_t)c.S * No * sizeof(float);
+  size_t n = (size_t)c.S * No * Nc * sizeof(float) + (size_t)c.S * No * sizeof(float);
+  WgPairCfg p;
+  if (make_pair_cfg(M, No, Nc, &p, 1)) {
+    const size_t np = (size_t)p.S * No * Nc * sizeof(float) + (size_t)p.S * No * sizeof(float);
+    n = n > np ? n : np;
+  }
+  return n;
 }
 
 int pdj_wgrad_mn_db(const void* x, const void* dy, void* dw, void* db, void* ws, int M, int No, int Nc, int ldx, int ldy,
