@@ -30,6 +30,26 @@ def test_wgrad_mn_also_returns_the_bias_gradient(m, no, nc):
     assert torch.equal(dw, wgrad_mn(dy, x))  # the weight gradient itself is unchanged, bit for bit
 
 
+@pytest.mark.parametrize("m,no,nc", [(32768, 400, 432), (1000, 256, 64), (777, 1000, 2048), (4096, 512, 1000), (300, 136, 16)])
+def test_wgrad_mn_cta_pair_kernel(m, no, nc, monkeypatch):
+    """cta_group::2 version (off by default, profiles/r2/wgrad_pair.md): 256 output channels per pair, the X columns
+    split between the two CTAs, two instructions per K step for tiles wider than 256 columns, ragged edges."""
+    from paddle_operator_b200.ops.gemm import wgrad_mn
+
+    monkeypatch.setenv("PDJ_WGRAD_PAIR", "1")  # read by the library on every call
+    torch.manual_seed(m + 3 * no + nc)
+    dy = (torch.randn(m, no, device="cuda") * 0.5).to(torch.bfloat16)
+    x = (torch.randn(m, nc, device="cuda") * 0.5).to(torch.bfloat16)
+    db = torch.empty(no, dtype=torch.bfloat16, device="cuda")
+    dw, filled = wgrad_mn(dy, x, db_out=db)
+    assert filled
+    torch.testing.assert_close(dw.float(), dy.float().t() @ x.float(), atol=0.05 * m ** 0.5, rtol=2e-2)
+    torch.testing.assert_close(db.float(), dy.float().sum(0), atol=0.02 * m ** 0.5 + 0.05, rtol=1e-2)
+    torch.testing.assert_close(wgrad_mn(dy, x).float(), dw.float(), atol=0.02 * m ** 0.5, rtol=1e-2)
+    monkeypatch.setenv("PDJ_WGRAD_PAIR", "0")
+    torch.testing.assert_close(wgrad_mn(dy, x).float(), dw.float(), atol=0.02 * m ** 0.5, rtol=1e-2)
+
+
 @pytest.mark.parametrize("m,n,k", [(128, 64, 64), (1000, 432, 400), (4096, 400, 400), (513, 216, 72), (300, 1000, 136)])
 def test_linear_with_weight_as_stored(m, n, k):
     """b_kn: out = a @ b with b given as [K, N] (dX = dZ W) - the MN-major B operand, incl. the mask epilogue."""
