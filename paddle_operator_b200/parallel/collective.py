@@ -244,8 +244,13 @@ class CollectiveTrainer:
             # communicator the bucket collective already overlaps the embedding push and the extra stream only adds
             # contention (0.699 -> 0.710 ms at N = 2), so it stays off there (PDJ_WGRAD_OVERLAP=2 forces it)
             _sink.begin_step(self.comm is None or _sink.WGRAD_OVERLAP_FORCE)
-        loss = self.loss_fn(self.model, *self.inputs)
-        loss.backward()
+        try:
+            loss = self.loss_fn(self.model, *self.inputs)
+            loss.backward()
+        except BaseException:
+            if cuda:
+                _sink.end_step()  # never leave the side-stream scope open behind a failed step
+            raise
         main = torch.cuda.current_stream() if cuda else None
         if cuda:
             _sink.wait_side_work(main)  # the optimizer below / the next step read what the side stream wrote

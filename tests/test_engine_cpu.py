@@ -118,3 +118,23 @@ def test_conv_ops_eligibility_rules():
     assert p1 is None and pd is None and yd.shape == (2, 256, 4, 4)
     ys, ps = conv_ops.stem_s2d_conv(torch.randn(1, 16, 19, 19), torch.randn(64, 16, 4, 4))
     assert ps is None and ys.shape == (1, 64, 16, 16)
+
+
+def test_sink_scope_bookkeeping_without_a_gpu():
+    """ops/_sink.py: the overlap scope is only open inside a trainer step and sinks are ignored for CPU parameters."""
+    import torch
+
+    from paddle_operator_b200.ops import _sink
+
+    p = torch.nn.Parameter(torch.zeros(4, 4))
+    p._grad_sink = torch.zeros(4, 4)
+    assert _sink.sink_of(p) is None and _sink.sink_of(None) is None  # CPU tensors / wrong dtype never sink
+    assert not _sink.overlap_enabled()
+    _sink.begin_step(True)
+    assert _sink.overlap_enabled() == _sink.WGRAD_OVERLAP
+    _sink.begin_step(False)
+    assert not _sink.overlap_enabled()
+    _sink.end_step()
+    assert not _sink.overlap_enabled() and not _sink._scope["events"] and not _sink._scope["keep"]
+    g = torch.ones(4, 4)
+    assert _sink.is_sunk(g, g) and not _sink.is_sunk(g.clone(), g) and not _sink.is_sunk(None, g)
